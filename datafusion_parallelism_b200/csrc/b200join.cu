@@ -1,0 +1,1095 @@
+// b200join.cu — host side of libb200join.so: the C ABI of include/b200join.h over the sm_100a kernels in
+// kernels.cuh / radix.cuh / gather.cuh.  C++17, CUDA runtime only (no torch, no arrow, no CPU fallback).
+//
+// Mirrors, for one join, what sits below ParallelHashJoin::execute in the reference
+// (src/operator/parallel_hash_join.rs:140-167 -> parallel_hash_join_executor.rs:86-122):
+// build_side() per partition, then one lookup_*_probe_batch per probe batch, then the finaliser.
+#include "../../include/b200join.h"
+#include "kernels.cuh"
+#include "radix.cuh"
+#include "gather.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+using namespace b200j;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+struct Fail {
+    int32_t code;
+    std::string msg;
+};
+
+#define CU(expr)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t _e = (expr);                                                                          \
+        if (_e != cudaSuccess) {                                                                          \
+            cudaGetLastError();                                                                           \
+            throw Fail{_e == cudaErrorMemoryAllocation ? B200J_ERR_OOM : B200J_ERR_CUDA,                  \
+                       std::string(#expr) + ": " + cudaGetErrorString(_e)};                               \
+        }                                                                                                 \
+    } while (0)
+
+#define REQUIRE(cond, code, text)                                                                         \
+    do {                                                                                                  \
+        if (!(cond)) throw Fail{(code), std::string(text)};                                               \
+    } while (0)
+
+// RandomState::from_keys over the fixed PI seeds (ahash random_state.rs), identical to oracle/join_oracle.c.
+void keys_with_seed(uint64_t seed, uint64_t out[4]) {
+    static const uint64_t PI[4] = {0x243f6a8885a308d3ULL, 0x13198a2e03707344ULL, 0xa4093822299f31d0ULL, 0x082efa98ec4e6c89ULL};
+    static const uint64_t PI2[4] = {0x452821e638d01377ULL, 0xbe5466cf34e90c6cULL, 0xc0ac29b7c97c50ddULL, 0x3f84d5b5b5470917ULL};
+    uint64_t buffer = PI[1];
+    const uint64_t pad = PI[0];
+    buffer = folded_multiply(seed ^ buffer, AHASH_MULTIPLE);
+    const int l[4] = {0, 1, 2, 3}, r[4] = {2, 3, 1, 0};
+    for (int i = 0; i < 4; i++) {
+        uint64_t b = buffer;
+        b = folded_multiply(PI2[l[i]] ^ b, AHASH_MULTIPLE);
+        b = folded_multiply(PI2[r[i]] ^ b, AHASH_MULTIPLE);
+        out[i] = rotl64(folded_multiply(b, pad), (unsigned)(b & 63));
+    }
+}
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+};
+
+struct ColStore {          // one column of the concatenated build side (JoinStateInstance::compact, a3)
+    int32_t type = 8;      // width or B200J_T_UTF8
+    DevBuf values;         // fixed width values, or Utf8 data
+    DevBuf offsets;        // Utf8: int64 offsets into `values` (the concatenated build side may pass 2 GiB)
+    DevBuf validity;       // u32 words, allocated on the first batch that carries nulls
+    bool has_nulls = false;
+    int64_t data_bytes = 0;
+};
+
+struct ResultOwner {
+    void *build_idx = nullptr;
+    void *probe_idx = nullptr;
+    int32_t mem = B200J_MEM_DEVICE;
+    size_t build_bytes = 0, probe_bytes = 0;
+};
+
+struct PinnedBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+};
+
+}  // namespace
+
+struct b200j_handle {
+    std::mutex mu;
+    std::string err;
+    b200j_config cfg{};
+    std::vector<int32_t> key_widths, build_payload_types, probe_payload_types;
+    HashKeys hk{};
+    cudaStream_t stream = nullptr;
+    cudaStream_t copy_in = nullptr, copy_out = nullptr;
+    bool own_stream = false;
+    int sm_count = 148;
+    int64_t l2_bytes = 0;
+    bool timing = false;
+
+    // build store
+    int64_t n_build = 0;
+    int64_t build_cap_rows = 0;
+    std::vector<ColStore> bkeys, bpayload;
+    std::vector<uint8_t> build_done, probe_done;
+    int n_build_done = 0, n_probe_done = 0;
+    bool built = false;
+
+    // table
+    int32_t layout = B200J_LAYOUT_DIRECT;
+    int32_t radix_bits = 0;
+    DevBuf slots;
+    uint64_t n_slots = 0;
+    DevBuf zero_slot;
+    DevBuf rowids;
+    DevBuf visited;
+    DevBuf part_base, part_mask;       // radix layout
+    RadixScratch rscratch;
+    Counters *d_ctr = nullptr;
+    Counters *h_ctr = nullptr;         // pinned mirror
+
+    std::vector<PinnedBuf> pinned_cache;
+    b200j_stats st{};
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+
+    TableView view() const {
+        TableView tv{};
+        tv.slots = (Slot *)slots.p;
+        tv.mask = n_slots ? n_slots - 1 : 0;
+        tv.zero_slot = (Slot *)zero_slot.p;
+        tv.rowids = (uint32_t *)rowids.p;
+        tv.part_base = (const uint64_t *)part_base.p;
+        tv.part_mask = (const uint32_t *)part_mask.p;
+        tv.radix_bits = radix_bits;
+        return tv;
+    }
+};
+
+namespace {
+
+using H = b200j_handle;
+
+// defined in radix_host.inl / gather_host.inl (included below, they need the complete handle type)
+void radix_build(H *h, const void *keys, const uint8_t *validity, int kw, int64_t n, float lf, int64_t budget);
+int64_t radix_probe(H *h, const void *d_keys, const uint8_t *d_validity, int64_t bit_offset, int64_t n, int mode, bool mark,
+                    bool count_only, int64_t cap, bool want_build, ResultOwner *ro, int64_t *n_build_null);
+void radix_release(H *h);
+void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, uint32_t want, b200j_gathered *out);
+void do_gathered_release(H *h, b200j_gathered *g);
+
+void dev_alloc(H *h, DevBuf &b, size_t bytes) {
+    if (bytes <= b.cap && b.p) return;
+    if (b.p) CU(cudaFreeAsync(b.p, h->stream));
+    b.p = nullptr;
+    b.cap = 0;
+    bytes = std::max<size_t>(bytes, 256);
+    CU(cudaMallocAsync(&b.p, bytes, h->stream));
+    b.cap = bytes;
+}
+
+// grow keeping the first `keep` bytes
+void dev_grow(H *h, DevBuf &b, size_t bytes, size_t keep) {
+    if (bytes <= b.cap && b.p) return;
+    size_t ncap = std::max<size_t>(std::max<size_t>(bytes, b.cap + b.cap / 2), 256);
+    void *np = nullptr;
+    CU(cudaMallocAsync(&np, ncap, h->stream));
+    if (b.p && keep) CU(cudaMemcpyAsync(np, b.p, keep, cudaMemcpyDeviceToDevice, h->stream));
+    if (b.p) CU(cudaFreeAsync(b.p, h->stream));
+    b.p = np;
+    b.cap = ncap;
+}
+
+void dev_free(H *h, DevBuf &b) {
+    if (b.p) cudaFreeAsync(b.p, h->stream);
+    b.p = nullptr;
+    b.cap = 0;
+}
+
+struct PinnedSizes {
+    std::mutex mu;
+    std::vector<std::pair<void *, size_t>> v;
+} g_pinned_sizes;
+
+void pinned_note(void *p, size_t bytes) {
+    std::lock_guard<std::mutex> g(g_pinned_sizes.mu);
+    g_pinned_sizes.v.emplace_back(p, bytes);
+}
+size_t pinned_size(void *p, bool erase) {
+    std::lock_guard<std::mutex> g(g_pinned_sizes.mu);
+    for (size_t i = 0; i < g_pinned_sizes.v.size(); i++)
+        if (g_pinned_sizes.v[i].first == p) {
+            size_t s = g_pinned_sizes.v[i].second;
+            if (erase) g_pinned_sizes.v.erase(g_pinned_sizes.v.begin() + i);
+            return s;
+        }
+    return 0;
+}
+
+void *pinned_take(H *h, size_t bytes) {
+    bytes = std::max<size_t>(bytes, 256);
+    int best = -1;
+    for (size_t i = 0; i < h->pinned_cache.size(); i++)
+        if (h->pinned_cache[i].cap >= bytes && (best < 0 || h->pinned_cache[i].cap < h->pinned_cache[best].cap)) best = (int)i;
+    if (best >= 0) {
+        void *p = h->pinned_cache[best].p;
+        h->pinned_cache.erase(h->pinned_cache.begin() + best);
+        return p;
+    }
+    void *p = nullptr;
+    CU(cudaHostAlloc(&p, bytes, cudaHostAllocDefault));
+    pinned_note(p, bytes);
+    return p;
+}
+
+void pinned_give(H *h, void *p) {
+    if (!p) return;
+    size_t s = pinned_size(p, false);
+    // keep at most 4 cached buffers; free the smallest beyond that
+    h->pinned_cache.push_back(PinnedBuf{p, s});
+    while (h->pinned_cache.size() > 4) {
+        size_t mi = 0;
+        for (size_t i = 1; i < h->pinned_cache.size(); i++)
+            if (h->pinned_cache[i].cap < h->pinned_cache[mi].cap) mi = i;
+        pinned_size(h->pinned_cache[mi].p, true);
+        cudaFreeHost(h->pinned_cache[mi].p);
+        h->pinned_cache.erase(h->pinned_cache.begin() + mi);
+    }
+}
+
+int grid_for(H *h, int64_t work_items, int per_block, int blocks_per_sm) {
+    int64_t blocks = (work_items + per_block - 1) / per_block;
+    int64_t cap = (int64_t)h->sm_count * blocks_per_sm;
+    return (int)std::max<int64_t>(1, std::min<int64_t>(blocks, cap));
+}
+
+struct PhaseTimer {            // CUDA-event timing of one phase on the handle's stream
+    H *h;
+    double *acc;
+    bool on;
+    PhaseTimer(H *h_, double *acc_) : h(h_), acc(acc_), on(h_->timing) {
+        if (on) cudaEventRecord(h->ev0, h->stream);
+    }
+    void stop() {
+        if (!on) return;
+        on = false;
+        cudaEventRecord(h->ev1, h->stream);
+        cudaEventSynchronize(h->ev1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+        *acc += ms;
+    }
+};
+
+void check_batch(H *h, const b200j_batch *b, int n_payload_expected) {
+    REQUIRE(b != nullptr, B200J_ERR_INVALID, "batch is NULL");
+    REQUIRE(b->struct_size >= sizeof(b200j_batch), B200J_ERR_INVALID, "batch.struct_size too small (ABI mismatch)");
+    REQUIRE(b->n_rows >= 0, B200J_ERR_INVALID, "batch.n_rows < 0");
+    REQUIRE(b->n_keys == h->cfg.n_keys, B200J_ERR_INVALID, "batch.n_keys differs from the join's key count");
+    REQUIRE(b->n_payload == 0 || b->n_payload == n_payload_expected, B200J_ERR_INVALID,
+            "batch.n_payload differs from the configured payload columns");
+    REQUIRE(b->mem == B200J_MEM_HOST || b->mem == B200J_MEM_DEVICE, B200J_ERR_INVALID, "batch.mem invalid");
+    if (b->n_rows > 0) {
+        REQUIRE(b->keys != nullptr, B200J_ERR_INVALID, "batch.keys is NULL");
+        for (int i = 0; i < b->n_keys; i++) REQUIRE(b->keys[i].values != nullptr, B200J_ERR_INVALID, "key column without values buffer");
+    }
+}
+
+// Brings a (possibly host) validity bitmap slice to the device. Returns a device pointer whose bit 0..7
+// alignment equals bit_offset & 7 (the returned *bit_off is the offset to use with it), or null.
+const uint8_t *stage_validity(H *h, const b200j_column &c, int64_t n_rows, int mem, std::vector<void *> &temps, int64_t *bit_off) {
+    *bit_off = 0;
+    if (!c.validity || n_rows == 0) return nullptr;
+    if (mem == B200J_MEM_DEVICE) {
+        *bit_off = c.bit_offset;
+        return c.validity;
+    }
+    const int64_t first = c.bit_offset >> 3, last = (c.bit_offset + n_rows + 7) >> 3;
+    void *d = nullptr;
+    CU(cudaMallocAsync(&d, (size_t)(last - first) + 16, h->stream));
+    temps.push_back(d);
+    CU(cudaMemcpyAsync(d, c.validity + first, (size_t)(last - first), cudaMemcpyHostToDevice, h->stream));
+    *bit_off = c.bit_offset & 7;
+    return (const uint8_t *)d;
+}
+
+void free_temps(H *h, std::vector<void *> &temps) {
+    for (void *p : temps) cudaFreeAsync(p, h->stream);
+    temps.clear();
+}
+
+// ---------------------------------------------------------------------------------------------
+// build
+// ---------------------------------------------------------------------------------------------
+void store_append(H *h, ColStore &cs, const b200j_column &c, int64_t n_old, int64_t n_add, int mem, std::vector<void *> &temps) {
+    const cudaMemcpyKind kind = mem == B200J_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
+    if (cs.type != B200J_T_UTF8) {
+        const size_t w = (size_t)cs.type;
+        dev_grow(h, cs.values, (size_t)(n_old + n_add) * w + 16, (size_t)n_old * w);
+        CU(cudaMemcpyAsync((char *)cs.values.p + (size_t)n_old * w, c.values, (size_t)n_add * w, kind, h->stream));
+    } else {
+        REQUIRE(c.offsets != nullptr, B200J_ERR_INVALID, "Utf8 column without offsets buffer");
+        // the first/last offsets are needed on the host to size the copy
+        int32_t o0 = 0, o1 = 0;
+        if (mem == B200J_MEM_HOST) {
+            o0 = c.offsets[0];
+            o1 = c.offsets[n_add];
+        } else {
+            CU(cudaMemcpyAsync(&o0, c.offsets, 4, cudaMemcpyDeviceToHost, h->stream));
+            CU(cudaMemcpyAsync(&o1, c.offsets + n_add, 4, cudaMemcpyDeviceToHost, h->stream));
+            CU(cudaStreamSynchronize(h->stream));
+        }
+        const int64_t nbytes = (int64_t)o1 - o0;
+        dev_grow(h, cs.values, (size_t)(cs.data_bytes + nbytes) + 16, (size_t)cs.data_bytes);
+        if (nbytes) CU(cudaMemcpyAsync((char *)cs.values.p + cs.data_bytes, (const char *)c.values + o0, (size_t)nbytes, kind, h->stream));
+        dev_grow(h, cs.offsets, (size_t)(n_old + n_add + 1) * 8, (size_t)(n_old + 1) * 8);
+        const int32_t *d_off = c.offsets;
+        if (mem == B200J_MEM_HOST) {
+            void *d = nullptr;
+            CU(cudaMallocAsync(&d, (size_t)(n_add + 1) * 4, h->stream));
+            temps.push_back(d);
+            CU(cudaMemcpyAsync(d, c.offsets, (size_t)(n_add + 1) * 4, cudaMemcpyHostToDevice, h->stream));
+            d_off = (const int32_t *)d;
+        }
+        rebase_offsets_kernel<<<grid_for(h, n_add + 1, 256, 8), 256, 0, h->stream>>>(d_off, n_add + 1, (int64_t)o0, cs.data_bytes,
+                                                                                     (int64_t *)cs.offsets.p + n_old);
+        h->st.kernel_launches++;
+        cs.data_bytes += nbytes;
+    }
+    // validity
+    if (c.validity && !cs.has_nulls) {
+        // first batch with a bitmap: earlier rows are all valid
+        dev_grow(h, cs.validity, (size_t)((std::max(h->build_cap_rows, n_old + n_add) + 31) / 32 + 1) * 4, 0);
+        if (n_old > 0) {
+            copy_bits_kernel<<<grid_for(h, (n_old + 31) / 32 + 1, 256, 8), 256, 0, h->stream>>>((uint32_t *)cs.validity.p, 0, nullptr, 0, n_old);
+            h->st.kernel_launches++;
+        }
+        cs.has_nulls = true;
+    }
+    if (cs.has_nulls) {
+        dev_grow(h, cs.validity, (size_t)((n_old + n_add + 31) / 32 + 1) * 4, (size_t)((n_old + 31) / 32) * 4);
+        int64_t boff = 0;
+        const uint8_t *dv = stage_validity(h, c, n_add, mem, temps, &boff);
+        copy_bits_kernel<<<grid_for(h, (n_add + 31) / 32 + 1, 256, 8), 256, 0, h->stream>>>((uint32_t *)cs.validity.p, n_old, dv, boff, n_add);
+        h->st.kernel_launches++;
+    }
+}
+
+void do_build_push(H *h, int32_t partition, const b200j_batch *b) {
+    REQUIRE(partition >= 0 && partition < h->cfg.n_partitions, B200J_ERR_INVALID, "partition out of range");
+    REQUIRE(!h->build_done[partition], B200J_ERR_STATE, "State already consumed: build_push after build_finish");
+    REQUIRE(!h->built, B200J_ERR_STATE, "build side already finished");
+    check_batch(h, b, h->cfg.n_build_payload);
+    if (b->n_rows == 0) return;
+    REQUIRE(b->n_payload == h->cfg.n_build_payload, B200J_ERR_INVALID, "build batch must carry every configured payload column");
+    REQUIRE(h->n_build + b->n_rows < 0x7fffffffLL, B200J_ERR_UNSUPPORTED, "more than 2^31-1 build rows on one device");
+    PhaseTimer tm(h, &h->st.ms_build_copy);
+    std::vector<void *> temps;
+    h->build_cap_rows = std::max(h->build_cap_rows, h->n_build + b->n_rows);
+    for (int i = 0; i < h->cfg.n_keys; i++) store_append(h, h->bkeys[i], b->keys[i], h->n_build, b->n_rows, b->mem, temps);
+    for (int i = 0; i < h->cfg.n_build_payload; i++) store_append(h, h->bpayload[i], b->payload[i], h->n_build, b->n_rows, b->mem, temps);
+    free_temps(h, temps);
+    h->n_build += b->n_rows;
+    // host buffers are borrowed for the call only
+    if (b->mem == B200J_MEM_HOST) CU(cudaStreamSynchronize(h->stream));
+    tm.stop();
+}
+
+template <typename F>
+void launch_by_kw(int kw, F &&f) {
+    if (kw == 8) f(std::integral_constant<int, 8>{});
+    else f(std::integral_constant<int, 4>{});
+}
+
+void run_build(H *h) {
+    const int64_t n = h->n_build;
+    const int kw = h->key_widths[0];
+    REQUIRE(h->cfg.n_keys == 1, B200J_ERR_UNSUPPORTED, "composite join keys are not implemented yet (single 4/8-byte key column only)");
+    const float lf = h->cfg.load_factor > 0.f ? std::min(h->cfg.load_factor, 0.9f) : 0.5f;
+
+    // ---- layout choice: direct while the table fits the L2 budget
+    uint64_t direct_slots = 1024;
+    while ((double)direct_slots * lf < (double)n) direct_slots <<= 1;
+    const int64_t budget = h->cfg.l2_budget_bytes > 0 ? h->cfg.l2_budget_bytes : h->l2_bytes / 2;
+    int32_t layout = h->cfg.layout;
+    if (layout == B200J_LAYOUT_AUTO) layout = ((int64_t)direct_slots * 16 <= budget) ? B200J_LAYOUT_DIRECT : B200J_LAYOUT_RADIX;
+    h->layout = layout;
+
+    dev_alloc(h, h->zero_slot, sizeof(Slot));
+    CU(cudaMemsetAsync(h->zero_slot.p, 0, sizeof(Slot), h->stream));
+    CU(cudaMemsetAsync(h->d_ctr, 0, sizeof(Counters), h->stream));
+    const int jt = h->cfg.join_type;
+    if (jt == B200J_LEFT || jt == B200J_FULL || jt == B200J_LEFT_SEMI || jt == B200J_LEFT_ANTI) {
+        dev_alloc(h, h->visited, (size_t)((n + 31) / 32 + 1) * 4);
+        CU(cudaMemsetAsync(h->visited.p, 0, (size_t)((n + 31) / 32 + 1) * 4, h->stream));
+    }
+    const void *keys = h->bkeys[0].values.p;
+    const uint8_t *validity = h->bkeys[0].has_nulls ? (const uint8_t *)h->bkeys[0].validity.p : nullptr;
+
+    BuildArgs a{};
+    a.hk = h->hk;
+    a.ctr = h->d_ctr;
+
+    if (layout == B200J_LAYOUT_DIRECT || n == 0) {
+        h->layout = B200J_LAYOUT_DIRECT;
+        h->radix_bits = 0;
+        PhaseTimer tm(h, &h->st.ms_build_insert);
+        h->n_slots = direct_slots;
+        dev_alloc(h, h->slots, (size_t)direct_slots * sizeof(Slot));
+        CU(cudaMemsetAsync(h->slots.p, 0, (size_t)direct_slots * sizeof(Slot), h->stream));
+        a.keys = keys;
+        a.validity = validity;
+        a.rowid = nullptr;
+        a.n = n;
+        a.mis = 0;      // the build store is 256 B aligned
+        a.tv = h->view();
+        if (n > 0) {
+            const int grid = grid_for(h, n, TILE_ROWS, 8);
+            launch_by_kw(kw, [&](auto KW) { build_insert_kernel<decltype(KW)::value, false><<<grid, TILE_THREADS, 0, h->stream>>>(a); });
+            h->st.kernel_launches++;
+        }
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        if (h->h_ctr->dup_rows > 0) {
+            const uint64_t need = h->h_ctr->dup_rows + 2 * h->h_ctr->multi_slots + 64;
+            REQUIRE(need < 0xffffffffULL, B200J_ERR_UNSUPPORTED, "duplicate-run index exceeds 32 bits");
+            dev_alloc(h, h->rowids, (size_t)need * 4);
+            a.tv = h->view();
+            csr_scan_kernel<<<grid_for(h, (int64_t)direct_slots + 1, 256, 8), 256, 0, h->stream>>>(a.tv, direct_slots, h->d_ctr);
+            const int grid = grid_for(h, n, TILE_ROWS, 8);
+            launch_by_kw(kw, [&](auto KW) { csr_fill_kernel<decltype(KW)::value, false><<<grid, TILE_THREADS, 0, h->stream>>>(a); });
+            h->st.kernel_launches += 2;
+            CU(cudaGetLastError());
+        }
+        tm.stop();
+    } else {
+        radix_build(h, keys, validity, kw, n, lf, budget);
+    }
+    CU(cudaStreamSynchronize(h->stream));
+    h->st.layout = h->layout;
+    h->st.radix_bits = h->radix_bits;
+    h->st.build_rows = n;
+    h->st.build_null_keys = (int64_t)h->h_ctr->null_keys;
+    h->st.distinct_keys = (int64_t)h->h_ctr->distinct;
+    h->st.duplicate_rows = (int64_t)h->h_ctr->dup_rows;
+    h->st.table_slots = (int64_t)h->n_slots;
+    h->st.table_bytes = (int64_t)h->n_slots * (int64_t)sizeof(Slot);
+    h->built = true;
+}
+
+void do_build_finish(H *h, int32_t partition) {
+    REQUIRE(partition >= 0 && partition < h->cfg.n_partitions, B200J_ERR_INVALID, "partition out of range");
+    REQUIRE(!h->build_done[partition], B200J_ERR_STATE, "State already consumed: build_finish called twice for this partition");
+    h->build_done[partition] = 1;
+    h->n_build_done++;
+    if (h->n_build_done == h->cfg.n_partitions) run_build(h);   // the last owner does the work (LimitedRc / InitializeLast)
+}
+
+// ---------------------------------------------------------------------------------------------
+// probe
+// ---------------------------------------------------------------------------------------------
+struct ProbePlan {
+    int mode;
+    bool mark;
+};
+
+ProbePlan plan_for(int join_type, bool matches_only) {
+    if (matches_only) return {PM_PAIRS, false};
+    switch (join_type) {
+        case B200J_INNER: return {PM_PAIRS, false};
+        case B200J_LEFT: return {PM_PAIRS, true};
+        case B200J_RIGHT: return {PM_OUTER, false};
+        case B200J_FULL: return {PM_OUTER, true};
+        case B200J_LEFT_SEMI:
+        case B200J_LEFT_ANTI: return {PM_MARK, true};
+        case B200J_RIGHT_SEMI: return {PM_SEMI, false};
+        default: return {PM_ANTI, false};
+    }
+}
+
+template <int KW, bool RADIX>
+void launch_probe_mode(const ProbePlan &pl, int grid, cudaStream_t s, const ProbeArgs &a) {
+    if (pl.mode == PM_PAIRS && !pl.mark) probe_kernel<KW, PM_PAIRS, false, RADIX><<<grid, TILE_THREADS, 0, s>>>(a);
+    else if (pl.mode == PM_PAIRS) probe_kernel<KW, PM_PAIRS, true, RADIX><<<grid, TILE_THREADS, 0, s>>>(a);
+    else if (pl.mode == PM_OUTER && !pl.mark) probe_kernel<KW, PM_OUTER, false, RADIX><<<grid, TILE_THREADS, 0, s>>>(a);
+    else if (pl.mode == PM_OUTER) probe_kernel<KW, PM_OUTER, true, RADIX><<<grid, TILE_THREADS, 0, s>>>(a);
+    else if (pl.mode == PM_SEMI) probe_kernel<KW, PM_SEMI, false, RADIX><<<grid, TILE_THREADS, 0, s>>>(a);
+    else if (pl.mode == PM_ANTI) probe_kernel<KW, PM_ANTI, false, RADIX><<<grid, TILE_THREADS, 0, s>>>(a);
+    else probe_kernel<KW, PM_MARK, true, RADIX><<<grid, TILE_THREADS, 0, s>>>(a);
+}
+
+void launch_probe(H *h, const ProbePlan &pl, const ProbeArgs &a, int kw, bool radix) {
+    const int grid = grid_for(h, a.n + a.mis, TILE_ROWS, 8);
+    if (kw == 8) {
+        if (radix) launch_probe_mode<8, true>(pl, grid, h->stream, a);
+        else launch_probe_mode<8, false>(pl, grid, h->stream, a);
+    } else {
+        if (radix) launch_probe_mode<4, true>(pl, grid, h->stream, a);
+        else launch_probe_mode<4, false>(pl, grid, h->stream, a);
+    }
+    h->st.kernel_launches++;
+    h->st.probe_launches++;
+}
+
+int64_t estimate_out_cap(H *h, int64_t n_probe, const ProbePlan &pl) {
+    if (pl.mode == PM_MARK) return 0;
+    if (pl.mode == PM_SEMI || pl.mode == PM_ANTI) return n_probe;
+    if (h->st.duplicate_rows == 0) return n_probe;      // unique build keys: at most one row per probe row
+    const double avg = h->st.distinct_keys > 0 ? (double)(h->st.build_rows - h->st.build_null_keys) / (double)h->st.distinct_keys : 1.0;
+    return (int64_t)((double)n_probe * avg * 1.25) + 4096 + (pl.mode == PM_OUTER ? n_probe : 0);
+}
+
+void fill_result(b200j_result *out, ResultOwner *ro, int64_t n, int mem) {
+    out->mem = mem;
+    out->n = n;
+    out->build_idx = (uint64_t *)ro->build_idx;
+    out->probe_idx = (uint32_t *)ro->probe_idx;
+    out->_owner = ro;
+}
+
+void release_owner(H *h, ResultOwner *ro) {
+    if (!ro) return;
+    if (ro->mem == B200J_MEM_DEVICE) {
+        if (ro->build_idx) cudaFreeAsync(ro->build_idx, h->stream);
+        if (ro->probe_idx) cudaFreeAsync(ro->probe_idx, h->stream);
+    } else {
+        pinned_give(h, ro->build_idx);
+        pinned_give(h, ro->probe_idx);
+    }
+    delete ro;
+}
+
+// Device-resident probe of `n` keys. Output arrays are device memory owned by *ro (sized to the exact result).
+// Returns rows produced.
+int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_t bit_offset, int64_t n, const ProbePlan &pl,
+                     bool count_only, ResultOwner *ro, int64_t *n_build_null) {
+    const int kw = h->key_widths[0];
+    const bool want_build = (pl.mode == PM_PAIRS || pl.mode == PM_OUTER);
+    int64_t cap = count_only ? 0 : estimate_out_cap(h, n, pl);
+    *n_build_null = 0;
+    if (n == 0) return 0;
+    if (h->layout == B200J_LAYOUT_RADIX)
+        return radix_probe(h, d_keys, d_validity, bit_offset, n, pl.mode, pl.mark, count_only, cap, want_build, ro, n_build_null);
+    for (int attempt = 0; attempt < 3; attempt++) {
+        void *ob = nullptr, *op = nullptr;
+        if (cap > 0) {
+            if (want_build) CU(cudaMallocAsync(&ob, (size_t)cap * 8, h->stream));
+            CU(cudaMallocAsync(&op, (size_t)cap * 4, h->stream));
+        }
+        CU(cudaMemsetAsync(&h->d_ctr->out_count, 0, 8, h->stream));
+        CU(cudaMemsetAsync(&h->d_ctr->build_null_out, 0, 8, h->stream));
+        ProbeArgs a{};
+        a.keys = d_keys;
+        a.validity = d_validity;
+        a.bit_offset = bit_offset;
+        a.rowid = nullptr;
+        a.n = n;
+        a.mis = (int)(((uintptr_t)d_keys & 15) / (uintptr_t)kw);
+        a.tv = h->view();
+        a.hk = h->hk;
+        a.out_build = (uint64_t *)ob;
+        a.out_probe = (uint32_t *)op;
+        a.out_cap = (uint64_t)cap;
+        a.visited = (uint32_t *)h->visited.p;
+        a.ctr = h->d_ctr;
+        {
+            PhaseTimer tm(h, &h->st.ms_probe);
+            launch_probe(h, pl, a, kw, false);
+            CU(cudaGetLastError());
+            tm.stop();
+        }
+        CU(cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        const int64_t total = (int64_t)h->h_ctr->out_count;
+        *n_build_null = (int64_t)h->h_ctr->build_null_out;
+        if (count_only || total <= cap) {
+            ro->build_idx = ob;
+            ro->probe_idx = op;
+            ro->build_bytes = (size_t)cap * 8;
+            ro->probe_bytes = (size_t)cap * 4;
+            return total;
+        }
+        // the pair buffer was too small (duplicate keys): the kernel counted everything, run again with room.
+        // Marking is idempotent, so the re-run is safe for the visited bitmap.
+        if (ob) cudaFreeAsync(ob, h->stream);
+        if (op) cudaFreeAsync(op, h->stream);
+        cap = total;
+        h->st.probe_retries++;
+    }
+    throw Fail{B200J_ERR_CUDA, "probe output did not converge"};
+}
+
+void move_result_to_host(H *h, ResultOwner *ro, int64_t n) {
+    void *hb = nullptr, *hp = nullptr;
+    if (ro->build_idx) {
+        hb = pinned_take(h, (size_t)std::max<int64_t>(n, 1) * 8);
+        CU(cudaMemcpyAsync(hb, ro->build_idx, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
+    }
+    if (ro->probe_idx) {
+        hp = pinned_take(h, (size_t)std::max<int64_t>(n, 1) * 4);
+        CU(cudaMemcpyAsync(hp, ro->probe_idx, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+    }
+    CU(cudaStreamSynchronize(h->stream));
+    if (ro->build_idx) cudaFreeAsync(ro->build_idx, h->stream);
+    if (ro->probe_idx) cudaFreeAsync(ro->probe_idx, h->stream);
+    ro->build_idx = hb;
+    ro->probe_idx = hp;
+    ro->mem = B200J_MEM_HOST;
+}
+
+void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want, b200j_result *out) {
+    REQUIRE(partition >= 0 && partition < h->cfg.n_partitions, B200J_ERR_INVALID, "partition out of range");
+    REQUIRE(h->built, B200J_ERR_INVALID, "probe before every partition finished the build side");
+    REQUIRE(!h->probe_done[partition], B200J_ERR_STATE, "probe_batch after probe_finish");
+    REQUIRE(out != nullptr && out->struct_size >= sizeof(b200j_result), B200J_ERR_INVALID, "result struct missing or too small");
+    check_batch(h, b, h->cfg.n_probe_payload);
+    REQUIRE(b->n_rows < 0xffffffffLL, B200J_ERR_UNSUPPORTED, "probe batch of 2^32-1 rows or more (probe indices are UInt32)");
+    const ProbePlan pl = plan_for(h->cfg.join_type, (want & B200J_OUT_MATCHES_ONLY) != 0);
+    const bool count_only = (want & B200J_OUT_COUNT_ONLY) != 0;
+    const int kw = h->key_widths[0];
+    const int64_t n = b->n_rows;
+    ResultOwner *ro = new ResultOwner();
+    std::vector<void *> temps;
+    try {
+        int64_t total = 0, n_bnull = 0;
+        if (b->mem == B200J_MEM_DEVICE || n == 0) {
+            const b200j_column &kc = b->keys[0];
+            total = probe_device(h, n ? kc.values : nullptr, n ? kc.validity : nullptr, n ? kc.bit_offset : 0, n, pl, count_only, ro, &n_bnull);
+        } else {
+            const b200j_column &kc = b->keys[0];
+            void *dk = nullptr;
+            CU(cudaMallocAsync(&dk, (size_t)n * kw + 16, h->stream));
+            temps.push_back(dk);
+            CU(cudaMemcpyAsync(dk, kc.values, (size_t)n * kw, cudaMemcpyHostToDevice, h->stream));
+            int64_t boff = 0;
+            const uint8_t *dv = stage_validity(h, kc, n, B200J_MEM_HOST, temps, &boff);
+            total = probe_device(h, dk, dv, boff, n, pl, count_only, ro, &n_bnull);
+        }
+        if (count_only) {
+            if (ro->build_idx) cudaFreeAsync(ro->build_idx, h->stream);
+            if (ro->probe_idx) cudaFreeAsync(ro->probe_idx, h->stream);
+            ro->build_idx = ro->probe_idx = nullptr;
+        } else if (want & B200J_OUT_HOST) {
+            move_result_to_host(h, ro, total);
+        }
+        free_temps(h, temps);
+        fill_result(out, ro, total, ro->mem);
+        out->n_build_null = n_bnull;
+        out->n_probe_null = 0;
+        h->st.probe_rows += n;
+        h->st.result_rows += total;
+    } catch (...) {
+        free_temps(h, temps);
+        release_owner(h, ro);
+        throw;
+    }
+}
+
+// bitmap -> indices on the device; returns count. out64/out32: which side receives the indices.
+int64_t select_bits(H *h, const uint32_t *bm, int64_t n, bool want_set, void **out64, void **out32) {
+    if (out64) *out64 = nullptr;
+    if (out32) *out32 = nullptr;
+    if (n == 0) return 0;
+    void *o64 = nullptr, *o32 = nullptr;
+    if (out64) CU(cudaMallocAsync(&o64, (size_t)n * 8, h->stream));
+    if (out32) CU(cudaMallocAsync(&o32, (size_t)n * 4, h->stream));
+    CU(cudaMemsetAsync(&h->d_ctr->out_count, 0, 8, h->stream));
+    bitmap_select_kernel<<<grid_for(h, (n + 31) / 32, 256, 8), 256, 0, h->stream>>>(bm, n, want_set ? 1 : 0, (uint64_t *)o64, (uint32_t *)o32,
+                                                                                     (uint64_t)n, &h->d_ctr->out_count);
+    h->st.kernel_launches++;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    if (out64) *out64 = o64;
+    if (out32) *out32 = o32;
+    return (int64_t)h->h_ctr->out_count;
+}
+
+void fill_null_side(H *h, ResultOwner *ro, int64_t n, bool null_build, bool null_probe) {
+    if (n == 0) return;
+    if (null_build && !ro->build_idx) {
+        CU(cudaMallocAsync(&ro->build_idx, (size_t)n * 8, h->stream));
+        fill_u64_kernel<<<grid_for(h, n, 256, 8), 256, 0, h->stream>>>((uint64_t *)ro->build_idx, n, ~0ULL);
+        h->st.kernel_launches++;
+    }
+    if (null_probe && !ro->probe_idx) {
+        CU(cudaMallocAsync(&ro->probe_idx, (size_t)n * 4, h->stream));
+        fill_u32_kernel<<<grid_for(h, n, 256, 8), 256, 0, h->stream>>>((uint32_t *)ro->probe_idx, n, 0xffffffffu);
+        h->st.kernel_launches++;
+    }
+}
+
+void do_probe_finish(H *h, int32_t partition, uint32_t want, b200j_result *out) {
+    REQUIRE(partition >= 0 && partition < h->cfg.n_partitions, B200J_ERR_INVALID, "partition out of range");
+    REQUIRE(h->built, B200J_ERR_INVALID, "probe_finish before the build side finished");
+    REQUIRE(!h->probe_done[partition], B200J_ERR_STATE, "State already consumed: probe_finish called twice for this partition");
+    REQUIRE(out != nullptr && out->struct_size >= sizeof(b200j_result), B200J_ERR_INVALID, "result struct missing or too small");
+    h->probe_done[partition] = 1;
+    h->n_probe_done++;
+    ResultOwner *ro = new ResultOwner();
+    try {
+        int64_t n = 0;
+        const int jt = h->cfg.join_type;
+        const bool last = h->n_probe_done == h->cfg.n_partitions;
+        const bool left_kind = jt == B200J_LEFT || jt == B200J_FULL || jt == B200J_LEFT_SEMI || jt == B200J_LEFT_ANTI;
+        if (last && left_kind && h->n_build > 0) {
+            // emit_unmatched_build_records (left_outer.rs:174-195, full.rs:181-201, left_anti.rs:166-179),
+            // emit_matched_build_records (left_semi.rs:166-179)
+            n = select_bits(h, (const uint32_t *)h->visited.p, h->n_build, jt == B200J_LEFT_SEMI, &ro->build_idx, nullptr);
+            if (!(want & B200J_OUT_COUNT_ONLY)) fill_null_side(h, ro, n, false, true);
+        }
+        if (want & B200J_OUT_COUNT_ONLY) {
+            if (ro->build_idx) cudaFreeAsync(ro->build_idx, h->stream);
+            ro->build_idx = nullptr;
+        } else if (want & B200J_OUT_HOST) {
+            move_result_to_host(h, ro, n);
+        }
+        fill_result(out, ro, n, ro->mem);
+        out->n_build_null = 0;
+        out->n_probe_null = n;
+        h->st.result_rows += n;
+    } catch (...) {
+        release_owner(h, ro);
+        throw;
+    }
+}
+
+void do_apply_pairs(H *h, int32_t partition, int64_t n_probe_rows, int32_t mem, int64_t n_pairs, const uint64_t *build_idx,
+                    const uint32_t *probe_idx, uint32_t want, b200j_result *out) {
+    REQUIRE(partition >= 0 && partition < h->cfg.n_partitions, B200J_ERR_INVALID, "partition out of range");
+    REQUIRE(h->built, B200J_ERR_INVALID, "apply_pairs before the build side finished");
+    REQUIRE(out != nullptr && out->struct_size >= sizeof(b200j_result), B200J_ERR_INVALID, "result struct missing or too small");
+    REQUIRE(n_pairs >= 0 && n_probe_rows >= 0 && n_probe_rows < 0xffffffffLL, B200J_ERR_INVALID, "bad pair / row counts");
+    REQUIRE(n_pairs == 0 || (build_idx && probe_idx), B200J_ERR_INVALID, "pair arrays missing");
+    const int jt = h->cfg.join_type;
+    const bool mark = jt == B200J_LEFT || jt == B200J_FULL || jt == B200J_LEFT_SEMI || jt == B200J_LEFT_ANTI;
+    const bool need_seen = jt == B200J_RIGHT || jt == B200J_FULL || jt == B200J_RIGHT_SEMI || jt == B200J_RIGHT_ANTI;
+    const bool keep_pairs = jt == B200J_INNER || jt == B200J_LEFT || jt == B200J_RIGHT || jt == B200J_FULL;
+    ResultOwner *ro = new ResultOwner();
+    std::vector<void *> temps;
+    try {
+        const uint64_t *db = build_idx;
+        const uint32_t *dp = probe_idx;
+        if (mem == B200J_MEM_HOST && n_pairs > 0) {
+            void *a = nullptr, *b = nullptr;
+            CU(cudaMallocAsync(&a, (size_t)n_pairs * 8, h->stream));
+            temps.push_back(a);
+            CU(cudaMallocAsync(&b, (size_t)n_pairs * 4, h->stream));
+            temps.push_back(b);
+            CU(cudaMemcpyAsync(a, build_idx, (size_t)n_pairs * 8, cudaMemcpyHostToDevice, h->stream));
+            CU(cudaMemcpyAsync(b, probe_idx, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, h->stream));
+            db = (const uint64_t *)a;
+            dp = (const uint32_t *)b;
+        }
+        uint32_t *seen = nullptr;
+        if (need_seen && n_probe_rows > 0) {
+            void *s = nullptr;
+            const size_t sb = (size_t)((n_probe_rows + 31) / 32 + 1) * 4;
+            CU(cudaMallocAsync(&s, sb, h->stream));
+            temps.push_back(s);
+            CU(cudaMemsetAsync(s, 0, sb, h->stream));
+            seen = (uint32_t *)s;
+        }
+        if (n_pairs > 0 && (mark || seen)) {
+            mark_pairs_kernel<<<grid_for(h, n_pairs, 256, 8), 256, 0, h->stream>>>(db, dp, n_pairs, seen, mark ? (uint32_t *)h->visited.p : nullptr);
+            h->st.kernel_launches++;
+        }
+        int64_t n_extra = 0;
+        void *extra32 = nullptr;
+        if (need_seen && n_probe_rows > 0) {
+            const bool want_set = jt == B200J_RIGHT_SEMI;
+            n_extra = select_bits(h, seen, n_probe_rows, want_set, nullptr, &extra32);
+            temps.push_back(extra32);
+        }
+        const int64_t n_keep = keep_pairs ? n_pairs : 0;
+        const int64_t n = n_keep + n_extra;
+        if (n > 0 && !(want & B200J_OUT_COUNT_ONLY)) {
+            CU(cudaMallocAsync(&ro->build_idx, (size_t)n * 8, h->stream));
+            CU(cudaMallocAsync(&ro->probe_idx, (size_t)n * 4, h->stream));
+            if (n_keep) {
+                CU(cudaMemcpyAsync(ro->build_idx, db, (size_t)n_keep * 8, cudaMemcpyDeviceToDevice, h->stream));
+                CU(cudaMemcpyAsync(ro->probe_idx, dp, (size_t)n_keep * 4, cudaMemcpyDeviceToDevice, h->stream));
+            }
+            if (n_extra) {
+                fill_u64_kernel<<<grid_for(h, n_extra, 256, 8), 256, 0, h->stream>>>((uint64_t *)ro->build_idx + n_keep, n_extra, ~0ULL);
+                h->st.kernel_launches++;
+                CU(cudaMemcpyAsync((uint32_t *)ro->probe_idx + n_keep, extra32, (size_t)n_extra * 4, cudaMemcpyDeviceToDevice, h->stream));
+            }
+        }
+        CU(cudaGetLastError());
+        if (!(want & B200J_OUT_COUNT_ONLY) && (want & B200J_OUT_HOST)) move_result_to_host(h, ro, n);
+        else CU(cudaStreamSynchronize(h->stream));
+        free_temps(h, temps);
+        fill_result(out, ro, n, ro->mem);
+        out->n_build_null = n_extra;
+        out->n_probe_null = 0;
+        h->st.result_rows += n;
+    } catch (...) {
+        free_temps(h, temps);
+        release_owner(h, ro);
+        throw;
+    }
+}
+
+void do_hash_keys(H *h, const b200j_batch *b, uint64_t *out) {
+    check_batch(h, b, 0);
+    REQUIRE(out != nullptr || b->n_rows == 0, B200J_ERR_INVALID, "hash output buffer is NULL");
+    REQUIRE(h->cfg.n_keys <= MAX_KEYS, B200J_ERR_UNSUPPORTED, "too many key columns");
+    const int64_t n = b->n_rows;
+    if (n == 0) return;
+    std::vector<void *> temps;
+    try {
+        KeyCols kc{};
+        kc.n = h->cfg.n_keys;
+        for (int i = 0; i < kc.n; i++) {
+            const int w = h->key_widths[i];
+            kc.c[i].width = w;
+            if (b->mem == B200J_MEM_DEVICE) {
+                kc.c[i].values = b->keys[i].values;
+                kc.c[i].validity = b->keys[i].validity;
+                kc.c[i].bit_offset = b->keys[i].bit_offset;
+            } else {
+                void *d = nullptr;
+                CU(cudaMallocAsync(&d, (size_t)n * w, h->stream));
+                temps.push_back(d);
+                CU(cudaMemcpyAsync(d, b->keys[i].values, (size_t)n * w, cudaMemcpyHostToDevice, h->stream));
+                kc.c[i].values = d;
+                int64_t boff = 0;
+                kc.c[i].validity = stage_validity(h, b->keys[i], n, B200J_MEM_HOST, temps, &boff);
+                kc.c[i].bit_offset = boff;
+            }
+        }
+        uint64_t *d_out = out;
+        if (b->mem == B200J_MEM_HOST) {
+            void *d = nullptr;
+            CU(cudaMallocAsync(&d, (size_t)n * 8, h->stream));
+            temps.push_back(d);
+            d_out = (uint64_t *)d;
+        }
+        hash_keys_kernel<<<grid_for(h, n, 256, 8), 256, 0, h->stream>>>(kc, n, h->hk, d_out);
+        h->st.kernel_launches++;
+        CU(cudaGetLastError());
+        if (b->mem == B200J_MEM_HOST) CU(cudaMemcpyAsync(out, d_out, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        free_temps(h, temps);
+    } catch (...) {
+        free_temps(h, temps);
+        throw;
+    }
+}
+
+template <typename F>
+int32_t guarded(b200j_handle *h, F &&f) {
+    if (!h) {
+        g_last_error = "handle is NULL";
+        return B200J_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> g(h->mu);
+    try {
+        int cur = -1;
+        if (cudaGetDevice(&cur) != cudaSuccess || cur != h->cfg.device) {
+            if (cudaSetDevice(h->cfg.device) != cudaSuccess) {
+                cudaGetLastError();
+                h->err = "cudaSetDevice failed (no CUDA device?)";
+                return B200J_ERR_CUDA;
+            }
+        }
+        f();
+        return B200J_OK;
+    } catch (const Fail &e) {
+        h->err = e.msg;
+        return e.code;
+    } catch (const std::bad_alloc &) {
+        h->err = "host allocation failed";
+        return B200J_ERR_OOM;
+    } catch (...) {
+        h->err = "unknown internal error";
+        return B200J_ERR_CUDA;
+    }
+}
+
+}  // namespace
+
+namespace {
+#include "radix_host.inl"
+#include "gather_host.inl"
+}  // namespace
+
+extern "C" {
+
+int32_t b200j_abi_version(void) { return B200J_ABI_VERSION; }
+
+int32_t b200j_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
+    if (!cfg || !out) {
+        g_last_error = "b200j_create: NULL argument";
+        return B200J_ERR_INVALID;
+    }
+    *out = nullptr;
+    b200j_handle *h = nullptr;
+    try {
+        REQUIRE(cfg->struct_size >= sizeof(b200j_config), B200J_ERR_INVALID, "config.struct_size too small (ABI mismatch)");
+        REQUIRE(cfg->join_type >= 0 && cfg->join_type <= 7, B200J_ERR_INVALID, "unknown join type");
+        REQUIRE(cfg->n_partitions >= 1, B200J_ERR_INVALID, "n_partitions must be >= 1");
+        REQUIRE(cfg->n_keys >= 1 && cfg->n_keys <= MAX_KEYS, B200J_ERR_INVALID, "n_keys must be in 1..8");
+        REQUIRE(cfg->key_widths != nullptr, B200J_ERR_INVALID, "key_widths is NULL");
+        for (int i = 0; i < cfg->n_keys; i++)
+            REQUIRE(cfg->key_widths[i] == 4 || cfg->key_widths[i] == 8, B200J_ERR_UNSUPPORTED, "key columns must be 4 or 8 bytes wide");
+        REQUIRE(cfg->n_build_payload >= 0 && cfg->n_probe_payload >= 0, B200J_ERR_INVALID, "negative payload count");
+        REQUIRE(cfg->n_build_payload == 0 || cfg->build_payload_types, B200J_ERR_INVALID, "build_payload_types is NULL");
+        REQUIRE(cfg->n_probe_payload == 0 || cfg->probe_payload_types, B200J_ERR_INVALID, "probe_payload_types is NULL");
+        REQUIRE(cfg->layout >= 0 && cfg->layout <= 2, B200J_ERR_INVALID, "unknown layout");
+        REQUIRE(cfg->radix_bits >= 0 && cfg->radix_bits <= 12, B200J_ERR_INVALID, "radix_bits must be in 0..12");
+        auto ok_type = [](int t) { return t == B200J_T_UTF8 || t == 1 || t == 2 || t == 4 || t == 8 || t == 16; };
+        for (int i = 0; i < cfg->n_build_payload; i++) REQUIRE(ok_type(cfg->build_payload_types[i]), B200J_ERR_UNSUPPORTED, "unsupported payload type");
+        for (int i = 0; i < cfg->n_probe_payload; i++) REQUIRE(ok_type(cfg->probe_payload_types[i]), B200J_ERR_UNSUPPORTED, "unsupported payload type");
+        int ndev = 0;
+        if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+            cudaGetLastError();
+            throw Fail{B200J_ERR_CUDA, "no CUDA device visible: this library has no CPU fallback"};
+        }
+        REQUIRE(cfg->device >= 0 && cfg->device < ndev, B200J_ERR_INVALID, "device ordinal out of range");
+        CU(cudaSetDevice(cfg->device));
+
+        h = new b200j_handle();
+        h->cfg = *cfg;
+        h->key_widths.assign(cfg->key_widths, cfg->key_widths + cfg->n_keys);
+        h->build_payload_types.assign(cfg->build_payload_types, cfg->build_payload_types + cfg->n_build_payload);
+        h->probe_payload_types.assign(cfg->probe_payload_types, cfg->probe_payload_types + cfg->n_probe_payload);
+        h->cfg.key_widths = h->key_widths.data();
+        h->cfg.build_payload_types = h->build_payload_types.data();
+        h->cfg.probe_payload_types = h->probe_payload_types.data();
+        uint64_t k[4] = {cfg->hash_keys[0], cfg->hash_keys[1], cfg->hash_keys[2], cfg->hash_keys[3]};
+        if (!(k[0] | k[1] | k[2] | k[3])) keys_with_seed(0, k);
+        h->hk = HashKeys{k[0], k[1], k[2], k[3], cfg->hash_flags, 0};
+        h->timing = (cfg->flags & B200J_FLAG_TIMING) != 0;
+        cudaDeviceProp prop{};
+        CU(cudaGetDeviceProperties(&prop, cfg->device));
+        h->sm_count = prop.multiProcessorCount;
+        h->l2_bytes = prop.l2CacheSize;
+        if (cfg->stream) {
+            h->stream = (cudaStream_t)cfg->stream;
+        } else {
+            CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+            h->own_stream = true;
+        }
+        CU(cudaStreamCreateWithFlags(&h->copy_in, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&h->copy_out, cudaStreamNonBlocking));
+        CU(cudaEventCreate(&h->ev0));
+        CU(cudaEventCreate(&h->ev1));
+        // keep freed blocks in the stream-ordered pool: result buffers are recycled, not returned to the driver
+        cudaMemPool_t pool;
+        CU(cudaDeviceGetDefaultMemPool(&pool, cfg->device));
+        uint64_t thr = UINT64_MAX;
+        CU(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+        CU(cudaMalloc((void **)&h->d_ctr, sizeof(Counters)));
+        CU(cudaHostAlloc((void **)&h->h_ctr, sizeof(Counters), cudaHostAllocDefault));
+        memset(h->h_ctr, 0, sizeof(Counters));
+        h->bkeys.resize(cfg->n_keys);
+        for (int i = 0; i < cfg->n_keys; i++) h->bkeys[i].type = cfg->key_widths[i];
+        h->bpayload.resize(cfg->n_build_payload);
+        for (int i = 0; i < cfg->n_build_payload; i++) h->bpayload[i].type = cfg->build_payload_types[i];
+        h->build_done.assign(cfg->n_partitions, 0);
+        h->probe_done.assign(cfg->n_partitions, 0);
+        h->build_cap_rows = std::max<int64_t>(cfg->expected_build_rows, 0);
+        h->st.struct_size = sizeof(b200j_stats);
+        if (h->build_cap_rows > 0)
+            for (auto &c : h->bkeys) dev_alloc(h, c.values, (size_t)h->build_cap_rows * c.type + 16);
+        *out = h;
+        return B200J_OK;
+    } catch (const Fail &e) {
+        g_last_error = e.msg;
+        delete h;
+        return e.code;
+    } catch (...) {
+        g_last_error = "unknown error in b200j_create";
+        delete h;
+        return B200J_ERR_CUDA;
+    }
+}
+
+int32_t b200j_destroy(b200j_handle *h) {
+    if (!h) return B200J_OK;
+    cudaSetDevice(h->cfg.device);
+    cudaStreamSynchronize(h->stream);
+    auto fr = [&](DevBuf &b) { if (b.p) cudaFreeAsync(b.p, h->stream); b.p = nullptr; };
+    for (auto *v : {&h->bkeys, &h->bpayload})
+        for (auto &c : *v) { fr(c.values); fr(c.offsets); fr(c.validity); }
+    radix_release(h);
+    fr(h->slots); fr(h->zero_slot); fr(h->rowids); fr(h->visited); fr(h->part_base); fr(h->part_mask);
+    cudaStreamSynchronize(h->stream);
+    for (auto &p : h->pinned_cache) { pinned_size(p.p, true); cudaFreeHost(p.p); }
+    if (h->d_ctr) cudaFree(h->d_ctr);
+    if (h->h_ctr) cudaFreeHost(h->h_ctr);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->copy_in) cudaStreamDestroy(h->copy_in);
+    if (h->copy_out) cudaStreamDestroy(h->copy_out);
+    if (h->own_stream) cudaStreamDestroy(h->stream);
+    cudaGetLastError();
+    delete h;
+    return B200J_OK;
+}
+
+const char *b200j_last_error(const b200j_handle *h) { return h ? h->err.c_str() : g_last_error.c_str(); }
+
+int32_t b200j_get_stats(b200j_handle *h, b200j_stats *out) {
+    if (!h || !out) return B200J_ERR_INVALID;
+    std::lock_guard<std::mutex> g(h->mu);
+    const uint32_t sz = std::min<uint32_t>(out->struct_size ? out->struct_size : sizeof(b200j_stats), sizeof(b200j_stats));
+    h->st.struct_size = sizeof(b200j_stats);
+    memcpy(out, &h->st, sz);
+    return B200J_OK;
+}
+
+int32_t b200j_reset_stats(b200j_handle *h) {
+    if (!h) return B200J_ERR_INVALID;
+    std::lock_guard<std::mutex> g(h->mu);
+    h->st.probe_rows = h->st.result_rows = 0;
+    h->st.ms_build_copy = h->st.ms_build_partition = h->st.ms_build_insert = 0;
+    h->st.ms_probe_partition = h->st.ms_probe = h->st.ms_gather = 0;
+    h->st.probe_launches = h->st.kernel_launches = h->st.probe_retries = 0;
+    return B200J_OK;
+}
+
+int32_t b200j_synchronize(b200j_handle *h) {
+    return guarded(h, [&] { CU(cudaStreamSynchronize(h->stream)); });
+}
+
+int32_t b200j_build_push(b200j_handle *h, int32_t partition, const b200j_batch *batch) {
+    return guarded(h, [&] { do_build_push(h, partition, batch); });
+}
+int32_t b200j_build_finish(b200j_handle *h, int32_t partition) {
+    return guarded(h, [&] { do_build_finish(h, partition); });
+}
+int32_t b200j_probe_batch(b200j_handle *h, int32_t partition, const b200j_batch *batch, uint32_t want, b200j_result *out) {
+    return guarded(h, [&] { do_probe_batch(h, partition, batch, want, out); });
+}
+int32_t b200j_apply_pairs(b200j_handle *h, int32_t partition, int64_t n_probe_rows, int32_t mem, int64_t n_pairs,
+                          const uint64_t *build_idx, const uint32_t *probe_idx, uint32_t want, b200j_result *out) {
+    return guarded(h, [&] { do_apply_pairs(h, partition, n_probe_rows, mem, n_pairs, build_idx, probe_idx, want, out); });
+}
+int32_t b200j_probe_finish(b200j_handle *h, int32_t partition, uint32_t want, b200j_result *out) {
+    return guarded(h, [&] { do_probe_finish(h, partition, want, out); });
+}
+int32_t b200j_result_release(b200j_handle *h, b200j_result *r) {
+    return guarded(h, [&] {
+        if (!r) return;
+        release_owner(h, (ResultOwner *)r->_owner);
+        r->_owner = nullptr;
+        r->build_idx = nullptr;
+        r->probe_idx = nullptr;
+        r->n = 0;
+    });
+}
+int32_t b200j_gather(b200j_handle *h, const b200j_result *pairs, const b200j_batch *probe_batch, uint32_t want, b200j_gathered *out) {
+    return guarded(h, [&] { do_gather(h, pairs, probe_batch, want, out); });
+}
+int32_t b200j_gathered_release(b200j_handle *h, b200j_gathered *g) {
+    return guarded(h, [&] { do_gathered_release(h, g); });
+}
+int32_t b200j_hash_keys(b200j_handle *h, const b200j_batch *batch, uint64_t *out) {
+    return guarded(h, [&] { do_hash_keys(h, batch, out); });
+}
+
+int32_t b200j_host_alloc(size_t bytes, void **out) {
+    if (!out) return B200J_ERR_INVALID;
+    *out = nullptr;
+    cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        g_last_error = std::string("cudaHostAlloc: ") + cudaGetErrorString(e);
+        return e == cudaErrorMemoryAllocation ? B200J_ERR_OOM : B200J_ERR_CUDA;
+    }
+    return B200J_OK;
+}
+int32_t b200j_host_free(void *p) {
+    if (p && cudaFreeHost(p) != cudaSuccess) {
+        cudaGetLastError();
+        return B200J_ERR_CUDA;
+    }
+    return B200J_OK;
+}
+
+}  // extern "C"

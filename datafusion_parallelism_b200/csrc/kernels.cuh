@@ -1,0 +1,628 @@
+// kernels.cuh — sm_100a device code of the B200 hash join (no tensor cores: nothing here is a contraction;
+// every kernel is HBM/L2-bound integer work, so the rules that matter are coalesced 128-bit loads,
+// warp-aggregated atomics, and keeping the random-access working set inside the 126 MB L2).
+//
+// What each kernel replaces in the reference (jamesfer/datafusion-parallelism @ 3e184de):
+//   hash_one / hash_keys_kernel      calculate_hash, src/shared/shared.rs:11-16 (create_hashes over ahash)
+//   build_insert_kernel              JoinStateInstance::add, version10/parallel_join_execution_state.rs:91-133
+//                                    + Inner::insert_atomically, version10/new_map_3/fixed_table.rs:560-672
+//   csr_scan_kernel/csr_fill_kernel  the overflow chain of version10 (parallel_join_execution_state.rs:101-106),
+//                                    re-laid out as contiguous row-id runs so long duplicate chains are copied
+//                                    warp-wide instead of pointer-chased
+//   probe_kernel                     get_matching_indices[_with_probe] (shared.rs:29-81) + Version10Lookup::get_iter
+//                                    (lookup_implementation_3.rs:31-59) + equal_rows_arr (datafusion_private.rs:40-80,
+//                                    fused: slots hold the key VALUE, so a slot match is a key match) +
+//                                    append_right_indices / get_semi_indices / get_anti_indices
+//                                    (datafusion_private.rs:85-185) + ConcurrentBitSet::set_ones (concurrent_bit_set.rs:28-52)
+//   bitmap_select_kernel             get_unset_indices_array / get_set_indices_array (concurrent_bit_set.rs:93-131)
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace b200j {
+
+// ------------------------------------------------------------------------------------------------
+// ahash 0.8.11 fallback arithmetic (bit-identical to oracle/join_oracle.c)
+// ------------------------------------------------------------------------------------------------
+constexpr uint64_t AHASH_MULTIPLE = 6364136223846793005ULL;
+
+struct HashKeys {
+    uint64_t k0, k1, k2, k3;
+    int32_t  flags;
+    int32_t  _pad;
+};
+
+// 64x64 -> 128 bit product folded to 64 bits (low ^ high). Schoolbook on 32-bit limbs: four IMAD.WIDE.U32
+// with 64-bit accumulate, no carry chains (every partial sum provably fits 64 bits).
+__host__ __device__ __forceinline__ uint64_t folded_multiply(uint64_t s, uint64_t by) {
+#ifdef __CUDA_ARCH__
+    const uint32_t a0 = (uint32_t)s, a1 = (uint32_t)(s >> 32);
+    const uint32_t b0 = (uint32_t)by, b1 = (uint32_t)(by >> 32);
+    const uint64_t p00 = (uint64_t)a0 * b0;
+    const uint64_t t1  = (uint64_t)a0 * b1 + (p00 >> 32);
+    const uint64_t t2  = (uint64_t)a1 * b0 + (uint32_t)t1;
+    const uint64_t hi  = (uint64_t)a1 * b1 + (t1 >> 32) + (t2 >> 32);
+    const uint64_t lo  = (t2 << 32) | (uint32_t)p00;
+    return lo ^ hi;
+#else
+    unsigned __int128 r = (unsigned __int128)s * (unsigned __int128)by;
+    return (uint64_t)r ^ (uint64_t)(r >> 64);
+#endif
+}
+
+__host__ __device__ __forceinline__ uint64_t rotl64(uint64_t x, unsigned r) {
+    r &= 63u;
+    return r ? (x << r) | (x >> (64u - r)) : x;
+}
+
+// hash_one of a <=64-bit integer (32-bit keys arrive zero-extended). flags bit0: stable-toolchain variant.
+__host__ __device__ __forceinline__ uint64_t hash_one(const HashKeys &k, uint64_t v) {
+    const uint64_t buffer = folded_multiply(v ^ k.k1, AHASH_MULTIPLE);
+    const uint64_t h = folded_multiply(buffer, k.k0);
+    return (k.flags & 1) ? rotl64(h, (unsigned)(buffer & 63u)) : h;
+}
+
+// datafusion-common hash_utils::combine_hashes
+__host__ __device__ __forceinline__ uint64_t combine_hashes(uint64_t l, uint64_t r) {
+    return ((uint64_t)(17 * 37) + l) * 37ULL + r;
+}
+
+// ------------------------------------------------------------------------------------------------
+// data descriptors
+// ------------------------------------------------------------------------------------------------
+constexpr int MAX_KEYS = 8;
+
+struct KeyCol {
+    const void    *values;
+    const uint8_t *validity;   // LSB-first bitmap, may be null
+    int64_t        bit_offset;
+    int32_t        width;      // 4 or 8
+    int32_t        _pad;
+};
+
+struct KeyCols {
+    KeyCol  c[MAX_KEYS];
+    int32_t n;
+    int32_t _pad;
+};
+
+__device__ __forceinline__ bool bit_valid(const uint8_t *bm, int64_t i) {
+    return bm == nullptr || ((bm[i >> 3] >> (i & 7)) & 1);
+}
+
+// Table slot: 16 B, two per 32 B sector. key == 0 marks an empty slot (the key value 0 lives in a side slot).
+//   count == 1 : `row` is the build row
+//   count >= 2 : `row` is the start of a run of `count` build rows in rowids[]
+struct __align__(16) Slot {
+    unsigned long long key;
+    uint32_t           row;
+    uint32_t           count;
+};
+
+struct Counters {
+    unsigned long long out_count;     // probe: rows produced (may exceed capacity: then nothing past capacity is written)
+    unsigned long long distinct;      // build
+    unsigned long long dup_rows;
+    unsigned long long multi_slots;
+    unsigned long long null_keys;
+    unsigned long long csr_cursor;
+    unsigned long long build_null_out;
+    unsigned long long probe_null_out;
+};
+
+struct TableView {
+    Slot           *slots;
+    uint64_t        mask;          // direct layout: capacity - 1
+    Slot           *zero_slot;     // the slot of key value 0
+    uint32_t       *rowids;        // runs of duplicate-key rows
+    // radix layout: partition p = hash >> (64 - radix_bits) owns slots [part_base[p], part_base[p] + part_mask[p] + 1)
+    const uint64_t *part_base;
+    const uint32_t *part_mask;
+    int32_t         radix_bits;
+    int32_t         _pad;
+};
+
+template <bool RADIX>
+__device__ __forceinline__ void locate(const TableView &tv, uint64_t h, uint64_t &base, uint64_t &mask) {
+    if (RADIX) {
+        const uint32_t p = (uint32_t)(h >> (64 - tv.radix_bits));
+        base = __ldg(tv.part_base + p);
+        mask = __ldg(tv.part_mask + p);
+    } else {
+        base = 0;
+        mask = tv.mask;
+    }
+}
+
+__device__ __forceinline__ Slot load_slot(const Slot *p) {
+    // 16 B load that bypasses L1 (random access: L1 only pollutes) and reads through L2.
+    const ulonglong2 v = __ldcg(reinterpret_cast<const ulonglong2 *>(p));
+    Slot s;
+    s.key = v.x;
+    s.row = (uint32_t)v.y;
+    s.count = (uint32_t)(v.y >> 32);
+    return s;
+}
+
+// ------------------------------------------------------------------------------------------------
+// vectorised key loads: 4 keys per thread per tile, 128-bit loads wherever the address allows
+// ------------------------------------------------------------------------------------------------
+constexpr int TILE_THREADS = 256;
+constexpr int TILE_ITEMS   = 4;
+constexpr int TILE_ROWS    = TILE_THREADS * TILE_ITEMS;
+
+// `keys` is the caller's pointer; `mis` = number of keys by which it is misaligned from 16 B. Rows are
+// addressed in the aligned "virtual" index space v = row + mis, so every full vector load is 16 B aligned.
+template <int KW>
+__device__ __forceinline__ void load_tile_keys(const void *keys, int mis, int64_t n, int64_t tile, int t,
+                                               uint64_t (&key)[TILE_ITEMS], int64_t (&row)[TILE_ITEMS]) {
+    const int64_t vbase = tile * TILE_ROWS;
+    const int64_t vend = n + mis;
+    if (KW == 8) {
+        const unsigned long long *k64 = reinterpret_cast<const unsigned long long *>(keys) - mis;
+#pragma unroll
+        for (int v = 0; v < 2; v++) {
+            const int64_t vi = vbase + ((int64_t)v * TILE_THREADS + t) * 2;
+            row[2 * v] = vi - mis;
+            row[2 * v + 1] = vi + 1 - mis;
+            if (vi >= mis && vi + 1 < vend) {
+                const ulonglong2 x = __ldcs(reinterpret_cast<const ulonglong2 *>(k64 + vi));
+                key[2 * v] = x.x;
+                key[2 * v + 1] = x.y;
+            } else {
+                key[2 * v] = (vi >= mis && vi < vend) ? __ldcs(k64 + vi) : 0ULL;
+                key[2 * v + 1] = (vi + 1 >= mis && vi + 1 < vend) ? __ldcs(k64 + vi + 1) : 0ULL;
+            }
+        }
+    } else {
+        const uint32_t *k32 = reinterpret_cast<const uint32_t *>(keys) - mis;
+        const int64_t vi = vbase + (int64_t)t * 4;
+#pragma unroll
+        for (int q = 0; q < 4; q++) row[q] = vi + q - mis;
+        if (vi >= mis && vi + 3 < vend) {
+            const uint4 x = __ldcs(reinterpret_cast<const uint4 *>(k32 + vi));
+            key[0] = x.x; key[1] = x.y; key[2] = x.z; key[3] = x.w;
+        } else {
+#pragma unroll
+            for (int q = 0; q < 4; q++) key[q] = (vi + q >= mis && vi + q < vend) ? (uint64_t)__ldcs(k32 + vi + q) : 0ULL;
+        }
+    }
+}
+
+__device__ __forceinline__ unsigned long long warp_sum_u32(uint32_t v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// a1: create_hashes
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) hash_keys_kernel(KeyCols cols, int64_t n, HashKeys hk, uint64_t *__restrict__ out) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        uint64_t h = 0;
+        for (int c = 0; c < cols.n; c++) {
+            const KeyCol &kc = cols.c[c];
+            if (!bit_valid(kc.validity, kc.bit_offset + i)) continue;     // NULL leaves the running hash unchanged
+            const uint64_t v = kc.width == 8 ? reinterpret_cast<const unsigned long long *>(kc.values)[i]
+                                             : (uint64_t)reinterpret_cast<const uint32_t *>(kc.values)[i];
+            const uint64_t hv = hash_one(hk, v);
+            h = (c == 0) ? hv : combine_hashes(hv, h);
+        }
+        out[i] = h;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// a2: build — open addressing, atomicCAS claim on the key word, atomicAdd on the slot's count
+// ------------------------------------------------------------------------------------------------
+struct BuildArgs {
+    const void     *keys;
+    const uint8_t  *validity;     // build store bitmap (bit 0 = row 0) or null
+    const uint32_t *rowid;        // radix layout: explicit row ids of the partitioned keys; null = identity
+    int64_t         n;
+    int32_t         mis;
+    int32_t         _pad;
+    TableView       tv;
+    HashKeys        hk;
+    Counters       *ctr;
+};
+
+template <bool RADIX>
+__device__ __forceinline__ Slot *find_or_claim(const TableView &tv, const HashKeys &hk, uint64_t key, uint32_t &distinct) {
+    if (key == 0) return tv.zero_slot;
+    const uint64_t h = hash_one(hk, key);
+    uint64_t base, mask;
+    locate<RADIX>(tv, h, base, mask);
+    uint64_t i = h & mask;
+    for (;;) {
+        Slot *s = tv.slots + base + i;
+        unsigned long long cur = __ldcg(&s->key);
+        if (cur == 0ULL) {
+            cur = atomicCAS(&s->key, 0ULL, (unsigned long long)key);
+            if (cur == 0ULL) { distinct++; return s; }
+        }
+        if (cur == key) return s;
+        i = (i + 1) & mask;
+    }
+}
+
+template <int KW, bool RADIX>
+__global__ void __launch_bounds__(TILE_THREADS) build_insert_kernel(BuildArgs a) {
+    const int t = threadIdx.x;
+    uint32_t distinct = 0, dups = 0, multi = 0, nulls = 0;
+    const int64_t n_tiles = (a.n + a.mis + TILE_ROWS - 1) / TILE_ROWS;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        uint64_t key[TILE_ITEMS];
+        int64_t row[TILE_ITEMS];
+        load_tile_keys<KW>(a.keys, a.mis, a.n, tile, t, key, row);
+#pragma unroll
+        for (int q = 0; q < TILE_ITEMS; q++) {
+            if (row[q] < 0 || row[q] >= a.n) continue;
+            if (!bit_valid(a.validity, row[q])) { nulls++; continue; }
+            const uint32_t r = a.rowid ? __ldcs(a.rowid + row[q]) : (uint32_t)row[q];
+            Slot *s = find_or_claim<RADIX>(a.tv, a.hk, key[q], distinct);
+            const uint32_t pos = atomicAdd(&s->count, 1u);
+            if (pos == 0) {
+                s->row = r;
+                if (key[q] == 0) distinct++;
+            } else {
+                dups++;
+                if (pos == 1) multi++;
+            }
+        }
+    }
+    const unsigned long long d = warp_sum_u32(distinct), u = warp_sum_u32(dups), m = warp_sum_u32(multi), z = warp_sum_u32(nulls);
+    if ((t & 31) == 0) {
+        if (d) atomicAdd(&a.ctr->distinct, d);
+        if (u) atomicAdd(&a.ctr->dup_rows, u);
+        if (m) atomicAdd(&a.ctr->multi_slots, m);
+        if (z) atomicAdd(&a.ctr->null_keys, z);
+    }
+}
+
+// Duplicate keys: turn every slot with count >= 2 into a run header. The run takes count + 1 entries of
+// rowids[]: [cursor][row 0][row 1]...; slot.row points at "row 0". One warp-aggregated claim per warp.
+__global__ void __launch_bounds__(256) csr_scan_kernel(TableView tv, uint64_t n_slots, Counters *ctr) {
+    const int lane = threadIdx.x & 31;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t start = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    // n_slots + 1: the extra index is the zero-key side slot
+    for (uint64_t i0 = start - lane; i0 < n_slots + 1; i0 += stride) {
+        const uint64_t i = i0 + lane;
+        Slot *s = nullptr;
+        uint32_t need = 0;
+        if (i < n_slots) s = tv.slots + i; else if (i == n_slots) s = tv.zero_slot;
+        Slot v{0, 0, 0};
+        if (s) { v = load_slot(s); if (v.count >= 2) need = v.count + 1; }
+        // warp exclusive scan of `need`
+        uint32_t incl = need;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+        const uint32_t tot = __shfl_sync(0xffffffffu, incl, 31);
+        unsigned long long base = 0;
+        if (tot) {
+            if (lane == 0) base = atomicAdd(&ctr->csr_cursor, (unsigned long long)tot);
+            base = __shfl_sync(0xffffffffu, base, 0);
+        }
+        if (need) {
+            const uint32_t off = (uint32_t)(base + incl - need);
+            tv.rowids[off] = 1u;            // fill cursor: position 0 is taken by the first row
+            tv.rowids[off + 1] = v.row;
+            s->row = off + 1;
+        }
+    }
+}
+
+template <int KW, bool RADIX>
+__global__ void __launch_bounds__(TILE_THREADS) csr_fill_kernel(BuildArgs a) {
+    const int t = threadIdx.x;
+    const int64_t n_tiles = (a.n + a.mis + TILE_ROWS - 1) / TILE_ROWS;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        uint64_t key[TILE_ITEMS];
+        int64_t row[TILE_ITEMS];
+        load_tile_keys<KW>(a.keys, a.mis, a.n, tile, t, key, row);
+#pragma unroll
+        for (int q = 0; q < TILE_ITEMS; q++) {
+            if (row[q] < 0 || row[q] >= a.n) continue;
+            if (!bit_valid(a.validity, row[q])) continue;
+            const uint32_t r = a.rowid ? __ldcs(a.rowid + row[q]) : (uint32_t)row[q];
+            uint32_t dummy = 0;
+            Slot *s = find_or_claim<RADIX>(a.tv, a.hk, key[q], dummy);      // key is present: never claims
+            const Slot v = load_slot(s);
+            if (v.count < 2) continue;
+            if (__ldcg(a.tv.rowids + v.row) == r) continue;                  // the run's first row is already placed
+            const uint32_t p = atomicAdd(a.tv.rowids + v.row - 1, 1u);
+            a.tv.rowids[v.row + p] = r;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// a4 + a5 + a7: probe
+// ------------------------------------------------------------------------------------------------
+enum ProbeMode : int {
+    PM_PAIRS = 0,   // Inner / Left: (build, probe) for every match
+    PM_OUTER = 1,   // Right / Full: + (NULL, probe) for probe rows without a match
+    PM_SEMI  = 2,   // RightSemi: probe rows with a match, once
+    PM_ANTI  = 3,   // RightAnti: probe rows without a match
+    PM_MARK  = 4,   // LeftSemi / LeftAnti: only mark visited build rows
+};
+
+struct ProbeArgs {
+    const void     *keys;
+    const uint8_t  *validity;
+    int64_t         bit_offset;
+    const uint32_t *rowid;        // explicit probe row ids (radix layout) or null = identity
+    int64_t         n;
+    int32_t         mis;
+    int32_t         _pad;
+    TableView       tv;
+    HashKeys        hk;
+    uint64_t       *out_build;    // may be null (semi / anti / mark)
+    uint32_t       *out_probe;
+    uint64_t        out_cap;
+    uint32_t       *visited;      // bitmap over build rows (MARK)
+    Counters       *ctr;
+};
+
+__device__ __forceinline__ void mark_visited(uint32_t *visited, uint32_t row) {
+    uint32_t *w = visited + (row >> 5);
+    const uint32_t bit = 1u << (row & 31);
+    if (!(__ldcg(w) & bit)) atomicOr(w, bit);
+}
+
+template <int KW, int MODE, bool MARK, bool RADIX>
+__global__ void __launch_bounds__(TILE_THREADS) probe_kernel(ProbeArgs a) {
+    constexpr uint32_t FULL = 0xffffffffu;
+    constexpr int NWARP = TILE_THREADS / 32;
+    __shared__ uint32_t s_warp[NWARP];
+    __shared__ unsigned long long s_base;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const int64_t n_tiles = (a.n + a.mis + TILE_ROWS - 1) / TILE_ROWS;
+    uint32_t null_build_out = 0;
+
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        uint64_t key[TILE_ITEMS];
+        int64_t row[TILE_ITEMS];
+        load_tile_keys<KW>(a.keys, a.mis, a.n, tile, t, key, row);
+
+        // ---- hash + first slot load for all items before any is consumed (4 independent random loads in flight)
+        bool inrange[TILE_ITEMS], look[TILE_ITEMS];
+        uint64_t base[TILE_ITEMS], mask[TILE_ITEMS], idx[TILE_ITEMS];
+        Slot s[TILE_ITEMS];
+#pragma unroll
+        for (int q = 0; q < TILE_ITEMS; q++) {
+            inrange[q] = row[q] >= 0 && row[q] < a.n;
+            look[q] = inrange[q] && bit_valid(a.validity, a.bit_offset + (inrange[q] ? row[q] : 0));
+            s[q] = Slot{0, 0, 0};
+            if (look[q]) {
+                if (key[q] == 0) {
+                    s[q] = load_slot(a.tv.zero_slot);
+                    s[q].key = s[q].count ? 0ULL : 1ULL;      // present iff count > 0; compare below is against key 0
+                    base[q] = mask[q] = idx[q] = 0;
+                } else {
+                    const uint64_t h = hash_one(a.hk, key[q]);
+                    locate<RADIX>(a.tv, h, base[q], mask[q]);
+                    idx[q] = h & mask[q];
+                    s[q] = load_slot(a.tv.slots + base[q] + idx[q]);
+                }
+            }
+        }
+        // ---- resolve collisions (linear probing; the next slot is in the same 32 B sector half of the time)
+        uint32_t m[TILE_ITEMS];        // output rows of this item
+        bool found[TILE_ITEMS];
+        bool multi = false;
+#pragma unroll
+        for (int q = 0; q < TILE_ITEMS; q++) {
+            found[q] = false;
+            if (look[q]) {
+                if (key[q] == 0) {
+                    found[q] = (s[q].key == 0ULL);
+                } else {
+                    while (s[q].key != key[q] && s[q].key != 0ULL) {
+                        idx[q] = (idx[q] + 1) & mask[q];
+                        s[q] = load_slot(a.tv.slots + base[q] + idx[q]);
+                    }
+                    found[q] = (s[q].key == key[q]);
+                }
+            }
+            if (MODE == PM_PAIRS) m[q] = found[q] ? s[q].count : 0u;
+            else if (MODE == PM_OUTER) m[q] = found[q] ? s[q].count : (inrange[q] ? 1u : 0u);
+            else if (MODE == PM_SEMI) m[q] = found[q] ? 1u : 0u;
+            else if (MODE == PM_ANTI) m[q] = (inrange[q] && !found[q]) ? 1u : 0u;
+            else m[q] = 0u;
+            if (found[q] && s[q].count > 1u && (MODE == PM_PAIRS || MODE == PM_OUTER || MARK)) multi = true;
+        }
+
+        if (MODE == PM_MARK) {
+            // LeftSemi / LeftAnti: nothing is produced per batch (left_semi.rs:158-163, left_anti.rs:158-163)
+#pragma unroll
+            for (int q = 0; q < TILE_ITEMS; q++) {
+                if (!found[q]) continue;
+                if (s[q].count == 1u) mark_visited(a.visited, s[q].row);
+                else for (uint32_t k = 0; k < s[q].count; k++) mark_visited(a.visited, __ldcg(a.tv.rowids + s[q].row + k));
+            }
+            continue;
+        }
+
+        // ---- warp-level positions: ballot fast path when every item produces at most one row
+        const bool any_multi = __any_sync(FULL, multi);
+        uint32_t off[TILE_ITEMS];
+        uint32_t wtot = 0;
+        if (!any_multi) {
+#pragma unroll
+            for (int q = 0; q < TILE_ITEMS; q++) {
+                const uint32_t b = __ballot_sync(FULL, m[q] != 0u);
+                off[q] = wtot + __popc(b & lt_mask);
+                wtot += __popc(b);
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < TILE_ITEMS; q++) {
+                uint32_t incl = m[q];
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += y; }
+                off[q] = wtot + incl - m[q];
+                wtot += __shfl_sync(FULL, incl, 31);
+            }
+        }
+        // ---- one atomic per tile: block-aggregated reservation of output rows
+        if (lane == 0) s_warp[warp] = wtot;
+        __syncthreads();
+        if (t == 0) {
+            unsigned long long tot = 0;
+#pragma unroll
+            for (int w = 0; w < NWARP; w++) tot += s_warp[w];
+            s_base = tot ? atomicAdd(&a.ctr->out_count, tot) : 0ULL;
+        }
+        __syncthreads();
+        unsigned long long gbase = s_base;
+        for (int w = 0; w < warp; w++) gbase += s_warp[w];
+        __syncthreads();
+
+        // ---- write. Fast path: consecutive lanes write consecutive rows of the output (coalesced 8 B + 4 B stores)
+#pragma unroll
+        for (int q = 0; q < TILE_ITEMS; q++) {
+            if (m[q] == 0u) continue;
+            const unsigned long long pos = gbase + off[q];
+            const uint32_t prow = a.rowid ? __ldcs(a.rowid + row[q]) : (uint32_t)row[q];
+            if (!found[q] || MODE == PM_SEMI || MODE == PM_ANTI) {
+                // (NULL, probe): unmatched row of Right/Full, or a RightSemi/RightAnti row
+                if (pos < a.out_cap) {
+                    if (a.out_build) a.out_build[pos] = ~0ULL;
+                    a.out_probe[pos] = prow;
+                }
+                null_build_out++;
+            } else if (s[q].count == 1u) {
+                if (pos < a.out_cap) {
+                    a.out_build[pos] = (uint64_t)s[q].row;
+                    a.out_probe[pos] = prow;
+                }
+                if (MARK) mark_visited(a.visited, s[q].row);
+            } else if (s[q].count < 32u) {
+                for (uint32_t k = 0; k < s[q].count; k++) {
+                    const uint32_t br = __ldcg(a.tv.rowids + s[q].row + k);
+                    if (pos + k < a.out_cap) {
+                        a.out_build[pos + k] = (uint64_t)br;
+                        a.out_probe[pos + k] = prow;
+                    }
+                    if (MARK) mark_visited(a.visited, br);
+                }
+            }
+        }
+        // ---- long duplicate runs: the whole warp copies one run at a time (coalesced reads of rowids[])
+        if (any_multi && (MODE == PM_PAIRS || MODE == PM_OUTER)) {
+#pragma unroll
+            for (int q = 0; q < TILE_ITEMS; q++) {
+                const bool heavy = found[q] && s[q].count >= 32u;
+                uint32_t pend = __ballot_sync(FULL, heavy);
+                while (pend) {
+                    const int src = __ffs(pend) - 1;
+                    pend &= pend - 1;
+                    const unsigned long long pos = __shfl_sync(FULL, gbase + off[q], src);
+                    const uint32_t cnt = __shfl_sync(FULL, s[q].count, src);
+                    const uint32_t rb = __shfl_sync(FULL, s[q].row, src);
+                    const uint32_t pr = __shfl_sync(FULL, a.rowid ? __ldcs(a.rowid + (inrange[q] ? row[q] : 0)) : (uint32_t)row[q], src);
+                    for (uint32_t k = lane; k < cnt; k += 32) {
+                        const uint32_t br = __ldcg(a.tv.rowids + rb + k);
+                        if (pos + k < a.out_cap) {
+                            a.out_build[pos + k] = (uint64_t)br;
+                            a.out_probe[pos + k] = pr;
+                        }
+                        if (MARK) mark_visited(a.visited, br);
+                    }
+                }
+            }
+        }
+    }
+    if (MODE == PM_OUTER || MODE == PM_SEMI || MODE == PM_ANTI) {
+        const unsigned long long z = warp_sum_u32(null_build_out);
+        if (lane == 0 && z) atomicAdd(&a.ctr->build_null_out, z);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// a7 helpers: bitmap -> indices, pairs -> bitmaps
+// ------------------------------------------------------------------------------------------------
+// Writes the indices i < n whose bit equals want_set, as u64 (out64) or u32 (out32).
+__global__ void __launch_bounds__(256) bitmap_select_kernel(const uint32_t *__restrict__ bm, int64_t n, int want_set,
+                                                            uint64_t *out64, uint32_t *out32, uint64_t out_cap,
+                                                            unsigned long long *counter) {
+    __shared__ uint32_t s_warp[8];
+    __shared__ unsigned long long s_base;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int64_t n_words = (n + 31) / 32;
+    const int64_t n_iter = (n_words + blockDim.x - 1) / blockDim.x;
+    for (int64_t it = blockIdx.x; it < n_iter; it += gridDim.x) {
+        const int64_t w = it * blockDim.x + t;
+        uint32_t bits = 0;
+        if (w < n_words) {
+            bits = bm[w];
+            if (!want_set) bits = ~bits;
+            const int64_t rem = n - w * 32;
+            if (rem < 32) bits &= (1u << rem) - 1u;
+        }
+        const uint32_t c = __popc(bits);
+        uint32_t incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        if (t == 0) {
+            unsigned long long tot = 0;
+            for (int i = 0; i < 8; i++) tot += s_warp[i];
+            s_base = tot ? atomicAdd(counter, tot) : 0ULL;
+        }
+        __syncthreads();
+        unsigned long long pos = s_base + incl - c;
+        for (int i = 0; i < warp; i++) pos += s_warp[i];
+        __syncthreads();
+        while (bits) {
+            const int b = __ffs(bits) - 1;
+            bits &= bits - 1;
+            if (pos < out_cap) {
+                if (out64) out64[pos] = (uint64_t)(w * 32 + b);
+                if (out32) out32[pos] = (uint32_t)(w * 32 + b);
+            }
+            pos++;
+        }
+    }
+}
+
+// apply_pairs: mark `seen` probe rows and `visited` build rows of caller-filtered pairs.
+__global__ void __launch_bounds__(256) mark_pairs_kernel(const uint64_t *__restrict__ build_idx, const uint32_t *__restrict__ probe_idx,
+                                                         int64_t n, uint32_t *seen, uint32_t *visited) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (seen) mark_visited(seen, probe_idx[i]);
+        if (visited && build_idx[i] != ~0ULL) mark_visited(visited, (uint32_t)build_idx[i]);
+    }
+}
+
+// Fills (NULL, probe) / (build, NULL) sides of index-only results.
+__global__ void __launch_bounds__(256) fill_u64_kernel(uint64_t *p, int64_t n, uint64_t v) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
+}
+__global__ void __launch_bounds__(256) fill_u32_kernel(uint32_t *p, int64_t n, uint32_t v) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
+}
+
+// Validity concat for the build store: dst bits [dst_off, dst_off + n) <- src bits [src_off, src_off + n)
+// (src == null: all ones). One thread per destination word; words are touched by one thread only.
+__global__ void __launch_bounds__(256) copy_bits_kernel(uint32_t *dst, int64_t dst_off, const uint8_t *src, int64_t src_off, int64_t n) {
+    const int64_t w0 = dst_off >> 5, w1 = (dst_off + n + 31) >> 5;
+    for (int64_t w = w0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < w1; w += (int64_t)gridDim.x * blockDim.x) {
+        uint32_t bits = 0, msk = 0;
+        for (int b = 0; b < 32; b++) {
+            const int64_t g = w * 32 + b - dst_off;
+            if (g < 0 || g >= n) continue;
+            msk |= 1u << b;
+            const int64_t sidx = src_off + g;
+            if (src == nullptr || ((src[sidx >> 3] >> (sidx & 7)) & 1)) bits |= 1u << b;
+        }
+        dst[w] = (dst[w] & ~msk) | bits;
+    }
+}
+
+}  // namespace b200j

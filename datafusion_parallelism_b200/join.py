@@ -1,0 +1,284 @@
+"""Thin Python veneer over the C ABI (include/b200join.h): one `HashJoin` = one b200j_handle.
+
+Everything that computes runs in libb200join.so on the GPU; this module only marshals buffers
+(numpy / pyarrow host buffers, torch CUDA tensors or raw device pointers) into `b200j_batch` structs.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _native as N
+
+JOIN_TYPES = {"inner": 0, "left": 1, "right": 2, "full": 3, "left_semi": 4, "right_semi": 5, "left_anti": 6, "right_anti": 7}
+LAYOUTS = {"auto": 0, "direct": 1, "radix": 2}
+MEM_HOST, MEM_DEVICE = 0, 1
+OUT_PAIRS, OUT_HOST, OUT_MATCHES_ONLY, OUT_COUNT_ONLY = 1, 2, 4, 8
+FLAG_TIMING = 1
+NULL_BUILD = np.uint64(0xFFFFFFFFFFFFFFFF)
+NULL_PROBE = np.uint32(0xFFFFFFFF)
+T_UTF8 = 0
+
+
+class B200JoinError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"b200join error {code}: {msg}")
+        self.code = code
+
+
+class ColumnRef:
+    """One Arrow-layout column: addresses + the Python objects that keep them alive."""
+
+    __slots__ = ("values", "offsets", "validity", "bit_offset", "n_rows", "mem", "type", "keep")
+
+    def __init__(self, values, offsets, validity, bit_offset, n_rows, mem, type_, keep):
+        self.values, self.offsets, self.validity = values, offsets, validity
+        self.bit_offset, self.n_rows, self.mem, self.type, self.keep = bit_offset, n_rows, mem, type_, keep
+
+
+def _is_torch(x) -> bool:
+    return type(x).__module__.startswith("torch")
+
+
+def column(x, validity=None) -> ColumnRef:
+    """numpy array / torch tensor (CPU or CUDA) / pyarrow Array -> ColumnRef."""
+    try:
+        import pyarrow as pa
+    except ImportError:  # pragma: no cover
+        pa = None
+    if isinstance(x, ColumnRef):
+        return x
+    if pa is not None and isinstance(x, pa.ChunkedArray):
+        x = x.combine_chunks()
+    if pa is not None and isinstance(x, pa.Array):
+        t = x.type
+        bufs = x.buffers()
+        vbuf = bufs[0]
+        val_addr = vbuf.address if (vbuf is not None and x.null_count > 0) else None
+        if pa.types.is_string(t) or pa.types.is_binary(t):
+            off_addr = bufs[1].address + 4 * x.offset
+            data_addr = bufs[2].address if bufs[2] is not None else 0
+            return ColumnRef(data_addr or None, off_addr, val_addr, x.offset, len(x), MEM_HOST, T_UTF8, (x,))
+        if pa.types.is_boolean(t):
+            raise TypeError("boolean columns are not supported (bit-packed values)")
+        width = t.bit_width // 8
+        addr = bufs[1].address + width * x.offset if bufs[1] is not None else None
+        return ColumnRef(addr, None, val_addr, x.offset, len(x), MEM_HOST, width, (x,))
+    if _is_torch(x):
+        assert x.is_contiguous()
+        mem = MEM_DEVICE if x.is_cuda else MEM_HOST
+        vaddr, keep = None, (x,)
+        if validity is not None:
+            vaddr = validity.data_ptr() if _is_torch(validity) else validity.ctypes.data
+            keep = (x, validity)
+        return ColumnRef(x.data_ptr() or None, None, vaddr, 0, x.shape[0], mem, x.element_size(), keep)
+    a = np.ascontiguousarray(x)
+    vaddr, keep = None, (a,)
+    if validity is not None:
+        validity = np.ascontiguousarray(validity, dtype=np.uint8)
+        vaddr, keep = validity.ctypes.data, (a, validity)
+    return ColumnRef(a.ctypes.data if a.size else None, None, vaddr, 0, a.shape[0], MEM_HOST, a.dtype.itemsize, keep)
+
+
+def make_batch(keys: Sequence, payload: Sequence = ()):
+    """-> (Batch struct, keepalive). All columns must live in the same memory space."""
+    kcols = [column(k) for k in keys]
+    pcols = [column(p) for p in payload]
+    cols = kcols + pcols
+    n_rows = cols[0].n_rows if cols else 0
+    mem = cols[0].mem if cols else MEM_HOST
+    for c in cols:
+        if c.n_rows != n_rows:
+            raise ValueError("columns differ in length")
+        if c.mem != mem:
+            raise ValueError("columns of one batch must all be host or all be device memory")
+    karr = (N.Column * max(1, len(kcols)))()
+    parr = (N.Column * max(1, len(pcols)))()
+    for arr, src in ((karr, kcols), (parr, pcols)):
+        for i, c in enumerate(src):
+            arr[i].values, arr[i].offsets, arr[i].validity, arr[i].bit_offset = c.values, c.offsets, c.validity, c.bit_offset
+    b = N.Batch()
+    b.struct_size = C.sizeof(N.Batch)
+    b.mem, b.n_rows, b.n_keys, b.n_payload = mem, n_rows, len(kcols), len(pcols)
+    b.keys = karr
+    b.payload = parr
+    return b, (karr, parr, cols)
+
+
+class DeviceArray:
+    """Zero-copy view of a device buffer owned by a result (torch.as_tensor(x, device='cuda') accepts it)."""
+
+    def __init__(self, ptr: int, n: int, typestr: str, owner):
+        self.ptr, self.n, self.owner = ptr, n, owner
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr or 0, False), "version": 3, "strides": None}
+
+
+class PairResult:
+    """Owns one b200j_result until .release()."""
+
+    def __init__(self, join: "HashJoin", res: N.Result):
+        self._join, self._res = join, res
+        self.n = int(res.n)
+        self.mem = int(res.mem)
+        self.n_build_null = int(res.n_build_null)
+        self.n_probe_null = int(res.n_probe_null)
+
+    @property
+    def build_ptr(self) -> int:
+        return self._res.build_idx or 0
+
+    @property
+    def probe_ptr(self) -> int:
+        return self._res.probe_idx or 0
+
+    def numpy(self):
+        """(build_idx u64, probe_idx u32) as numpy copies; host results only."""
+        if self.mem != MEM_HOST:
+            raise ValueError("device result: request OUT_HOST or use .device_arrays()")
+        n = self.n
+        b = np.full(n, NULL_BUILD, dtype=np.uint64)
+        p = np.full(n, NULL_PROBE, dtype=np.uint32)
+        if n and self._res.build_idx:
+            b = np.ctypeslib.as_array(C.cast(self._res.build_idx, C.POINTER(C.c_uint64)), shape=(n,)).copy()
+        if n and self._res.probe_idx:
+            p = np.ctypeslib.as_array(C.cast(self._res.probe_idx, C.POINTER(C.c_uint32)), shape=(n,)).copy()
+        return b, p
+
+    def device_arrays(self):
+        if self.mem != MEM_DEVICE:
+            raise ValueError("host result")
+        b = DeviceArray(self._res.build_idx, self.n, "<i8", self) if self._res.build_idx else None
+        p = DeviceArray(self._res.probe_idx, self.n, "<i4", self) if self._res.probe_idx else None
+        return b, p
+
+    def release(self):
+        if self._res is not None and self._join._h:
+            N.lib().b200j_result_release(self._join._h, C.byref(self._res))
+        self._res = None
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:
+            pass
+
+
+class HashJoin:
+    """One join = one b200j_handle: build_push* -> build_finish (per partition) -> probe_batch* -> probe_finish."""
+
+    def __init__(self, join_type="inner", key_widths=(8,), n_partitions=1, device=0, build_payload_types=(),
+                 probe_payload_types=(), layout="auto", radix_bits=0, load_factor=0.0, expected_build_rows=0,
+                 l2_budget_bytes=0, hash_keys=None, hash_flags=0, stream=None, timing=False):
+        L = N.lib()
+        self._h = None
+        cfg = N.Config()
+        cfg.struct_size = C.sizeof(N.Config)
+        cfg.join_type = JOIN_TYPES[join_type] if isinstance(join_type, str) else int(join_type)
+        cfg.n_partitions, cfg.device = n_partitions, device
+        self._kw = (C.c_int32 * max(1, len(key_widths)))(*key_widths)
+        self._bp = (C.c_int32 * max(1, len(build_payload_types)))(*build_payload_types)
+        self._pp = (C.c_int32 * max(1, len(probe_payload_types)))(*probe_payload_types)
+        cfg.n_keys, cfg.key_widths = len(key_widths), self._kw
+        cfg.n_build_payload, cfg.build_payload_types = len(build_payload_types), self._bp
+        cfg.n_probe_payload, cfg.probe_payload_types = len(probe_payload_types), self._pp
+        if hash_keys is not None:
+            for i in range(4):
+                cfg.hash_keys[i] = int(hash_keys[i])
+        cfg.hash_flags = hash_flags
+        cfg.layout = LAYOUTS[layout] if isinstance(layout, str) else int(layout)
+        cfg.radix_bits, cfg.load_factor = radix_bits, load_factor
+        cfg.expected_build_rows, cfg.l2_budget_bytes = expected_build_rows, l2_budget_bytes
+        cfg.stream = stream
+        cfg.flags = FLAG_TIMING if timing else 0
+        h = C.c_void_p()
+        rc = L.b200j_create(C.byref(cfg), C.byref(h))
+        if rc != 0:
+            raise B200JoinError(rc, (L.b200j_last_error(None) or b"").decode())
+        self._h = h
+        self.join_type = cfg.join_type
+        self.n_partitions = n_partitions
+
+    # -- plumbing ---------------------------------------------------------------------------------
+    def _check(self, rc: int):
+        if rc != 0:
+            raise B200JoinError(rc, (N.lib().b200j_last_error(self._h) or b"").decode())
+
+    def close(self):
+        if self._h:
+            N.lib().b200j_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # -- build ------------------------------------------------------------------------------------
+    def build_push(self, partition: int, keys: Sequence, payload: Sequence = ()):
+        b, keep = make_batch(keys, payload)
+        self._check(N.lib().b200j_build_push(self._h, partition, C.byref(b)))
+
+    def build_finish(self, partition: int):
+        self._check(N.lib().b200j_build_finish(self._h, partition))
+
+    # -- probe ------------------------------------------------------------------------------------
+    def probe_batch(self, partition: int, keys: Sequence, payload: Sequence = (), want: int = OUT_PAIRS | OUT_HOST) -> PairResult:
+        b, keep = make_batch(keys, payload)
+        r = N.Result()
+        r.struct_size = C.sizeof(N.Result)
+        self._check(N.lib().b200j_probe_batch(self._h, partition, C.byref(b), want, C.byref(r)))
+        return PairResult(self, r)
+
+    def apply_pairs(self, partition: int, n_probe_rows: int, build_idx, probe_idx, want: int = OUT_PAIRS | OUT_HOST) -> PairResult:
+        bi = np.ascontiguousarray(build_idx, dtype=np.uint64)
+        pi = np.ascontiguousarray(probe_idx, dtype=np.uint32)
+        r = N.Result()
+        r.struct_size = C.sizeof(N.Result)
+        self._check(N.lib().b200j_apply_pairs(self._h, partition, n_probe_rows, MEM_HOST, bi.shape[0],
+                                              bi.ctypes.data if bi.size else None, pi.ctypes.data if pi.size else None,
+                                              want, C.byref(r)))
+        return PairResult(self, r)
+
+    def probe_finish(self, partition: int, want: int = OUT_PAIRS | OUT_HOST) -> PairResult:
+        r = N.Result()
+        r.struct_size = C.sizeof(N.Result)
+        self._check(N.lib().b200j_probe_finish(self._h, partition, want, C.byref(r)))
+        return PairResult(self, r)
+
+    # -- misc -------------------------------------------------------------------------------------
+    def hash_keys(self, keys: Sequence) -> np.ndarray:
+        b, keep = make_batch(keys)
+        if b.mem != MEM_HOST:
+            raise ValueError("hash_keys() veneer takes host columns; pass device pointers through the C ABI directly")
+        out = np.zeros(b.n_rows, dtype=np.uint64)
+        self._check(N.lib().b200j_hash_keys(self._h, C.byref(b), out.ctypes.data if out.size else None))
+        return out
+
+    def hash_keys_device(self, keys: Sequence, out_ptr: int):
+        b, keep = make_batch(keys)
+        self._check(N.lib().b200j_hash_keys(self._h, C.byref(b), out_ptr))
+
+    def stats(self) -> dict:
+        s = N.Stats()
+        s.struct_size = C.sizeof(N.Stats)
+        self._check(N.lib().b200j_get_stats(self._h, C.byref(s)))
+        return s.as_dict()
+
+    def reset_stats(self):
+        self._check(N.lib().b200j_reset_stats(self._h))
+
+    def synchronize(self):
+        self._check(N.lib().b200j_synchronize(self._h))
+
+
+def device_count() -> int:
+    return int(N.lib().b200j_device_count())

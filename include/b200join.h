@@ -1,0 +1,245 @@
+/*
+ * b200join.h — C ABI of libb200join.so, the B200-native (sm_100a) parallel hash join that drops in
+ * behind the DataFusion operator surface of jamesfer/datafusion-parallelism.
+ *
+ * The library replaces, for ONE join, everything below `ParallelHashJoin::execute`
+ * (reference src/operator/parallel_hash_join.rs:140-167):
+ *
+ *   reference (Rust, CPU)                                               this ABI
+ *   -----------------------------------------------------------------   -----------------------------
+ *   ParallelHashJoinExecutor::new            parallel_hash_join_executor.rs:72-84      b200j_create
+ *   BuildImplementation::build_side          operator/build_implementation.rs:50-112   b200j_build_push (per batch)
+ *     Version10::process_input_batch         version10/build_implementation.rs:60-71     "
+ *     JoinStateInstance::add                 version10/parallel_join_execution_state.rs:91-133
+ *     JoinStateInstance::compact             version10/parallel_join_execution_state.rs:135-213   b200j_build_finish
+ *   calculate_hash                           src/shared/shared.rs:11-16                b200j_hash_keys (and fused in build/probe)
+ *   lookup_*_probe_batch                     operator/probe_lookup_implementation/*.rs b200j_probe_batch
+ *     get_matching_indices[_with_probe]      src/shared/shared.rs:29-81                  "  (index pairs)
+ *     equal_rows_arr                         src/shared/datafusion_private.rs:40-80      "  (fused: slots hold key values)
+ *     append_right_indices / semi / anti     src/shared/datafusion_private.rs:85-185     "
+ *     take_multiple_record_batch             src/shared/shared.rs:83-92                b200j_gather
+ *   emit_(un)matched_build_records           full.rs:181-201, left_outer.rs:174-195,
+ *                                            left_semi.rs:166-179, left_anti.rs:166-179 b200j_probe_finish
+ *   apply_join_filter_to_indices             src/shared/datafusion_private.rs:295-328  stays with the caller: take the
+ *                                            pairs of b200j_probe_batch(B200J_OUT_MATCHES_ONLY), filter them, hand them back
+ *                                            through b200j_apply_pairs, gather with b200j_gather.
+ *
+ * Rules of the boundary
+ *   - plain C: pointers, sizes, PODs. No C++/torch/arrow types. All structs start with `struct_size`
+ *     so the ABI can grow.
+ *   - every function returns a status (0 = ok, < 0 = error). The message of the last error on this
+ *     handle is b200j_last_error(h); b200j_last_error(NULL) is the last error of a failed create/free call
+ *     on this thread. Nothing throws or aborts across the boundary.
+ *   - input buffers are BORROWED for the duration of the call only. Results are OWNED by the handle
+ *     until b200j_result_release.
+ *   - there is NO CPU fallback: without a CUDA device every compute call returns B200J_ERR_CUDA.
+ *   - handle methods may be called concurrently from different threads for distinct `partition`
+ *     ids; the library serialises them onto its CUDA streams.
+ */
+#ifndef B200JOIN_H
+#define B200JOIN_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200J_ABI_VERSION 1
+
+/* status codes */
+#define B200J_OK             0
+#define B200J_ERR_INVALID   -1   /* bad argument / call order (e.g. probe before build finished)       */
+#define B200J_ERR_CUDA      -2   /* CUDA runtime / driver error, or no device                          */
+#define B200J_ERR_OOM       -3   /* device or pinned-host allocation failed                            */
+#define B200J_ERR_UNSUPPORTED -4 /* valid request the library does not implement (yet)                 */
+#define B200J_ERR_STATE     -5   /* "State already consumed" (version10/build_implementation.rs:32-33) */
+#define B200J_ERR_NCCL      -6
+
+/* DataFusion JoinType discriminants (datafusion-common 40, join_type.rs order) */
+#define B200J_INNER       0
+#define B200J_LEFT        1
+#define B200J_RIGHT       2
+#define B200J_FULL        3
+#define B200J_LEFT_SEMI   4
+#define B200J_RIGHT_SEMI  5
+#define B200J_LEFT_ANTI   6
+#define B200J_RIGHT_ANTI  7
+
+/* where a batch's buffers live */
+#define B200J_MEM_HOST    0      /* pageable or pinned host memory: staged to the device in chunks     */
+#define B200J_MEM_DEVICE  1      /* device pointers on the handle's device (north_star: "as device pointers") */
+
+/* column type: a fixed width in bytes (1,2,4,8,16), or B200J_T_UTF8 (32-bit offsets + data) */
+#define B200J_T_UTF8      0
+
+/* table layout chosen at build_finish */
+#define B200J_LAYOUT_AUTO    0   /* direct while the table fits the L2 budget, else radix-partitioned  */
+#define B200J_LAYOUT_DIRECT  1   /* one open-addressing table                                          */
+#define B200J_LAYOUT_RADIX   2   /* radix-partition both sides, one table per partition (L2-resident)  */
+
+/* NULL markers in index outputs (an Arrow validity bitmap is produced as well when requested) */
+#define B200J_NULL_BUILD  UINT64_MAX
+#define B200J_NULL_PROBE  UINT32_MAX
+
+/* b200j_probe_batch `want` flags */
+#define B200J_OUT_PAIRS         1u   /* (build_idx u64, probe_idx u32) index pairs — ProbeBuildIndices, shared.rs:24-27 */
+#define B200J_OUT_HOST          2u   /* results in pinned host memory instead of device memory           */
+#define B200J_OUT_MATCHES_ONLY  4u   /* only steps 1-3 (hash, lookup, equality): no join-type post-processing,
+                                        no visited marking — the caller applies a JoinFilter and comes back
+                                        through b200j_apply_pairs                                          */
+#define B200J_OUT_COUNT_ONLY    8u   /* count the result rows, write nothing                              */
+
+typedef struct b200j_handle b200j_handle;
+
+/* One Arrow array's buffers (Arrow columnar format: LSB-first validity bitmap, 32-bit Utf8 offsets). */
+typedef struct {
+    const void    *values;      /* fixed width: values buffer; Utf8: data buffer                     */
+    const int32_t *offsets;     /* Utf8 only: n_rows + 1 offsets; NULL otherwise                     */
+    const uint8_t *validity;    /* NULL => no nulls                                                  */
+    int64_t        bit_offset;  /* offset (in rows) of row 0 inside `validity` (Arrow array offset)  */
+} b200j_column;
+
+typedef struct {
+    uint32_t            struct_size;
+    int32_t             mem;          /* B200J_MEM_*                                                  */
+    int64_t             n_rows;
+    int32_t             n_keys;       /* must equal the config's n_keys                              */
+    int32_t             n_payload;    /* must equal the config's payload count of that side, or 0    */
+    const b200j_column *keys;
+    const b200j_column *payload;
+} b200j_batch;
+
+typedef struct {
+    uint32_t  struct_size;
+    int32_t   join_type;              /* B200J_INNER ...                                              */
+    int32_t   n_partitions;           /* number of DataFusion partitions that will call build/probe   */
+    int32_t   device;                 /* CUDA device ordinal                                          */
+    int32_t   n_keys;
+    const int32_t *key_widths;        /* [n_keys] 4 or 8 (Int32/UInt32/Date32 | Int64/UInt64/Timestamp ...) */
+    int32_t   n_build_payload;
+    const int32_t *build_payload_types;   /* [n_build_payload] width or B200J_T_UTF8                  */
+    int32_t   n_probe_payload;
+    const int32_t *probe_payload_types;
+    uint64_t  hash_keys[4];           /* ahash RandomState keys; all zero => RandomState::with_seed(0) over the
+                                         fixed PI seeds (shared.rs:14)                                */
+    int32_t   hash_flags;             /* bit0: 0 = `specialize` integer path (nightly, as the reference), 1 = stable */
+    int32_t   layout;                 /* B200J_LAYOUT_*                                               */
+    int32_t   radix_bits;             /* 0 = choose; else log2(number of radix partitions)            */
+    float     load_factor;            /* 0 = default 0.5                                              */
+    int64_t   expected_build_rows;    /* sizing hint, 0 = unknown                                     */
+    int64_t   l2_budget_bytes;        /* 0 = 1/2 of cudaDevAttrL2CacheSize                            */
+    void     *stream;                 /* cudaStream_t to run on; NULL = the library creates its own   */
+    uint32_t  flags;                  /* B200J_FLAG_*                                                 */
+} b200j_config;
+
+#define B200J_FLAG_TIMING  1u         /* record CUDA-event timings of every phase into b200j_stats     */
+
+/* Result of one probe call (or of the finaliser). Arrays are device or pinned-host memory according to
+ * B200J_OUT_HOST. `n` rows; build_idx[i] == B200J_NULL_BUILD / probe_idx[i] == B200J_NULL_PROBE mark the
+ * NULL side of outer rows; semi/anti results fill only the side they output. */
+typedef struct {
+    uint32_t  struct_size;
+    int32_t   mem;
+    int64_t   n;
+    uint64_t *build_idx;
+    uint32_t *probe_idx;
+    int64_t   n_build_null;           /* rows whose build side is NULL                                */
+    int64_t   n_probe_null;
+    void     *_owner;                 /* private                                                      */
+} b200j_result;
+
+/* Gathered output column (Arrow layout), produced by b200j_gather. */
+typedef struct {
+    void     *values;
+    int32_t  *offsets;
+    uint8_t  *validity;               /* NULL when the column has no nulls                            */
+    int64_t   null_count;
+    int64_t   values_bytes;
+} b200j_out_column;
+
+typedef struct {
+    uint32_t          struct_size;
+    int32_t           mem;
+    int64_t           n_rows;
+    int32_t           n_cols;         /* build key+payload columns first, then probe key+payload columns
+                                         (build_join_schema, probe_lookup_implementation.rs:77-94)    */
+    b200j_out_column *cols;
+    void             *_owner;
+} b200j_gathered;
+
+typedef struct {
+    uint32_t struct_size;
+    int32_t  layout;                  /* layout actually used                                         */
+    int64_t  build_rows;
+    int64_t  build_null_keys;
+    int64_t  distinct_keys;
+    int64_t  duplicate_rows;          /* build rows whose key was already present                     */
+    int64_t  table_slots;
+    int64_t  table_bytes;
+    int32_t  radix_bits;
+    int32_t  _pad;
+    int64_t  probe_rows;              /* accumulated over probe calls                                 */
+    int64_t  result_rows;
+    /* device time, ms (CUDA events on the library's stream), accumulated; valid with B200J_FLAG_TIMING */
+    double   ms_build_copy;           /* concat of pushed batches (compact, a3)                       */
+    double   ms_build_partition;      /* radix histogram + scatter of the build side                  */
+    double   ms_build_insert;         /* table clear + hash + CAS insert (+ duplicate CSR)            */
+    double   ms_probe_partition;      /* radix histogram + scatter of probe batches                   */
+    double   ms_probe;                /* hash + lookup + pair compaction (the dominant kernel)        */
+    double   ms_gather;
+    int64_t  probe_launches;          /* launches of the dominant probe kernel                        */
+    int64_t  kernel_launches;         /* all kernel launches of this handle                           */
+    int64_t  probe_retries;           /* probe kernels re-run because the pair buffer was too small   */
+} b200j_stats;
+
+/* ---- lifecycle ------------------------------------------------------------------------------- */
+int32_t     b200j_abi_version(void);
+int32_t     b200j_device_count(void);                       /* 0 when no CUDA device is visible    */
+int32_t     b200j_create(const b200j_config *cfg, b200j_handle **out);
+int32_t     b200j_destroy(b200j_handle *h);
+const char *b200j_last_error(const b200j_handle *h);
+int32_t     b200j_get_stats(b200j_handle *h, b200j_stats *out);
+int32_t     b200j_reset_stats(b200j_handle *h);
+int32_t     b200j_synchronize(b200j_handle *h);             /* wait for the handle's stream        */
+
+/* ---- build side ------------------------------------------------------------------------------ */
+/* Append one build batch (rows are numbered in arrival order, like offset_counter.fetch_add,
+ * parallel_join_execution_state.rs:95). */
+int32_t b200j_build_push(b200j_handle *h, int32_t partition, const b200j_batch *batch);
+/* End of this partition's build stream. The LAST partition to call runs the build
+ * (partition → insert → duplicate CSR); the others return immediately.  A partition calling
+ * twice gets B200J_ERR_STATE. */
+int32_t b200j_build_finish(b200j_handle *h, int32_t partition);
+
+/* ---- probe side ------------------------------------------------------------------------------ */
+int32_t b200j_probe_batch(b200j_handle *h, int32_t partition, const b200j_batch *batch, uint32_t want,
+                          b200j_result *out);
+/* Join-type post-processing (a7) of caller-filtered pairs of one probe batch of `n_probe_rows` rows. */
+int32_t b200j_apply_pairs(b200j_handle *h, int32_t partition, int64_t n_probe_rows, int32_t mem, int64_t n_pairs,
+                          const uint64_t *build_idx, const uint32_t *probe_idx, uint32_t want, b200j_result *out);
+/* End of this partition's probe stream. The LAST partition gets the finaliser rows of
+ * Left / Full / LeftSemi / LeftAnti (build rows, probe side NULL); everybody else gets n = 0. */
+int32_t b200j_probe_finish(b200j_handle *h, int32_t partition, uint32_t want, b200j_result *out);
+int32_t b200j_result_release(b200j_handle *h, b200j_result *r);
+
+/* Output gather (a6): build columns at build_idx, then probe columns of `probe_batch` at probe_idx.
+ * probe_batch may be NULL for the finaliser (probe columns all NULL). */
+int32_t b200j_gather(b200j_handle *h, const b200j_result *pairs, const b200j_batch *probe_batch, uint32_t want,
+                     b200j_gathered *out);
+int32_t b200j_gathered_release(b200j_handle *h, b200j_gathered *g);
+
+/* ---- hashing (a1) ---------------------------------------------------------------------------- */
+/* create_hashes over the key columns of `batch` with the handle's RandomState: one u64 per row into
+ * `out` (same memory space as the batch). Bit-identical to oracle/join_oracle.c:orc_create_hashes. */
+int32_t b200j_hash_keys(b200j_handle *h, const b200j_batch *batch, uint64_t *out);
+
+/* ---- pinned host memory for callers that want full-speed PCIe copies -------------------------- */
+int32_t b200j_host_alloc(size_t bytes, void **out);
+int32_t b200j_host_free(void *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200JOIN_H */
