@@ -9,7 +9,7 @@ import sys
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
-LIB_PATH = os.path.join(_HERE, "libb200join.so")
+LIB_PATH = os.environ.get("B200J_LIB") or os.path.join(_HERE, "libb200join.so")   # B200J_LIB: tuning variants only
 CSRC = os.path.join(_HERE, "csrc")
 HEADER = os.path.join(_ROOT, "include", "b200join.h")
 

@@ -13,6 +13,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -77,7 +78,6 @@ struct ResultOwner {
     void *build_idx = nullptr;
     void *probe_idx = nullptr;
     int32_t mem = B200J_MEM_DEVICE;
-    size_t build_bytes = 0, probe_bytes = 0;
 };
 
 struct PinnedBuf {
@@ -144,8 +144,8 @@ using H = b200j_handle;
 
 // defined in radix_host.inl / gather_host.inl (included below, they need the complete handle type)
 void radix_build(H *h, const void *keys, const uint8_t *validity, int kw, int64_t n, float lf, int64_t budget);
-int64_t radix_probe(H *h, const void *d_keys, const uint8_t *d_validity, int64_t bit_offset, int64_t n, int mode, bool mark,
-                    bool count_only, int64_t cap, bool want_build, ResultOwner *ro, int64_t *n_build_null);
+void radix_partition(H *h, const void *keys, const uint8_t *validity, int64_t bit_offset, int kw, int64_t n, int bits,
+                     void *out_keys, uint32_t *out_rid, double *ms_acc);
 void radix_release(H *h);
 void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, uint32_t want, b200j_gathered *out);
 void do_gathered_release(H *h, b200j_gathered *g);
@@ -387,8 +387,8 @@ void run_build(H *h) {
     if (layout == B200J_LAYOUT_AUTO) layout = ((int64_t)direct_slots * 16 <= budget) ? B200J_LAYOUT_DIRECT : B200J_LAYOUT_RADIX;
     h->layout = layout;
 
-    dev_alloc(h, h->zero_slot, sizeof(Slot));
-    CU(cudaMemsetAsync(h->zero_slot.p, 0, sizeof(Slot), h->stream));
+    dev_alloc(h, h->zero_slot, 2 * sizeof(Slot));       // a whole bucket: the probe loads 32 B
+    CU(cudaMemsetAsync(h->zero_slot.p, 0, 2 * sizeof(Slot), h->stream));
     CU(cudaMemsetAsync(h->d_ctr, 0, sizeof(Counters), h->stream));
     const int jt = h->cfg.join_type;
     if (jt == B200J_LEFT || jt == B200J_FULL || jt == B200J_LEFT_SEMI || jt == B200J_LEFT_ANTI) {
@@ -482,17 +482,17 @@ ProbePlan plan_for(int join_type, bool matches_only) {
 
 template <int KW, bool RADIX>
 void launch_probe_mode(const ProbePlan &pl, int grid, cudaStream_t s, const ProbeArgs &a) {
-    if (pl.mode == PM_PAIRS && !pl.mark) probe_kernel<KW, PM_PAIRS, false, RADIX><<<grid, TILE_THREADS, 0, s>>>(a);
-    else if (pl.mode == PM_PAIRS) probe_kernel<KW, PM_PAIRS, true, RADIX><<<grid, TILE_THREADS, 0, s>>>(a);
-    else if (pl.mode == PM_OUTER && !pl.mark) probe_kernel<KW, PM_OUTER, false, RADIX><<<grid, TILE_THREADS, 0, s>>>(a);
-    else if (pl.mode == PM_OUTER) probe_kernel<KW, PM_OUTER, true, RADIX><<<grid, TILE_THREADS, 0, s>>>(a);
-    else if (pl.mode == PM_SEMI) probe_kernel<KW, PM_SEMI, false, RADIX><<<grid, TILE_THREADS, 0, s>>>(a);
-    else if (pl.mode == PM_ANTI) probe_kernel<KW, PM_ANTI, false, RADIX><<<grid, TILE_THREADS, 0, s>>>(a);
-    else probe_kernel<KW, PM_MARK, true, RADIX><<<grid, TILE_THREADS, 0, s>>>(a);
+    if (pl.mode == PM_PAIRS && !pl.mark) probe_kernel<KW, PM_PAIRS, false, RADIX><<<grid, PROBE_THREADS, 0, s>>>(a);
+    else if (pl.mode == PM_PAIRS) probe_kernel<KW, PM_PAIRS, true, RADIX><<<grid, PROBE_THREADS, 0, s>>>(a);
+    else if (pl.mode == PM_OUTER && !pl.mark) probe_kernel<KW, PM_OUTER, false, RADIX><<<grid, PROBE_THREADS, 0, s>>>(a);
+    else if (pl.mode == PM_OUTER) probe_kernel<KW, PM_OUTER, true, RADIX><<<grid, PROBE_THREADS, 0, s>>>(a);
+    else if (pl.mode == PM_SEMI) probe_kernel<KW, PM_SEMI, false, RADIX><<<grid, PROBE_THREADS, 0, s>>>(a);
+    else if (pl.mode == PM_ANTI) probe_kernel<KW, PM_ANTI, false, RADIX><<<grid, PROBE_THREADS, 0, s>>>(a);
+    else probe_kernel<KW, PM_MARK, true, RADIX><<<grid, PROBE_THREADS, 0, s>>>(a);
 }
 
 void launch_probe(H *h, const ProbePlan &pl, const ProbeArgs &a, int kw, bool radix) {
-    const int grid = grid_for(h, a.n + a.mis, TILE_ROWS, 8);
+    const int grid = grid_for(h, a.n + a.mis, PROBE_TILE, 2048 / PROBE_THREADS);
     if (kw == 8) {
         if (radix) launch_probe_mode<8, true>(pl, grid, h->stream, a);
         else launch_probe_mode<8, false>(pl, grid, h->stream, a);
@@ -532,64 +532,94 @@ void release_owner(H *h, ResultOwner *ro) {
     delete ro;
 }
 
-// Device-resident probe of `n` keys. Output arrays are device memory owned by *ro (sized to the exact result).
-// Returns rows produced.
+// Device-resident probe of `n` keys. Output arrays are device memory owned by *ro. Returns rows produced.
 int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_t bit_offset, int64_t n, const ProbePlan &pl,
                      bool count_only, ResultOwner *ro, int64_t *n_build_null) {
     const int kw = h->key_widths[0];
     const bool want_build = (pl.mode == PM_PAIRS || pl.mode == PM_OUTER);
+    const bool radix = h->layout == B200J_LAYOUT_RADIX;
     int64_t cap = count_only ? 0 : estimate_out_cap(h, n, pl);
     *n_build_null = 0;
     if (n == 0) return 0;
-    if (h->layout == B200J_LAYOUT_RADIX)
-        return radix_probe(h, d_keys, d_validity, bit_offset, n, pl.mode, pl.mark, count_only, cap, want_build, ro, n_build_null);
-    for (int attempt = 0; attempt < 3; attempt++) {
-        void *ob = nullptr, *op = nullptr;
-        if (cap > 0) {
-            if (want_build) CU(cudaMallocAsync(&ob, (size_t)cap * 8, h->stream));
-            CU(cudaMallocAsync(&op, (size_t)cap * 4, h->stream));
+    std::vector<void *> temps;
+    try {
+        // what the probe kernel reads: the caller's keys (direct) or the partitioned (key, row id) stream (radix)
+        const void *pkeys = d_keys;
+        const uint8_t *pvalid = d_validity;
+        int64_t pboff = bit_offset, pn = n, n_null_rows = 0;
+        const uint32_t *prid = nullptr;
+        if (radix) {
+            void *tk = nullptr, *tr = nullptr;
+            CU(cudaMallocAsync(&tk, (size_t)n * kw + 16, h->stream));
+            temps.push_back(tk);
+            CU(cudaMallocAsync(&tr, (size_t)n * 4 + 16, h->stream));
+            temps.push_back(tr);
+            radix_partition(h, d_keys, d_validity, bit_offset, kw, n, h->radix_bits, tk, (uint32_t *)tr, &h->st.ms_probe_partition);
+            pkeys = tk;
+            pvalid = nullptr;
+            pboff = 0;
+            prid = (const uint32_t *)tr;
+            pn = (int64_t)h->rscratch.h_off[1 << h->radix_bits];
+            n_null_rows = n - pn;
         }
-        CU(cudaMemsetAsync(&h->d_ctr->out_count, 0, 8, h->stream));
-        CU(cudaMemsetAsync(&h->d_ctr->build_null_out, 0, 8, h->stream));
-        ProbeArgs a{};
-        a.keys = d_keys;
-        a.validity = d_validity;
-        a.bit_offset = bit_offset;
-        a.rowid = nullptr;
-        a.n = n;
-        a.mis = (int)(((uintptr_t)d_keys & 15) / (uintptr_t)kw);
-        a.tv = h->view();
-        a.hk = h->hk;
-        a.out_build = (uint64_t *)ob;
-        a.out_probe = (uint32_t *)op;
-        a.out_cap = (uint64_t)cap;
-        a.visited = (uint32_t *)h->visited.p;
-        a.ctr = h->d_ctr;
-        {
-            PhaseTimer tm(h, &h->st.ms_probe);
-            launch_probe(h, pl, a, kw, false);
-            CU(cudaGetLastError());
-            tm.stop();
+        const int64_t extra = (pl.mode == PM_OUTER || pl.mode == PM_ANTI) ? n_null_rows : 0;
+        for (int attempt = 0; attempt < 3; attempt++) {
+            void *ob = nullptr, *op = nullptr;
+            if (cap > 0) {
+                if (want_build) CU(cudaMallocAsync(&ob, (size_t)cap * 8, h->stream));
+                CU(cudaMallocAsync(&op, (size_t)cap * 4, h->stream));
+            }
+            CU(cudaMemsetAsync(&h->d_ctr->out_count, 0, 8, h->stream));
+            CU(cudaMemsetAsync(&h->d_ctr->build_null_out, 0, 8, h->stream));
+            ProbeArgs a{};
+            a.keys = pkeys;
+            a.validity = pvalid;
+            a.bit_offset = pboff;
+            a.rowid = prid;
+            a.n = pn;
+            a.mis = (int)(((uintptr_t)pkeys & 15) / (uintptr_t)kw);
+            a.tv = h->view();
+            a.hk = h->hk;
+            a.out_build = (uint64_t *)ob;
+            a.out_probe = (uint32_t *)op;
+            a.out_cap = (uint64_t)cap;
+            a.visited = (uint32_t *)h->visited.p;
+            a.ctr = h->d_ctr;
+            if (pn > 0) {
+                PhaseTimer tm(h, &h->st.ms_probe);
+                launch_probe(h, pl, a, kw, radix);
+                CU(cudaGetLastError());
+                tm.stop();
+            }
+            CU(cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
+            CU(cudaStreamSynchronize(h->stream));
+            const int64_t total = (int64_t)h->h_ctr->out_count;
+            *n_build_null = (int64_t)h->h_ctr->build_null_out + extra;
+            if (count_only || total + extra <= cap) {
+                if (extra > 0 && !count_only) {
+                    emit_null_rows_kernel<<<grid_for(h, extra, 256, 8), 256, 0, h->stream>>>(prid + pn, extra, (uint64_t *)ob, (uint32_t *)op,
+                                                                                             (uint64_t)total);
+                    h->st.kernel_launches++;
+                    CU(cudaGetLastError());
+                    CU(cudaStreamSynchronize(h->stream));
+                }
+                ro->build_idx = ob;
+                ro->probe_idx = op;
+                free_temps(h, temps);
+                return total + extra;
+            }
+            // the pair buffer was too small (duplicate keys): the kernel counted everything, run again with room.
+            // Marking is idempotent, so the re-run is safe for the visited bitmap.
+            if (ob) cudaFreeAsync(ob, h->stream);
+            if (op) cudaFreeAsync(op, h->stream);
+            cap = total + extra;
+            h->st.probe_retries++;
         }
-        CU(cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
-        CU(cudaStreamSynchronize(h->stream));
-        const int64_t total = (int64_t)h->h_ctr->out_count;
-        *n_build_null = (int64_t)h->h_ctr->build_null_out;
-        if (count_only || total <= cap) {
-            ro->build_idx = ob;
-            ro->probe_idx = op;
-            ro->build_bytes = (size_t)cap * 8;
-            ro->probe_bytes = (size_t)cap * 4;
-            return total;
-        }
-        // the pair buffer was too small (duplicate keys): the kernel counted everything, run again with room.
-        // Marking is idempotent, so the re-run is safe for the visited bitmap.
-        if (ob) cudaFreeAsync(ob, h->stream);
-        if (op) cudaFreeAsync(op, h->stream);
-        cap = total;
-        h->st.probe_retries++;
+        throw Fail{B200J_ERR_CUDA, "probe output did not converge"};
+    } catch (...) {
+        free_temps(h, temps);
+        throw;
     }
-    throw Fail{B200J_ERR_CUDA, "probe output did not converge"};
 }
 
 void move_result_to_host(H *h, ResultOwner *ro, int64_t n) {
@@ -616,7 +646,7 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
     REQUIRE(!h->probe_done[partition], B200J_ERR_STATE, "probe_batch after probe_finish");
     REQUIRE(out != nullptr && out->struct_size >= sizeof(b200j_result), B200J_ERR_INVALID, "result struct missing or too small");
     check_batch(h, b, h->cfg.n_probe_payload);
-    REQUIRE(b->n_rows < 0xffffffffLL, B200J_ERR_UNSUPPORTED, "probe batch of 2^32-1 rows or more (probe indices are UInt32)");
+    REQUIRE(b->n_rows < 0xffff0000LL, B200J_ERR_UNSUPPORTED, "probe batch of more than 2^32 - 2^16 rows (probe indices are UInt32)");
     const ProbePlan pl = plan_for(h->cfg.join_type, (want & B200J_OUT_MATCHES_ONLY) != 0);
     const bool count_only = (want & B200J_OUT_COUNT_ONLY) != 0;
     const int kw = h->key_widths[0];
@@ -931,6 +961,9 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
         }
         REQUIRE(cfg->device >= 0 && cfg->device < ndev, B200J_ERR_INVALID, "device ordinal out of range");
         CU(cudaSetDevice(cfg->device));
+        if (const char *g = getenv("B200J_L2_FETCH_GRANULARITY")) {      // tuning knob: L2 sector promotion on random table reads
+            if (cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(g)) != cudaSuccess) cudaGetLastError();
+        }
 
         h = new b200j_handle();
         h->cfg = *cfg;

@@ -122,15 +122,16 @@ struct TableView {
     int32_t         _pad;
 };
 
+// hp = top 32 bits of the row hash. Tables never exceed 2^32 slots (build rows < 2^31), so masks are 32-bit.
 template <bool RADIX>
-__device__ __forceinline__ void locate(const TableView &tv, uint64_t h, uint64_t &base, uint64_t &mask) {
+__device__ __forceinline__ void locate(const TableView &tv, uint32_t hp, uint64_t &base, uint32_t &mask) {
     if (RADIX) {
-        const uint32_t p = (uint32_t)(h >> (64 - tv.radix_bits));
+        const uint32_t p = hp >> (32 - tv.radix_bits);
         base = __ldg(tv.part_base + p);
         mask = __ldg(tv.part_mask + p);
     } else {
         base = 0;
-        mask = tv.mask;
+        mask = (uint32_t)tv.mask;
     }
 }
 
@@ -144,6 +145,13 @@ __device__ __forceinline__ Slot load_slot(const Slot *p) {
     return s;
 }
 
+// One 32 B sector = one bucket of two slots, fetched with a single 256-bit load (LDG.E.256, sm_100+).
+// Linear probing always starts at the even slot of the home bucket, so a probe step is exactly one sector.
+__device__ __forceinline__ void load_bucket(const Slot *p, unsigned long long &k0, unsigned long long &v0,
+                                            unsigned long long &k1, unsigned long long &v1) {
+    asm volatile("ld.global.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(k0), "=l"(v0), "=l"(k1), "=l"(v1) : "l"(p));
+}
+
 // ------------------------------------------------------------------------------------------------
 // vectorised key loads: 4 keys per thread per tile, 128-bit loads wherever the address allows
 // ------------------------------------------------------------------------------------------------
@@ -153,16 +161,18 @@ constexpr int TILE_ROWS    = TILE_THREADS * TILE_ITEMS;
 
 // `keys` is the caller's pointer; `mis` = number of keys by which it is misaligned from 16 B. Rows are
 // addressed in the aligned "virtual" index space v = row + mis, so every full vector load is 16 B aligned.
-template <int KW>
-__device__ __forceinline__ void load_tile_keys(const void *keys, int mis, int64_t n, int64_t tile, int t,
-                                               uint64_t (&key)[TILE_ITEMS], int64_t (&row)[TILE_ITEMS]) {
-    const int64_t vbase = tile * TILE_ROWS;
+// A tile is THREADS * ITEMS consecutive rows; each thread takes ITEMS * KW / 16 vectors, THREADS vectors apart,
+// so a warp's loads are 512 contiguous bytes.
+template <int KW, int THREADS, int ITEMS>
+__device__ __forceinline__ void load_keys_tile(const void *keys, int mis, int64_t n, int64_t tile, int t,
+                                               uint64_t (&key)[ITEMS], int64_t (&row)[ITEMS]) {
+    const int64_t vbase = tile * (int64_t)(THREADS * ITEMS);
     const int64_t vend = n + mis;
     if (KW == 8) {
         const unsigned long long *k64 = reinterpret_cast<const unsigned long long *>(keys) - mis;
 #pragma unroll
-        for (int v = 0; v < 2; v++) {
-            const int64_t vi = vbase + ((int64_t)v * TILE_THREADS + t) * 2;
+        for (int v = 0; v < ITEMS / 2; v++) {
+            const int64_t vi = vbase + ((int64_t)v * THREADS + t) * 2;
             row[2 * v] = vi - mis;
             row[2 * v + 1] = vi + 1 - mis;
             if (vi >= mis && vi + 1 < vend) {
@@ -176,17 +186,27 @@ __device__ __forceinline__ void load_tile_keys(const void *keys, int mis, int64_
         }
     } else {
         const uint32_t *k32 = reinterpret_cast<const uint32_t *>(keys) - mis;
-        const int64_t vi = vbase + (int64_t)t * 4;
 #pragma unroll
-        for (int q = 0; q < 4; q++) row[q] = vi + q - mis;
-        if (vi >= mis && vi + 3 < vend) {
-            const uint4 x = __ldcs(reinterpret_cast<const uint4 *>(k32 + vi));
-            key[0] = x.x; key[1] = x.y; key[2] = x.z; key[3] = x.w;
-        } else {
+        for (int v = 0; v < ITEMS / 4; v++) {
+            const int64_t vi = vbase + ((int64_t)v * THREADS + t) * 4;
 #pragma unroll
-            for (int q = 0; q < 4; q++) key[q] = (vi + q >= mis && vi + q < vend) ? (uint64_t)__ldcs(k32 + vi + q) : 0ULL;
+            for (int q = 0; q < 4; q++) row[4 * v + q] = vi + q - mis;
+            if (vi >= mis && vi + 3 < vend) {
+                const uint4 x = __ldcs(reinterpret_cast<const uint4 *>(k32 + vi));
+                key[4 * v] = x.x; key[4 * v + 1] = x.y; key[4 * v + 2] = x.z; key[4 * v + 3] = x.w;
+            } else {
+#pragma unroll
+                for (int q = 0; q < 4; q++)
+                    key[4 * v + q] = (vi + q >= mis && vi + q < vend) ? (uint64_t)__ldcs(k32 + vi + q) : 0ULL;
+            }
         }
     }
+}
+
+template <int KW>
+__device__ __forceinline__ void load_tile_keys(const void *keys, int mis, int64_t n, int64_t tile, int t,
+                                               uint64_t (&key)[TILE_ITEMS], int64_t (&row)[TILE_ITEMS]) {
+    load_keys_tile<KW, TILE_THREADS, TILE_ITEMS>(keys, mis, n, tile, t, key, row);
 }
 
 __device__ __forceinline__ unsigned long long warp_sum_u32(uint32_t v) {
@@ -232,9 +252,10 @@ template <bool RADIX>
 __device__ __forceinline__ Slot *find_or_claim(const TableView &tv, const HashKeys &hk, uint64_t key, uint32_t &distinct) {
     if (key == 0) return tv.zero_slot;
     const uint64_t h = hash_one(hk, key);
-    uint64_t base, mask;
-    locate<RADIX>(tv, h, base, mask);
-    uint64_t i = h & mask;
+    uint64_t base;
+    uint32_t mask;
+    locate<RADIX>(tv, (uint32_t)(h >> 32), base, mask);
+    uint32_t i = (uint32_t)h & mask & ~1u;      // probe sequences start at the even slot of the home bucket
     for (;;) {
         Slot *s = tv.slots + base + i;
         unsigned long long cur = __ldcg(&s->key);
@@ -354,7 +375,7 @@ struct ProbeArgs {
     const uint8_t  *validity;
     int64_t         bit_offset;
     const uint32_t *rowid;        // explicit probe row ids (radix layout) or null = identity
-    int64_t         n;
+    int64_t         n;            // < 2^32 - 16
     int32_t         mis;
     int32_t         _pad;
     TableView       tv;
@@ -366,180 +387,290 @@ struct ProbeArgs {
     Counters       *ctr;
 };
 
+#ifndef B200J_PROBE_THREADS
+#define B200J_PROBE_THREADS 128
+#endif
+#ifndef B200J_PROBE_ITEMS
+#define B200J_PROBE_ITEMS 4
+#endif
+constexpr int PROBE_THREADS = B200J_PROBE_THREADS;
+constexpr int PROBE_ITEMS   = B200J_PROBE_ITEMS;
+constexpr int PROBE_TILE    = PROBE_THREADS * PROBE_ITEMS;
+
 __device__ __forceinline__ void mark_visited(uint32_t *visited, uint32_t row) {
     uint32_t *w = visited + (row >> 5);
     const uint32_t bit = 1u << (row & 31);
     if (!(__ldcg(w) & bit)) atomicOr(w, bit);
 }
 
-template <int KW, int MODE, bool MARK, bool RADIX>
-__global__ void __launch_bounds__(TILE_THREADS) probe_kernel(ProbeArgs a) {
+// Keys of one tile. GUARD = false: the tile lies fully inside the batch and there is no validity bitmap, so
+// there is not a single range or NULL check on the hot path. `in` / `look`: bit q set = item q is a row of the
+// batch / is a row with a non-NULL key.
+template <int KW, bool GUARD>
+__device__ __forceinline__ void probe_load_tile(const ProbeArgs &a, uint32_t tile, int t, uint64_t (&key)[PROBE_ITEMS],
+                                                uint32_t (&row)[PROBE_ITEMS], uint32_t &in, uint32_t &look) {
+    constexpr int PER_VEC = 16 / KW;
+    constexpr int NVEC = PROBE_ITEMS / PER_VEC;
+    const uint32_t vbase = tile * (uint32_t)PROBE_TILE;
+    const uint32_t mis = (uint32_t)a.mis, vend = (uint32_t)a.n + mis;
+    in = look = (PROBE_ITEMS == 32) ? 0xffffffffu : ((1u << PROBE_ITEMS) - 1u);
+    if (KW == 8) {
+        const unsigned long long *k64 = reinterpret_cast<const unsigned long long *>(a.keys) - mis;
+#pragma unroll
+        for (int v = 0; v < NVEC; v++) {
+            const uint32_t vi = vbase + ((uint32_t)v * PROBE_THREADS + t) * 2u;
+            row[2 * v] = vi - mis;
+            row[2 * v + 1] = vi + 1 - mis;
+            if (!GUARD || (vi >= mis && vi + 1 < vend)) {
+                const ulonglong2 x = __ldcs(reinterpret_cast<const ulonglong2 *>(k64 + vi));
+                key[2 * v] = x.x;
+                key[2 * v + 1] = x.y;
+            } else {
+                const bool i0 = vi >= mis && vi < vend, i1 = vi + 1 >= mis && vi + 1 < vend;
+                key[2 * v] = i0 ? __ldcs(k64 + vi) : 0ULL;
+                key[2 * v + 1] = i1 ? __ldcs(k64 + vi + 1) : 0ULL;
+                if (!i0) in &= ~(1u << (2 * v));
+                if (!i1) in &= ~(1u << (2 * v + 1));
+            }
+        }
+    } else {
+        const uint32_t *k32 = reinterpret_cast<const uint32_t *>(a.keys) - mis;
+#pragma unroll
+        for (int v = 0; v < NVEC; v++) {
+            const uint32_t vi = vbase + ((uint32_t)v * PROBE_THREADS + t) * 4u;
+#pragma unroll
+            for (int q = 0; q < 4; q++) row[4 * v + q] = vi + q - mis;
+            if (!GUARD || (vi >= mis && vi + 3 < vend)) {
+                const uint4 x = __ldcs(reinterpret_cast<const uint4 *>(k32 + vi));
+                key[4 * v] = x.x; key[4 * v + 1] = x.y; key[4 * v + 2] = x.z; key[4 * v + 3] = x.w;
+            } else {
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const bool i0 = vi + q >= mis && vi + q < vend;
+                    key[4 * v + q] = i0 ? (uint64_t)__ldcs(k32 + vi + q) : 0ULL;
+                    if (!i0) in &= ~(1u << (4 * v + q));
+                }
+            }
+        }
+    }
+    look = in;
+    if (GUARD && a.validity != nullptr) {
+#pragma unroll
+        for (int q = 0; q < PROBE_ITEMS; q++)
+            if (((in >> q) & 1u) && !bit_valid(a.validity, a.bit_offset + (int64_t)row[q])) look &= ~(1u << q);
+    }
+}
+
+template <int KW, int MODE, bool MARK, bool RADIX, bool GUARD>
+__device__ __forceinline__ void probe_tile(const ProbeArgs &a, uint32_t tile, int t, uint32_t (&s_warp)[2][PROBE_THREADS / 32],
+                                           unsigned long long (&s_base)[2], int buf, uint32_t &null_build_out) {
     constexpr uint32_t FULL = 0xffffffffu;
-    constexpr int NWARP = TILE_THREADS / 32;
-    __shared__ uint32_t s_warp[NWARP];
-    __shared__ unsigned long long s_base;
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    constexpr int NWARP = PROBE_THREADS / 32;
+    const int lane = t & 31, warp = t >> 5;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    const int64_t n_tiles = (a.n + a.mis + TILE_ROWS - 1) / TILE_ROWS;
-    uint32_t null_build_out = 0;
 
-    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        uint64_t key[TILE_ITEMS];
-        int64_t row[TILE_ITEMS];
-        load_tile_keys<KW>(a.keys, a.mis, a.n, tile, t, key, row);
+    uint64_t key[PROBE_ITEMS];
+    uint32_t row[PROBE_ITEMS];
+    uint32_t in, look;
+    probe_load_tile<KW, GUARD>(a, tile, t, key, row, in, look);
 
-        // ---- hash + first slot load for all items before any is consumed (4 independent random loads in flight)
-        bool inrange[TILE_ITEMS], look[TILE_ITEMS];
-        uint64_t base[TILE_ITEMS], mask[TILE_ITEMS], idx[TILE_ITEMS];
-        Slot s[TILE_ITEMS];
+    // ---- hash + first slot load of every item before any is consumed: PROBE_ITEMS independent random loads in flight.
+    // The key value 0 lives in the side slot (whose key word is 0 as well), so the same compare serves both.
+    // Lock-step rounds: in every round each unresolved item loads ONE bucket, so a tile costs
+    // max-over-items(chain length) L2 round trips instead of their sum.
+    uint32_t idx[PROBE_ITEMS], hp[PROBE_ITEMS];
+    Slot s[PROBE_ITEMS];                      // the matching slot (count == 0: no match)
+    uint32_t pending = GUARD ? look : in;
+    {
+        unsigned long long k0[PROBE_ITEMS], v0[PROBE_ITEMS], k1[PROBE_ITEMS], v1[PROBE_ITEMS];
 #pragma unroll
-        for (int q = 0; q < TILE_ITEMS; q++) {
-            inrange[q] = row[q] >= 0 && row[q] < a.n;
-            look[q] = inrange[q] && bit_valid(a.validity, a.bit_offset + (inrange[q] ? row[q] : 0));
-            s[q] = Slot{0, 0, 0};
-            if (look[q]) {
-                if (key[q] == 0) {
-                    s[q] = load_slot(a.tv.zero_slot);
-                    s[q].key = s[q].count ? 0ULL : 1ULL;      // present iff count > 0; compare below is against key 0
-                    base[q] = mask[q] = idx[q] = 0;
-                } else {
-                    const uint64_t h = hash_one(a.hk, key[q]);
-                    locate<RADIX>(a.tv, h, base[q], mask[q]);
-                    idx[q] = h & mask[q];
-                    s[q] = load_slot(a.tv.slots + base[q] + idx[q]);
+        for (int q = 0; q < PROBE_ITEMS; q++) {
+            const uint64_t h = hash_one(a.hk, key[q]);
+            uint64_t base;
+            uint32_t mask;
+            hp[q] = (uint32_t)(h >> 32);
+            locate<RADIX>(a.tv, hp[q], base, mask);
+            idx[q] = (uint32_t)h & mask & ~1u;
+            const Slot *p = key[q] ? a.tv.slots + base + idx[q] : a.tv.zero_slot;
+            k0[q] = v0[q] = k1[q] = v1[q] = 0ULL;
+            if (!GUARD || ((pending >> q) & 1u)) load_bucket(p, k0[q], v0[q], k1[q], v1[q]);
+        }
+#pragma unroll
+        for (int q = 0; q < PROBE_ITEMS; q++) {
+            unsigned long long v = 0ULL;
+            bool done = true;
+            if (k0[q] == key[q]) v = v0[q];
+            else if (k0[q] == 0ULL) v = 0ULL;
+            else if (k1[q] == key[q]) v = v1[q];
+            else if (k1[q] == 0ULL) v = 0ULL;
+            else done = false;
+            s[q].key = key[q];
+            s[q].row = (uint32_t)v;
+            s[q].count = (uint32_t)(v >> 32);
+            if (done) pending &= ~(1u << q);
+        }
+    }
+    while (pending) {
+#pragma unroll
+        for (int q = 0; q < PROBE_ITEMS; q++) {
+            if (!((pending >> q) & 1u)) continue;
+            uint64_t base;
+            uint32_t mask;
+            locate<RADIX>(a.tv, hp[q], base, mask);
+            idx[q] = (idx[q] + 2u) & mask;
+            unsigned long long k0, v0, k1, v1;
+            load_bucket(a.tv.slots + base + idx[q], k0, v0, k1, v1);
+            unsigned long long v = 0ULL;
+            bool done = true;
+            if (k0 == key[q]) v = v0;
+            else if (k0 == 0ULL) v = 0ULL;
+            else if (k1 == key[q]) v = v1;
+            else if (k1 == 0ULL) v = 0ULL;
+            else done = false;
+            s[q].row = (uint32_t)v;
+            s[q].count = (uint32_t)(v >> 32);
+            if (done) pending &= ~(1u << q);
+        }
+    }
+    uint32_t m[PROBE_ITEMS];
+    uint32_t found = 0;
+    bool multi = false;
+#pragma unroll
+    for (int q = 0; q < PROBE_ITEMS; q++) {
+        const bool f = (!GUARD || ((look >> q) & 1u)) && s[q].count != 0u;
+        if (f) found |= 1u << q;
+        const bool inq = !GUARD || ((in >> q) & 1u);
+        if (MODE == PM_PAIRS) m[q] = f ? s[q].count : 0u;
+        else if (MODE == PM_OUTER) m[q] = f ? s[q].count : (inq ? 1u : 0u);
+        else if (MODE == PM_SEMI) m[q] = f ? 1u : 0u;
+        else if (MODE == PM_ANTI) m[q] = (inq && !f) ? 1u : 0u;
+        else m[q] = 0u;
+        if (f && s[q].count > 1u && (MODE == PM_PAIRS || MODE == PM_OUTER || MARK)) multi = true;
+    }
+
+    if (MODE == PM_MARK) {
+        // LeftSemi / LeftAnti: nothing is produced per batch (left_semi.rs:158-163, left_anti.rs:158-163)
+#pragma unroll
+        for (int q = 0; q < PROBE_ITEMS; q++) {
+            if (!((found >> q) & 1u)) continue;
+            if (s[q].count == 1u) mark_visited(a.visited, s[q].row);
+            else for (uint32_t k = 0; k < s[q].count; k++) mark_visited(a.visited, __ldcg(a.tv.rowids + s[q].row + k));
+        }
+        return;
+    }
+
+    // ---- warp-level positions: ballot fast path when every item produces at most one row
+    const bool any_multi = __any_sync(FULL, multi);
+    uint32_t off[PROBE_ITEMS];
+    uint32_t wtot = 0;
+    if (!any_multi) {
+#pragma unroll
+        for (int q = 0; q < PROBE_ITEMS; q++) {
+            const uint32_t b = __ballot_sync(FULL, m[q] != 0u);
+            off[q] = wtot + __popc(b & lt_mask);
+            wtot += __popc(b);
+        }
+    } else {
+#pragma unroll
+        for (int q = 0; q < PROBE_ITEMS; q++) {
+            uint32_t incl = m[q];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += y; }
+            off[q] = wtot + incl - m[q];
+            wtot += __shfl_sync(FULL, incl, 31);
+        }
+    }
+    // ---- one atomic per tile: block-aggregated reservation of output rows (double-buffered: 2 barriers per tile)
+    if (lane == 0) s_warp[buf][warp] = wtot;
+    __syncthreads();
+    if (t == 0) {
+        unsigned long long tot = 0;
+#pragma unroll
+        for (int w = 0; w < NWARP; w++) tot += s_warp[buf][w];
+        s_base[buf] = tot ? atomicAdd(&a.ctr->out_count, tot) : 0ULL;
+    }
+    __syncthreads();
+    unsigned long long gbase = s_base[buf];
+#pragma unroll
+    for (int w = 0; w < NWARP; w++) gbase += (w < warp) ? s_warp[buf][w] : 0u;
+
+    // ---- write. Fast path: consecutive lanes write consecutive rows of the output (coalesced 8 B + 4 B stores)
+#pragma unroll
+    for (int q = 0; q < PROBE_ITEMS; q++) {
+        if (m[q] == 0u) continue;
+        const unsigned long long pos = gbase + off[q];
+        const uint32_t prow = a.rowid ? __ldcs(a.rowid + row[q]) : row[q];
+        const bool f = (found >> q) & 1u;
+        if (!f || MODE == PM_SEMI || MODE == PM_ANTI) {
+            // (NULL, probe): unmatched row of Right/Full, or a RightSemi/RightAnti row
+            if (pos < a.out_cap) {
+                if (a.out_build) a.out_build[pos] = ~0ULL;
+                a.out_probe[pos] = prow;
+            }
+            null_build_out++;
+        } else if (s[q].count == 1u) {
+            if (pos < a.out_cap) {
+                a.out_build[pos] = (uint64_t)s[q].row;
+                a.out_probe[pos] = prow;
+            }
+            if (MARK) mark_visited(a.visited, s[q].row);
+        } else if (s[q].count < 32u) {
+            for (uint32_t k = 0; k < s[q].count; k++) {
+                const uint32_t br = __ldcg(a.tv.rowids + s[q].row + k);
+                if (pos + k < a.out_cap) {
+                    a.out_build[pos + k] = (uint64_t)br;
+                    a.out_probe[pos + k] = prow;
                 }
+                if (MARK) mark_visited(a.visited, br);
             }
         }
-        // ---- resolve collisions (linear probing; the next slot is in the same 32 B sector half of the time)
-        uint32_t m[TILE_ITEMS];        // output rows of this item
-        bool found[TILE_ITEMS];
-        bool multi = false;
+    }
+    // ---- long duplicate runs: the whole warp copies one run at a time (coalesced reads of rowids[])
+    if (any_multi && (MODE == PM_PAIRS || MODE == PM_OUTER)) {
 #pragma unroll
-        for (int q = 0; q < TILE_ITEMS; q++) {
-            found[q] = false;
-            if (look[q]) {
-                if (key[q] == 0) {
-                    found[q] = (s[q].key == 0ULL);
-                } else {
-                    while (s[q].key != key[q] && s[q].key != 0ULL) {
-                        idx[q] = (idx[q] + 1) & mask[q];
-                        s[q] = load_slot(a.tv.slots + base[q] + idx[q]);
-                    }
-                    found[q] = (s[q].key == key[q]);
-                }
-            }
-            if (MODE == PM_PAIRS) m[q] = found[q] ? s[q].count : 0u;
-            else if (MODE == PM_OUTER) m[q] = found[q] ? s[q].count : (inrange[q] ? 1u : 0u);
-            else if (MODE == PM_SEMI) m[q] = found[q] ? 1u : 0u;
-            else if (MODE == PM_ANTI) m[q] = (inrange[q] && !found[q]) ? 1u : 0u;
-            else m[q] = 0u;
-            if (found[q] && s[q].count > 1u && (MODE == PM_PAIRS || MODE == PM_OUTER || MARK)) multi = true;
-        }
-
-        if (MODE == PM_MARK) {
-            // LeftSemi / LeftAnti: nothing is produced per batch (left_semi.rs:158-163, left_anti.rs:158-163)
-#pragma unroll
-            for (int q = 0; q < TILE_ITEMS; q++) {
-                if (!found[q]) continue;
-                if (s[q].count == 1u) mark_visited(a.visited, s[q].row);
-                else for (uint32_t k = 0; k < s[q].count; k++) mark_visited(a.visited, __ldcg(a.tv.rowids + s[q].row + k));
-            }
-            continue;
-        }
-
-        // ---- warp-level positions: ballot fast path when every item produces at most one row
-        const bool any_multi = __any_sync(FULL, multi);
-        uint32_t off[TILE_ITEMS];
-        uint32_t wtot = 0;
-        if (!any_multi) {
-#pragma unroll
-            for (int q = 0; q < TILE_ITEMS; q++) {
-                const uint32_t b = __ballot_sync(FULL, m[q] != 0u);
-                off[q] = wtot + __popc(b & lt_mask);
-                wtot += __popc(b);
-            }
-        } else {
-#pragma unroll
-            for (int q = 0; q < TILE_ITEMS; q++) {
-                uint32_t incl = m[q];
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += y; }
-                off[q] = wtot + incl - m[q];
-                wtot += __shfl_sync(FULL, incl, 31);
-            }
-        }
-        // ---- one atomic per tile: block-aggregated reservation of output rows
-        if (lane == 0) s_warp[warp] = wtot;
-        __syncthreads();
-        if (t == 0) {
-            unsigned long long tot = 0;
-#pragma unroll
-            for (int w = 0; w < NWARP; w++) tot += s_warp[w];
-            s_base = tot ? atomicAdd(&a.ctr->out_count, tot) : 0ULL;
-        }
-        __syncthreads();
-        unsigned long long gbase = s_base;
-        for (int w = 0; w < warp; w++) gbase += s_warp[w];
-        __syncthreads();
-
-        // ---- write. Fast path: consecutive lanes write consecutive rows of the output (coalesced 8 B + 4 B stores)
-#pragma unroll
-        for (int q = 0; q < TILE_ITEMS; q++) {
-            if (m[q] == 0u) continue;
-            const unsigned long long pos = gbase + off[q];
-            const uint32_t prow = a.rowid ? __ldcs(a.rowid + row[q]) : (uint32_t)row[q];
-            if (!found[q] || MODE == PM_SEMI || MODE == PM_ANTI) {
-                // (NULL, probe): unmatched row of Right/Full, or a RightSemi/RightAnti row
-                if (pos < a.out_cap) {
-                    if (a.out_build) a.out_build[pos] = ~0ULL;
-                    a.out_probe[pos] = prow;
-                }
-                null_build_out++;
-            } else if (s[q].count == 1u) {
-                if (pos < a.out_cap) {
-                    a.out_build[pos] = (uint64_t)s[q].row;
-                    a.out_probe[pos] = prow;
-                }
-                if (MARK) mark_visited(a.visited, s[q].row);
-            } else if (s[q].count < 32u) {
-                for (uint32_t k = 0; k < s[q].count; k++) {
-                    const uint32_t br = __ldcg(a.tv.rowids + s[q].row + k);
+        for (int q = 0; q < PROBE_ITEMS; q++) {
+            const bool heavy = ((found >> q) & 1u) && s[q].count >= 32u;
+            uint32_t pend = __ballot_sync(FULL, heavy);
+            while (pend) {
+                const int src = __ffs(pend) - 1;
+                pend &= pend - 1;
+                const unsigned long long pos = __shfl_sync(FULL, gbase + off[q], src);
+                const uint32_t cnt = __shfl_sync(FULL, s[q].count, src);
+                const uint32_t rb = __shfl_sync(FULL, s[q].row, src);
+                const uint32_t mine = (a.rowid && heavy) ? __ldcs(a.rowid + row[q]) : row[q];
+                const uint32_t pr = __shfl_sync(FULL, mine, src);
+                for (uint32_t k = lane; k < cnt; k += 32) {
+                    const uint32_t br = __ldcg(a.tv.rowids + rb + k);
                     if (pos + k < a.out_cap) {
                         a.out_build[pos + k] = (uint64_t)br;
-                        a.out_probe[pos + k] = prow;
+                        a.out_probe[pos + k] = pr;
                     }
                     if (MARK) mark_visited(a.visited, br);
                 }
             }
         }
-        // ---- long duplicate runs: the whole warp copies one run at a time (coalesced reads of rowids[])
-        if (any_multi && (MODE == PM_PAIRS || MODE == PM_OUTER)) {
-#pragma unroll
-            for (int q = 0; q < TILE_ITEMS; q++) {
-                const bool heavy = found[q] && s[q].count >= 32u;
-                uint32_t pend = __ballot_sync(FULL, heavy);
-                while (pend) {
-                    const int src = __ffs(pend) - 1;
-                    pend &= pend - 1;
-                    const unsigned long long pos = __shfl_sync(FULL, gbase + off[q], src);
-                    const uint32_t cnt = __shfl_sync(FULL, s[q].count, src);
-                    const uint32_t rb = __shfl_sync(FULL, s[q].row, src);
-                    const uint32_t pr = __shfl_sync(FULL, a.rowid ? __ldcs(a.rowid + (inrange[q] ? row[q] : 0)) : (uint32_t)row[q], src);
-                    for (uint32_t k = lane; k < cnt; k += 32) {
-                        const uint32_t br = __ldcg(a.tv.rowids + rb + k);
-                        if (pos + k < a.out_cap) {
-                            a.out_build[pos + k] = (uint64_t)br;
-                            a.out_probe[pos + k] = pr;
-                        }
-                        if (MARK) mark_visited(a.visited, br);
-                    }
-                }
-            }
-        }
+    }
+}
+
+template <int KW, int MODE, bool MARK, bool RADIX>
+__global__ void __launch_bounds__(PROBE_THREADS) probe_kernel(ProbeArgs a) {
+    __shared__ uint32_t s_warp[2][PROBE_THREADS / 32];
+    __shared__ unsigned long long s_base[2];
+    const int t = threadIdx.x;
+    const uint32_t mis = (uint32_t)a.mis;
+    const uint32_t vend = (uint32_t)a.n + mis;
+    const uint32_t n_tiles = (vend + PROBE_TILE - 1) / PROBE_TILE;
+    const bool no_nulls = a.validity == nullptr;
+    uint32_t null_build_out = 0;
+    int buf = 0;
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, buf ^= 1) {
+        const bool inner = no_nulls && (tile > 0 || mis == 0) && (tile + 1) * (uint32_t)PROBE_TILE <= vend;
+        if (inner) probe_tile<KW, MODE, MARK, RADIX, false>(a, tile, t, s_warp, s_base, buf, null_build_out);
+        else probe_tile<KW, MODE, MARK, RADIX, true>(a, tile, t, s_warp, s_base, buf, null_build_out);
     }
     if (MODE == PM_OUTER || MODE == PM_SEMI || MODE == PM_ANTI) {
         const unsigned long long z = warp_sum_u32(null_build_out);
-        if (lane == 0 && z) atomicAdd(&a.ctr->build_null_out, z);
+        if ((t & 31) == 0 && z) atomicAdd(&a.ctr->build_null_out, z);
     }
 }
 
