@@ -492,7 +492,7 @@ void launch_probe_mode(const ProbePlan &pl, int grid, cudaStream_t s, const Prob
 }
 
 void launch_probe(H *h, const ProbePlan &pl, const ProbeArgs &a, int kw, bool radix) {
-    const int grid = grid_for(h, a.n + a.mis, PROBE_TILE, 2048 / PROBE_THREADS);
+    const int grid = grid_for(h, a.n + a.mis, PROBE_STAGE, 2048 / PROBE_THREADS);
     if (kw == 8) {
         if (radix) launch_probe_mode<8, true>(pl, grid, h->stream, a);
         else launch_probe_mode<8, false>(pl, grid, h->stream, a);
@@ -569,8 +569,7 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
                 if (want_build) CU(cudaMallocAsync(&ob, (size_t)cap * 8, h->stream));
                 CU(cudaMallocAsync(&op, (size_t)cap * 4, h->stream));
             }
-            CU(cudaMemsetAsync(&h->d_ctr->out_count, 0, 8, h->stream));
-            CU(cudaMemsetAsync(&h->d_ctr->build_null_out, 0, 8, h->stream));
+            CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
             ProbeArgs a{};
             a.keys = pkeys;
             a.validity = pvalid;
@@ -696,7 +695,7 @@ int64_t select_bits(H *h, const uint32_t *bm, int64_t n, bool want_set, void **o
     void *o64 = nullptr, *o32 = nullptr;
     if (out64) CU(cudaMallocAsync(&o64, (size_t)n * 8, h->stream));
     if (out32) CU(cudaMallocAsync(&o32, (size_t)n * 4, h->stream));
-    CU(cudaMemsetAsync(&h->d_ctr->out_count, 0, 8, h->stream));
+    CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
     bitmap_select_kernel<<<grid_for(h, (n + 31) / 32, 256, 8), 256, 0, h->stream>>>(bm, n, want_set ? 1 : 0, (uint64_t *)o64, (uint32_t *)o32,
                                                                                      (uint64_t)n, &h->d_ctr->out_count);
     h->st.kernel_launches++;

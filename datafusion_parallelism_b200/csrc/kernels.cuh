@@ -100,15 +100,19 @@ struct __align__(16) Slot {
 };
 
 struct Counters {
-    unsigned long long out_count;     // probe: rows produced (may exceed capacity: then nothing past capacity is written)
-    unsigned long long distinct;      // build
+    // reset before every probe launch (24 contiguous bytes)
+    unsigned long long out_count;     // rows produced (may exceed capacity: then nothing past capacity is written)
+    unsigned long long build_null_out;
+    unsigned int       next_tile;     // dynamic tile scheduler
+    unsigned int       _pad;
+    // build
+    unsigned long long distinct;
     unsigned long long dup_rows;
     unsigned long long multi_slots;
     unsigned long long null_keys;
     unsigned long long csr_cursor;
-    unsigned long long build_null_out;
-    unsigned long long probe_null_out;
 };
+constexpr size_t COUNTERS_LAUNCH_BYTES = 24;
 
 struct TableView {
     Slot           *slots;
@@ -145,11 +149,13 @@ __device__ __forceinline__ Slot load_slot(const Slot *p) {
     return s;
 }
 
-// One 32 B sector = one bucket of two slots, fetched with a single 256-bit load (LDG.E.256, sm_100+).
+// One 32 B sector = one bucket of two slots, fetched with a single 256-bit load (LDG.E.256, sm_100+) that
+// bypasses L1 and asks L2 to keep the line (evict_last): the table is the only data with reuse, everything
+// else in the probe is a stream marked evict-first.
 // Linear probing always starts at the even slot of the home bucket, so a probe step is exactly one sector.
 __device__ __forceinline__ void load_bucket(const Slot *p, unsigned long long &k0, unsigned long long &v0,
                                             unsigned long long &k1, unsigned long long &v1) {
-    asm volatile("ld.global.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(k0), "=l"(v0), "=l"(k1), "=l"(v1) : "l"(p));
+    asm volatile("ld.global.L1::no_allocate.L2::evict_last.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(k0), "=l"(v0), "=l"(k1), "=l"(v1) : "l"(p));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -273,7 +279,14 @@ __global__ void __launch_bounds__(TILE_THREADS) build_insert_kernel(BuildArgs a)
     const int t = threadIdx.x;
     uint32_t distinct = 0, dups = 0, multi = 0, nulls = 0;
     const int64_t n_tiles = (a.n + a.mis + TILE_ROWS - 1) / TILE_ROWS;
-    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    __shared__ unsigned int s_tile;
+    for (;;) {
+        // dynamic tile order (see probe_kernel): keeps the running CTAs inside one or two radix partitions
+        __syncthreads();
+        if (t == 0) s_tile = atomicAdd(&a.ctr->next_tile, 1u);
+        __syncthreads();
+        const int64_t tile = s_tile;
+        if (tile >= n_tiles) break;
         uint64_t key[TILE_ITEMS];
         int64_t row[TILE_ITEMS];
         load_tile_keys<KW>(a.keys, a.mis, a.n, tile, t, key, row);
@@ -461,12 +474,27 @@ __device__ __forceinline__ void probe_load_tile(const ProbeArgs &a, uint32_t til
     }
 }
 
+#ifndef B200J_PROBE_SUB
+#define B200J_PROBE_SUB 4
+#endif
+constexpr int PROBE_SUB   = B200J_PROBE_SUB;                 // tiles per output flush
+constexpr int PROBE_STAGE = PROBE_TILE * PROBE_SUB;          // rows staged in shared memory per global atomic
+
+struct ProbeStage {                                          // block-local staging of single-row results
+    uint32_t brow[PROBE_STAGE];                              // build row (0xffffffff = NULL)
+    uint32_t prow[PROBE_STAGE];
+    uint32_t count;
+    uint32_t next;                                           // next super-tile of this CTA
+    unsigned long long gbase;
+};
+
+// One tile of PROBE_TILE rows. No block barrier in here: warps run free inside a super-tile; rows that produce
+// exactly one output go to the shared-memory stage (one warp-aggregated shared atomic per warp), duplicate-key
+// runs (count >= 2) reserve their own global range with one warp-aggregated global atomic.
 template <int KW, int MODE, bool MARK, bool RADIX, bool GUARD>
-__device__ __forceinline__ void probe_tile(const ProbeArgs &a, uint32_t tile, int t, uint32_t (&s_warp)[2][PROBE_THREADS / 32],
-                                           unsigned long long (&s_base)[2], int buf, uint32_t &null_build_out) {
+__device__ __forceinline__ void probe_tile(const ProbeArgs &a, uint32_t tile, int t, ProbeStage &st, uint32_t &null_build_out) {
     constexpr uint32_t FULL = 0xffffffffu;
-    constexpr int NWARP = PROBE_THREADS / 32;
-    const int lane = t & 31, warp = t >> 5;
+    const int lane = t & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
 
     uint64_t key[PROBE_ITEMS];
@@ -474,12 +502,10 @@ __device__ __forceinline__ void probe_tile(const ProbeArgs &a, uint32_t tile, in
     uint32_t in, look;
     probe_load_tile<KW, GUARD>(a, tile, t, key, row, in, look);
 
-    // ---- hash + first slot load of every item before any is consumed: PROBE_ITEMS independent random loads in flight.
-    // The key value 0 lives in the side slot (whose key word is 0 as well), so the same compare serves both.
-    // Lock-step rounds: in every round each unresolved item loads ONE bucket, so a tile costs
-    // max-over-items(chain length) L2 round trips instead of their sum.
+    // ---- round 0: hash + bucket load of every item before any is consumed (PROBE_ITEMS random 32 B loads in flight).
+    // The key value 0 lives in the side bucket (whose key word is 0 as well), so the same compare serves both.
     uint32_t idx[PROBE_ITEMS], hp[PROBE_ITEMS];
-    Slot s[PROBE_ITEMS];                      // the matching slot (count == 0: no match)
+    uint32_t srow[PROBE_ITEMS], scnt[PROBE_ITEMS];          // the matching slot (scnt == 0: no match)
     uint32_t pending = GUARD ? look : in;
     {
         unsigned long long k0[PROBE_ITEMS], v0[PROBE_ITEMS], k1[PROBE_ITEMS], v1[PROBE_ITEMS];
@@ -497,151 +523,132 @@ __device__ __forceinline__ void probe_tile(const ProbeArgs &a, uint32_t tile, in
         }
 #pragma unroll
         for (int q = 0; q < PROBE_ITEMS; q++) {
-            unsigned long long v = 0ULL;
-            bool done = true;
-            if (k0[q] == key[q]) v = v0[q];
-            else if (k0[q] == 0ULL) v = 0ULL;
-            else if (k1[q] == key[q]) v = v1[q];
-            else if (k1[q] == 0ULL) v = 0ULL;
-            else done = false;
-            s[q].key = key[q];
-            s[q].row = (uint32_t)v;
-            s[q].count = (uint32_t)(v >> 32);
+            const bool hit0 = k0[q] == key[q], hit1 = k1[q] == key[q];
+            const bool done = hit0 | hit1 | (k0[q] == 0ULL) | (k1[q] == 0ULL);
+            const unsigned long long v = hit0 ? v0[q] : ((hit1 && k0[q] != 0ULL) ? v1[q] : 0ULL);
+            srow[q] = (uint32_t)v;
+            scnt[q] = (uint32_t)(v >> 32);
             if (done) pending &= ~(1u << q);
         }
     }
+    // ---- later rounds (about one lookup in ten at load factor 0.5): each lane walks its lowest unresolved item
     while (pending) {
+        const int q = __ffs(pending) - 1;
+        uint64_t k = key[0];
+        uint32_t i = idx[0], p = hp[0];
 #pragma unroll
-        for (int q = 0; q < PROBE_ITEMS; q++) {
-            if (!((pending >> q) & 1u)) continue;
-            uint64_t base;
-            uint32_t mask;
-            locate<RADIX>(a.tv, hp[q], base, mask);
-            idx[q] = (idx[q] + 2u) & mask;
+        for (int j = 1; j < PROBE_ITEMS; j++)
+            if (q == j) { k = key[j]; i = idx[j]; p = hp[j]; }
+        uint64_t base;
+        uint32_t mask;
+        locate<RADIX>(a.tv, p, base, mask);
+        for (;;) {
+            i = (i + 2u) & mask;
             unsigned long long k0, v0, k1, v1;
-            load_bucket(a.tv.slots + base + idx[q], k0, v0, k1, v1);
-            unsigned long long v = 0ULL;
-            bool done = true;
-            if (k0 == key[q]) v = v0;
-            else if (k0 == 0ULL) v = 0ULL;
-            else if (k1 == key[q]) v = v1;
-            else if (k1 == 0ULL) v = 0ULL;
-            else done = false;
-            s[q].row = (uint32_t)v;
-            s[q].count = (uint32_t)(v >> 32);
-            if (done) pending &= ~(1u << q);
+            load_bucket(a.tv.slots + base + i, k0, v0, k1, v1);
+            const bool hit0 = k0 == k, hit1 = k1 == k;
+            if (hit0 | hit1 | (k0 == 0ULL) | (k1 == 0ULL)) {
+                const unsigned long long v = hit0 ? v0 : ((hit1 && k0 != 0ULL) ? v1 : 0ULL);
+#pragma unroll
+                for (int j = 0; j < PROBE_ITEMS; j++)
+                    if (q == j) { srow[j] = (uint32_t)v; scnt[j] = (uint32_t)(v >> 32); }
+                break;
+            }
         }
+        pending &= pending - 1u;
     }
-    uint32_t m[PROBE_ITEMS];
-    uint32_t found = 0;
-    bool multi = false;
+
+    // ---- classify: `one` = items producing exactly one staged row, `multi` = duplicate-key runs
+    uint32_t one = 0, multi = 0, found = 0;
 #pragma unroll
     for (int q = 0; q < PROBE_ITEMS; q++) {
-        const bool f = (!GUARD || ((look >> q) & 1u)) && s[q].count != 0u;
-        if (f) found |= 1u << q;
+        const bool f = (!GUARD || ((look >> q) & 1u)) && scnt[q] != 0u;
         const bool inq = !GUARD || ((in >> q) & 1u);
-        if (MODE == PM_PAIRS) m[q] = f ? s[q].count : 0u;
-        else if (MODE == PM_OUTER) m[q] = f ? s[q].count : (inq ? 1u : 0u);
-        else if (MODE == PM_SEMI) m[q] = f ? 1u : 0u;
-        else if (MODE == PM_ANTI) m[q] = (inq && !f) ? 1u : 0u;
-        else m[q] = 0u;
-        if (f && s[q].count > 1u && (MODE == PM_PAIRS || MODE == PM_OUTER || MARK)) multi = true;
+        if (f) found |= 1u << q;
+        if (MODE == PM_PAIRS) { if (f && scnt[q] == 1u) one |= 1u << q; if (f && scnt[q] > 1u) multi |= 1u << q; }
+        else if (MODE == PM_OUTER) { if ((f && scnt[q] == 1u) || (inq && !f)) one |= 1u << q; if (f && scnt[q] > 1u) multi |= 1u << q; }
+        else if (MODE == PM_SEMI) { if (f) one |= 1u << q; }
+        else if (MODE == PM_ANTI) { if (inq && !f) one |= 1u << q; }
+        if (MARK && MODE != PM_PAIRS && MODE != PM_OUTER && f && scnt[q] > 1u) multi |= 1u << q;
     }
 
-    if (MODE == PM_MARK) {
-        // LeftSemi / LeftAnti: nothing is produced per batch (left_semi.rs:158-163, left_anti.rs:158-163)
+    // ---- single rows -> shared-memory stage: ballot positions, one shared atomic per warp
+    if (MODE != PM_MARK) {
+        uint32_t off[PROBE_ITEMS];
+        uint32_t wtot = 0;
 #pragma unroll
         for (int q = 0; q < PROBE_ITEMS; q++) {
-            if (!((found >> q) & 1u)) continue;
-            if (s[q].count == 1u) mark_visited(a.visited, s[q].row);
-            else for (uint32_t k = 0; k < s[q].count; k++) mark_visited(a.visited, __ldcg(a.tv.rowids + s[q].row + k));
-        }
-        return;
-    }
-
-    // ---- warp-level positions: ballot fast path when every item produces at most one row
-    const bool any_multi = __any_sync(FULL, multi);
-    uint32_t off[PROBE_ITEMS];
-    uint32_t wtot = 0;
-    if (!any_multi) {
-#pragma unroll
-        for (int q = 0; q < PROBE_ITEMS; q++) {
-            const uint32_t b = __ballot_sync(FULL, m[q] != 0u);
+            const uint32_t b = __ballot_sync(FULL, (one >> q) & 1u);
             off[q] = wtot + __popc(b & lt_mask);
             wtot += __popc(b);
         }
+        uint32_t wbase = 0;
+        if (lane == 0 && wtot) wbase = atomicAdd(&st.count, wtot);
+        wbase = __shfl_sync(FULL, wbase, 0);
+#pragma unroll
+        for (int q = 0; q < PROBE_ITEMS; q++) {
+            if (!((one >> q) & 1u)) continue;
+            const bool f = (found >> q) & 1u;
+            const bool null_build = !f || MODE == PM_SEMI || MODE == PM_ANTI;
+            st.brow[wbase + off[q]] = null_build ? 0xffffffffu : srow[q];
+            st.prow[wbase + off[q]] = a.rowid ? __ldcs(a.rowid + row[q]) : row[q];
+            if (null_build) null_build_out++;
+            else if (MARK) mark_visited(a.visited, srow[q]);
+        }
     } else {
 #pragma unroll
-        for (int q = 0; q < PROBE_ITEMS; q++) {
-            uint32_t incl = m[q];
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += y; }
-            off[q] = wtot + incl - m[q];
-            wtot += __shfl_sync(FULL, incl, 31);
-        }
+        for (int q = 0; q < PROBE_ITEMS; q++)
+            if (((found >> q) & 1u) && scnt[q] == 1u) mark_visited(a.visited, srow[q]);
     }
-    // ---- one atomic per tile: block-aggregated reservation of output rows (double-buffered: 2 barriers per tile)
-    if (lane == 0) s_warp[buf][warp] = wtot;
-    __syncthreads();
-    if (t == 0) {
-        unsigned long long tot = 0;
-#pragma unroll
-        for (int w = 0; w < NWARP; w++) tot += s_warp[buf][w];
-        s_base[buf] = tot ? atomicAdd(&a.ctr->out_count, tot) : 0ULL;
-    }
-    __syncthreads();
-    unsigned long long gbase = s_base[buf];
-#pragma unroll
-    for (int w = 0; w < NWARP; w++) gbase += (w < warp) ? s_warp[buf][w] : 0u;
 
-    // ---- write. Fast path: consecutive lanes write consecutive rows of the output (coalesced 8 B + 4 B stores)
+    // ---- duplicate-key runs (rare unless the build side is skewed): own global reservation per warp
+    if (__any_sync(FULL, multi != 0u)) {
+        const bool emit = (MODE == PM_PAIRS || MODE == PM_OUTER);
+        uint32_t off[PROBE_ITEMS];
+        uint32_t wtot = 0;
+        if (emit) {
 #pragma unroll
-    for (int q = 0; q < PROBE_ITEMS; q++) {
-        if (m[q] == 0u) continue;
-        const unsigned long long pos = gbase + off[q];
-        const uint32_t prow = a.rowid ? __ldcs(a.rowid + row[q]) : row[q];
-        const bool f = (found >> q) & 1u;
-        if (!f || MODE == PM_SEMI || MODE == PM_ANTI) {
-            // (NULL, probe): unmatched row of Right/Full, or a RightSemi/RightAnti row
-            if (pos < a.out_cap) {
-                if (a.out_build) a.out_build[pos] = ~0ULL;
-                a.out_probe[pos] = prow;
-            }
-            null_build_out++;
-        } else if (s[q].count == 1u) {
-            if (pos < a.out_cap) {
-                a.out_build[pos] = (uint64_t)s[q].row;
-                a.out_probe[pos] = prow;
-            }
-            if (MARK) mark_visited(a.visited, s[q].row);
-        } else if (s[q].count < 32u) {
-            for (uint32_t k = 0; k < s[q].count; k++) {
-                const uint32_t br = __ldcg(a.tv.rowids + s[q].row + k);
-                if (pos + k < a.out_cap) {
-                    a.out_build[pos + k] = (uint64_t)br;
-                    a.out_probe[pos + k] = prow;
-                }
-                if (MARK) mark_visited(a.visited, br);
+            for (int q = 0; q < PROBE_ITEMS; q++) {
+                const uint32_t mq = ((multi >> q) & 1u) ? scnt[q] : 0u;
+                uint32_t incl = mq;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += y; }
+                off[q] = wtot + incl - mq;
+                wtot += __shfl_sync(FULL, incl, 31);
             }
         }
-    }
-    // ---- long duplicate runs: the whole warp copies one run at a time (coalesced reads of rowids[])
-    if (any_multi && (MODE == PM_PAIRS || MODE == PM_OUTER)) {
+        unsigned long long gbase = 0;
+        if (emit) {
+            if (lane == 0) gbase = atomicAdd(&a.ctr->out_count, (unsigned long long)wtot);
+            gbase = __shfl_sync(FULL, gbase, 0);
+        }
 #pragma unroll
         for (int q = 0; q < PROBE_ITEMS; q++) {
-            const bool heavy = ((found >> q) & 1u) && s[q].count >= 32u;
-            uint32_t pend = __ballot_sync(FULL, heavy);
+            const bool mine = (multi >> q) & 1u;
+            const uint32_t prow = (mine && a.rowid) ? __ldcs(a.rowid + row[q]) : row[q];
+            // short runs: the owning lane copies; long runs: the whole warp copies one run at a time (coalesced)
+            if (mine && scnt[q] < 32u) {
+                const unsigned long long pos = gbase + off[q];
+                for (uint32_t k = 0; k < scnt[q]; k++) {
+                    const uint32_t br = __ldcg(a.tv.rowids + srow[q] + k);
+                    if (emit && pos + k < a.out_cap) {
+                        a.out_build[pos + k] = (uint64_t)br;
+                        a.out_probe[pos + k] = prow;
+                    }
+                    if (MARK) mark_visited(a.visited, br);
+                }
+            }
+            uint32_t pend = __ballot_sync(FULL, mine && scnt[q] >= 32u);
             while (pend) {
                 const int src = __ffs(pend) - 1;
                 pend &= pend - 1;
-                const unsigned long long pos = __shfl_sync(FULL, gbase + off[q], src);
-                const uint32_t cnt = __shfl_sync(FULL, s[q].count, src);
-                const uint32_t rb = __shfl_sync(FULL, s[q].row, src);
-                const uint32_t mine = (a.rowid && heavy) ? __ldcs(a.rowid + row[q]) : row[q];
-                const uint32_t pr = __shfl_sync(FULL, mine, src);
+                const unsigned long long pos = __shfl_sync(FULL, gbase + (emit ? off[q] : 0u), src);
+                const uint32_t cnt = __shfl_sync(FULL, scnt[q], src);
+                const uint32_t rb = __shfl_sync(FULL, srow[q], src);
+                const uint32_t pr = __shfl_sync(FULL, prow, src);
                 for (uint32_t k = lane; k < cnt; k += 32) {
                     const uint32_t br = __ldcg(a.tv.rowids + rb + k);
-                    if (pos + k < a.out_cap) {
+                    if (emit && pos + k < a.out_cap) {
                         a.out_build[pos + k] = (uint64_t)br;
                         a.out_probe[pos + k] = pr;
                     }
@@ -654,19 +661,54 @@ __device__ __forceinline__ void probe_tile(const ProbeArgs &a, uint32_t tile, in
 
 template <int KW, int MODE, bool MARK, bool RADIX>
 __global__ void __launch_bounds__(PROBE_THREADS) probe_kernel(ProbeArgs a) {
-    __shared__ uint32_t s_warp[2][PROBE_THREADS / 32];
-    __shared__ unsigned long long s_base[2];
+    __shared__ ProbeStage st;
     const int t = threadIdx.x;
     const uint32_t mis = (uint32_t)a.mis;
     const uint32_t vend = (uint32_t)a.n + mis;
     const uint32_t n_tiles = (vend + PROBE_TILE - 1) / PROBE_TILE;
+    const uint32_t n_super = (n_tiles + PROBE_SUB - 1) / PROBE_SUB;
     const bool no_nulls = a.validity == nullptr;
     uint32_t null_build_out = 0;
-    int buf = 0;
-    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, buf ^= 1) {
-        const bool inner = no_nulls && (tile > 0 || mis == 0) && (tile + 1) * (uint32_t)PROBE_TILE <= vend;
-        if (inner) probe_tile<KW, MODE, MARK, RADIX, false>(a, tile, t, s_warp, s_base, buf, null_build_out);
-        else probe_tile<KW, MODE, MARK, RADIX, true>(a, tile, t, s_warp, s_base, buf, null_build_out);
+    // Super-tiles are handed out by a global counter, not by a static grid stride: the running CTAs then always
+    // work on the most recent ~1200 super-tiles, i.e. on one or two radix partitions, whose tables stay in L2.
+    // (With a static stride the CTAs drift apart by dozens of partitions and every lookup goes to HBM.)
+    if (t == 0) { st.count = 0; st.next = atomicAdd(&a.ctr->next_tile, 1u); }
+    __syncthreads();
+    for (;;) {
+        const uint32_t sup = st.next;
+        if (sup >= n_super) break;
+#pragma unroll 1
+        for (int sub = 0; sub < PROBE_SUB; sub++) {
+            const uint32_t tile = sup * PROBE_SUB + sub;
+            if (tile >= n_tiles) break;
+            const bool inner = no_nulls && (tile > 0 || mis == 0) && (tile + 1) * (uint32_t)PROBE_TILE <= vend;
+            if (inner) probe_tile<KW, MODE, MARK, RADIX, false>(a, tile, t, st, null_build_out);
+            else probe_tile<KW, MODE, MARK, RADIX, true>(a, tile, t, st, null_build_out);
+        }
+        // ---- flush: one global atomic per super-tile, then fully coalesced streaming 8 B + 4 B stores
+        __syncthreads();
+        const uint32_t cnt = st.count;
+        if (t == 0) st.gbase = cnt ? atomicAdd(&a.ctr->out_count, (unsigned long long)cnt) : 0ULL;
+        __syncthreads();
+        const unsigned long long gbase = st.gbase;
+        if (gbase + cnt <= a.out_cap) {
+            if (a.out_build)
+                for (uint32_t i = t; i < cnt; i += PROBE_THREADS) {
+                    const uint32_t br = st.brow[i];
+                    __stcs(reinterpret_cast<unsigned long long *>(a.out_build) + gbase + i, br == 0xffffffffu ? ~0ULL : (unsigned long long)br);
+                }
+            for (uint32_t i = t; i < cnt; i += PROBE_THREADS) __stcs(a.out_probe + gbase + i, st.prow[i]);
+        } else {
+            for (uint32_t i = t; i < cnt; i += PROBE_THREADS) {
+                if (gbase + i >= a.out_cap) break;
+                const uint32_t br = st.brow[i];
+                if (a.out_build) a.out_build[gbase + i] = br == 0xffffffffu ? ~0ULL : (uint64_t)br;
+                a.out_probe[gbase + i] = st.prow[i];
+            }
+        }
+        __syncthreads();
+        if (t == 0) { st.count = 0; st.next = atomicAdd(&a.ctr->next_tile, 1u); }
+        __syncthreads();
     }
     if (MODE == PM_OUTER || MODE == PM_SEMI || MODE == PM_ANTI) {
         const unsigned long long z = warp_sum_u32(null_build_out);
