@@ -1,0 +1,396 @@
+#!/usr/bin/env python
+"""bench.py — the contract benchmark of the B200 hash join (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One STEP = one whole join of the workload: build side pushed and built, probe side probed in chunks,
+(build_idx, probe_idx) pairs materialised.  N = 1 runs config C2 (100 M-row int64 unique build x 1 B-row
+uniform probe, 1:1 matches); N > 1 (launched by torchrun, one rank per GPU) runs the same per-GPU volume on
+every rank over an N-times larger key space: both sides are hash-partitioned on the device and exchanged
+over NVLink, then every GPU joins its own partition ("weak" scaling, C4's shape).
+
+`value`      whole-job (build + probe) tuples/s, inputs resident in HBM, CUDA events on the join's stream,
+             max over ranks.
+`e2e`        same metric through the public host-buffer API (the call the Rust operator makes): every step
+             copies the key buffers from pinned host memory and reads the index pairs back to pinned host memory.
+`roofline`   the dominant kernel (probe), algorithmic bytes / its CUDA-event launch time / measured HBM peak.
+`cpu_baseline`  oracle/cpu_join_mt.c (C restatement of the reference's version10 algorithm, all host threads)
+             on a bounded sample of the same workload (rank 0, N = 1 only).
+`--impl reference`  times that CPU implementation alone (the Rust crate cannot be built here: no cargo).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "build+probe tuples/sec"
+UNIT = "tuples/s"
+HBM_FALLBACK_GBS = 6650.0          # B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
+NVLINK_GBS = 770.0                 # measured peer copy per direction (B200_PROFILING.md)
+
+# algorithmic bytes per tuple (SURVEY.md §8d / BASELINE.md §3)
+B_BUILD = 24                       # 8 key read + 16 slot write
+B_PROBE = 36                       # 8 key read + 16 slot read + 12 pair write
+B_PROBE_KERNEL_RADIX = 24          # the probe KERNEL of the radix layout: 12 (key, row id) read + 12 pair write, table in L2
+B_PARTITION = 28                   # histogram 8 read + scatter 8 read + 12 write
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--build-rows", type=int, default=100_000_000)
+    ap.add_argument("--probe-rows", type=int, default=1_000_000_000)
+    ap.add_argument("--chunk-rows", type=int, default=1 << 28, help="probe rows per b200j_probe_batch call")
+    ap.add_argument("--layout", default="auto")
+    ap.add_argument("--radix-bits", type=int, default=0)
+    ap.add_argument("--load-factor", type=float, default=0.0)
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-probe-sample", type=int, default=250_000_000)
+    ap.add_argument("--shuffle", default="p2p", choices=["p2p", "nccl"], help="N>1: fused peer-store scatter or NCCL all-to-all")
+    return ap.parse_args()
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return HBM_FALLBACK_GBS, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md clocks line)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line)
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=3)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "power_w_max": max(pw), "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------------------------------
+# the reference arm / cpu_baseline: oracle/cpu_join_mt.c on the host cores
+# --------------------------------------------------------------------------------------------------
+def cpu_join_sample(n_build: int, n_probe_full: int, probe_sample: int, reps: int = 1, warmup: int = 0):
+    """Times the CPU join: full-size build, `probe_sample` probe rows; the whole-job figure scales the probe
+    time to n_probe_full rows (the probe loop is a stream of independent 8192-row batches)."""
+    import numpy as np
+    import oracle
+    oracle.build()
+    bk = oracle.gen_permutation_i64(n_build, 3)
+    pk = oracle.gen_uniform_i64(min(probe_sample, n_probe_full), n_build, 4)
+    cores = oracle.MtJoin.max_threads()
+    out = []
+    for it in range(warmup + reps):
+        j = oracle.MtJoin(bk)
+        tb = j.build_seconds
+        tp, matched, _ = j.probe(pk)
+        assert matched == pk.shape[0], (matched, pk.shape[0])
+        del j
+        if it >= warmup:
+            out.append((tb, tp))
+    tb = sum(x[0] for x in out) / len(out)
+    tp = sum(x[1] for x in out) / len(out)
+    build_tps = n_build / tb
+    probe_tps = pk.shape[0] / tp
+    whole = (n_build + n_probe_full) / (n_build / build_tps + n_probe_full / probe_tps)
+    return {"value": whole, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"full {n_build}-row build + {pk.shape[0]}-row probe sample of the {n_probe_full}-row probe side "
+                      f"(probe time scaled to the full side); oracle/cpu_join_mt.c, OpenMP x {cores} threads",
+            "build_tuples_per_s": build_tps, "probe_tuples_per_s": probe_tps,
+            "build_s": tb, "probe_sample_s": tp}, tb + tp
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    t0 = time.time()
+    res, _ = cpu_join_sample(args.build_rows, args.probe_rows, args.cpu_probe_sample, reps=args.steps, warmup=args.warmup)
+    per_step = (time.time() - t0) / max(1, args.steps + args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": per_step * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "int64", "data": "synthetic",
+        "config": workload_config(args, 1),
+        "cpu_baseline": res,
+        "e2e": {"value": res["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference's own Rust crate is not buildable here (no cargo, nightly, aarch64-only version10): "
+                "this is the C restatement of its version10 algorithm on all host threads",
+    }
+    print(json.dumps(line))
+
+
+def workload_config(args, n_gpus):
+    return {"workload": f"C2: {args.build_rows}-row int64 unique-key build x {args.probe_rows}-row uniform probe, 1:1 matches, "
+                        f"inner join, (build_idx u64, probe_idx u32) pairs out" + (f"; per GPU, {n_gpus} GPUs, key space x{n_gpus}, "
+                        "hash-partition + NVLink exchange of both sides" if n_gpus > 1 else ""),
+            "build_rows_per_gpu": args.build_rows, "probe_rows_per_gpu": args.probe_rows, "probe_chunk_rows": args.chunk_rows,
+            "l2": "inputs (8 GB probe keys per step) are far larger than the 126 MB L2; no flush needed"}
+
+
+# --------------------------------------------------------------------------------------------------
+# the B200 arm
+# --------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import numpy as np
+    import torch
+    import datafusion_parallelism_b200 as d
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if d.device_count() < 1:
+        raise SystemExit("bench.py needs a CUDA device: the join has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist = dist_mod
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    n_build, n_probe, chunk = args.build_rows, args.probe_rows, args.chunk_rows
+    hbm_gbs, peak_src = measured_peaks()
+    stream = torch.cuda.Stream(device=dev)
+
+    # ---- synthetic inputs, generated on the device (SURVEY §8d C2 / C4 shapes)
+    g = torch.Generator(device=dev)
+    g.manual_seed(3 + 1000 * rank)
+    key_space = n_build * world
+    if world == 1:
+        bk = torch.randperm(n_build, device=dev, generator=g, dtype=torch.int64)
+    else:
+        # rank r owns the build keys congruent to r modulo world (unique across ranks), in random order
+        bk = torch.randperm(n_build, device=dev, generator=g, dtype=torch.int64) * world + rank
+    pk = torch.randint(0, key_space, (n_probe,), device=dev, generator=g, dtype=torch.int64)
+    torch.cuda.synchronize()
+
+    if world > 1:
+        from datafusion_parallelism_b200.exchange import DistributedJoin
+        join = DistributedJoin("inner", key_width=8, stream=stream, layout=args.layout, radix_bits=args.radix_bits,
+                               load_factor=args.load_factor, expected_build_rows=int(n_build * 1.1), mode=args.shuffle, timing=True)
+    else:
+        join = d.HashJoin("inner", key_widths=(8,), layout=args.layout, radix_bits=args.radix_bits, load_factor=args.load_factor,
+                          expected_build_rows=n_build, stream=stream.cuda_stream, timing=True)
+
+    def step_device():
+        """one whole join, inputs resident in HBM; returns matched rows"""
+        join.reset()
+        join.build_push(0, [bk])
+        join.build_finish(0)
+        tot = 0
+        for lo in range(0, n_probe, chunk):
+            r = join.probe_batch(0, [pk[lo:lo + chunk]], want=d.OUT_PAIRS)
+            tot += r.n
+            r.release()
+        return tot
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    expect = None
+    for _ in range(args.warmup):
+        tot = step_device()
+        expect = tot
+    if world == 1 and expect is not None:
+        assert expect == n_probe, f"1:1 workload produced {expect} rows for {n_probe} probe rows"
+
+    join.reset_stats()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    ev1.record(stream)
+    barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    clocks = sampler.stop() if rank == 0 else None
+    st = join.stats()
+    t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    ms_step = ms_total / args.steps
+    value = (n_build + n_probe) * world / (ms_step * 1e-3)
+
+    # ---- phases (device time from the library's own CUDA events, per step)
+    K = args.steps
+    ph = {k: st[k] / K for k in ("ms_build_copy", "ms_build_partition", "ms_build_insert", "ms_probe_partition", "ms_probe")}
+    for k in ("ms_exchange_build", "ms_exchange_probe"):
+        if k in st:
+            ph[k] = st[k] / K
+    build_ms = ph["ms_build_copy"] + ph["ms_build_partition"] + ph["ms_build_insert"]
+    probe_ms = ph["ms_probe_partition"] + ph["ms_probe"]
+    radix = st["layout"] == 2
+    probe_launch_ms = st["ms_probe"] / max(1, st["probe_launches"])
+    rows_per_launch = n_probe * K / max(1, st["probe_launches"]) if world == 1 else st["probe_rows"] / max(1, st["probe_launches"])
+    bpt = B_PROBE_KERNEL_RADIX if radix else B_PROBE
+    achieved = rows_per_launch * bpt / (probe_launch_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "probe_kernel<8,PM_PAIRS,false,%s>" % ("true" if radix else "false"),
+                "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s", "frac": achieved / hbm_gbs, "traffic": None,
+                "peak_source": peak_src, "bytes_per_tuple": bpt, "tuples_per_launch": rows_per_launch, "ms_per_launch": probe_launch_ms}
+    tr = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr):
+        try:
+            with open(tr) as f:
+                roofline["traffic"] = json.load(f).get("probe_kernel_dram_bytes_per_launch")
+        except Exception:
+            pass
+    local_build = st["build_rows"]
+    phases = {
+        "ms_per_step": ph,
+        "build_tuples_per_s": local_build / (build_ms * 1e-3) if build_ms > 0 else None,
+        "probe_tuples_per_s": (st["probe_rows"] / K) / (probe_ms * 1e-3) if probe_ms > 0 else None,
+        "build_roofline_frac_24B": local_build * B_BUILD / (build_ms * 1e-3) / 1e9 / hbm_gbs if build_ms > 0 else None,
+        "probe_roofline_frac_36B": (st["probe_rows"] / K) * B_PROBE / (probe_ms * 1e-3) / 1e9 / hbm_gbs if probe_ms > 0 else None,
+        "layout": {1: "direct", 2: "radix"}.get(st["layout"], st["layout"]), "radix_bits": st["radix_bits"], "table_bytes": st["table_bytes"],
+    }
+    gpu_launches = int(st["kernel_launches"])
+
+    # ---- e2e: host buffers through the public API
+    e2e = None
+    if not args.no_e2e:
+        e2e = run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        del bk, pk
+        torch.cuda.empty_cache()
+        cpu, _ = cpu_join_sample(n_build, n_probe, args.cpu_probe_sample, reps=1, warmup=0)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64",
+            "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e, "gpu_launches": gpu_launches,
+            "roofline": roofline, "cpu_baseline": cpu, "phases": phases,
+        }
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
+    """Same join through host buffers: pinned Arrow key buffers in, pinned index pairs out, every step."""
+    import numpy as np
+    n_build, n_probe, chunk = args.build_rows, args.probe_rows, args.chunk_rows
+    # bound pinned memory by what the host has (keys 8 B + pairs 12 B per probe row)
+    try:
+        with open("/proc/meminfo") as f:
+            avail = [int(l.split()[1]) * 1024 for l in f if l.startswith("MemAvailable")][0]
+    except Exception:
+        avail = 64 << 30
+    hb = d.PinnedArray(n_build, np.int64)
+    hp = d.PinnedArray(n_probe, np.int64)
+    torch.from_numpy(hb.array).copy_(bk)
+    torch.from_numpy(hp.array).copy_(pk)
+    torch.cuda.synchronize()
+    steps = max(1, min(args.e2e_steps, args.steps))
+    checksum = 0
+
+    def step_host():
+        nonlocal checksum
+        join.reset()
+        join.build_push(0, [hb.array])
+        join.build_finish(0)
+        tot = 0
+        for lo in range(0, n_probe, chunk):
+            r = join.probe_batch(0, [hp.array[lo:lo + chunk]], want=d.OUT_PAIRS | d.OUT_HOST)
+            tot += r.n
+            r.release()
+        return tot
+
+    step_host()                       # warm-up: pinned result buffers, pool growth
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        tot = step_host()
+    barrier()
+    dt = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([dt], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+    hb.free()
+    hp.free()
+    return {"value": (n_build + n_probe) * world / (dt / steps), "unit": UNIT, "h2d_bytes_per_step": 8 * (n_build + n_probe),
+            "d2h_bytes_per_step": 12 * tot, "steps": steps, "ms_per_step": dt / steps * 1e3,
+            "api": "HashJoin.build_push/probe_batch(host numpy over b200j_host_alloc pinned buffers, OUT_PAIRS|OUT_HOST) -> b200j_* C ABI"}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

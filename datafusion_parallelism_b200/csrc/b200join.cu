@@ -1065,6 +1065,20 @@ int32_t b200j_reset_stats(b200j_handle *h) {
     return B200J_OK;
 }
 
+int32_t b200j_reset(b200j_handle *h) {
+    return guarded(h, [&] {
+        CU(cudaStreamSynchronize(h->stream));
+        h->n_build = 0;
+        for (auto *v : {&h->bkeys, &h->bpayload})
+            for (auto &c : *v) { c.has_nulls = false; c.data_bytes = 0; }
+        std::fill(h->build_done.begin(), h->build_done.end(), 0);
+        std::fill(h->probe_done.begin(), h->probe_done.end(), 0);
+        h->n_build_done = h->n_probe_done = 0;
+        h->built = false;
+        h->n_slots = 0;
+    });
+}
+
 int32_t b200j_synchronize(b200j_handle *h) {
     return guarded(h, [&] { CU(cudaStreamSynchronize(h->stream)); });
 }

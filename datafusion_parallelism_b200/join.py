@@ -279,6 +279,37 @@ class HashJoin:
     def synchronize(self):
         self._check(N.lib().b200j_synchronize(self._h))
 
+    def reset(self):
+        """Re-arm for another execution of the same join (keeps streams and device allocations)."""
+        self._check(N.lib().b200j_reset(self._h))
+
+
+class PinnedArray:
+    """Page-locked host memory from b200j_host_alloc, viewed as a numpy array (full-speed PCIe copies)."""
+
+    def __init__(self, n: int, dtype):
+        self.dtype = np.dtype(dtype)
+        self.nbytes = int(n) * self.dtype.itemsize
+        p = C.c_void_p()
+        rc = N.lib().b200j_host_alloc(max(self.nbytes, 1), C.byref(p))
+        if rc != 0:
+            raise B200JoinError(rc, (N.lib().b200j_last_error(None) or b"").decode())
+        self._p = p
+        buf = (C.c_char * max(self.nbytes, 1)).from_address(p.value)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=int(n))
+
+    def free(self):
+        if self._p:
+            self.array = None
+            N.lib().b200j_host_free(self._p)
+            self._p = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
 
 def device_count() -> int:
     return int(N.lib().b200j_device_count())

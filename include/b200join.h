@@ -203,6 +203,10 @@ const char *b200j_last_error(const b200j_handle *h);
 int32_t     b200j_get_stats(b200j_handle *h, b200j_stats *out);
 int32_t     b200j_reset_stats(b200j_handle *h);
 int32_t     b200j_synchronize(b200j_handle *h);             /* wait for the handle's stream        */
+/* Re-arm the handle for another execution of the same join (the plan being executed again,
+ * ParallelHashJoin::execute on a fresh OnceLock, parallel_hash_join.rs:144-151): drops the build
+ * side and the table, keeps streams and device allocations. Outstanding results stay valid. */
+int32_t     b200j_reset(b200j_handle *h);
 
 /* ---- build side ------------------------------------------------------------------------------ */
 /* Append one build batch (rows are numbered in arrival order, like offset_counter.fetch_add,
