@@ -52,7 +52,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--build-rows", type=int, default=100_000_000)
     ap.add_argument("--probe-rows", type=int, default=1_000_000_000)
-    ap.add_argument("--chunk-rows", type=int, default=1 << 28, help="probe rows per b200j_probe_batch call")
+    ap.add_argument("--chunk-rows", type=int, default=1 << 30, help="probe rows per b200j_probe_batch call")
     ap.add_argument("--layout", default="auto")
     ap.add_argument("--radix-bits", type=int, default=0)
     ap.add_argument("--load-factor", type=float, default=0.0)

@@ -7,6 +7,7 @@
 #include "../../include/b200join.h"
 #include "kernels.cuh"
 #include "radix.cuh"
+#include "probe.cuh"
 #include "gather.cuh"
 
 #include <algorithm>
@@ -97,6 +98,9 @@ struct b200j_handle {
     cudaStream_t copy_in = nullptr, copy_out = nullptr;
     bool own_stream = false;
     int sm_count = 148;
+    int probe_ctas_per_sm = 4;
+    int dense_ctas_per_sm = 4;
+    bool dense_ok = true;              // B200J_NO_DENSE=1 forces the staged probe kernel (tuning / tests)
     int64_t l2_bytes = 0;
     bool timing = false;
 
@@ -116,7 +120,7 @@ struct b200j_handle {
     DevBuf zero_slot;
     DevBuf rowids;
     DevBuf visited;
-    DevBuf part_base, part_mask;       // radix layout
+    DevBuf parts;                      // radix layout: PartEnt per partition
     RadixScratch rscratch;
     Counters *d_ctr = nullptr;
     Counters *h_ctr = nullptr;         // pinned mirror
@@ -128,11 +132,10 @@ struct b200j_handle {
     TableView view() const {
         TableView tv{};
         tv.slots = (Slot *)slots.p;
-        tv.mask = n_slots ? n_slots - 1 : 0;
         tv.zero_slot = (Slot *)zero_slot.p;
         tv.rowids = (uint32_t *)rowids.p;
-        tv.part_base = (const uint64_t *)part_base.p;
-        tv.part_mask = (const uint32_t *)part_mask.p;
+        tv.parts = (const PartEnt *)parts.p;
+        tv.nb = (uint32_t)(n_slots / 2);
         tv.radix_bits = radix_bits;
         return tv;
     }
@@ -373,6 +376,12 @@ void launch_by_kw(int kw, F &&f) {
     else f(std::integral_constant<int, 4>{});
 }
 
+// slots of a table for `n` keys at load factor lf: whole buckets, at least 8 buckets, NOT rounded to a power of two
+uint64_t table_slots_for(int64_t n, float lf) {
+    const uint64_t buckets = (uint64_t)std::ceil((double)n / (2.0 * (double)lf)) + 8;
+    return buckets * 2;
+}
+
 void run_build(H *h) {
     const int64_t n = h->n_build;
     const int kw = h->key_widths[0];
@@ -380,8 +389,7 @@ void run_build(H *h) {
     const float lf = h->cfg.load_factor > 0.f ? std::min(h->cfg.load_factor, 0.9f) : 0.5f;
 
     // ---- layout choice: direct while the table fits the L2 budget
-    uint64_t direct_slots = 1024;
-    while ((double)direct_slots * lf < (double)n) direct_slots <<= 1;
+    const uint64_t direct_slots = table_slots_for(n, lf);
     const int64_t budget = h->cfg.l2_budget_bytes > 0 ? h->cfg.l2_budget_bytes : h->l2_bytes / 2;
     int32_t layout = h->cfg.layout;
     if (layout == B200J_LAYOUT_AUTO) layout = ((int64_t)direct_slots * 16 <= budget) ? B200J_LAYOUT_DIRECT : B200J_LAYOUT_RADIX;
@@ -491,7 +499,32 @@ void launch_probe_mode(const ProbePlan &pl, int grid, cudaStream_t s, const Prob
     else probe_kernel<KW, PM_MARK, true, RADIX><<<grid, PROBE_THREADS, 0, s>>>(a);
 }
 
+template <int KW, bool RADIX>
+void launch_probe_fast(const ProbePlan &pl, int grid, cudaStream_t s, const ProbeArgs &a) {
+    if (pl.mode == PM_PAIRS && !pl.mark) probe_fast_kernel<KW, PM_PAIRS, false, RADIX><<<grid, PF_THREADS, 0, s>>>(a);
+    else if (pl.mode == PM_PAIRS) probe_fast_kernel<KW, PM_PAIRS, true, RADIX><<<grid, PF_THREADS, 0, s>>>(a);
+    else if (pl.mode == PM_OUTER && !pl.mark) probe_fast_kernel<KW, PM_OUTER, false, RADIX><<<grid, PF_THREADS, 0, s>>>(a);
+    else if (pl.mode == PM_OUTER) probe_fast_kernel<KW, PM_OUTER, true, RADIX><<<grid, PF_THREADS, 0, s>>>(a);
+    else if (pl.mode == PM_SEMI) probe_fast_kernel<KW, PM_SEMI, false, RADIX><<<grid, PF_THREADS, 0, s>>>(a);
+    else if (pl.mode == PM_ANTI) probe_fast_kernel<KW, PM_ANTI, false, RADIX><<<grid, PF_THREADS, 0, s>>>(a);
+    else probe_fast_kernel<KW, PM_MARK, true, RADIX><<<grid, PF_THREADS, 0, s>>>(a);
+}
+
 void launch_probe(H *h, const ProbePlan &pl, const ProbeArgs &a, int kw, bool radix) {
+    h->st.kernel_launches++;
+    h->st.probe_launches++;
+    if (a.mis == 0 && a.validity == nullptr && (!radix || a.rowid != nullptr)) {
+        // the lean kernel: aligned keys, no validity bitmap (always the case behind the partition pass)
+        const int grid = grid_for(h, a.n, PF_STAGE, h->probe_ctas_per_sm);
+        if (kw == 8) {
+            if (radix) launch_probe_fast<8, true>(pl, grid, h->stream, a);
+            else launch_probe_fast<8, false>(pl, grid, h->stream, a);
+        } else {
+            if (radix) launch_probe_fast<4, true>(pl, grid, h->stream, a);
+            else launch_probe_fast<4, false>(pl, grid, h->stream, a);
+        }
+        return;
+    }
     const int grid = grid_for(h, a.n + a.mis, PROBE_STAGE, 2048 / PROBE_THREADS);
     if (kw == 8) {
         if (radix) launch_probe_mode<8, true>(pl, grid, h->stream, a);
@@ -500,8 +533,6 @@ void launch_probe(H *h, const ProbePlan &pl, const ProbeArgs &a, int kw, bool ra
         if (radix) launch_probe_mode<4, true>(pl, grid, h->stream, a);
         else launch_probe_mode<4, false>(pl, grid, h->stream, a);
     }
-    h->st.kernel_launches++;
-    h->st.probe_launches++;
 }
 
 int64_t estimate_out_cap(H *h, int64_t n_probe, const ProbePlan &pl) {
@@ -563,6 +594,95 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
             n_null_rows = n - pn;
         }
         const int64_t extra = (pl.mode == PM_OUTER || pl.mode == PM_ANTI) ? n_null_rows : 0;
+        // Dense path (probe.cuh): unique build keys behind the partition pass. The partitioned row-id array becomes the
+        // result's probe-index column as it is; the kernel writes one build index (or NULL) per partitioned row.
+        if (radix && !count_only && h->dense_ok && h->st.duplicate_rows == 0 && pn > 0 && (pl.mode == PM_PAIRS || pl.mode == PM_OUTER)) {
+            void *tr = temps.back();              // the row-id array: owned by the result from here on
+            temps.pop_back();
+            void *ob = nullptr;
+            try {
+                const int64_t rows = pl.mode == PM_OUTER ? n : pn;
+                CU(cudaMallocAsync(&ob, (size_t)rows * 8 + 16, h->stream));
+                CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
+                ProbeArgs a{};
+                a.keys = pkeys;
+                a.rowid = prid;
+                a.n = pn;
+                a.tv = h->view();
+                a.hk = h->hk;
+                a.out_build = (uint64_t *)ob;
+                a.out_probe = (uint32_t *)tr;
+                a.out_cap = (uint64_t)rows;
+                a.visited = (uint32_t *)h->visited.p;
+                a.ctr = h->d_ctr;
+                {
+                    PhaseTimer tm(h, &h->st.ms_probe);
+                    const int grid = grid_for(h, pn, PD_SUPER, h->dense_ctas_per_sm);
+                    if (kw == 8) {
+                        if (pl.mark) probe_dense_kernel<8, true><<<grid, PD_THREADS, 0, h->stream>>>(a);
+                        else probe_dense_kernel<8, false><<<grid, PD_THREADS, 0, h->stream>>>(a);
+                    } else {
+                        if (pl.mark) probe_dense_kernel<4, true><<<grid, PD_THREADS, 0, h->stream>>>(a);
+                        else probe_dense_kernel<4, false><<<grid, PD_THREADS, 0, h->stream>>>(a);
+                    }
+                    h->st.kernel_launches++;
+                    h->st.probe_launches++;
+                    CU(cudaGetLastError());
+                    tm.stop();
+                }
+                CU(cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
+                CU(cudaStreamSynchronize(h->stream));
+                const int64_t misses = (int64_t)h->h_ctr->build_null_out;
+                if (pl.mode == PM_OUTER) {
+                    if (extra > 0) {      // NULL-key probe rows: their row ids already sit at the tail of the row-id array
+                        fill_u64_kernel<<<grid_for(h, extra, 256, 8), 256, 0, h->stream>>>((uint64_t *)ob + pn, extra, ~0ULL);
+                        h->st.kernel_launches++;
+                        CU(cudaGetLastError());
+                        CU(cudaStreamSynchronize(h->stream));
+                    }
+                    *n_build_null = misses + extra;
+                    ro->build_idx = ob;
+                    ro->probe_idx = tr;
+                    free_temps(h, temps);
+                    return n;
+                }
+                if (misses == 0) {
+                    ro->build_idx = ob;
+                    ro->probe_idx = tr;
+                    free_temps(h, temps);
+                    return pn;
+                }
+                // Inner / Left with misses: one compaction pass
+                const int64_t keep = pn - misses;
+                void *ob2 = nullptr, *op2 = nullptr;
+                try {
+                    CU(cudaMallocAsync(&ob2, (size_t)std::max<int64_t>(keep, 1) * 8, h->stream));
+                    CU(cudaMallocAsync(&op2, (size_t)std::max<int64_t>(keep, 1) * 4, h->stream));
+                    CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
+                    PhaseTimer tm(h, &h->st.ms_probe);
+                    compact_pairs_kernel<<<grid_for(h, pn, CP_TILE, 8), CP_THREADS, 0, h->stream>>>((const uint64_t *)ob, (const uint32_t *)tr, (uint64_t)pn,
+                                                                                                    (uint64_t *)ob2, (uint32_t *)op2, &h->d_ctr->out_count);
+                    h->st.kernel_launches++;
+                    CU(cudaGetLastError());
+                    tm.stop();
+                    CU(cudaStreamSynchronize(h->stream));
+                } catch (...) {
+                    if (ob2) cudaFreeAsync(ob2, h->stream);
+                    if (op2) cudaFreeAsync(op2, h->stream);
+                    throw;
+                }
+                cudaFreeAsync(ob, h->stream);
+                cudaFreeAsync(tr, h->stream);
+                ro->build_idx = ob2;
+                ro->probe_idx = op2;
+                free_temps(h, temps);
+                return keep;
+            } catch (...) {
+                if (ob) cudaFreeAsync(ob, h->stream);
+                cudaFreeAsync(tr, h->stream);
+                throw;
+            }
+        }
         for (int attempt = 0; attempt < 3; attempt++) {
             void *ob = nullptr, *op = nullptr;
             if (cap > 0) {
@@ -979,6 +1099,18 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
         cudaDeviceProp prop{};
         CU(cudaGetDeviceProperties(&prop, cfg->device));
         h->sm_count = prop.multiProcessorCount;
+        {
+            int occ = 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, probe_fast_kernel<8, PM_PAIRS, false, true>, PF_THREADS, 0) == cudaSuccess && occ > 0)
+                h->probe_ctas_per_sm = occ;
+            else
+                cudaGetLastError();
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, probe_dense_kernel<8, false>, PD_THREADS, 0) == cudaSuccess && occ > 0)
+                h->dense_ctas_per_sm = occ;
+            else
+                cudaGetLastError();
+            if (const char *e = getenv("B200J_NO_DENSE")) h->dense_ok = atoi(e) == 0;
+        }
         h->l2_bytes = prop.l2CacheSize;
         if (cfg->stream) {
             h->stream = (cudaStream_t)cfg->stream;
@@ -1029,7 +1161,7 @@ int32_t b200j_destroy(b200j_handle *h) {
     for (auto *v : {&h->bkeys, &h->bpayload})
         for (auto &c : *v) { fr(c.values); fr(c.offsets); fr(c.validity); }
     radix_release(h);
-    fr(h->slots); fr(h->zero_slot); fr(h->rowids); fr(h->visited); fr(h->part_base); fr(h->part_mask);
+    fr(h->slots); fr(h->zero_slot); fr(h->rowids); fr(h->visited); fr(h->parts);
     cudaStreamSynchronize(h->stream);
     for (auto &p : h->pinned_cache) { pinned_size(p.p, true); cudaFreeHost(p.p); }
     if (h->d_ctr) cudaFree(h->d_ctr);

@@ -32,18 +32,11 @@ struct HashKeys {
     int32_t  _pad;
 };
 
-// 64x64 -> 128 bit product folded to 64 bits (low ^ high). Schoolbook on 32-bit limbs: four IMAD.WIDE.U32
-// with 64-bit accumulate, no carry chains (every partial sum provably fits 64 bits).
+// 64x64 -> 128 bit product folded to 64 bits (low ^ high). Written as mul.lo ^ mul.hi: ptxas turns the pair into
+// four IMAD.WIDE.U32 plus three carry instructions (9 SASS instructions; a hand-written limb version compiled to 21).
 __host__ __device__ __forceinline__ uint64_t folded_multiply(uint64_t s, uint64_t by) {
 #ifdef __CUDA_ARCH__
-    const uint32_t a0 = (uint32_t)s, a1 = (uint32_t)(s >> 32);
-    const uint32_t b0 = (uint32_t)by, b1 = (uint32_t)(by >> 32);
-    const uint64_t p00 = (uint64_t)a0 * b0;
-    const uint64_t t1  = (uint64_t)a0 * b1 + (p00 >> 32);
-    const uint64_t t2  = (uint64_t)a1 * b0 + (uint32_t)t1;
-    const uint64_t hi  = (uint64_t)a1 * b1 + (t1 >> 32) + (t2 >> 32);
-    const uint64_t lo  = (t2 << 32) | (uint32_t)p00;
-    return lo ^ hi;
+    return (s * by) ^ __umul64hi(s, by);
 #else
     unsigned __int128 r = (unsigned __int128)s * (unsigned __int128)by;
     return (uint64_t)r ^ (uint64_t)(r >> 64);
@@ -114,29 +107,39 @@ struct Counters {
 };
 constexpr size_t COUNTERS_LAUNCH_BYTES = 24;
 
-struct TableView {
-    Slot           *slots;
-    uint64_t        mask;          // direct layout: capacity - 1
-    Slot           *zero_slot;     // the slot of key value 0
-    uint32_t       *rowids;        // runs of duplicate-key rows
-    // radix layout: partition p = hash >> (64 - radix_bits) owns slots [part_base[p], part_base[p] + part_mask[p] + 1)
-    const uint64_t *part_base;
-    const uint32_t *part_mask;
-    int32_t         radix_bits;
-    int32_t         _pad;
+// One radix partition's table: buckets [base, base + nb) of the slot array (bucket = 2 slots = one 32 B sector).
+struct __align__(8) PartEnt {
+    uint32_t base;
+    uint32_t nb;
 };
 
-// hp = top 32 bits of the row hash. Tables never exceed 2^32 slots (build rows < 2^31), so masks are 32-bit.
+struct TableView {
+    Slot           *slots;
+    Slot           *zero_slot;     // the bucket of key value 0
+    uint32_t       *rowids;        // runs of duplicate-key rows
+    const PartEnt  *parts;         // radix layout: partition p = hash >> (64 - radix_bits)
+    uint32_t        nb;            // direct layout: number of buckets
+    int32_t         radix_bits;
+};
+
+// hp = top 32 bits of the row hash. Table sizes are not powers of two (the load factor is what the caller asked
+// for, not what rounding gives): the home bucket is mulhi(low 32 hash bits, nb). Tables never exceed 2^32 buckets.
 template <bool RADIX>
-__device__ __forceinline__ void locate(const TableView &tv, uint32_t hp, uint64_t &base, uint32_t &mask) {
+__device__ __forceinline__ void locate(const TableView &tv, uint32_t hp, uint32_t &base, uint32_t &nb) {
     if (RADIX) {
-        const uint32_t p = hp >> (32 - tv.radix_bits);
-        base = __ldg(tv.part_base + p);
-        mask = __ldg(tv.part_mask + p);
+        const uint2 e = __ldg(reinterpret_cast<const uint2 *>(tv.parts + (hp >> (32 - tv.radix_bits))));
+        base = e.x;
+        nb = e.y;
     } else {
         base = 0;
-        mask = (uint32_t)tv.mask;
+        nb = tv.nb;
     }
+}
+
+__device__ __forceinline__ uint32_t home_bucket(uint64_t h, uint32_t nb) { return __umulhi((uint32_t)h, nb); }
+__device__ __forceinline__ uint32_t next_bucket(uint32_t b, uint32_t nb) { return b + 1u == nb ? 0u : b + 1u; }
+__device__ __forceinline__ Slot *bucket_ptr(const TableView &tv, uint32_t base, uint32_t b) {
+    return tv.slots + 2ull * ((unsigned long long)base + b);
 }
 
 __device__ __forceinline__ Slot load_slot(const Slot *p) {
@@ -258,19 +261,21 @@ template <bool RADIX>
 __device__ __forceinline__ Slot *find_or_claim(const TableView &tv, const HashKeys &hk, uint64_t key, uint32_t &distinct) {
     if (key == 0) return tv.zero_slot;
     const uint64_t h = hash_one(hk, key);
-    uint64_t base;
-    uint32_t mask;
-    locate<RADIX>(tv, (uint32_t)(h >> 32), base, mask);
-    uint32_t i = (uint32_t)h & mask & ~1u;      // probe sequences start at the even slot of the home bucket
+    uint32_t base, nb;
+    locate<RADIX>(tv, (uint32_t)(h >> 32), base, nb);
+    uint32_t b = home_bucket(h, nb);
     for (;;) {
-        Slot *s = tv.slots + base + i;
-        unsigned long long cur = __ldcg(&s->key);
-        if (cur == 0ULL) {
-            cur = atomicCAS(&s->key, 0ULL, (unsigned long long)key);
-            if (cur == 0ULL) { distinct++; return s; }
+        Slot *s = bucket_ptr(tv, base, b);      // slots of a bucket fill in order: even first
+#pragma unroll
+        for (int j = 0; j < 2; j++, s++) {
+            unsigned long long cur = __ldcg(&s->key);
+            if (cur == 0ULL) {
+                cur = atomicCAS(&s->key, 0ULL, (unsigned long long)key);
+                if (cur == 0ULL) { distinct++; return s; }
+            }
+            if (cur == key) return s;
         }
-        if (cur == key) return s;
-        i = (i + 1) & mask;
+        b = next_bucket(b, nb);
     }
 }
 
@@ -504,7 +509,7 @@ __device__ __forceinline__ void probe_tile(const ProbeArgs &a, uint32_t tile, in
 
     // ---- round 0: hash + bucket load of every item before any is consumed (PROBE_ITEMS random 32 B loads in flight).
     // The key value 0 lives in the side bucket (whose key word is 0 as well), so the same compare serves both.
-    uint32_t idx[PROBE_ITEMS], hp[PROBE_ITEMS];
+    uint32_t idx[PROBE_ITEMS], hp[PROBE_ITEMS];               // idx = bucket inside the partition
     uint32_t srow[PROBE_ITEMS], scnt[PROBE_ITEMS];          // the matching slot (scnt == 0: no match)
     uint32_t pending = GUARD ? look : in;
     {
@@ -512,12 +517,11 @@ __device__ __forceinline__ void probe_tile(const ProbeArgs &a, uint32_t tile, in
 #pragma unroll
         for (int q = 0; q < PROBE_ITEMS; q++) {
             const uint64_t h = hash_one(a.hk, key[q]);
-            uint64_t base;
-            uint32_t mask;
+            uint32_t base, nb;
             hp[q] = (uint32_t)(h >> 32);
-            locate<RADIX>(a.tv, hp[q], base, mask);
-            idx[q] = (uint32_t)h & mask & ~1u;
-            const Slot *p = key[q] ? a.tv.slots + base + idx[q] : a.tv.zero_slot;
+            locate<RADIX>(a.tv, hp[q], base, nb);
+            idx[q] = home_bucket(h, nb);
+            const Slot *p = key[q] ? bucket_ptr(a.tv, base, idx[q]) : a.tv.zero_slot;
             k0[q] = v0[q] = k1[q] = v1[q] = 0ULL;
             if (!GUARD || ((pending >> q) & 1u)) load_bucket(p, k0[q], v0[q], k1[q], v1[q]);
         }
@@ -539,13 +543,12 @@ __device__ __forceinline__ void probe_tile(const ProbeArgs &a, uint32_t tile, in
 #pragma unroll
         for (int j = 1; j < PROBE_ITEMS; j++)
             if (q == j) { k = key[j]; i = idx[j]; p = hp[j]; }
-        uint64_t base;
-        uint32_t mask;
-        locate<RADIX>(a.tv, p, base, mask);
+        uint32_t base, nb;
+        locate<RADIX>(a.tv, p, base, nb);
         for (;;) {
-            i = (i + 2u) & mask;
+            i = next_bucket(i, nb);
             unsigned long long k0, v0, k1, v1;
-            load_bucket(a.tv.slots + base + i, k0, v0, k1, v1);
+            load_bucket(bucket_ptr(a.tv, base, i), k0, v0, k1, v1);
             const bool hit0 = k0 == k, hit1 = k1 == k;
             if (hit0 | hit1 | (k0 == 0ULL) | (k1 == 0ULL)) {
                 const unsigned long long v = hit0 ? v0 : ((hit1 && k0 != 0ULL) ? v1 : 0ULL);

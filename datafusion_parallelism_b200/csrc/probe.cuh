@@ -1,0 +1,541 @@
+// probe.cuh — the lean probe kernel (the dominant kernel of the join).
+//
+// Replaces, per probe batch, get_matching_indices[_with_probe] (src/shared/shared.rs:29-81) + Version10Lookup::get_iter
+// (version10/lookup_implementation_3.rs:31-59) + equal_rows_arr (src/shared/datafusion_private.rs:40-80, fused: slots
+// hold key VALUES) + the per-batch index algebra of the eight join types (datafusion_private.rs:85-185).
+//
+// Shape (why it looks like this — ncu of the first version showed 172 thread-instructions per row and 3.2
+// serialised dependent L2 round trips per warp iteration for the ~10 % of lookups whose home bucket is full):
+//   fast path   every thread hashes PF_ITEMS keys and issues PF_ITEMS independent 32 B bucket loads (one sector =
+//               one bucket of two 16 B slots), then resolves each lookup from that single bucket: hit with one
+//               build row, or provable miss (the bucket has a free slot). No loops, no dynamic register indexing.
+//   slow queue  lookups that need a second bucket, and duplicate-key runs, are pushed to a shared-memory queue and
+//               drained densely (one queued lookup per lane) once per super-tile, so stragglers never hold a warp
+//               of finished lookups hostage.
+//   staging     single-row results are compacted into shared memory (ballot positions, one shared atomic per warp)
+//               and flushed with ONE global atomic per super-tile of PF_STAGE rows and fully coalesced stores.
+//   scheduling  super-tiles are handed out by a global counter so the running CTAs sweep the partitioned probe
+//               stream front to back: the one or two partitions' tables being probed stay in L2.
+// Requires 16 B-aligned keys without a validity bitmap (always true for the radix layout, whose partition pass
+// strips NULL keys; the direct layout falls back to probe_kernel in kernels.cuh otherwise).
+#pragma once
+#include "kernels.cuh"
+
+namespace b200j {
+
+constexpr int PF_THREADS = 256;
+constexpr int PF_ITEMS   = 4;
+constexpr int PF_TILE    = PF_THREADS * PF_ITEMS;     // 1024 rows
+constexpr int PF_SUB     = 2;
+constexpr int PF_STAGE   = PF_TILE * PF_SUB;          // 2048 rows per global atomic
+
+struct PFShared {
+    unsigned long long qkey[PF_STAGE];                // slow queue
+    uint32_t           qrow[PF_STAGE];
+    uint32_t           brow[PF_STAGE];                // staged single-row results (0xffffffff = NULL build side)
+    uint32_t           prow[PF_STAGE];
+    unsigned long long gbase;
+    uint32_t           count, qcount, next;
+};
+
+// Copies the duplicate-key runs of one warp's lanes (one run per lane, `mine` lanes only) to the output and/or marks
+// them visited. Short runs are copied by their lane, long runs by the whole warp (coalesced).
+template <int MODE, bool MARK>
+__device__ __forceinline__ void emit_runs(const ProbeArgs &a, bool mine, uint32_t scnt, uint32_t srow, uint32_t prow, int lane) {
+    constexpr uint32_t FULL = 0xffffffffu;
+    constexpr bool emit = (MODE == PM_PAIRS || MODE == PM_OUTER);
+    uint32_t off = 0;
+    unsigned long long gbase = 0;
+    if (emit) {
+        const uint32_t mq = mine ? scnt : 0u;
+        uint32_t incl = mq;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += y; }
+        off = incl - mq;
+        const uint32_t wtot = __shfl_sync(FULL, incl, 31);
+        if (lane == 0) gbase = atomicAdd(&a.ctr->out_count, (unsigned long long)wtot);
+        gbase = __shfl_sync(FULL, gbase, 0);
+    }
+    if (mine && scnt < 32u) {
+        const unsigned long long pos = gbase + off;
+        for (uint32_t k = 0; k < scnt; k++) {
+            const uint32_t br = __ldcg(a.tv.rowids + srow + k);
+            if (emit && pos + k < a.out_cap) {
+                a.out_build[pos + k] = (uint64_t)br;
+                a.out_probe[pos + k] = prow;
+            }
+            if (MARK) mark_visited(a.visited, br);
+        }
+    }
+    uint32_t pend = __ballot_sync(FULL, mine && scnt >= 32u);
+    while (pend) {
+        const int src = __ffs(pend) - 1;
+        pend &= pend - 1;
+        const unsigned long long pos = __shfl_sync(FULL, gbase + off, src);
+        const uint32_t cnt = __shfl_sync(FULL, scnt, src);
+        const uint32_t rb = __shfl_sync(FULL, srow, src);
+        const uint32_t pr = __shfl_sync(FULL, prow, src);
+        for (uint32_t k = lane; k < cnt; k += 32) {
+            const uint32_t br = __ldcg(a.tv.rowids + rb + k);
+            if (emit && pos + k < a.out_cap) {
+                a.out_build[pos + k] = (uint64_t)br;
+                a.out_probe[pos + k] = pr;
+            }
+            if (MARK) mark_visited(a.visited, br);
+        }
+    }
+}
+
+template <int KW, int MODE, bool MARK, bool RADIX>
+__global__ void __launch_bounds__(PF_THREADS) probe_fast_kernel(ProbeArgs a) {
+    constexpr uint32_t FULL = 0xffffffffu;
+    constexpr int PER_VEC = 16 / KW;
+    constexpr int NVEC = PF_ITEMS / PER_VEC;
+    __shared__ PFShared sh;
+    const int t = threadIdx.x, lane = t & 31;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t n = (uint32_t)a.n;
+    const uint32_t n_tiles = (n + PF_TILE - 1) / PF_TILE;
+    const uint32_t n_super = (n_tiles + PF_SUB - 1) / PF_SUB;
+    uint32_t null_build_out = 0;
+
+    if (t == 0) { sh.count = 0; sh.qcount = 0; sh.next = atomicAdd(&a.ctr->next_tile, 1u); }
+    __syncthreads();
+    for (;;) {
+        const uint32_t sup = sh.next;
+        if (sup >= n_super) break;
+#pragma unroll 1
+        for (int sub = 0; sub < PF_SUB; sub++) {
+            const uint32_t tb = (sup * PF_SUB + sub) * (uint32_t)PF_TILE;
+            if (tb >= n) break;
+            // ---- keys + probe row ids of this thread's items
+            uint64_t key[PF_ITEMS];
+            uint32_t prow[PF_ITEMS];
+            bool inb[PF_ITEMS];
+#pragma unroll
+            for (int v = 0; v < NVEC; v++) {
+                const uint32_t r0 = tb + ((uint32_t)v * PF_THREADS + t) * PER_VEC;
+                if (KW == 8) {
+                    const unsigned long long *k64 = reinterpret_cast<const unsigned long long *>(a.keys);
+                    inb[2 * v] = r0 < n;
+                    inb[2 * v + 1] = r0 + 1 < n;
+                    if (inb[2 * v + 1]) {
+                        const ulonglong2 x = __ldcs(reinterpret_cast<const ulonglong2 *>(k64 + r0));
+                        key[2 * v] = x.x; key[2 * v + 1] = x.y;
+                        if (RADIX) { const uint2 r = __ldcs(reinterpret_cast<const uint2 *>(a.rowid + r0)); prow[2 * v] = r.x; prow[2 * v + 1] = r.y; }
+                    } else {
+                        key[2 * v] = inb[2 * v] ? __ldcs(k64 + r0) : 0ULL;
+                        key[2 * v + 1] = 0ULL;
+                        if (RADIX) { prow[2 * v] = inb[2 * v] ? __ldcs(a.rowid + r0) : 0u; prow[2 * v + 1] = 0u; }
+                    }
+                    if (!RADIX) { prow[2 * v] = r0; prow[2 * v + 1] = r0 + 1; }
+                } else {
+                    const uint32_t *k32 = reinterpret_cast<const uint32_t *>(a.keys);
+#pragma unroll
+                    for (int q = 0; q < 4; q++) inb[4 * v + q] = r0 + q < n;
+                    if (inb[4 * v + 3]) {
+                        const uint4 x = __ldcs(reinterpret_cast<const uint4 *>(k32 + r0));
+                        key[4 * v] = x.x; key[4 * v + 1] = x.y; key[4 * v + 2] = x.z; key[4 * v + 3] = x.w;
+                        if (RADIX) {
+                            const uint4 r = __ldcs(reinterpret_cast<const uint4 *>(a.rowid + r0));
+                            prow[4 * v] = r.x; prow[4 * v + 1] = r.y; prow[4 * v + 2] = r.z; prow[4 * v + 3] = r.w;
+                        }
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            key[4 * v + q] = inb[4 * v + q] ? (uint64_t)__ldcs(k32 + r0 + q) : 0ULL;
+                            if (RADIX) prow[4 * v + q] = inb[4 * v + q] ? __ldcs(a.rowid + r0 + q) : 0u;
+                        }
+                    }
+                    if (!RADIX) {
+#pragma unroll
+                        for (int q = 0; q < 4; q++) prow[4 * v + q] = r0 + q;
+                    }
+                }
+            }
+            // ---- hash + one bucket load per item, all in flight before any is consumed
+            unsigned long long k0[PF_ITEMS], v0[PF_ITEMS], k1[PF_ITEMS], v1[PF_ITEMS];
+#pragma unroll
+            for (int q = 0; q < PF_ITEMS; q++) {
+                const uint64_t h = hash_one(a.hk, key[q]);
+                uint32_t base, nb;
+                locate<RADIX>(a.tv, (uint32_t)(h >> 32), base, nb);
+                const Slot *p = key[q] ? bucket_ptr(a.tv, base, home_bucket(h, nb)) : a.tv.zero_slot;
+                load_bucket(p, k0[q], v0[q], k1[q], v1[q]);
+            }
+            // ---- resolve from that bucket: hit, provable miss (bucket has a free slot; slots fill in order, so a free
+            //      slot shows in the odd one), or "needs the slow path" (bucket full without the key, or a run)
+            bool one[PF_ITEMS], slow[PF_ITEMS];
+            uint32_t srow[PF_ITEMS], n_one = 0, n_slow = 0;
+#pragma unroll
+            for (int q = 0; q < PF_ITEMS; q++) {
+                const bool hit0 = k0[q] == key[q], hit1 = k1[q] == key[q];
+                const unsigned long long v = hit0 ? v0[q] : (hit1 ? v1[q] : 0ULL);
+                const uint32_t cnt = (uint32_t)(v >> 32);
+                const bool resolved = hit0 | hit1 | (k1[q] == 0ULL);
+                srow[q] = (uint32_t)v;
+                bool o, s;
+                if (MODE == PM_PAIRS) { o = cnt == 1u; s = !resolved || cnt > 1u; }
+                else if (MODE == PM_OUTER) { o = resolved && cnt <= 1u; s = !resolved || cnt > 1u; if (cnt == 0u) srow[q] = 0xffffffffu; }
+                else if (MODE == PM_SEMI) { o = cnt != 0u; s = !resolved; srow[q] = 0xffffffffu; }
+                else if (MODE == PM_ANTI) { o = resolved && cnt == 0u; s = !resolved; srow[q] = 0xffffffffu; }
+                else { o = false; s = !resolved || cnt > 1u; if (cnt == 1u && inb[q]) mark_visited(a.visited, (uint32_t)v); }
+                one[q] = o && inb[q];
+                slow[q] = s && inb[q];
+                n_one += one[q] ? 1u : 0u;
+                n_slow += slow[q] ? 1u : 0u;
+                if (MARK && MODE != PM_MARK && one[q] && cnt == 1u) mark_visited(a.visited, (uint32_t)v);
+            }
+            // ---- single rows -> shared-memory stage. Every lane writes its rows back to back; the lane's base is the
+            //      warp-exclusive prefix of n_one (0..4), taken from three ballots over its bits.
+            if (MODE != PM_MARK) {
+                const uint32_t b0 = __ballot_sync(FULL, n_one & 1u), b1 = __ballot_sync(FULL, n_one & 2u), b2 = __ballot_sync(FULL, n_one & 4u);
+                const uint32_t wtot = __popc(b0) + 2u * __popc(b1) + 4u * __popc(b2);
+                uint32_t pos = __popc(b0 & lt_mask) + 2u * __popc(b1 & lt_mask) + 4u * __popc(b2 & lt_mask);
+                uint32_t wbase = 0;
+                if (lane == 0 && wtot) wbase = atomicAdd(&sh.count, wtot);
+                pos += __shfl_sync(FULL, wbase, 0);
+#pragma unroll
+                for (int q = 0; q < PF_ITEMS; q++) {
+                    if (!one[q]) continue;
+                    sh.brow[pos] = srow[q];
+                    sh.prow[pos] = prow[q];
+                    pos++;
+                    if (MODE != PM_PAIRS && srow[q] == 0xffffffffu) null_build_out++;
+                }
+            }
+            // ---- everything else -> slow queue (one reservation per lane; ptxas aggregates it per warp)
+            if (n_slow) {
+                uint32_t pos = atomicAdd(&sh.qcount, n_slow);
+#pragma unroll
+                for (int q = 0; q < PF_ITEMS; q++) {
+                    if (!slow[q]) continue;
+                    sh.qkey[pos] = key[q];
+                    sh.qrow[pos] = prow[q];
+                    pos++;
+                }
+            }
+        }
+        __syncthreads();
+        // ---- drain the slow queue: one queued lookup per lane, full probe-sequence walk
+        const uint32_t qn = sh.qcount;
+        for (uint32_t i0 = 0; i0 < qn; i0 += PF_THREADS) {
+            const uint32_t i = i0 + t;
+            const bool act = i < qn;
+            const uint64_t key = act ? sh.qkey[i] : 0ULL;
+            const uint32_t prow = act ? sh.qrow[i] : 0u;
+            uint32_t srow = 0, scnt = 0;
+            if (act) {
+                const uint64_t h = hash_one(a.hk, key);
+                uint32_t base, nb;
+                locate<RADIX>(a.tv, (uint32_t)(h >> 32), base, nb);
+                uint32_t idx = home_bucket(h, nb);
+                const Slot *p = key ? bucket_ptr(a.tv, base, idx) : a.tv.zero_slot;
+                for (;;) {
+                    unsigned long long k0, v0, k1, v1;
+                    load_bucket(p, k0, v0, k1, v1);
+                    const bool hit0 = k0 == key, hit1 = k1 == key;
+                    if (hit0 | hit1 | (k1 == 0ULL)) {
+                        const unsigned long long v = hit0 ? v0 : (hit1 ? v1 : 0ULL);
+                        srow = (uint32_t)v;
+                        scnt = (uint32_t)(v >> 32);
+                        break;
+                    }
+                    idx = next_bucket(idx, nb);
+                    p = bucket_ptr(a.tv, base, idx);
+                }
+            }
+            const bool found = act && scnt != 0u;
+            bool o = false, multi = false;
+            uint32_t sr = srow;
+            if (MODE == PM_PAIRS) { o = found && scnt == 1u; multi = found && scnt > 1u; }
+            else if (MODE == PM_OUTER) { o = act && scnt <= 1u; multi = found && scnt > 1u; if (!found) sr = 0xffffffffu; }
+            else if (MODE == PM_SEMI) { o = found; sr = 0xffffffffu; }
+            else if (MODE == PM_ANTI) { o = act && !found; sr = 0xffffffffu; }
+            else { multi = found && scnt > 1u; if (found && scnt == 1u) mark_visited(a.visited, srow); }
+            if (MODE != PM_MARK) {
+                const uint32_t b = __ballot_sync(FULL, o);
+                uint32_t wbase = 0;
+                if (lane == 0 && b) wbase = atomicAdd(&sh.count, (uint32_t)__popc(b));
+                wbase = __shfl_sync(FULL, wbase, 0);
+                if (o) {
+                    const uint32_t pos = wbase + __popc(b & lt_mask);
+                    sh.brow[pos] = sr;
+                    sh.prow[pos] = prow;
+                    if (MODE != PM_PAIRS && sr == 0xffffffffu) null_build_out++;
+                    if (MARK && sr != 0xffffffffu) mark_visited(a.visited, sr);
+                }
+            }
+            if (MODE == PM_PAIRS || MODE == PM_OUTER || MARK) {
+                if (__any_sync(FULL, multi)) emit_runs<MODE, MARK>(a, multi, scnt, srow, prow, lane);
+            }
+        }
+        __syncthreads();
+        // ---- flush: one global atomic per super-tile, then fully coalesced streaming stores
+        const uint32_t cnt = sh.count;
+        if (t == 0) sh.gbase = cnt ? atomicAdd(&a.ctr->out_count, (unsigned long long)cnt) : 0ULL;
+        __syncthreads();
+        const unsigned long long gbase = sh.gbase;
+        if (gbase + cnt <= a.out_cap) {
+            if (a.out_build)
+                for (uint32_t i = t; i < cnt; i += PF_THREADS) {
+                    const uint32_t br = sh.brow[i];
+                    __stcs(reinterpret_cast<unsigned long long *>(a.out_build) + gbase + i, br == 0xffffffffu ? ~0ULL : (unsigned long long)br);
+                }
+            for (uint32_t i = t; i < cnt; i += PF_THREADS) __stcs(a.out_probe + gbase + i, sh.prow[i]);
+        } else {
+            for (uint32_t i = t; i < cnt; i += PF_THREADS) {
+                if (gbase + i >= a.out_cap) break;
+                const uint32_t br = sh.brow[i];
+                if (a.out_build) a.out_build[gbase + i] = br == 0xffffffffu ? ~0ULL : (uint64_t)br;
+                a.out_probe[gbase + i] = sh.prow[i];
+            }
+        }
+        __syncthreads();
+        if (t == 0) { sh.count = 0; sh.qcount = 0; sh.next = atomicAdd(&a.ctr->next_tile, 1u); }
+        __syncthreads();
+    }
+    if (MODE == PM_OUTER || MODE == PM_SEMI || MODE == PM_ANTI) {
+        const unsigned long long z = warp_sum_u32(null_build_out);
+        if ((t & 31) == 0 && z) atomicAdd(&a.ctr->build_null_out, z);
+    }
+}
+
+
+// =====================================================================================================================
+// Dense probe (radix layout, build keys unique): the output is NOT compacted. Row i of the partitioned probe stream
+// writes out_build[i] = its build row or NULL; the partition pass's row-id array IS the probe-index column of the
+// result, so this kernel neither reads nor writes it: 8 B key in, 8 B build index out per probe row (16 B/row of HBM
+// traffic instead of 24 B), no shared-memory staging, no block barrier on the hot path, no output atomics.
+// Inner / Left joins whose batch had misses get one compaction pass afterwards (compact_pairs_kernel); Right / Full
+// want the NULL rows anyway. A foreign-key probe (every probe row matches once) is exactly dense.
+//
+// Lookups whose home bucket is full without the key (~10 % at load factor 0.5) go to a warp-private shared-memory
+// queue and are drained 32 at a time — one per lane, two buckets fetched per round — so the warp's other 31 lanes
+// never wait for one lane's probe sequence.
+// =====================================================================================================================
+constexpr int PD_THREADS = 256;
+constexpr int PD_WARPS   = PD_THREADS / 32;
+constexpr int PD_ITEMS   = 4;
+constexpr int PD_WTILE   = 32 * PD_ITEMS;             // rows per warp iteration
+constexpr int PD_SUPER   = 16384;                     // rows per CTA claim (one global atomic)
+constexpr int PD_QCAP    = 32 + PD_WTILE;             // a queue holds < 32 entries between iterations
+
+struct PDShared {
+    unsigned long long qkey[PD_WARPS][PD_QCAP];
+    uint32_t           qidx[PD_WARPS][PD_QCAP];
+    uint32_t           next;
+};
+
+template <bool MARK>
+__device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long long *qkey, uint32_t *qidx, uint32_t first, uint32_t cnt,
+                                            int lane, uint32_t &misses) {
+    // entries [first, first + cnt) of the warp's queue, one per lane (cnt <= 32)
+    const bool act = (uint32_t)lane < cnt;
+    const uint64_t key = act ? qkey[first + lane] : 0ULL;
+    const uint32_t oi = act ? qidx[first + lane] : 0u;
+    if (act) {
+        const uint64_t h = hash_one(a.hk, key);
+        uint32_t base, nb;
+        locate<true>(a.tv, (uint32_t)(h >> 32), base, nb);
+        uint32_t b = next_bucket(home_bucket(h, nb), nb);          // the home bucket was full without the key
+        unsigned long long res = ~0ULL;
+        for (;;) {
+            const uint32_t b2 = next_bucket(b, nb);
+            unsigned long long k0, v0, k1, v1, k2, v2, k3, v3;
+            load_bucket(bucket_ptr(a.tv, base, b), k0, v0, k1, v1);
+            load_bucket(bucket_ptr(a.tv, base, b2), k2, v2, k3, v3);
+            if (k0 == key) { res = (uint32_t)v0; break; }
+            if (k1 == key) { res = (uint32_t)v1; break; }
+            if (k1 == 0ULL) break;
+            if (k2 == key) { res = (uint32_t)v2; break; }
+            if (k3 == key) { res = (uint32_t)v3; break; }
+            if (k3 == 0ULL) break;
+            b = next_bucket(b2, nb);
+        }
+        a.out_build[oi] = res;
+        if (res == ~0ULL) misses++;
+        else if (MARK) mark_visited(a.visited, (uint32_t)res);
+    }
+}
+
+template <int KW, bool MARK>
+__global__ void __launch_bounds__(PD_THREADS) probe_dense_kernel(ProbeArgs a) {
+    constexpr int PER_VEC = 16 / KW;
+    constexpr int NVEC = PD_ITEMS / PER_VEC;
+    constexpr uint32_t FULL = 0xffffffffu;
+    __shared__ PDShared sh;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const uint32_t n = (uint32_t)a.n;
+    const uint32_t n_super = (uint32_t)(((uint64_t)n + PD_SUPER - 1) / PD_SUPER);
+    unsigned long long *qkey = sh.qkey[warp];
+    uint32_t *qidx = sh.qidx[warp];
+    uint32_t qn = 0;                                      // warp-uniform
+    uint32_t misses = 0;
+    for (;;) {
+        __syncthreads();
+        if (t == 0) sh.next = atomicAdd(&a.ctr->next_tile, 1u);
+        __syncthreads();
+        const uint32_t sup = sh.next;
+        if (sup >= n_super) break;
+        const uint32_t s0 = sup * (uint32_t)PD_SUPER;
+        const uint32_t s1 = (uint32_t)min((uint64_t)s0 + PD_SUPER, (uint64_t)n);
+        for (uint32_t wb = s0 + (uint32_t)warp * PD_WTILE; wb < s1; wb += PD_WARPS * PD_WTILE) {
+            // ---- keys: lane takes NVEC vectors, 32 vectors apart
+            uint64_t key[PD_ITEMS];
+            uint32_t idx0[NVEC];
+            bool inb[PD_ITEMS];
+#pragma unroll
+            for (int v = 0; v < NVEC; v++) {
+                const uint32_t r0 = wb + ((uint32_t)v * 32u + lane) * PER_VEC;
+                idx0[v] = r0;
+                if (KW == 8) {
+                    const unsigned long long *k64 = reinterpret_cast<const unsigned long long *>(a.keys);
+                    inb[2 * v] = r0 < s1;
+                    inb[2 * v + 1] = r0 + 1 < s1;
+                    if (inb[2 * v + 1]) {
+                        const ulonglong2 x = __ldcs(reinterpret_cast<const ulonglong2 *>(k64 + r0));
+                        key[2 * v] = x.x; key[2 * v + 1] = x.y;
+                    } else {
+                        key[2 * v] = inb[2 * v] ? __ldcs(k64 + r0) : 0ULL;
+                        key[2 * v + 1] = 0ULL;
+                    }
+                } else {
+                    const uint32_t *k32 = reinterpret_cast<const uint32_t *>(a.keys);
+#pragma unroll
+                    for (int q = 0; q < 4; q++) inb[4 * v + q] = r0 + q < s1;
+                    if (inb[4 * v + 3]) {
+                        const uint4 x = __ldcs(reinterpret_cast<const uint4 *>(k32 + r0));
+                        key[4 * v] = x.x; key[4 * v + 1] = x.y; key[4 * v + 2] = x.z; key[4 * v + 3] = x.w;
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < 4; q++) key[4 * v + q] = inb[4 * v + q] ? (uint64_t)__ldcs(k32 + r0 + q) : 0ULL;
+                    }
+                }
+            }
+            // ---- one bucket load per item, all in flight
+            unsigned long long k0[PD_ITEMS], v0[PD_ITEMS], k1[PD_ITEMS], v1[PD_ITEMS];
+#pragma unroll
+            for (int q = 0; q < PD_ITEMS; q++) {
+                const uint64_t h = hash_one(a.hk, key[q]);
+                uint32_t base, nb;
+                locate<true>(a.tv, (uint32_t)(h >> 32), base, nb);
+                const Slot *p = key[q] ? bucket_ptr(a.tv, base, home_bucket(h, nb)) : a.tv.zero_slot;
+                load_bucket(p, k0[q], v0[q], k1[q], v1[q]);
+            }
+            // ---- resolve; unresolved lookups go to the warp's queue
+            unsigned long long res[PD_ITEMS];
+            bool pend[PD_ITEMS];
+            uint32_t n_pend = 0;
+#pragma unroll
+            for (int q = 0; q < PD_ITEMS; q++) {
+                const bool hit0 = k0[q] == key[q], hit1 = k1[q] == key[q];
+                const unsigned long long v = hit0 ? v0[q] : v1[q];
+                const bool hit = (hit0 | hit1) && (uint32_t)(v >> 32) != 0u;      // count 0: the zero-key side bucket when key 0 is absent
+                pend[q] = inb[q] && !(hit0 | hit1) && k1[q] != 0ULL;
+                res[q] = hit ? (unsigned long long)(uint32_t)v : ~0ULL;
+                n_pend += pend[q] ? 1u : 0u;
+                if (inb[q] && !pend[q]) {
+                    if (!hit) misses++;
+                    else if (MARK) mark_visited(a.visited, (uint32_t)v);
+                }
+            }
+            // ---- dense store: 16 B per pair of rows when neither is pending
+#pragma unroll
+            for (int v = 0; v < NVEC; v++) {
+                if (KW == 8) {
+                    unsigned long long *o = reinterpret_cast<unsigned long long *>(a.out_build) + idx0[v];
+                    if (inb[2 * v + 1] && !pend[2 * v] && !pend[2 * v + 1]) {
+                        __stcs(reinterpret_cast<ulonglong2 *>(o), make_ulonglong2(res[2 * v], res[2 * v + 1]));
+                    } else {
+                        if (inb[2 * v] && !pend[2 * v]) __stcs(o, res[2 * v]);
+                        if (inb[2 * v + 1] && !pend[2 * v + 1]) __stcs(o + 1, res[2 * v + 1]);
+                    }
+                } else {
+                    unsigned long long *o = reinterpret_cast<unsigned long long *>(a.out_build) + idx0[v];
+                    const bool all = inb[4 * v + 3] && !pend[4 * v] && !pend[4 * v + 1] && !pend[4 * v + 2] && !pend[4 * v + 3];
+                    if (all) {
+                        __stcs(reinterpret_cast<ulonglong2 *>(o), make_ulonglong2(res[4 * v], res[4 * v + 1]));
+                        __stcs(reinterpret_cast<ulonglong2 *>(o) + 1, make_ulonglong2(res[4 * v + 2], res[4 * v + 3]));
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < 4; q++)
+                            if (inb[4 * v + q] && !pend[4 * v + q]) __stcs(o + q, res[4 * v + q]);
+                    }
+                }
+            }
+            // ---- queue the pending ones (warp-private: ballots, no atomics)
+            const uint32_t b0 = __ballot_sync(FULL, n_pend & 1u), b1 = __ballot_sync(FULL, n_pend & 2u), b2 = __ballot_sync(FULL, n_pend & 4u);
+            const uint32_t wtot = __popc(b0) + 2u * __popc(b1) + 4u * __popc(b2);
+            if (wtot) {
+                const uint32_t lt = (1u << lane) - 1u;
+                uint32_t pos = qn + __popc(b0 & lt) + 2u * __popc(b1 & lt) + 4u * __popc(b2 & lt);
+#pragma unroll
+                for (int q = 0; q < PD_ITEMS; q++) {
+                    if (!pend[q]) continue;
+                    qkey[pos] = key[q];
+                    qidx[pos] = idx0[q / PER_VEC] + (q % PER_VEC);
+                    pos++;
+                }
+                qn += wtot;
+                __syncwarp();
+                while (qn >= 32u) {
+                    qn -= 32u;
+                    dense_drain<MARK>(a, qkey, qidx, qn, 32u, lane, misses);
+                    __syncwarp();
+                }
+            }
+        }
+    }
+    if (qn) dense_drain<MARK>(a, qkey, qidx, 0u, qn, lane, misses);
+    const unsigned long long z = warp_sum_u32(misses);
+    if (lane == 0 && z) atomicAdd(&a.ctr->build_null_out, z);
+}
+
+// Compaction of a dense result: keeps the rows whose build index is not NULL. One global atomic per tile.
+constexpr int CP_THREADS = 256;
+constexpr int CP_ITEMS   = 8;
+constexpr int CP_TILE    = CP_THREADS * CP_ITEMS;
+__global__ void __launch_bounds__(CP_THREADS) compact_pairs_kernel(const uint64_t *__restrict__ in_build, const uint32_t *__restrict__ in_probe,
+                                                                   uint64_t n, uint64_t *__restrict__ out_build, uint32_t *__restrict__ out_probe,
+                                                                   unsigned long long *counter) {
+    __shared__ uint32_t s_w[CP_THREADS / 32];
+    __shared__ unsigned long long s_base;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const uint64_t n_tiles = (n + CP_TILE - 1) / CP_TILE;
+    for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const uint64_t i0 = tile * CP_TILE + (uint64_t)t * CP_ITEMS;      // CP_ITEMS consecutive rows per thread
+        uint64_t b[CP_ITEMS];
+        uint32_t p[CP_ITEMS], c = 0;
+#pragma unroll
+        for (int q = 0; q < CP_ITEMS; q++) {
+            const bool in = i0 + q < n;
+            b[q] = in ? __ldcs(reinterpret_cast<const unsigned long long *>(in_build) + i0 + q) : ~0ULL;
+            p[q] = in ? __ldcs(in_probe + i0 + q) : 0u;
+            c += b[q] != ~0ULL ? 1u : 0u;
+        }
+        uint32_t incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+        if (lane == 31) s_w[warp] = incl;
+        __syncthreads();
+        if (t == 0) {
+            unsigned long long tot = 0;
+            for (int i = 0; i < CP_THREADS / 32; i++) tot += s_w[i];
+            s_base = tot ? atomicAdd(counter, tot) : 0ULL;
+        }
+        __syncthreads();
+        unsigned long long pos = s_base + incl - c;
+        for (int i = 0; i < warp; i++) pos += s_w[i];
+#pragma unroll
+        for (int q = 0; q < CP_ITEMS; q++) {
+            if (b[q] == ~0ULL) continue;
+            out_build[pos] = b[q];
+            out_probe[pos] = p[q];
+            pos++;
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace b200j

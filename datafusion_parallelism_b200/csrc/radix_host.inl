@@ -1,28 +1,104 @@
 // radix_host.inl — host side of the radix-partitioned layout (included inside b200join.cu's anonymous namespace).
 
-void radix_ensure(H *h, int bits) {
+void radix_ensure(H *h, int n_bins1, int grid) {
     RadixScratch &rs = h->rscratch;
-    if (rs.alloc_bits >= bits) return;
-    if (rs.hist) cudaFreeAsync(rs.hist, h->stream);
-    if (rs.off) cudaFreeAsync(rs.off, h->stream);
-    if (rs.cursor) cudaFreeAsync(rs.cursor, h->stream);
-    if (rs.h_off) cudaFreeHost(rs.h_off);
-    rs = RadixScratch{};
-    const size_t bytes = (((size_t)1 << bits) + 2) * 8;
-    CU(cudaMallocAsync((void **)&rs.hist, bytes, h->stream));
-    CU(cudaMallocAsync((void **)&rs.off, bytes, h->stream));
-    CU(cudaMallocAsync((void **)&rs.cursor, bytes, h->stream));
-    CU(cudaHostAlloc((void **)&rs.h_off, bytes, cudaHostAllocDefault));
-    rs.alloc_bits = bits;
+    const size_t need = (size_t)n_bins1 * (size_t)grid;
+    if (rs.hist_cap >= need && rs.bins_cap >= n_bins1) return;
+    const size_t cap = std::max(need, rs.hist_cap);
+    const int bcap = std::max(n_bins1, rs.bins_cap);
+    radix_release(h);
+    CU(cudaMallocAsync((void **)&rs.cta_hist, cap * 4, h->stream));
+    CU(cudaMallocAsync((void **)&rs.bin_tot, (size_t)(bcap + 1) * 4, h->stream));
+    CU(cudaMallocAsync((void **)&rs.bin_base, (size_t)(bcap + 1) * 4, h->stream));
+    CU(cudaMallocAsync((void **)&rs.off, (size_t)(bcap + 1) * 8, h->stream));
+    CU(cudaHostAlloc((void **)&rs.h_off, (size_t)(bcap + 1) * 8, cudaHostAllocDefault));
+    rs.hist_cap = cap;
+    rs.bins_cap = bcap;
 }
 
 void radix_release(H *h) {
     RadixScratch &rs = h->rscratch;
-    if (rs.hist) cudaFreeAsync(rs.hist, h->stream);
+    if (rs.cta_hist) cudaFreeAsync(rs.cta_hist, h->stream);
+    if (rs.bin_tot) cudaFreeAsync(rs.bin_tot, h->stream);
+    if (rs.bin_base) cudaFreeAsync(rs.bin_base, h->stream);
     if (rs.off) cudaFreeAsync(rs.off, h->stream);
-    if (rs.cursor) cudaFreeAsync(rs.cursor, h->stream);
     if (rs.h_off) cudaFreeHost(rs.h_off);
     rs = RadixScratch{};
+}
+
+struct PartPlan {
+    PartArgs a{};
+    int grid = 1;
+    int kw = 8;
+    bool dest = false;
+};
+
+// Plans the partitioning of `n` keys into n_bins bins (+ the NULL bin): radix mode (n_dest == 0, n_bins = 1 << bits)
+// or destination mode (n_bins = n_dest ranks).
+PartPlan part_plan(H *h, const void *keys, const uint8_t *validity, int64_t bit_offset, int kw, int64_t n, int bits, int n_dest) {
+    REQUIRE(n >= 0 && n < 0xffff0000LL, B200J_ERR_UNSUPPORTED, "more than 2^32 - 2^16 rows in one partitioning pass");
+    PartPlan pl;
+    pl.kw = kw;
+    pl.dest = n_dest > 0;
+    PartArgs &a = pl.a;
+    a.keys = keys;
+    a.validity = validity;
+    a.bit_offset = bit_offset;
+    a.n = (uint32_t)n;
+    a.mis = (uint32_t)(((uintptr_t)keys & 15) / (uintptr_t)kw);
+    a.radix_bits = bits;
+    a.n_dest = n_dest;
+    a.n_bins = pl.dest ? (uint32_t)n_dest : (1u << bits);
+    a.hk = h->hk;
+    const int64_t n_tiles = (n + a.mis + SC_TILE - 1) / SC_TILE;
+    pl.grid = (int)std::max<int64_t>(1, std::min<int64_t>(n_tiles, (int64_t)h->sm_count * 2));
+    a.tiles_per_cta = (uint32_t)((n_tiles + pl.grid - 1) / pl.grid);
+    radix_ensure(h, (int)a.n_bins + 1, pl.grid);
+    a.cta_hist = h->rscratch.cta_hist;
+    a.bin_base = h->rscratch.bin_base;
+    return pl;
+}
+
+// Histogram + scans. On return (stream synchronised) h->rscratch.h_off[0..n_bins+1] holds the bin offsets
+// (h_off[n_bins] = number of non-NULL keys, h_off[n_bins + 1] = n) and, in radix mode, bin_base = those offsets.
+void part_hist(H *h, PartPlan &pl, bool sync) {
+    RadixScratch &rs = h->rscratch;
+    const PartArgs &a = pl.a;
+    const int P1 = (int)a.n_bins + 1;
+    const size_t hist_smem = (size_t)P1 * 4;
+    if (pl.kw == 8) {
+        if (pl.dest) part_hist_kernel<8, true><<<pl.grid, RP_THREADS, hist_smem, h->stream>>>(a);
+        else part_hist_kernel<8, false><<<pl.grid, RP_THREADS, hist_smem, h->stream>>>(a);
+    } else {
+        if (pl.dest) part_hist_kernel<4, true><<<pl.grid, RP_THREADS, hist_smem, h->stream>>>(a);
+        else part_hist_kernel<4, false><<<pl.grid, RP_THREADS, hist_smem, h->stream>>>(a);
+    }
+    part_scan_rows_kernel<<<P1, 256, 0, h->stream>>>(rs.cta_hist, (uint32_t)pl.grid, rs.bin_tot);
+    part_scan_bins_kernel<<<1, 1024, 0, h->stream>>>(rs.bin_tot, P1, rs.off, pl.dest ? nullptr : rs.bin_base);
+    h->st.kernel_launches += 3;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(rs.h_off, rs.off, (size_t)(P1 + 1) * 8, cudaMemcpyDeviceToHost, h->stream));
+    if (sync) CU(cudaStreamSynchronize(h->stream));
+}
+
+template <int KW, bool DEST>
+void part_scatter_launch(H *h, PartPlan &pl) {
+    static bool attr = false;
+    if (!attr) {
+        CU(cudaFuncSetAttribute(part_scatter_kernel<KW, DEST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        attr = true;
+    }
+    part_scatter_kernel<KW, DEST><<<pl.grid, SC_THREADS, part_scatter_smem(KW, pl.a.n_bins), h->stream>>>(pl.a);
+}
+
+void part_scatter(H *h, PartPlan &pl) {
+    if (pl.kw == 8) {
+        if (pl.dest) part_scatter_launch<8, true>(h, pl); else part_scatter_launch<8, false>(h, pl);
+    } else {
+        if (pl.dest) part_scatter_launch<4, true>(h, pl); else part_scatter_launch<4, false>(h, pl);
+    }
+    h->st.kernel_launches++;
+    CU(cudaGetLastError());
 }
 
 // Partition `n` keys on the top `bits` hash bits into out_keys / out_rid (both sized for n rows).
@@ -30,51 +106,22 @@ void radix_release(H *h) {
 // (h_off[P] = number of non-NULL keys, h_off[P+1] = n).
 void radix_partition(H *h, const void *keys, const uint8_t *validity, int64_t bit_offset, int kw, int64_t n, int bits,
                      void *out_keys, uint32_t *out_rid, double *ms_acc) {
-    radix_ensure(h, bits);
-    RadixScratch &rs = h->rscratch;
-    const int P1 = (1 << bits) + 1;
     PhaseTimer tm(h, ms_acc);
-    CU(cudaMemsetAsync(rs.hist, 0, (size_t)(P1 + 1) * 8, h->stream));
-    PartArgs a{};
-    a.keys = keys;
-    a.validity = validity;
-    a.bit_offset = bit_offset;
-    a.n = n;
-    a.mis = (int)(((uintptr_t)keys & 15) / (uintptr_t)kw);
-    a.radix_bits = bits;
-    a.hk = h->hk;
-    a.hist = rs.hist;
-    a.cursor = rs.cursor;
-    a.out_keys = out_keys;
-    a.out_rid = out_rid;
-    const int grid = grid_for(h, n + a.mis, RP_TILE, 2);
-    const size_t hist_smem = (size_t)P1 * 4;
-    const size_t sc_smem = radix_scatter_smem(kw, bits);
-    if (kw == 8) {
-        static bool attr8 = false;
-        if (!attr8) { CU(cudaFuncSetAttribute(radix_scatter_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); attr8 = true; }
-        radix_hist_kernel<8><<<grid, RP_THREADS, hist_smem, h->stream>>>(a);
-        radix_scan_kernel<<<1, 1024, 0, h->stream>>>(rs.hist, P1, rs.off, rs.cursor);
-        radix_scatter_kernel<8><<<grid, RP_THREADS, sc_smem, h->stream>>>(a);
-    } else {
-        static bool attr4 = false;
-        if (!attr4) { CU(cudaFuncSetAttribute(radix_scatter_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); attr4 = true; }
-        radix_hist_kernel<4><<<grid, RP_THREADS, hist_smem, h->stream>>>(a);
-        radix_scan_kernel<<<1, 1024, 0, h->stream>>>(rs.hist, P1, rs.off, rs.cursor);
-        radix_scatter_kernel<4><<<grid, RP_THREADS, sc_smem, h->stream>>>(a);
-    }
-    h->st.kernel_launches += 3;
-    CU(cudaGetLastError());
-    CU(cudaMemcpyAsync(rs.h_off, rs.off, (size_t)(P1 + 1) * 8, cudaMemcpyDeviceToHost, h->stream));
+    PartPlan pl = part_plan(h, keys, validity, bit_offset, kw, n, bits, 0);
+    pl.a.out_keys = out_keys;
+    pl.a.out_rid = out_rid;
+    part_hist(h, pl, false);
+    part_scatter(h, pl);
     tm.stop();
     CU(cudaStreamSynchronize(h->stream));
 }
 
 int choose_radix_bits(H *h, int64_t n, float lf, int64_t budget) {
     if (h->cfg.radix_bits > 0) return h->cfg.radix_bits;
-    // aim at per-partition tables of a quarter of the L2 budget: two or three of them are live at any time
-    double table_bytes = 16.0 * (double)n / lf * 1.5;      // power-of-two rounding of every partition's table
-    const double target = std::max<double>((double)budget / 4.0, 1 << 20);
+    // aim at per-partition tables of half the L2 budget (a quarter of L2): measured on B200, the probe kernel runs at the
+    // same speed from 2^7 to 2^10 partitions at 100 M build rows, while the partition pass gets slower with every bit
+    double table_bytes = 16.0 * (double)n / lf;
+    const double target = std::max<double>((double)budget / 2.0, 1 << 20);
     int bits = 1;
     while (bits < RP_MAX_BITS && table_bytes / (double)(1 << bits) > target) bits++;
     return bits;
@@ -96,26 +143,23 @@ void radix_build(H *h, const void *keys, const uint8_t *validity, int kw, int64_
         const int64_t n_valid = (int64_t)off[P];
 
         PhaseTimer tm(h, &h->st.ms_build_insert);
-        std::vector<uint64_t> base(P);
-        std::vector<uint32_t> mask(P);
-        uint64_t total = 0;
+        std::vector<PartEnt> parts(P);
+        uint64_t total_buckets = 0;
         for (int p = 0; p < P; p++) {
             const uint64_t cnt = off[p + 1] - off[p];
-            uint64_t cap = 16;
-            while ((double)cap * lf < (double)cnt) cap <<= 1;
-            REQUIRE(cap - 1 <= 0xffffffffULL, B200J_ERR_UNSUPPORTED, "partition table too large");
-            base[p] = total;
-            mask[p] = (uint32_t)(cap - 1);
-            total += cap;
+            const uint64_t nb = table_slots_for((int64_t)cnt, lf) / 2;
+            REQUIRE(total_buckets + nb <= 0xffffffffULL, B200J_ERR_UNSUPPORTED, "table too large");
+            parts[p].base = (uint32_t)total_buckets;
+            parts[p].nb = (uint32_t)nb;
+            total_buckets += nb;
         }
+        const uint64_t total = total_buckets * 2;
         h->n_slots = total;
         dev_alloc(h, h->slots, (size_t)total * sizeof(Slot));
         CU(cudaMemsetAsync(h->slots.p, 0, (size_t)total * sizeof(Slot), h->stream));
-        dev_alloc(h, h->part_base, (size_t)P * 8);
-        dev_alloc(h, h->part_mask, (size_t)P * 4);
-        CU(cudaMemcpyAsync(h->part_base.p, base.data(), (size_t)P * 8, cudaMemcpyHostToDevice, h->stream));
-        CU(cudaMemcpyAsync(h->part_mask.p, mask.data(), (size_t)P * 4, cudaMemcpyHostToDevice, h->stream));
-        CU(cudaStreamSynchronize(h->stream));      // base/mask are stack vectors
+        dev_alloc(h, h->parts, (size_t)P * sizeof(PartEnt));
+        CU(cudaMemcpyAsync(h->parts.p, parts.data(), (size_t)P * sizeof(PartEnt), cudaMemcpyHostToDevice, h->stream));
+        CU(cudaStreamSynchronize(h->stream));      // parts is a stack vector
 
         BuildArgs a{};
         a.hk = h->hk;
