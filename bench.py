@@ -41,6 +41,7 @@ NVLINK_GBS = 770.0                 # measured peer copy per direction (B200_PROF
 B_BUILD = 24                       # 8 key read + 16 slot write
 B_PROBE = 36                       # 8 key read + 16 slot read + 12 pair write
 B_PROBE_KERNEL_RADIX = 24          # the probe KERNEL of the radix layout: 12 (key, row id) read + 12 pair write, table in L2
+B_PROBE_DENSE = 16                 # dense probe kernel: 8 key read + 8 build-index write (row ids come from the partition pass)
 B_PARTITION = 28                   # histogram 8 read + scatter 8 read + 12 write
 
 
@@ -289,11 +290,19 @@ def run_b200(args):
     radix = st["layout"] == 2
     probe_launch_ms = st["ms_probe"] / max(1, st["probe_launches"])
     rows_per_launch = n_probe * K / max(1, st["probe_launches"]) if world == 1 else st["probe_rows"] / max(1, st["probe_launches"])
-    bpt = B_PROBE_KERNEL_RADIX if radix else B_PROBE
-    achieved = rows_per_launch * bpt / (probe_launch_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "probe_kernel<8,PM_PAIRS,false,%s>" % ("true" if radix else "false"),
+    dense = st.get("dense_probe_launches", 0) == st["probe_launches"] and st["probe_launches"] > 0
+    if dense:        # 8 B key in + 8 B build index out per row, plus ONE pass over the table per launch (it is L2-resident per partition)
+        bpt, kname, table_b = B_PROBE_DENSE, "probe_dense_kernel<8,false>", st["table_bytes"]
+    elif radix:
+        bpt, kname, table_b = B_PROBE_KERNEL_RADIX, "probe_fast_kernel<8,PM_PAIRS,false,true>", st["table_bytes"]
+    else:
+        bpt, kname, table_b = B_PROBE, "probe_fast_kernel<8,PM_PAIRS,false,false>", 0
+    bytes_per_launch = rows_per_launch * bpt + table_b
+    achieved = bytes_per_launch / (probe_launch_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": kname,
                 "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s", "frac": achieved / hbm_gbs, "traffic": None,
-                "peak_source": peak_src, "bytes_per_tuple": bpt, "tuples_per_launch": rows_per_launch, "ms_per_launch": probe_launch_ms}
+                "peak_source": peak_src, "bytes_per_tuple": bpt, "table_bytes_per_launch": table_b,
+                "tuples_per_launch": rows_per_launch, "ms_per_launch": probe_launch_ms}
     tr = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr):
         try:

@@ -82,7 +82,8 @@ class Stats(C.Structure):
                 ("radix_bits", C.c_int32), ("_pad", C.c_int32), ("probe_rows", C.c_int64), ("result_rows", C.c_int64),
                 ("ms_build_copy", C.c_double), ("ms_build_partition", C.c_double), ("ms_build_insert", C.c_double),
                 ("ms_probe_partition", C.c_double), ("ms_probe", C.c_double), ("ms_gather", C.c_double),
-                ("probe_launches", C.c_int64), ("kernel_launches", C.c_int64), ("probe_retries", C.c_int64)]
+                ("probe_launches", C.c_int64), ("kernel_launches", C.c_int64), ("probe_retries", C.c_int64),
+                ("dense_probe_launches", C.c_int64), ("compact_launches", C.c_int64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_ if not n.startswith("_") and n != "struct_size"}

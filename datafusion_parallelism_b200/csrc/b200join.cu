@@ -15,6 +15,7 @@
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
+#include <ctime>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -81,6 +82,12 @@ struct ResultOwner {
     int32_t mem = B200J_MEM_DEVICE;
 };
 
+struct CachedBlock {
+    void *p = nullptr;
+    size_t cap = 0;
+    bool in_use = false;
+};
+
 struct PinnedBuf {
     void *p = nullptr;
     size_t cap = 0;
@@ -126,6 +133,8 @@ struct b200j_handle {
     Counters *h_ctr = nullptr;         // pinned mirror
 
     std::vector<PinnedBuf> pinned_cache;
+    std::vector<CachedBlock> blocks;   // device buffers >= 1 MiB, reused across calls (see big_alloc)
+    size_t blocks_free_bytes = 0;
     b200j_stats st{};
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 
@@ -153,13 +162,77 @@ void radix_release(H *h);
 void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, uint32_t want, b200j_gathered *out);
 void do_gathered_release(H *h, b200j_gathered *g);
 
+// Device allocation for everything a join touches. Small blocks go to the stream-ordered pool. Large ones are cached in
+// the handle: measured on B200, cudaMallocAsync of an 8 GB block cost 6.7 ms per probe call even with the pool's
+// release threshold at its maximum, more than the probe kernel itself. All work of a handle is ordered on one stream, so
+// a block freed here may be handed out again at once.
+constexpr size_t BIG_BLOCK = (size_t)1 << 20;
+constexpr size_t BIG_CACHE_LIMIT = (size_t)96 << 30;
+
+template <typename T>
+cudaError_t big_alloc(H *h, T **out, size_t bytes) {
+    *out = nullptr;
+    if (bytes < BIG_BLOCK) return cudaMallocAsync((void **)out, bytes, h->stream);
+    int best = -1;
+    for (size_t i = 0; i < h->blocks.size(); i++) {
+        const CachedBlock &b = h->blocks[i];
+        if (!b.in_use && b.cap >= bytes && b.cap <= bytes + bytes / 4 && (best < 0 || b.cap < h->blocks[best].cap)) best = (int)i;
+    }
+    if (best >= 0) {
+        h->blocks[best].in_use = true;
+        h->blocks_free_bytes -= h->blocks[best].cap;
+        *out = (T *)h->blocks[best].p;
+        return cudaSuccess;
+    }
+    void *p = nullptr;
+    cudaError_t e = cudaMallocAsync(&p, bytes, h->stream);
+    if (e != cudaSuccess) {
+        // make room: drop every cached free block and try once more
+        cudaGetLastError();
+        for (size_t i = 0; i < h->blocks.size();) {
+            if (!h->blocks[i].in_use) {
+                cudaFreeAsync(h->blocks[i].p, h->stream);
+                h->blocks_free_bytes -= h->blocks[i].cap;
+                h->blocks.erase(h->blocks.begin() + i);
+            } else i++;
+        }
+        cudaStreamSynchronize(h->stream);
+        e = cudaMallocAsync(&p, bytes, h->stream);
+        if (e != cudaSuccess) return e;
+    }
+    h->blocks.push_back(CachedBlock{p, bytes, true});
+    *out = (T *)p;
+    return cudaSuccess;
+}
+
+cudaError_t big_free(H *h, void *p) {
+    if (!p) return cudaSuccess;
+    for (size_t i = 0; i < h->blocks.size(); i++)
+        if (h->blocks[i].p == p) {
+            h->blocks[i].in_use = false;
+            h->blocks_free_bytes += h->blocks[i].cap;
+            // bounded cache: give the largest free blocks back to the pool beyond the limit
+            while (h->blocks_free_bytes > BIG_CACHE_LIMIT) {
+                int big = -1;
+                for (size_t j = 0; j < h->blocks.size(); j++)
+                    if (!h->blocks[j].in_use && (big < 0 || h->blocks[j].cap > h->blocks[big].cap)) big = (int)j;
+                if (big < 0) break;
+                cudaFreeAsync(h->blocks[big].p, h->stream);
+                h->blocks_free_bytes -= h->blocks[big].cap;
+                h->blocks.erase(h->blocks.begin() + big);
+            }
+            return cudaSuccess;
+        }
+    return cudaFreeAsync(p, h->stream);
+}
+
 void dev_alloc(H *h, DevBuf &b, size_t bytes) {
     if (bytes <= b.cap && b.p) return;
-    if (b.p) CU(cudaFreeAsync(b.p, h->stream));
+    if (b.p) CU(big_free(h, b.p));
     b.p = nullptr;
     b.cap = 0;
     bytes = std::max<size_t>(bytes, 256);
-    CU(cudaMallocAsync(&b.p, bytes, h->stream));
+    CU(big_alloc(h, &b.p, bytes));
     b.cap = bytes;
 }
 
@@ -168,15 +241,15 @@ void dev_grow(H *h, DevBuf &b, size_t bytes, size_t keep) {
     if (bytes <= b.cap && b.p) return;
     size_t ncap = std::max<size_t>(std::max<size_t>(bytes, b.cap + b.cap / 2), 256);
     void *np = nullptr;
-    CU(cudaMallocAsync(&np, ncap, h->stream));
+    CU(big_alloc(h, &np, ncap));
     if (b.p && keep) CU(cudaMemcpyAsync(np, b.p, keep, cudaMemcpyDeviceToDevice, h->stream));
-    if (b.p) CU(cudaFreeAsync(b.p, h->stream));
+    if (b.p) CU(big_free(h, b.p));
     b.p = np;
     b.cap = ncap;
 }
 
 void dev_free(H *h, DevBuf &b) {
-    if (b.p) cudaFreeAsync(b.p, h->stream);
+    if (b.p) big_free(h, b.p);
     b.p = nullptr;
     b.cap = 0;
 }
@@ -238,6 +311,14 @@ int grid_for(H *h, int64_t work_items, int per_block, int blocks_per_sm) {
     return (int)std::max<int64_t>(1, std::min<int64_t>(blocks, cap));
 }
 
+struct Trace {                 // B200J_TRACE=1: wall-clock trace of the host side of a call (stderr)
+    bool on;
+    double t0;
+    static double now() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; }
+    Trace() : on(getenv("B200J_TRACE") != nullptr), t0(now()) {}
+    void mark(const char *what) { if (on) { const double t = now(); fprintf(stderr, "[b200j] %-28s +%.3f ms\n", what, t - t0); t0 = t; } }
+};
+
 struct PhaseTimer {            // CUDA-event timing of one phase on the handle's stream
     H *h;
     double *acc;
@@ -281,7 +362,7 @@ const uint8_t *stage_validity(H *h, const b200j_column &c, int64_t n_rows, int m
     }
     const int64_t first = c.bit_offset >> 3, last = (c.bit_offset + n_rows + 7) >> 3;
     void *d = nullptr;
-    CU(cudaMallocAsync(&d, (size_t)(last - first) + 16, h->stream));
+    CU(big_alloc(h, &d, (size_t)(last - first) + 16));
     temps.push_back(d);
     CU(cudaMemcpyAsync(d, c.validity + first, (size_t)(last - first), cudaMemcpyHostToDevice, h->stream));
     *bit_off = c.bit_offset & 7;
@@ -289,7 +370,7 @@ const uint8_t *stage_validity(H *h, const b200j_column &c, int64_t n_rows, int m
 }
 
 void free_temps(H *h, std::vector<void *> &temps) {
-    for (void *p : temps) cudaFreeAsync(p, h->stream);
+    for (void *p : temps) big_free(h, p);
     temps.clear();
 }
 
@@ -321,7 +402,7 @@ void store_append(H *h, ColStore &cs, const b200j_column &c, int64_t n_old, int6
         const int32_t *d_off = c.offsets;
         if (mem == B200J_MEM_HOST) {
             void *d = nullptr;
-            CU(cudaMallocAsync(&d, (size_t)(n_add + 1) * 4, h->stream));
+            CU(big_alloc(h, &d, (size_t)(n_add + 1) * 4));
             temps.push_back(d);
             CU(cudaMemcpyAsync(d, c.offsets, (size_t)(n_add + 1) * 4, cudaMemcpyHostToDevice, h->stream));
             d_off = (const int32_t *)d;
@@ -554,8 +635,8 @@ void fill_result(b200j_result *out, ResultOwner *ro, int64_t n, int mem) {
 void release_owner(H *h, ResultOwner *ro) {
     if (!ro) return;
     if (ro->mem == B200J_MEM_DEVICE) {
-        if (ro->build_idx) cudaFreeAsync(ro->build_idx, h->stream);
-        if (ro->probe_idx) cudaFreeAsync(ro->probe_idx, h->stream);
+        if (ro->build_idx) big_free(h, ro->build_idx);
+        if (ro->probe_idx) big_free(h, ro->probe_idx);
     } else {
         pinned_give(h, ro->build_idx);
         pinned_give(h, ro->probe_idx);
@@ -573,6 +654,7 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
     *n_build_null = 0;
     if (n == 0) return 0;
     std::vector<void *> temps;
+    Trace tr_;
     try {
         // what the probe kernel reads: the caller's keys (direct) or the partitioned (key, row id) stream (radix)
         const void *pkeys = d_keys;
@@ -581,11 +663,13 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
         const uint32_t *prid = nullptr;
         if (radix) {
             void *tk = nullptr, *tr = nullptr;
-            CU(cudaMallocAsync(&tk, (size_t)n * kw + 16, h->stream));
+            CU(big_alloc(h, &tk, (size_t)n * kw + 16));
             temps.push_back(tk);
-            CU(cudaMallocAsync(&tr, (size_t)n * 4 + 16, h->stream));
+            CU(big_alloc(h, &tr, (size_t)n * 4 + 16));
             temps.push_back(tr);
+            tr_.mark("alloc partition buffers");
             radix_partition(h, d_keys, d_validity, bit_offset, kw, n, h->radix_bits, tk, (uint32_t *)tr, &h->st.ms_probe_partition);
+            tr_.mark("radix_partition");
             pkeys = tk;
             pvalid = nullptr;
             pboff = 0;
@@ -602,7 +686,8 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
             void *ob = nullptr;
             try {
                 const int64_t rows = pl.mode == PM_OUTER ? n : pn;
-                CU(cudaMallocAsync(&ob, (size_t)rows * 8 + 16, h->stream));
+                CU(big_alloc(h, &ob, (size_t)rows * 8 + 16));
+                tr_.mark("alloc out_build");
                 CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
                 ProbeArgs a{};
                 a.keys = pkeys;
@@ -627,12 +712,14 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
                     }
                     h->st.kernel_launches++;
                     h->st.probe_launches++;
+                    h->st.dense_probe_launches++;
                     CU(cudaGetLastError());
                     tm.stop();
                 }
                 CU(cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
                 CU(cudaStreamSynchronize(h->stream));
                 const int64_t misses = (int64_t)h->h_ctr->build_null_out;
+                tr_.mark("dense probe + counters");
                 if (pl.mode == PM_OUTER) {
                     if (extra > 0) {      // NULL-key probe rows: their row ids already sit at the tail of the row-id array
                         fill_u64_kernel<<<grid_for(h, extra, 256, 8), 256, 0, h->stream>>>((uint64_t *)ob + pn, extra, ~0ULL);
@@ -650,44 +737,46 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
                     ro->build_idx = ob;
                     ro->probe_idx = tr;
                     free_temps(h, temps);
+                    tr_.mark("free temps");
                     return pn;
                 }
                 // Inner / Left with misses: one compaction pass
                 const int64_t keep = pn - misses;
                 void *ob2 = nullptr, *op2 = nullptr;
                 try {
-                    CU(cudaMallocAsync(&ob2, (size_t)std::max<int64_t>(keep, 1) * 8, h->stream));
-                    CU(cudaMallocAsync(&op2, (size_t)std::max<int64_t>(keep, 1) * 4, h->stream));
+                    CU(big_alloc(h, &ob2, (size_t)std::max<int64_t>(keep, 1) * 8));
+                    CU(big_alloc(h, &op2, (size_t)std::max<int64_t>(keep, 1) * 4));
                     CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
                     PhaseTimer tm(h, &h->st.ms_probe);
                     compact_pairs_kernel<<<grid_for(h, pn, CP_TILE, 8), CP_THREADS, 0, h->stream>>>((const uint64_t *)ob, (const uint32_t *)tr, (uint64_t)pn,
                                                                                                     (uint64_t *)ob2, (uint32_t *)op2, &h->d_ctr->out_count);
                     h->st.kernel_launches++;
+                    h->st.compact_launches++;
                     CU(cudaGetLastError());
                     tm.stop();
                     CU(cudaStreamSynchronize(h->stream));
                 } catch (...) {
-                    if (ob2) cudaFreeAsync(ob2, h->stream);
-                    if (op2) cudaFreeAsync(op2, h->stream);
+                    if (ob2) big_free(h, ob2);
+                    if (op2) big_free(h, op2);
                     throw;
                 }
-                cudaFreeAsync(ob, h->stream);
-                cudaFreeAsync(tr, h->stream);
+                big_free(h, ob);
+                big_free(h, tr);
                 ro->build_idx = ob2;
                 ro->probe_idx = op2;
                 free_temps(h, temps);
                 return keep;
             } catch (...) {
-                if (ob) cudaFreeAsync(ob, h->stream);
-                cudaFreeAsync(tr, h->stream);
+                if (ob) big_free(h, ob);
+                big_free(h, tr);
                 throw;
             }
         }
         for (int attempt = 0; attempt < 3; attempt++) {
             void *ob = nullptr, *op = nullptr;
             if (cap > 0) {
-                if (want_build) CU(cudaMallocAsync(&ob, (size_t)cap * 8, h->stream));
-                CU(cudaMallocAsync(&op, (size_t)cap * 4, h->stream));
+                if (want_build) CU(big_alloc(h, &ob, (size_t)cap * 8));
+                CU(big_alloc(h, &op, (size_t)cap * 4));
             }
             CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
             ProbeArgs a{};
@@ -729,8 +818,8 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
             }
             // the pair buffer was too small (duplicate keys): the kernel counted everything, run again with room.
             // Marking is idempotent, so the re-run is safe for the visited bitmap.
-            if (ob) cudaFreeAsync(ob, h->stream);
-            if (op) cudaFreeAsync(op, h->stream);
+            if (ob) big_free(h, ob);
+            if (op) big_free(h, op);
             cap = total + extra;
             h->st.probe_retries++;
         }
@@ -752,8 +841,8 @@ void move_result_to_host(H *h, ResultOwner *ro, int64_t n) {
         CU(cudaMemcpyAsync(hp, ro->probe_idx, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
     }
     CU(cudaStreamSynchronize(h->stream));
-    if (ro->build_idx) cudaFreeAsync(ro->build_idx, h->stream);
-    if (ro->probe_idx) cudaFreeAsync(ro->probe_idx, h->stream);
+    if (ro->build_idx) big_free(h, ro->build_idx);
+    if (ro->probe_idx) big_free(h, ro->probe_idx);
     ro->build_idx = hb;
     ro->probe_idx = hp;
     ro->mem = B200J_MEM_HOST;
@@ -780,7 +869,7 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
         } else {
             const b200j_column &kc = b->keys[0];
             void *dk = nullptr;
-            CU(cudaMallocAsync(&dk, (size_t)n * kw + 16, h->stream));
+            CU(big_alloc(h, &dk, (size_t)n * kw + 16));
             temps.push_back(dk);
             CU(cudaMemcpyAsync(dk, kc.values, (size_t)n * kw, cudaMemcpyHostToDevice, h->stream));
             int64_t boff = 0;
@@ -788,8 +877,8 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
             total = probe_device(h, dk, dv, boff, n, pl, count_only, ro, &n_bnull);
         }
         if (count_only) {
-            if (ro->build_idx) cudaFreeAsync(ro->build_idx, h->stream);
-            if (ro->probe_idx) cudaFreeAsync(ro->probe_idx, h->stream);
+            if (ro->build_idx) big_free(h, ro->build_idx);
+            if (ro->probe_idx) big_free(h, ro->probe_idx);
             ro->build_idx = ro->probe_idx = nullptr;
         } else if (want & B200J_OUT_HOST) {
             move_result_to_host(h, ro, total);
@@ -813,8 +902,8 @@ int64_t select_bits(H *h, const uint32_t *bm, int64_t n, bool want_set, void **o
     if (out32) *out32 = nullptr;
     if (n == 0) return 0;
     void *o64 = nullptr, *o32 = nullptr;
-    if (out64) CU(cudaMallocAsync(&o64, (size_t)n * 8, h->stream));
-    if (out32) CU(cudaMallocAsync(&o32, (size_t)n * 4, h->stream));
+    if (out64) CU(big_alloc(h, &o64, (size_t)n * 8));
+    if (out32) CU(big_alloc(h, &o32, (size_t)n * 4));
     CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
     bitmap_select_kernel<<<grid_for(h, (n + 31) / 32, 256, 8), 256, 0, h->stream>>>(bm, n, want_set ? 1 : 0, (uint64_t *)o64, (uint32_t *)o32,
                                                                                      (uint64_t)n, &h->d_ctr->out_count);
@@ -830,12 +919,12 @@ int64_t select_bits(H *h, const uint32_t *bm, int64_t n, bool want_set, void **o
 void fill_null_side(H *h, ResultOwner *ro, int64_t n, bool null_build, bool null_probe) {
     if (n == 0) return;
     if (null_build && !ro->build_idx) {
-        CU(cudaMallocAsync(&ro->build_idx, (size_t)n * 8, h->stream));
+        CU(big_alloc(h, &ro->build_idx, (size_t)n * 8));
         fill_u64_kernel<<<grid_for(h, n, 256, 8), 256, 0, h->stream>>>((uint64_t *)ro->build_idx, n, ~0ULL);
         h->st.kernel_launches++;
     }
     if (null_probe && !ro->probe_idx) {
-        CU(cudaMallocAsync(&ro->probe_idx, (size_t)n * 4, h->stream));
+        CU(big_alloc(h, &ro->probe_idx, (size_t)n * 4));
         fill_u32_kernel<<<grid_for(h, n, 256, 8), 256, 0, h->stream>>>((uint32_t *)ro->probe_idx, n, 0xffffffffu);
         h->st.kernel_launches++;
     }
@@ -861,7 +950,7 @@ void do_probe_finish(H *h, int32_t partition, uint32_t want, b200j_result *out) 
             if (!(want & B200J_OUT_COUNT_ONLY)) fill_null_side(h, ro, n, false, true);
         }
         if (want & B200J_OUT_COUNT_ONLY) {
-            if (ro->build_idx) cudaFreeAsync(ro->build_idx, h->stream);
+            if (ro->build_idx) big_free(h, ro->build_idx);
             ro->build_idx = nullptr;
         } else if (want & B200J_OUT_HOST) {
             move_result_to_host(h, ro, n);
@@ -894,9 +983,9 @@ void do_apply_pairs(H *h, int32_t partition, int64_t n_probe_rows, int32_t mem, 
         const uint32_t *dp = probe_idx;
         if (mem == B200J_MEM_HOST && n_pairs > 0) {
             void *a = nullptr, *b = nullptr;
-            CU(cudaMallocAsync(&a, (size_t)n_pairs * 8, h->stream));
+            CU(big_alloc(h, &a, (size_t)n_pairs * 8));
             temps.push_back(a);
-            CU(cudaMallocAsync(&b, (size_t)n_pairs * 4, h->stream));
+            CU(big_alloc(h, &b, (size_t)n_pairs * 4));
             temps.push_back(b);
             CU(cudaMemcpyAsync(a, build_idx, (size_t)n_pairs * 8, cudaMemcpyHostToDevice, h->stream));
             CU(cudaMemcpyAsync(b, probe_idx, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, h->stream));
@@ -907,7 +996,7 @@ void do_apply_pairs(H *h, int32_t partition, int64_t n_probe_rows, int32_t mem, 
         if (need_seen && n_probe_rows > 0) {
             void *s = nullptr;
             const size_t sb = (size_t)((n_probe_rows + 31) / 32 + 1) * 4;
-            CU(cudaMallocAsync(&s, sb, h->stream));
+            CU(big_alloc(h, &s, sb));
             temps.push_back(s);
             CU(cudaMemsetAsync(s, 0, sb, h->stream));
             seen = (uint32_t *)s;
@@ -926,8 +1015,8 @@ void do_apply_pairs(H *h, int32_t partition, int64_t n_probe_rows, int32_t mem, 
         const int64_t n_keep = keep_pairs ? n_pairs : 0;
         const int64_t n = n_keep + n_extra;
         if (n > 0 && !(want & B200J_OUT_COUNT_ONLY)) {
-            CU(cudaMallocAsync(&ro->build_idx, (size_t)n * 8, h->stream));
-            CU(cudaMallocAsync(&ro->probe_idx, (size_t)n * 4, h->stream));
+            CU(big_alloc(h, &ro->build_idx, (size_t)n * 8));
+            CU(big_alloc(h, &ro->probe_idx, (size_t)n * 4));
             if (n_keep) {
                 CU(cudaMemcpyAsync(ro->build_idx, db, (size_t)n_keep * 8, cudaMemcpyDeviceToDevice, h->stream));
                 CU(cudaMemcpyAsync(ro->probe_idx, dp, (size_t)n_keep * 4, cudaMemcpyDeviceToDevice, h->stream));
@@ -972,7 +1061,7 @@ void do_hash_keys(H *h, const b200j_batch *b, uint64_t *out) {
                 kc.c[i].bit_offset = b->keys[i].bit_offset;
             } else {
                 void *d = nullptr;
-                CU(cudaMallocAsync(&d, (size_t)n * w, h->stream));
+                CU(big_alloc(h, &d, (size_t)n * w));
                 temps.push_back(d);
                 CU(cudaMemcpyAsync(d, b->keys[i].values, (size_t)n * w, cudaMemcpyHostToDevice, h->stream));
                 kc.c[i].values = d;
@@ -984,7 +1073,7 @@ void do_hash_keys(H *h, const b200j_batch *b, uint64_t *out) {
         uint64_t *d_out = out;
         if (b->mem == B200J_MEM_HOST) {
             void *d = nullptr;
-            CU(cudaMallocAsync(&d, (size_t)n * 8, h->stream));
+            CU(big_alloc(h, &d, (size_t)n * 8));
             temps.push_back(d);
             d_out = (uint64_t *)d;
         }
@@ -1157,11 +1246,14 @@ int32_t b200j_destroy(b200j_handle *h) {
     if (!h) return B200J_OK;
     cudaSetDevice(h->cfg.device);
     cudaStreamSynchronize(h->stream);
-    auto fr = [&](DevBuf &b) { if (b.p) cudaFreeAsync(b.p, h->stream); b.p = nullptr; };
+    auto fr = [&](DevBuf &b) { if (b.p) big_free(h, b.p); b.p = nullptr; };
     for (auto *v : {&h->bkeys, &h->bpayload})
         for (auto &c : *v) { fr(c.values); fr(c.offsets); fr(c.validity); }
     radix_release(h);
     fr(h->slots); fr(h->zero_slot); fr(h->rowids); fr(h->visited); fr(h->parts);
+    cudaStreamSynchronize(h->stream);
+    for (auto &b : h->blocks) cudaFreeAsync(b.p, h->stream);
+    h->blocks.clear();
     cudaStreamSynchronize(h->stream);
     for (auto &p : h->pinned_cache) { pinned_size(p.p, true); cudaFreeHost(p.p); }
     if (h->d_ctr) cudaFree(h->d_ctr);
@@ -1194,6 +1286,7 @@ int32_t b200j_reset_stats(b200j_handle *h) {
     h->st.ms_build_copy = h->st.ms_build_partition = h->st.ms_build_insert = 0;
     h->st.ms_probe_partition = h->st.ms_probe = h->st.ms_gather = 0;
     h->st.probe_launches = h->st.kernel_launches = h->st.probe_retries = 0;
+    h->st.dense_probe_launches = h->st.compact_launches = 0;
     return B200J_OK;
 }
 

@@ -7,10 +7,10 @@ void radix_ensure(H *h, int n_bins1, int grid) {
     const size_t cap = std::max(need, rs.hist_cap);
     const int bcap = std::max(n_bins1, rs.bins_cap);
     radix_release(h);
-    CU(cudaMallocAsync((void **)&rs.cta_hist, cap * 4, h->stream));
-    CU(cudaMallocAsync((void **)&rs.bin_tot, (size_t)(bcap + 1) * 4, h->stream));
-    CU(cudaMallocAsync((void **)&rs.bin_base, (size_t)(bcap + 1) * 4, h->stream));
-    CU(cudaMallocAsync((void **)&rs.off, (size_t)(bcap + 1) * 8, h->stream));
+    CU(big_alloc(h, (void **)&rs.cta_hist, cap * 4));
+    CU(big_alloc(h, (void **)&rs.bin_tot, (size_t)(bcap + 1) * 4));
+    CU(big_alloc(h, (void **)&rs.bin_base, (size_t)(bcap + 1) * 4));
+    CU(big_alloc(h, (void **)&rs.off, (size_t)(bcap + 1) * 8));
     CU(cudaHostAlloc((void **)&rs.h_off, (size_t)(bcap + 1) * 8, cudaHostAllocDefault));
     rs.hist_cap = cap;
     rs.bins_cap = bcap;
@@ -18,10 +18,10 @@ void radix_ensure(H *h, int n_bins1, int grid) {
 
 void radix_release(H *h) {
     RadixScratch &rs = h->rscratch;
-    if (rs.cta_hist) cudaFreeAsync(rs.cta_hist, h->stream);
-    if (rs.bin_tot) cudaFreeAsync(rs.bin_tot, h->stream);
-    if (rs.bin_base) cudaFreeAsync(rs.bin_base, h->stream);
-    if (rs.off) cudaFreeAsync(rs.off, h->stream);
+    if (rs.cta_hist) big_free(h, rs.cta_hist);
+    if (rs.bin_tot) big_free(h, rs.bin_tot);
+    if (rs.bin_base) big_free(h, rs.bin_base);
+    if (rs.off) big_free(h, rs.off);
     if (rs.h_off) cudaFreeHost(rs.h_off);
     rs = RadixScratch{};
 }
@@ -134,9 +134,9 @@ void radix_build(H *h, const void *keys, const uint8_t *validity, int kw, int64_
     void *pk = nullptr, *prid = nullptr;
     std::vector<void *> temps;
     try {
-        CU(cudaMallocAsync(&pk, (size_t)n * kw + 16, h->stream));
+        CU(big_alloc(h, &pk, (size_t)n * kw + 16));
         temps.push_back(pk);
-        CU(cudaMallocAsync(&prid, (size_t)n * 4 + 16, h->stream));
+        CU(big_alloc(h, &prid, (size_t)n * 4 + 16));
         temps.push_back(prid);
         radix_partition(h, keys, validity, 0, kw, n, bits, pk, (uint32_t *)prid, &h->st.ms_build_partition);
         const unsigned long long *off = h->rscratch.h_off;

@@ -192,6 +192,10 @@ typedef struct {
     int64_t  probe_launches;          /* launches of the dominant probe kernel                        */
     int64_t  kernel_launches;         /* all kernel launches of this handle                           */
     int64_t  probe_retries;           /* probe kernels re-run because the pair buffer was too small   */
+    int64_t  dense_probe_launches;    /* probe launches that took the dense path (unique build keys behind the
+                                         partition pass: 8 B key in, 8 B build index out per row, the partitioned
+                                         row-id array is the result's probe-index column)               */
+    int64_t  compact_launches;        /* dense results with misses compacted afterwards (Inner / Left)  */
 } b200j_stats;
 
 /* ---- lifecycle ------------------------------------------------------------------------------- */
