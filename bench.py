@@ -363,14 +363,42 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
     steps = max(1, min(args.e2e_steps, args.steps))
     checksum = 0
 
+    if world > 1:
+        # N > 1: the distributed join takes device batches; the host<->device copies are explicit here and inside the timed region
+        bdev = torch.empty_like(bk)
+        pdev = torch.empty(min(chunk, n_probe), dtype=torch.int64, device=dev)
+        out_b = torch.empty(int(min(chunk, n_probe) * 1.3) + 4096, dtype=torch.int64).pin_memory()
+        out_p = torch.empty(int(min(chunk, n_probe) * 1.3) + 4096, dtype=torch.int32).pin_memory()
+        hb_t, hp_t = torch.from_numpy(hb.array), torch.from_numpy(hp.array)
+
     def step_host():
+        if world > 1:
+            with torch.cuda.stream(join.stream):
+                return step_host_inner()
+        return step_host_inner()
+
+    def step_host_inner():
         nonlocal checksum
         join.reset()
-        join.build_push(0, [hb.array])
+        if world > 1:
+            bdev.copy_(hb_t, non_blocking=True)
+            join.build_push(0, [bdev])
+        else:
+            join.build_push(0, [hb.array])
         join.build_finish(0)
         tot = 0
         for lo in range(0, n_probe, chunk):
-            r = join.probe_batch(0, [hp.array[lo:lo + chunk]], want=d.OUT_PAIRS | d.OUT_HOST)
+            if world > 1:
+                m = min(chunk, n_probe - lo)
+                pdev[:m].copy_(hp_t[lo:lo + m], non_blocking=True)
+                r = join.probe_batch(0, [pdev[:m]], want=d.OUT_PAIRS)
+                b_, p_ = r.device_arrays()
+                if r.n:
+                    out_b[:r.n].copy_(torch.as_tensor(b_, device=dev), non_blocking=True)
+                    out_p[:r.n].copy_(torch.as_tensor(p_, device=dev), non_blocking=True)
+                    torch.cuda.synchronize()
+            else:
+                r = join.probe_batch(0, [hp.array[lo:lo + chunk]], want=d.OUT_PAIRS | d.OUT_HOST)
             tot += r.n
             r.release()
         return tot

@@ -83,7 +83,7 @@ class Stats(C.Structure):
                 ("ms_build_copy", C.c_double), ("ms_build_partition", C.c_double), ("ms_build_insert", C.c_double),
                 ("ms_probe_partition", C.c_double), ("ms_probe", C.c_double), ("ms_gather", C.c_double),
                 ("probe_launches", C.c_int64), ("kernel_launches", C.c_int64), ("probe_retries", C.c_int64),
-                ("dense_probe_launches", C.c_int64), ("compact_launches", C.c_int64)]
+                ("dense_probe_launches", C.c_int64), ("compact_launches", C.c_int64), ("ms_exchange_partition", C.c_double)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_ if not n.startswith("_") and n != "struct_size"}
@@ -110,6 +110,12 @@ SIGNATURES = {
     "b200j_gather": (C.c_int32, [C.c_void_p, C.POINTER(Result), C.POINTER(Batch), C.c_uint32, C.POINTER(Gathered)]),
     "b200j_gathered_release": (C.c_int32, [C.c_void_p, C.POINTER(Gathered)]),
     "b200j_hash_keys": (C.c_int32, [C.c_void_p, C.POINTER(Batch), C.c_void_p]),
+    "b200j_shuffle_count": (C.c_int32, [C.c_void_p, C.POINTER(Batch), C.c_int32, C.POINTER(C.c_int64)]),
+    "b200j_shuffle_scatter": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.c_uint32]),
+    "b200j_ipc_alloc": (C.c_int32, [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]),
+    "b200j_ipc_open": (C.c_int32, [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p)]),
+    "b200j_ipc_close": (C.c_int32, [C.c_void_p, C.c_void_p]),
+    "b200j_ipc_free": (C.c_int32, [C.c_void_p, C.c_void_p]),
     "b200j_host_alloc": (C.c_int32, [C.c_size_t, C.POINTER(C.c_void_p)]),
     "b200j_host_free": (C.c_int32, [C.c_void_p]),
 }

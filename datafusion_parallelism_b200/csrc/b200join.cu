@@ -88,6 +88,13 @@ struct CachedBlock {
     bool in_use = false;
 };
 
+struct PartPlan {            // one planned partitioning pass (radix_host.inl)
+    PartArgs a{};
+    int grid = 1;
+    int kw = 8;
+    bool dest = false;
+};
+
 struct PinnedBuf {
     void *p = nullptr;
     size_t cap = 0;
@@ -129,6 +136,9 @@ struct b200j_handle {
     DevBuf visited;
     DevBuf parts;                      // radix layout: PartEnt per partition
     RadixScratch rscratch;
+    bool shuffle_armed = false;        // b200j_shuffle_count done, b200j_shuffle_scatter pending
+    PartPlan shuffle_plan;
+    int64_t shuffle_n = 0;
     Counters *d_ctr = nullptr;
     Counters *h_ctr = nullptr;         // pinned mirror
 
@@ -1089,6 +1099,9 @@ void do_hash_keys(H *h, const b200j_batch *b, uint64_t *out) {
     }
 }
 
+void do_shuffle_count(H *h, const b200j_batch *b, int32_t n_dest, int64_t *counts);
+void do_shuffle_scatter(H *h, int32_t n_dest, void *const *dest_keys, uint32_t *const *dest_rowid, const int64_t *dest_offset, uint32_t rowid_base);
+
 template <typename F>
 int32_t guarded(b200j_handle *h, F &&f) {
     if (!h) {
@@ -1287,6 +1300,7 @@ int32_t b200j_reset_stats(b200j_handle *h) {
     h->st.ms_probe_partition = h->st.ms_probe = h->st.ms_gather = 0;
     h->st.probe_launches = h->st.kernel_launches = h->st.probe_retries = 0;
     h->st.dense_probe_launches = h->st.compact_launches = 0;
+    h->st.ms_exchange_partition = 0;
     return B200J_OK;
 }
 
@@ -1342,6 +1356,44 @@ int32_t b200j_gathered_release(b200j_handle *h, b200j_gathered *g) {
 }
 int32_t b200j_hash_keys(b200j_handle *h, const b200j_batch *batch, uint64_t *out) {
     return guarded(h, [&] { do_hash_keys(h, batch, out); });
+}
+
+int32_t b200j_shuffle_count(b200j_handle *h, const b200j_batch *batch, int32_t n_dest, int64_t *counts) {
+    return guarded(h, [&] { do_shuffle_count(h, batch, n_dest, counts); });
+}
+int32_t b200j_shuffle_scatter(b200j_handle *h, int32_t n_dest, void *const *dest_keys, uint32_t *const *dest_rowid, const int64_t *dest_offset,
+                              uint32_t rowid_base) {
+    return guarded(h, [&] { do_shuffle_scatter(h, n_dest, dest_keys, dest_rowid, dest_offset, rowid_base); });
+}
+int32_t b200j_ipc_alloc(b200j_handle *h, size_t bytes, void **ptr, uint8_t *handle_out) {
+    return guarded(h, [&] {
+        REQUIRE(ptr && handle_out, B200J_ERR_INVALID, "b200j_ipc_alloc: NULL argument");
+        static_assert(sizeof(cudaIpcMemHandle_t) == B200J_IPC_HANDLE_BYTES, "cudaIpcMemHandle_t is 64 bytes");
+        *ptr = nullptr;
+        CU(cudaMalloc(ptr, std::max<size_t>(bytes, 256)));      // legacy IPC needs cudaMalloc memory, not the stream-ordered pool
+        cudaIpcMemHandle_t ih;
+        cudaError_t e = cudaIpcGetMemHandle(&ih, *ptr);
+        if (e != cudaSuccess) {
+            cudaFree(*ptr);
+            *ptr = nullptr;
+            CU(e);
+        }
+        memcpy(handle_out, &ih, sizeof(ih));
+    });
+}
+int32_t b200j_ipc_open(b200j_handle *h, const uint8_t *handle, void **peer_ptr) {
+    return guarded(h, [&] {
+        REQUIRE(handle && peer_ptr, B200J_ERR_INVALID, "b200j_ipc_open: NULL argument");
+        cudaIpcMemHandle_t ih;
+        memcpy(&ih, handle, sizeof(ih));
+        CU(cudaIpcOpenMemHandle(peer_ptr, ih, cudaIpcMemLazyEnablePeerAccess));
+    });
+}
+int32_t b200j_ipc_close(b200j_handle *h, void *peer_ptr) {
+    return guarded(h, [&] { if (peer_ptr) CU(cudaIpcCloseMemHandle(peer_ptr)); });
+}
+int32_t b200j_ipc_free(b200j_handle *h, void *ptr) {
+    return guarded(h, [&] { if (ptr) CU(cudaFree(ptr)); });
 }
 
 int32_t b200j_host_alloc(size_t bytes, void **out) {

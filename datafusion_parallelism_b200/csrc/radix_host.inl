@@ -26,13 +26,6 @@ void radix_release(H *h) {
     rs = RadixScratch{};
 }
 
-struct PartPlan {
-    PartArgs a{};
-    int grid = 1;
-    int kw = 8;
-    bool dest = false;
-};
-
 // Plans the partitioning of `n` keys into n_bins bins (+ the NULL bin): radix mode (n_dest == 0, n_bins = 1 << bits)
 // or destination mode (n_bins = n_dest ranks).
 PartPlan part_plan(H *h, const void *keys, const uint8_t *validity, int64_t bit_offset, int kw, int64_t n, int bits, int n_dest) {
@@ -196,4 +189,54 @@ void radix_build(H *h, const void *keys, const uint8_t *validity, int kw, int64_
         free_temps(h, temps);
         throw;
     }
+}
+
+// ---- multi-GPU exchange: count, then scatter into per-destination buffers (local or peer memory) ----------------
+void do_shuffle_count(H *h, const b200j_batch *b, int32_t n_dest, int64_t *counts) {
+    check_batch(h, b, 0);
+    REQUIRE(h->cfg.n_keys == 1, B200J_ERR_UNSUPPORTED, "the exchange takes a single 4/8-byte key column");
+    REQUIRE(n_dest >= 1 && n_dest <= B200J_MAX_DEST, B200J_ERR_INVALID, "n_dest must be in 1..16");
+    REQUIRE(counts != nullptr, B200J_ERR_INVALID, "counts is NULL");
+    REQUIRE(b->mem == B200J_MEM_DEVICE || b->n_rows == 0, B200J_ERR_UNSUPPORTED, "the exchange takes device-resident batches");
+    h->shuffle_armed = false;
+    for (int d = 0; d <= n_dest; d++) counts[d] = 0;
+    if (b->n_rows == 0) {
+        h->shuffle_n = 0;
+        h->shuffle_armed = true;
+        return;
+    }
+    const b200j_column &kc = b->keys[0];
+    h->shuffle_plan = part_plan(h, kc.values, kc.validity, kc.bit_offset, h->key_widths[0], b->n_rows, 0, n_dest);
+    PhaseTimer tm(h, &h->st.ms_exchange_partition);
+    part_hist(h, h->shuffle_plan, true);
+    tm.stop();
+    const unsigned long long *off = h->rscratch.h_off;
+    for (int d = 0; d <= n_dest; d++) counts[d] = (int64_t)(off[d + 1] - off[d]);
+    h->shuffle_n = b->n_rows;
+    h->shuffle_armed = true;
+}
+
+void do_shuffle_scatter(H *h, int32_t n_dest, void *const *dest_keys, uint32_t *const *dest_rowid, const int64_t *dest_offset, uint32_t rowid_base) {
+    REQUIRE(h->shuffle_armed, B200J_ERR_STATE, "b200j_shuffle_scatter without a preceding b200j_shuffle_count");
+    h->shuffle_armed = false;
+    if (h->shuffle_n == 0) return;
+    PartPlan &pl = h->shuffle_plan;
+    REQUIRE(n_dest == pl.a.n_dest, B200J_ERR_INVALID, "n_dest differs from the b200j_shuffle_count call");
+    REQUIRE(dest_keys && dest_rowid && dest_offset, B200J_ERR_INVALID, "destination arrays missing");
+    uint32_t base[B200J_MAX_DEST + 1];
+    const unsigned long long *off = h->rscratch.h_off;
+    for (int d = 0; d <= n_dest; d++) {
+        const bool used = off[d + 1] > off[d];
+        REQUIRE(!used || (dest_keys[d] && dest_rowid[d]), B200J_ERR_INVALID, "destination buffer missing for a non-empty destination");
+        REQUIRE(dest_offset[d] >= 0 && dest_offset[d] < 0xffff0000LL, B200J_ERR_INVALID, "destination offset out of range");
+        base[d] = (uint32_t)dest_offset[d];
+        pl.a.dest_keys[d] = dest_keys[d];
+        pl.a.dest_rid[d] = dest_rowid[d];
+    }
+    pl.a.rid_base = rowid_base;
+    PhaseTimer tm(h, &h->st.ms_exchange_partition);
+    CU(cudaMemcpyAsync(h->rscratch.bin_base, base, (size_t)(n_dest + 1) * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));      // `base` is a stack array
+    part_scatter(h, pl);
+    tm.stop();
 }

@@ -1,0 +1,285 @@
+"""Multi-GPU hash join: one process per GPU, both join sides hash-partitioned by destination rank and exchanged
+over NVLink, then every GPU joins its own partition locally (the reference is single-process, so this
+has no counterpart there).
+
+torch.distributed is the plumbing only (count exchange, barriers, the NCCL all-to-all of mode "nccl"). The
+partitioning and, in mode "p2p", the exchange itself are libb200join kernels: b200j_shuffle_scatter writes every
+(key, row id) straight into the destination GPU's receive buffer through cudaIpc-mapped peer pointers, so the
+scatter kernel IS the all-to-all (no send buffer, no second pass over the data).
+
+Host-side planning (`ExchangePlan`) is pure Python over the count matrix, so it is unit-tested on CPU with gloo.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from . import _native as N
+from .join import HashJoin, B200JoinError, MEM_DEVICE, OUT_PAIRS, make_batch
+
+IPC_BYTES = 64
+
+
+class ExchangePlan:
+    """What every rank derives from the all-gathered count matrix counts[src][dst] (rows of src that hash to dst)."""
+
+    def __init__(self, counts: np.ndarray, rank: int):
+        counts = np.asarray(counts, dtype=np.int64)
+        world = counts.shape[0]
+        assert counts.shape == (world, world)
+        self.world, self.rank, self.counts = world, rank, counts
+        self.recv_rows = counts.sum(axis=0)                      # rows every rank receives
+        self.max_recv = int(self.recv_rows.max())
+        # where MY rows start inside destination d's receive buffer: after the rows of lower ranks
+        self.dest_offset = np.array([int(counts[:rank, d].sum()) for d in range(world)], dtype=np.int64)
+        # where rank s's rows start inside MY receive buffer
+        self.src_offset = np.concatenate([[0], np.cumsum(counts[:, rank])]).astype(np.int64)
+        self.send_split = [int(x) for x in counts[rank, :]]
+        self.recv_split = [int(x) for x in counts[:, rank]]
+        self.send_offset = np.concatenate([[0], np.cumsum(counts[rank, :])]).astype(np.int64)
+
+    def origin_of(self, recv_index: np.ndarray):
+        """(source rank, position inside that source's segment) of rows of my receive buffer."""
+        src = np.searchsorted(self.src_offset[1:], recv_index, side="right")
+        return src, recv_index - self.src_offset[src]
+
+
+class _PeerBuffer:
+    """A device buffer every rank of the node can write: cudaMalloc + cudaIpc handle, opened by all peers."""
+
+    def __init__(self, join: HashJoin, dist, nbytes: int):
+        L = N.lib()
+        self.join, self.nbytes = join, nbytes
+        p = C.c_void_p()
+        hbuf = C.create_string_buffer(IPC_BYTES)
+        join._check(L.b200j_ipc_alloc(join._h, nbytes, C.byref(p), hbuf))
+        self.local = p.value
+        world, rank = dist.get_world_size(), dist.get_rank()
+        handles: List[Optional[bytes]] = [None] * world
+        dist.all_gather_object(handles, hbuf.raw)
+        self.ptrs: List[int] = []
+        self._opened: List[int] = []
+        for r in range(world):
+            if r == rank:
+                self.ptrs.append(self.local)
+                continue
+            q = C.c_void_p()
+            join._check(L.b200j_ipc_open(join._h, handles[r], C.byref(q)))
+            self.ptrs.append(q.value)
+            self._opened.append(q.value)
+
+    def close(self, dist):
+        L = N.lib()
+        dist.barrier()
+        for q in self._opened:
+            L.b200j_ipc_close(self.join._h, q)
+        self._opened = []
+        dist.barrier()
+        if self.local:
+            L.b200j_ipc_free(self.join._h, self.local)
+            self.local = None
+
+
+def _dev_column(ptr: int, n_rows: int, width: int, keep=None):
+    from .join import ColumnRef
+    return ColumnRef(ptr or None, None, None, 0, n_rows, MEM_DEVICE, width, keep)
+
+
+def shuffle_count(join: HashJoin, keys, n_dest: int) -> np.ndarray:
+    """b200j_shuffle_count: rows of `keys` (device column) per destination rank; [n_dest] = NULL-key rows."""
+    b, keep = make_batch([keys])
+    counts = (C.c_int64 * (n_dest + 1))()
+    join._check(N.lib().b200j_shuffle_count(join._h, C.byref(b), n_dest, counts))
+    return np.array(list(counts), dtype=np.int64)
+
+
+def shuffle_scatter(join: HashJoin, n_dest: int, dest_keys: Sequence[int], dest_rowid: Sequence[int], dest_offset: Sequence[int],
+                    rowid_base: int = 0):
+    """b200j_shuffle_scatter: write every (key, row id) of the counted batch to its destination buffer."""
+    dk = (C.c_void_p * (n_dest + 1))(*[C.c_void_p(int(p) if p else None) for p in dest_keys])
+    dr = (C.c_void_p * (n_dest + 1))(*[C.c_void_p(int(p) if p else None) for p in dest_rowid])
+    do = (C.c_int64 * (n_dest + 1))(*[int(x) for x in dest_offset])
+    join._check(N.lib().b200j_shuffle_scatter(join._h, n_dest, dk, dr, do, rowid_base))
+
+
+class _Side:
+    """Receive (and, for NCCL, send) buffers of one join side on this rank."""
+
+    def __init__(self):
+        self.cap = 0
+        self.keys = None        # _PeerBuffer (p2p) or torch tensor (nccl)
+        self.rid = None
+        self.send_keys = None   # nccl only
+        self.send_rid = None
+        self.plan: Optional[ExchangePlan] = None
+        self.null_keys = None
+        self.null_rid = None
+
+
+class DistributedJoin:
+    """HashJoin over `world` GPUs. Same call shape as HashJoin for one partition per rank; inputs are device tensors."""
+
+    def __init__(self, join_type="inner", key_width=8, stream=None, mode="p2p", group=None, **join_kwargs):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.group = group
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.mode, self.kw = mode, key_width
+        self.stream = stream if stream is not None else torch.cuda.current_stream()
+        join_kwargs.setdefault("device", torch.cuda.current_device())     # one process per GPU: the handle lives on this rank's device
+        self.join = HashJoin(join_type, key_widths=(key_width,), stream=self.stream.cuda_stream, **join_kwargs)
+        self.build, self.probe = _Side(), _Side()
+        self.ms_exchange = {"build": 0.0, "probe": 0.0}
+        self.build_rows_local = 0
+        self._key_dtype = torch.int64 if key_width == 8 else torch.int32
+
+    # ---- buffers ----------------------------------------------------------------------------------------------
+    def _ensure(self, side: _Side, rows: int):
+        """Collective: every rank calls with the same `rows` (the max over ranks of what anyone receives)."""
+        if rows <= side.cap:
+            return
+        torch = self.torch
+        cap = int(rows * 1.1) + 4096
+        if self.mode == "p2p":
+            for b in (side.keys, side.rid):
+                if b is not None:
+                    b.close(self.dist)
+            side.keys = _PeerBuffer(self.join, self.dist, cap * self.kw + 64)
+            side.rid = _PeerBuffer(self.join, self.dist, cap * 4 + 64)
+        else:
+            dev = torch.device("cuda", torch.cuda.current_device())
+            side.keys = torch.empty(cap, dtype=self._key_dtype, device=dev)
+            side.rid = torch.empty(cap, dtype=torch.int32, device=dev)
+        side.cap = cap
+
+    def _exchange(self, side: _Side, keys, rowid_base: int = 0) -> int:
+        """Partition `keys` by destination rank and deliver them; returns the rows this rank received."""
+        torch, dist = self.torch, self.dist
+        W = self.world
+        n = int(keys.shape[0])
+        counts = shuffle_count(self.join, keys, W)
+        with torch.cuda.stream(self.stream):
+            mine = torch.from_numpy(counts[:W].copy()).to(keys.device)
+            allc = torch.empty(W * W, dtype=torch.int64, device=keys.device)
+            dist.all_gather_into_tensor(allc, mine, group=self.group)
+            matrix = allc.cpu().numpy().reshape(W, W)
+        plan = ExchangePlan(matrix, self.rank)
+        side.plan = plan
+        self._ensure(side, plan.max_recv)
+        n_null = int(counts[W])
+        nk = nr = 0
+        if n_null:
+            side.null_keys = torch.empty(n_null, dtype=self._key_dtype, device=keys.device)
+            side.null_rid = torch.empty(n_null, dtype=torch.int32, device=keys.device)
+            nk, nr = side.null_keys.data_ptr(), side.null_rid.data_ptr()
+        if self.mode == "p2p":
+            # the count all-gather above doubles as the "everyone is done with the previous contents" barrier
+            shuffle_scatter(self.join, W, list(side.keys.ptrs) + [nk], list(side.rid.ptrs) + [nr],
+                            list(plan.dest_offset) + [0], rowid_base)
+            self.join.synchronize()
+            dist.barrier(group=self.group)          # every peer's stores have landed in my receive buffer
+            recv_keys_ptr, recv_rid_ptr = side.keys.local, side.rid.local
+        else:
+            if side.send_keys is None or side.send_keys.shape[0] < n:
+                side.send_keys = torch.empty(int(n * 1.1) + 4096, dtype=self._key_dtype, device=keys.device)
+                side.send_rid = torch.empty(int(n * 1.1) + 4096, dtype=torch.int32, device=keys.device)
+            sk, sr = side.send_keys.data_ptr(), side.send_rid.data_ptr()
+            shuffle_scatter(self.join, W, [sk] * W + [nk], [sr] * W + [nr], list(plan.send_offset[:W]) + [0], rowid_base)
+            n_recv = int(plan.recv_rows[self.rank])
+            n_send = int(plan.send_offset[W])
+            with torch.cuda.stream(self.stream):
+                dist.all_to_all_single(side.keys[:n_recv], side.send_keys[:n_send], plan.recv_split, plan.send_split, group=self.group)
+                dist.all_to_all_single(side.rid[:n_recv], side.send_rid[:n_send], plan.recv_split, plan.send_split, group=self.group)
+            self.stream.synchronize()
+            recv_keys_ptr, recv_rid_ptr = side.keys.data_ptr(), side.rid.data_ptr()
+        side.recv_keys_ptr, side.recv_rid_ptr = recv_keys_ptr, recv_rid_ptr
+        return int(plan.recv_rows[self.rank])
+
+    # ---- the HashJoin call shape --------------------------------------------------------------------------------
+    def _timed(self, which: str, fn):
+        torch = self.torch
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(self.stream)
+        out = fn()
+        e1.record(self.stream)
+        e1.synchronize()
+        self.ms_exchange[which] += e0.elapsed_time(e1)
+        return out
+
+    def reset(self):
+        self.join.reset()
+        self.build_rows_local = 0
+
+    def build_push(self, partition: int, keys: Sequence):
+        """Exchange this rank's build rows, then append what this rank received to its local build side."""
+        k = keys[0]
+        n_recv = self._timed("build", lambda: self._exchange(self.build, k, rowid_base=0))
+        self.build_rows_local += n_recv
+        self.join.build_push(partition, [_dev_column(self.build.recv_keys_ptr, n_recv, self.kw, keep=(self.build.keys,))])
+
+    def build_finish(self, partition: int):
+        self.join.build_finish(partition)
+
+    def probe_batch(self, partition: int, keys: Sequence, want: int = OUT_PAIRS):
+        """Exchange one probe batch, probe the received rows locally. The result's indices are LOCAL: build_idx counts
+        the build rows this rank received (in arrival order), probe_idx the rows of the received probe batch; map them to
+        (source rank, source row) with `origin_build` / `origin_probe`."""
+        k = keys[0]
+        n_recv = self._timed("probe", lambda: self._exchange(self.probe, k, rowid_base=0))
+        res = self.join.probe_batch(partition, [_dev_column(self.probe.recv_keys_ptr, n_recv, self.kw, keep=(self.probe.keys,))], want=want)
+        res.exchange_plan = self.probe.plan
+        return res
+
+    def probe_finish(self, partition: int, want: int = OUT_PAIRS):
+        return self.join.probe_finish(partition, want=want)
+
+    def _origin(self, side: _Side, idx: np.ndarray):
+        """(source rank, source row) of received rows `idx` of one side (host arrays; for tests and late materialisation)."""
+        torch = self.torch
+        n_recv = int(side.plan.recv_rows[self.rank])
+        if self.mode == "p2p":
+            rid = np.empty(n_recv, dtype=np.uint32)
+            if n_recv:
+                t = torch.empty(n_recv, dtype=torch.int32, device="cuda")
+                import ctypes
+                # device-to-device view through cudaMemcpy via torch: wrap the raw pointer
+                src = _RawCudaArray(side.recv_rid_ptr, n_recv, "<i4")
+                t.copy_(torch.as_tensor(src, device="cuda"))
+                rid = t.cpu().numpy().view(np.uint32)
+        else:
+            rid = side.rid[:n_recv].cpu().numpy().view(np.uint32)
+        src_rank, _ = side.plan.origin_of(np.asarray(idx, dtype=np.int64))
+        return src_rank, rid[np.asarray(idx, dtype=np.int64)]
+
+    def origin_build(self, build_idx):
+        return self._origin(self.build, build_idx)
+
+    def origin_probe(self, probe_idx):
+        return self._origin(self.probe, probe_idx)
+
+    def stats(self) -> dict:
+        st = self.join.stats()
+        st["ms_exchange_build"] = self.ms_exchange["build"]
+        st["ms_exchange_probe"] = self.ms_exchange["probe"]
+        return st
+
+    def reset_stats(self):
+        self.join.reset_stats()
+        self.ms_exchange = {"build": 0.0, "probe": 0.0}
+
+    def close(self):
+        if self.mode == "p2p":
+            for side in (self.build, self.probe):
+                for b in (side.keys, side.rid):
+                    if b is not None:
+                        b.close(self.dist)
+                side.keys = side.rid = None
+        self.join.close()
+
+
+class _RawCudaArray:
+    def __init__(self, ptr: int, n: int, typestr: str):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr or 0, False), "version": 3, "strides": None}

@@ -196,6 +196,7 @@ typedef struct {
                                          partition pass: 8 B key in, 8 B build index out per row, the partitioned
                                          row-id array is the result's probe-index column)               */
     int64_t  compact_launches;        /* dense results with misses compacted afterwards (Inner / Left)  */
+    double   ms_exchange_partition;   /* b200j_shuffle_count + b200j_shuffle_scatter kernels             */
 } b200j_stats;
 
 /* ---- lifecycle ------------------------------------------------------------------------------- */
@@ -237,6 +238,27 @@ int32_t b200j_result_release(b200j_handle *h, b200j_result *r);
 int32_t b200j_gather(b200j_handle *h, const b200j_result *pairs, const b200j_batch *probe_batch, uint32_t want,
                      b200j_gathered *out);
 int32_t b200j_gathered_release(b200j_handle *h, b200j_gathered *g);
+
+/* ---- multi-GPU exchange (no counterpart in the reference, which is single-process) ----------
+ * One process per GPU; every rank hash-partitions BOTH join sides by destination rank
+ *     dest = (((hash >> 32) & 0xfffff) * n_dest) >> 20        (independent of the radix and slot bits)
+ * and the scatter kernel writes each (key, row id) straight into the destination's receive buffer: the
+ * per-destination base pointers may be peer-GPU memory mapped over NVLink (b200j_ipc_*), in which case the
+ * scatter IS the all-to-all, or regions of a local send buffer handed to ncclSend/Recv by the caller.
+ * Call order per batch: b200j_shuffle_count -> (ranks exchange the counts) -> b200j_shuffle_scatter.
+ * No other call on the handle may come between the two. Rows whose key is NULL are counted in
+ * counts[n_dest] and written to destination n_dest (keep that one local: NULL keys never match). */
+#define B200J_MAX_DEST 16
+int32_t b200j_shuffle_count(b200j_handle *h, const b200j_batch *batch, int32_t n_dest, int64_t *counts /* [n_dest + 1] */);
+int32_t b200j_shuffle_scatter(b200j_handle *h, int32_t n_dest, void *const *dest_keys /* [n_dest + 1] */,
+                              uint32_t *const *dest_rowid /* [n_dest + 1] */, const int64_t *dest_offset /* [n_dest + 1] first row to
+                              write in each destination buffer */, uint32_t rowid_base /* added to the batch-local row index */);
+/* Device buffers that peers on the same node can map (cudaIpc): `handle_out` is 64 opaque bytes to send to the peers. */
+#define B200J_IPC_HANDLE_BYTES 64
+int32_t b200j_ipc_alloc(b200j_handle *h, size_t bytes, void **ptr, uint8_t *handle_out);
+int32_t b200j_ipc_open(b200j_handle *h, const uint8_t *handle, void **peer_ptr);
+int32_t b200j_ipc_close(b200j_handle *h, void *peer_ptr);
+int32_t b200j_ipc_free(b200j_handle *h, void *ptr);
 
 /* ---- hashing (a1) ---------------------------------------------------------------------------- */
 /* create_hashes over the key columns of `batch` with the handle's RandomState: one u64 per row into

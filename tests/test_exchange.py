@@ -1,0 +1,130 @@
+"""Multi-GPU exchange: host-side planning on CPU (gloo, world_size 2 and 3) and the partition/scatter kernels on one GPU
+with the ranks emulated in one process (B200_PROFILING.md: with fewer GPUs than ranks, emulate the ranks)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+import oracle
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _plan_worker(rank, world, port, seed, out_dir):
+    import torch
+    import torch.distributed as dist
+    # importing the package needs the built library (CPU box: built by build()); the plan itself is pure host logic
+    from datafusion_parallelism_b200.exchange import ExchangePlan
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rng = np.random.default_rng(seed + rank)
+    mine = torch.from_numpy(rng.integers(0, 1000, world).astype(np.int64))
+    if rank == 1:
+        mine[0] = 0                       # an empty segment
+    allc = [torch.zeros(world, dtype=torch.int64) for _ in range(world)]
+    dist.all_gather(allc, mine)
+    matrix = torch.stack(allc).numpy()
+    plan = ExchangePlan(matrix, rank)
+    gathered = [None] * world
+    dist.all_gather_object(gathered, {"dest_offset": plan.dest_offset.tolist(), "src_offset": plan.src_offset.tolist(),
+                                      "recv": int(plan.recv_rows[rank]), "send_split": plan.send_split, "recv_split": plan.recv_split})
+    if rank == 0:
+        np.save(os.path.join(out_dir, "matrix.npy"), matrix)
+        import json
+        with open(os.path.join(out_dir, "plans.json"), "w") as f:
+            json.dump(gathered, f)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_exchange_plan_is_consistent_across_ranks(world, tmp_path):
+    import json
+    import torch.multiprocessing as mp
+    port = _free_port()
+    mp.spawn(_plan_worker, args=(world, port, 11, str(tmp_path)), nprocs=world, join=True)
+    matrix = np.load(tmp_path / "matrix.npy")
+    plans = json.load(open(tmp_path / "plans.json"))
+    for d in range(world):
+        # the segments the sources write into destination d tile [0, recv_rows[d]) exactly, in rank order
+        segs = sorted((plans[s]["dest_offset"][d], plans[s]["dest_offset"][d] + int(matrix[s, d])) for s in range(world))
+        pos = 0
+        for lo, hi in segs:
+            assert lo == pos
+            pos = hi
+        assert pos == plans[d]["recv"] == int(matrix[:, d].sum())
+        # and the destination's view of where each source starts agrees
+        assert plans[d]["src_offset"][:-1] == [plans[s]["dest_offset"][d] for s in range(world)]
+        assert plans[d]["recv_split"] == [int(matrix[s, d]) for s in range(world)]
+        assert plans[d]["send_split"] == [int(matrix[d, s]) for s in range(world)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world,dtype", [(2, np.int64), (3, np.int64), (4, np.int32)])
+def test_emulated_ranks_join_matches_oracle(world, dtype):
+    """All ranks live on cuda:0: every rank's scatter writes into every rank's receive buffer (plain device pointers here,
+    cudaIpc peer pointers on a real node), then every rank joins what it received. The union of the per-rank results,
+    mapped back to global row ids, must equal the single-table oracle join."""
+    import torch
+    import datafusion_parallelism_b200 as d
+    from datafusion_parallelism_b200.exchange import ExchangePlan, shuffle_count, shuffle_scatter, _dev_column
+    rng = np.random.default_rng(5)
+    nb, npr = 30_000, 100_000
+    kw = np.dtype(dtype).itemsize
+    tdt = torch.int64 if kw == 8 else torch.int32
+    bkeys = [rng.integers(0, 50_000, nb).astype(dtype) for _ in range(world)]        # duplicates across and inside ranks
+    pkeys = [rng.integers(-1000, 60_000, npr).astype(dtype) for _ in range(world)]
+    joins = [d.HashJoin("inner", key_widths=(kw,), layout="radix", radix_bits=3) for _ in range(world)]
+    try:
+        def exchange(keys_per_rank):
+            dev = [torch.from_numpy(k).cuda() for k in keys_per_rank]
+            counts = [shuffle_count(joins[r], dev[r], world) for r in range(world)]
+            matrix = np.stack([c[:world] for c in counts])
+            plans = [ExchangePlan(matrix, r) for r in range(world)]
+            recv_k = [torch.empty(int(plans[r].recv_rows[r]) + 8, dtype=tdt, device="cuda") for r in range(world)]
+            recv_r = [torch.empty(int(plans[r].recv_rows[r]) + 8, dtype=torch.int32, device="cuda") for r in range(world)]
+            # counts were taken rank by rank, so re-count right before each rank's scatter (count -> scatter must be adjacent)
+            for r in range(world):
+                c = shuffle_count(joins[r], dev[r], world)
+                assert np.array_equal(c, counts[r])
+                shuffle_scatter(joins[r], world, [t.data_ptr() for t in recv_k] + [0], [t.data_ptr() for t in recv_r] + [0],
+                                list(plans[r].dest_offset) + [0])
+                joins[r].synchronize()
+            return plans, recv_k, recv_r
+
+        bplans, bk, br = exchange(bkeys)
+        for r in range(world):
+            n = int(bplans[r].recv_rows[r])
+            joins[r].build_push(0, [_dev_column(bk[r].data_ptr(), n, kw, keep=bk[r])])
+            joins[r].build_finish(0)
+        pplans, pk, pr = exchange(pkeys)
+        got_b, got_p = [], []
+        for r in range(world):
+            n = int(pplans[r].recv_rows[r])
+            res = joins[r].probe_batch(0, [_dev_column(pk[r].data_ptr(), n, kw, keep=pk[r])])
+            lb, lp = res.numpy()
+            res.release()
+            # local -> global ids: (source rank, row id at the source)
+            brid, prid = br[r].cpu().numpy().view(np.uint32), pr[r].cpu().numpy().view(np.uint32)
+            bsrc, _ = bplans[r].origin_of(lb.astype(np.int64))
+            psrc, _ = pplans[r].origin_of(lp.astype(np.int64))
+            got_b.append(bsrc.astype(np.uint64) * nb + brid[lb.astype(np.int64)])
+            got_p.append(psrc.astype(np.uint64) * npr + prid[lp.astype(np.int64)])
+        got_b, got_p = np.concatenate(got_b), np.concatenate(got_p)
+    finally:
+        for j in joins:
+            j.close()
+    oj = oracle.OracleJoin("inner", [np.concatenate(bkeys)])
+    ob, op = oj.probe_batch([np.concatenate(pkeys)], world * npr)
+    assert got_b.shape == ob.shape
+    o1 = np.lexsort((got_b, got_p))
+    o2 = np.lexsort((ob, op.astype(np.uint64)))
+    assert np.array_equal(got_b[o1], ob[o2]) and np.array_equal(got_p[o1], op.astype(np.uint64)[o2])
