@@ -1,5 +1,241 @@
 // gather_host.inl — host side of b200j_gather (included inside b200join.cu's anonymous namespace).
-void do_gather(H *, const b200j_result *, const b200j_batch *, uint32_t, b200j_gathered *) {
-    throw Fail{B200J_ERR_UNSUPPORTED, "gather not built in"};
+// take_multiple_record_batch (src/shared/shared.rs:83-92): build columns (keys, then payload) at build_idx, then the probe
+// batch's columns (keys, then payload) at probe_idx. LeftSemi/LeftAnti output only the build side, RightSemi/RightAnti
+// only the probe side (build_join_schema, probe_lookup_implementation.rs:77-94).
+
+struct GatheredOwner {
+    std::vector<b200j_out_column> cols;
+    std::vector<void *> bufs;          // every buffer handed out (device: big_free; host: pinned_give)
+    int32_t mem = B200J_MEM_DEVICE;
+};
+
+struct GatherCtx {
+    H *h;
+    int64_t n;
+    const uint64_t *bidx;              // device
+    const uint32_t *pidx;              // device
+    std::vector<void *> temps;
+    GatheredOwner *own;
+    unsigned long long *d_nulls;       // device counter per column (array)
+};
+
+void *gather_dev_alloc(GatherCtx &g, size_t bytes) {
+    void *p = nullptr;
+    CU(big_alloc(g.h, &p, std::max<size_t>(bytes, 256)));
+    g.own->bufs.push_back(p);
+    return p;
 }
-void do_gathered_release(H *, b200j_gathered *) {}
+
+template <typename IdxT>
+void gather_one_column(GatherCtx &g, int col, int type, const GatherSrc &src, const IdxT *idx) {
+    H *h = g.h;
+    const int64_t n = g.n;
+    b200j_out_column &oc = g.own->cols[col];
+    oc = b200j_out_column{};
+    const size_t vwords = (size_t)((n + 31) / 32 + 1);
+    uint32_t *dvalid = (uint32_t *)gather_dev_alloc(g, vwords * 4);
+    oc.validity = (uint8_t *)dvalid;
+    unsigned long long *nulls = g.d_nulls + col;
+    const int grid = grid_for(h, n, 256, 8);
+    if (type != B200J_T_UTF8) {
+        void *dst = gather_dev_alloc(g, (size_t)n * type + 16);
+        oc.values = dst;
+        oc.values_bytes = n * type;
+        if (n > 0) {
+            switch (type) {
+                case 1: gather_fixed_kernel<uint8_t, IdxT><<<grid, 256, 0, h->stream>>>(src, idx, n, (uint8_t *)dst, dvalid, nulls); break;
+                case 2: gather_fixed_kernel<uint16_t, IdxT><<<grid, 256, 0, h->stream>>>(src, idx, n, (uint16_t *)dst, dvalid, nulls); break;
+                case 4: gather_fixed_kernel<uint32_t, IdxT><<<grid, 256, 0, h->stream>>>(src, idx, n, (uint32_t *)dst, dvalid, nulls); break;
+                case 8: gather_fixed_kernel<unsigned long long, IdxT><<<grid, 256, 0, h->stream>>>(src, idx, n, (unsigned long long *)dst, dvalid, nulls); break;
+                default: gather_fixed_kernel<ulonglong2, IdxT><<<grid, 256, 0, h->stream>>>(src, idx, n, (ulonglong2 *)dst, dvalid, nulls); break;
+            }
+            h->st.kernel_launches++;
+            CU(cudaGetLastError());
+        }
+        return;
+    }
+    // Utf8: lengths -> exclusive scan -> offsets, then the byte copy
+    int32_t *ooff = (int32_t *)gather_dev_alloc(g, (size_t)(n + 1) * 4 + 16);
+    oc.offsets = ooff;
+    if (n == 0) {
+        CU(cudaMemsetAsync(ooff, 0, 4, h->stream));
+        oc.values = gather_dev_alloc(g, 256);
+        return;
+    }
+    int64_t *len = nullptr, *start = nullptr, *bsum = nullptr, *dtotal = nullptr;
+    const int64_t n_tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    CU(big_alloc(h, &len, (size_t)n * 8)); g.temps.push_back(len);
+    CU(big_alloc(h, &start, (size_t)n * 8)); g.temps.push_back(start);
+    CU(big_alloc(h, &bsum, (size_t)(n_tiles + 1) * 8)); g.temps.push_back(bsum);
+    dtotal = bsum + n_tiles;
+    gather_utf8_len_kernel<IdxT><<<grid, 256, 0, h->stream>>>(src, idx, n, len, dvalid, nulls);
+    scan_block_sums_kernel<<<(unsigned)n_tiles, SCAN_THREADS, 0, h->stream>>>(len, n, bsum);
+    scan_serial_kernel<<<1, 1024, 0, h->stream>>>(bsum, n_tiles, dtotal);
+    scan_apply_kernel<<<(unsigned)n_tiles, SCAN_THREADS, 0, h->stream>>>(len, n, bsum, start, ooff);
+    h->st.kernel_launches += 4;
+    CU(cudaGetLastError());
+    int64_t total = 0;
+    CU(cudaMemcpyAsync(&total, dtotal, 8, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    {   // out32[n] = total (the apply kernel only covers it when n is not a multiple of the scan tile)
+        const int32_t t32 = (int32_t)std::min<int64_t>(total, 0x7fffffffLL);
+        CU(cudaMemcpyAsync(ooff + n, &t32, 4, cudaMemcpyHostToDevice, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+    }
+    REQUIRE(total <= 0x7fffffffLL, B200J_ERR_UNSUPPORTED, "gathered Utf8 column exceeds 2 GiB (32-bit Arrow offsets): gather fewer rows per call");
+    char *dst = (char *)gather_dev_alloc(g, (size_t)total + 16);
+    oc.values = dst;
+    oc.values_bytes = total;
+    if (total > 0) {
+        gather_utf8_copy_kernel<IdxT><<<grid_for(h, n * 32, 256, 16), 256, 0, h->stream>>>(src, idx, n, start, len, dst);
+        h->st.kernel_launches++;
+        CU(cudaGetLastError());
+    }
+}
+
+// stages one column of a (host or device) batch; returns the device-side source descriptor
+GatherSrc gather_stage_column(GatherCtx &g, const b200j_column &c, int type, int64_t n_rows, int mem) {
+    H *h = g.h;
+    GatherSrc s{};
+    if (n_rows == 0) return s;
+    if (mem == B200J_MEM_DEVICE) {
+        s.values = c.values;
+        s.offsets = c.offsets;
+        s.validity = c.validity;
+        s.bit_offset = c.bit_offset;
+        return s;
+    }
+    if (type != B200J_T_UTF8) {
+        void *d = nullptr;
+        CU(big_alloc(h, &d, (size_t)n_rows * type + 16)); g.temps.push_back(d);
+        CU(cudaMemcpyAsync(d, c.values, (size_t)n_rows * type, cudaMemcpyHostToDevice, h->stream));
+        s.values = d;
+    } else {
+        REQUIRE(c.offsets != nullptr, B200J_ERR_INVALID, "Utf8 column without offsets buffer");
+        const int32_t o0 = c.offsets[0], o1 = c.offsets[n_rows];
+        void *doff = nullptr, *dd = nullptr;
+        CU(big_alloc(h, &doff, (size_t)(n_rows + 1) * 4)); g.temps.push_back(doff);
+        CU(cudaMemcpyAsync(doff, c.offsets, (size_t)(n_rows + 1) * 4, cudaMemcpyHostToDevice, h->stream));
+        CU(big_alloc(h, &dd, (size_t)std::max<int64_t>(o1 - o0, 1) + 16)); g.temps.push_back(dd);
+        if (o1 > o0) CU(cudaMemcpyAsync(dd, (const char *)c.values + o0, (size_t)(o1 - o0), cudaMemcpyHostToDevice, h->stream));
+        s.offsets = doff;
+        s.values = (const char *)dd - o0;          // offsets stay absolute
+    }
+    int64_t boff = 0;
+    s.validity = stage_validity(h, c, n_rows, B200J_MEM_HOST, g.temps, &boff);
+    s.bit_offset = boff;
+    return s;
+}
+
+void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, uint32_t want, b200j_gathered *out) {
+    REQUIRE(h->built, B200J_ERR_INVALID, "gather before the build side finished");
+    REQUIRE(pairs != nullptr && out != nullptr && out->struct_size >= sizeof(b200j_gathered), B200J_ERR_INVALID, "gather: missing argument");
+    const int jt = h->cfg.join_type;
+    const bool want_build = !(jt == B200J_RIGHT_SEMI || jt == B200J_RIGHT_ANTI);
+    const bool want_probe = !(jt == B200J_LEFT_SEMI || jt == B200J_LEFT_ANTI);
+    const int nk = h->cfg.n_keys, nbp = h->cfg.n_build_payload, npp = h->cfg.n_probe_payload;
+    if (probe_batch) {
+        check_batch(h, probe_batch, npp);
+        REQUIRE(probe_batch->n_payload == npp, B200J_ERR_INVALID, "gather needs every configured probe payload column");
+    }
+    const int64_t n = pairs->n;
+    GatheredOwner *own = new GatheredOwner();
+    GatherCtx g{h, n, nullptr, nullptr, {}, own, nullptr};
+    try {
+        const int n_cols = (want_build ? nk + nbp : 0) + (want_probe ? nk + npp : 0);
+        own->cols.resize(std::max(n_cols, 1));
+        // index arrays on the device
+        auto stage_idx = [&](const void *p, size_t w) -> const void * {
+            if (!p || n == 0) return nullptr;
+            if (pairs->mem == B200J_MEM_DEVICE) return p;
+            void *d = nullptr;
+            CU(big_alloc(h, &d, (size_t)n * w)); g.temps.push_back(d);
+            CU(cudaMemcpyAsync(d, p, (size_t)n * w, cudaMemcpyHostToDevice, h->stream));
+            return d;
+        };
+        g.bidx = (const uint64_t *)stage_idx(pairs->build_idx, 8);
+        g.pidx = (const uint32_t *)stage_idx(pairs->probe_idx, 4);
+        void *dn = nullptr;
+        CU(big_alloc(h, &dn, (size_t)(n_cols + 1) * 8)); g.temps.push_back(dn);
+        CU(cudaMemsetAsync(dn, 0, (size_t)(n_cols + 1) * 8, h->stream));
+        g.d_nulls = (unsigned long long *)dn;
+        PhaseTimer tm(h, &h->st.ms_gather);
+        int col = 0;
+        if (want_build) {
+            for (int i = 0; i < nk + nbp; i++, col++) {
+                const ColStore &cs = i < nk ? h->bkeys[i] : h->bpayload[i - nk];
+                GatherSrc s{};
+                s.values = cs.values.p;
+                s.offsets = cs.offsets.p;
+                s.offsets64 = 1;
+                s.validity = cs.has_nulls ? (const uint8_t *)cs.validity.p : nullptr;
+                if (h->n_build == 0) s.values = s.offsets = nullptr;
+                gather_one_column<uint64_t>(g, col, cs.type, s, g.bidx);
+            }
+        }
+        if (want_probe) {
+            for (int i = 0; i < nk + npp; i++, col++) {
+                const int type = i < nk ? h->key_widths[i] : h->probe_payload_types[i - nk];
+                GatherSrc s{};
+                if (probe_batch && probe_batch->n_rows > 0)
+                    s = gather_stage_column(g, i < nk ? probe_batch->keys[i] : probe_batch->payload[i - nk], type, probe_batch->n_rows, probe_batch->mem);
+                gather_one_column<uint32_t>(g, col, type, s, (probe_batch && probe_batch->n_rows > 0) ? g.pidx : nullptr);
+            }
+        }
+        tm.stop();
+        // null counts; a column without nulls drops its validity buffer pointer (Arrow: NULL bitmap = no nulls)
+        std::vector<unsigned long long> hn(n_cols + 1, 0);
+        CU(cudaMemcpyAsync(hn.data(), dn, (size_t)n_cols * 8, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        for (int c = 0; c < n_cols; c++) {
+            own->cols[c].null_count = (int64_t)hn[c];
+            if (hn[c] == 0) own->cols[c].validity = nullptr;
+        }
+        if (want & B200J_OUT_HOST) {
+            // move every buffer to pinned host memory
+            std::vector<void *> host_bufs;
+            for (int c = 0; c < n_cols; c++) {
+                b200j_out_column &oc = own->cols[c];
+                auto to_host = [&](void *d, size_t bytes) -> void * {
+                    if (!d) return nullptr;
+                    void *hp = pinned_take(h, std::max<size_t>(bytes, 1));
+                    host_bufs.push_back(hp);
+                    if (bytes) CU(cudaMemcpyAsync(hp, d, bytes, cudaMemcpyDeviceToHost, h->stream));
+                    return hp;
+                };
+                oc.values = to_host(oc.values, (size_t)oc.values_bytes);
+                oc.offsets = (int32_t *)to_host(oc.offsets, oc.offsets ? (size_t)(n + 1) * 4 : 0);
+                oc.validity = (uint8_t *)to_host(oc.validity, (size_t)((n + 31) / 32) * 4);
+            }
+            CU(cudaStreamSynchronize(h->stream));
+            for (void *p : own->bufs) big_free(h, p);
+            own->bufs = host_bufs;
+            own->mem = B200J_MEM_HOST;
+        }
+        free_temps(h, g.temps);
+        out->mem = own->mem;
+        out->n_rows = n;
+        out->n_cols = n_cols;
+        out->cols = own->cols.data();
+        out->_owner = own;
+    } catch (...) {
+        free_temps(h, g.temps);
+        for (void *p : own->bufs) big_free(h, p);
+        delete own;
+        throw;
+    }
+}
+
+void do_gathered_release(H *h, b200j_gathered *gth) {
+    if (!gth || !gth->_owner) return;
+    GatheredOwner *own = (GatheredOwner *)gth->_owner;
+    for (void *p : own->bufs) {
+        if (own->mem == B200J_MEM_DEVICE) big_free(h, p);
+        else pinned_give(h, p);
+    }
+    delete own;
+    gth->_owner = nullptr;
+    gth->cols = nullptr;
+    gth->n_cols = 0;
+    gth->n_rows = 0;
+}

@@ -165,6 +165,52 @@ class PairResult:
             pass
 
 
+class GatheredResult:
+    """Owns one b200j_gathered until .release(). Host results convert to pyarrow arrays (copies)."""
+
+    def __init__(self, join: "HashJoin", g: N.Gathered):
+        self._join, self._g = join, g
+        self.n_rows, self.n_cols, self.mem = int(g.n_rows), int(g.n_cols), int(g.mem)
+
+    def column_buffers(self, i: int):
+        c = self._g.cols[i]
+        return {"values": c.values, "offsets": c.offsets, "validity": c.validity, "null_count": int(c.null_count),
+                "values_bytes": int(c.values_bytes)}
+
+    def to_arrow(self, types: Sequence) -> list:
+        """Host results only: one pyarrow array per output column, `types` = their Arrow types in output order."""
+        import pyarrow as pa
+        if self.mem != MEM_HOST:
+            raise ValueError("device result: request OUT_HOST")
+        n, out = self.n_rows, []
+
+        def grab(ptr, nbytes):
+            if not ptr or nbytes == 0:
+                return pa.py_buffer(b"")
+            return pa.py_buffer(C.string_at(ptr, nbytes))
+
+        for i, t in enumerate(types):
+            c = self._g.cols[i]
+            validity = grab(c.validity, ((n + 31) // 32) * 4) if c.validity else None
+            if pa.types.is_string(t) or pa.types.is_binary(t):
+                bufs = [validity, grab(c.offsets, (n + 1) * 4), grab(c.values, int(c.values_bytes))]
+            else:
+                bufs = [validity, grab(c.values, int(c.values_bytes))]
+            out.append(pa.Array.from_buffers(t, n, bufs, null_count=int(c.null_count)))
+        return out
+
+    def release(self):
+        if self._g is not None and self._join._h:
+            N.lib().b200j_gathered_release(self._join._h, C.byref(self._g))
+        self._g = None
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:
+            pass
+
+
 class HashJoin:
     """One join = one b200j_handle: build_push* -> build_finish (per partition) -> probe_batch* -> probe_finish."""
 
@@ -253,6 +299,21 @@ class HashJoin:
         r.struct_size = C.sizeof(N.Result)
         self._check(N.lib().b200j_probe_finish(self._h, partition, want, C.byref(r)))
         return PairResult(self, r)
+
+    # -- gather (a6) ------------------------------------------------------------------------------
+    def gather(self, pairs: PairResult, probe_keys: Optional[Sequence] = None, probe_payload: Sequence = (),
+               want: int = OUT_HOST) -> "GatheredResult":
+        """take_multiple_record_batch (shared.rs:83-92): build key+payload columns at build_idx, then the probe batch's
+        key+payload columns at probe_idx. probe_keys=None (the finaliser) yields all-NULL probe columns."""
+        g = N.Gathered()
+        g.struct_size = C.sizeof(N.Gathered)
+        if probe_keys is not None:
+            b, keep = make_batch(probe_keys, probe_payload)
+            bp = C.byref(b)
+        else:
+            bp, keep = None, None
+        self._check(N.lib().b200j_gather(self._h, C.byref(pairs._res), bp, want, C.byref(g)))
+        return GatheredResult(self, g)
 
     # -- misc -------------------------------------------------------------------------------------
     def hash_keys(self, keys: Sequence) -> np.ndarray:
