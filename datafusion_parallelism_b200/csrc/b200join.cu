@@ -125,6 +125,8 @@ struct b200j_handle {
     std::vector<uint8_t> build_done, probe_done;
     int n_build_done = 0, n_probe_done = 0;
     bool built = false;
+    bool composite = false;            // n_keys > 1: the table is keyed on the 64-bit row hash, equality checked on candidate pairs
+    int table_kw = 8;                  // width of what the table stores: the key column's, or 8 (row hash)
 
     // table
     int32_t layout = B200J_LAYOUT_DIRECT;
@@ -136,6 +138,7 @@ struct b200j_handle {
     DevBuf visited;
     DevBuf parts;                      // radix layout: PartEnt per partition
     RadixScratch rscratch;
+    uint32_t probe_rid_base = 0;       // chunked host probe: row id of the chunk's first row inside the caller's batch
     bool shuffle_armed = false;        // b200j_shuffle_count done, b200j_shuffle_scatter pending
     PartPlan shuffle_plan;
     int64_t shuffle_n = 0;
@@ -473,10 +476,22 @@ uint64_t table_slots_for(int64_t n, float lf) {
     return buckets * 2;
 }
 
+// the build store's key columns as the kernels' KeyCols descriptor (row i of the store = bit i of the bitmap)
+KeyCols build_key_cols(H *h) {
+    KeyCols kc{};
+    kc.n = h->cfg.n_keys;
+    for (int i = 0; i < kc.n; i++) {
+        kc.c[i].values = h->bkeys[i].values.p;
+        kc.c[i].validity = h->bkeys[i].has_nulls ? (const uint8_t *)h->bkeys[i].validity.p : nullptr;
+        kc.c[i].bit_offset = 0;
+        kc.c[i].width = h->key_widths[i];
+    }
+    return kc;
+}
+
 void run_build(H *h) {
     const int64_t n = h->n_build;
-    const int kw = h->key_widths[0];
-    REQUIRE(h->cfg.n_keys == 1, B200J_ERR_UNSUPPORTED, "composite join keys are not implemented yet (single 4/8-byte key column only)");
+    const int kw = h->table_kw;
     const float lf = h->cfg.load_factor > 0.f ? std::min(h->cfg.load_factor, 0.9f) : 0.5f;
 
     // ---- layout choice: direct while the table fits the L2 budget
@@ -496,6 +511,20 @@ void run_build(H *h) {
     }
     const void *keys = h->bkeys[0].values.p;
     const uint8_t *validity = h->bkeys[0].has_nulls ? (const uint8_t *)h->bkeys[0].validity.p : nullptr;
+    void *comp_hash = nullptr, *comp_ok = nullptr;      // composite keys: row hashes + joinable bitmap, needed during the build only
+    struct CompGuard { H *h; void **a, **b; ~CompGuard() { if (*a) big_free(h, *a); if (*b) big_free(h, *b); } } comp_guard{h, &comp_hash, &comp_ok};
+    if (h->composite && n > 0) {
+        CU(big_alloc(h, &comp_hash, (size_t)n * 8 + 16));
+        CU(big_alloc(h, &comp_ok, (size_t)((n + 31) / 32 + 1) * 4));
+        const KeyCols kc = build_key_cols(h);
+        PhaseTimer tm(h, &h->st.ms_build_insert);
+        composite_hash_kernel<<<grid_for(h, n, 256, 8), 256, 0, h->stream>>>(kc, n, h->hk, (uint64_t *)comp_hash, (uint32_t *)comp_ok);
+        h->st.kernel_launches++;
+        CU(cudaGetLastError());
+        tm.stop();
+        keys = comp_hash;
+        validity = (const uint8_t *)comp_ok;
+    }
 
     BuildArgs a{};
     a.hk = h->hk;
@@ -657,7 +686,7 @@ void release_owner(H *h, ResultOwner *ro) {
 // Device-resident probe of `n` keys. Output arrays are device memory owned by *ro. Returns rows produced.
 int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_t bit_offset, int64_t n, const ProbePlan &pl,
                      bool count_only, ResultOwner *ro, int64_t *n_build_null) {
-    const int kw = h->key_widths[0];
+    const int kw = h->table_kw;
     const bool want_build = (pl.mode == PM_PAIRS || pl.mode == PM_OUTER);
     const bool radix = h->layout == B200J_LAYOUT_RADIX;
     int64_t cap = count_only ? 0 : estimate_out_cap(h, n, pl);
@@ -858,6 +887,281 @@ void move_result_to_host(H *h, ResultOwner *ro, int64_t n) {
     ro->mem = B200J_MEM_HOST;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Host batch -> host result, pipelined (the double-buffered pinned-memory feeder).
+// The batch is cut into chunks; while chunk k is partitioned and probed on the join's stream, chunk k+1 is already
+// crossing PCIe on `copy_in` and the pairs of chunk k-1 are going back on `copy_out`: H2D, kernels and D2H overlap and
+// the call runs at the speed of the slower PCIe direction instead of the sum of all three. Chunk results land back to
+// back in ONE pinned result (row ids rebased to the caller's batch), so the caller sees the same b200j_result as from
+// the unchunked path. Every chunk sweeps the whole table once (3.2 GB of HBM reads at C2: noise next to PCIe).
+// ---------------------------------------------------------------------------------------------
+int64_t host_chunk_rows() {
+    const char *e = getenv("B200J_HOST_CHUNK_ROWS");      // read per call: tests shrink it to exercise many chunks
+    const long long x = e ? atoll(e) : 0;
+    return (int64_t)(x > 0 ? x : (32LL << 20));
+}
+
+struct HostPipe {               // everything the pipelined probe must give back on every exit path
+    H *h;
+    void *dk[2] = {nullptr, nullptr};
+    void *dv[2] = {nullptr, nullptr};
+    cudaEvent_t ev_in[2] = {nullptr, nullptr};
+    struct Pending { ResultOwner ro; cudaEvent_t done = nullptr; };
+    std::vector<Pending> pending;            // device results whose D2H copy is still in flight
+    void *hb = nullptr, *hp = nullptr;       // pinned result
+    explicit HostPipe(H *h_) : h(h_) {}
+    void retire(size_t keep) {               // wait for the oldest copies and recycle their device buffers
+        while (pending.size() > keep) {
+            Pending &p = pending.front();
+            if (p.done) { cudaEventSynchronize(p.done); cudaEventDestroy(p.done); }
+            if (p.ro.build_idx) big_free(h, p.ro.build_idx);
+            if (p.ro.probe_idx) big_free(h, p.ro.probe_idx);
+            pending.erase(pending.begin());
+        }
+    }
+    ~HostPipe() {
+        h->probe_rid_base = 0;
+        cudaStreamSynchronize(h->copy_in);
+        cudaStreamSynchronize(h->copy_out);
+        retire(0);
+        for (int i = 0; i < 2; i++) {
+            if (dk[i]) big_free(h, dk[i]);
+            if (dv[i]) big_free(h, dv[i]);
+            if (ev_in[i]) cudaEventDestroy(ev_in[i]);
+        }
+        if (hb) pinned_give(h, hb);
+        if (hp) pinned_give(h, hp);
+    }
+};
+
+int64_t probe_host_pipelined(H *h, const b200j_column &kc, int64_t n, const ProbePlan &pl, bool count_only, ResultOwner *ro,
+                             int64_t *n_build_null) {
+    const int kw = h->table_kw;
+    const int64_t chunk = host_chunk_rows();
+    const int64_t n_chunks = (n + chunk - 1) / chunk;
+    const bool want_build = (pl.mode == PM_PAIRS || pl.mode == PM_OUTER);
+    const bool want_probe = pl.mode != PM_MARK;
+    HostPipe hp(h);
+    for (int i = 0; i < 2; i++) {
+        CU(big_alloc(h, &hp.dk[i], (size_t)chunk * kw + 16));
+        if (kc.validity) CU(big_alloc(h, &hp.dv[i], (size_t)(chunk / 8) + 64));
+        CU(cudaEventCreateWithFlags(&hp.ev_in[i], cudaEventDisableTiming));
+    }
+    // the buffers may have been used by earlier work on the join's stream: the copy stream starts after it
+    cudaEvent_t ev_start = nullptr;
+    CU(cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming));
+    cudaEventRecord(ev_start, h->stream);
+    cudaStreamWaitEvent(h->copy_in, ev_start, 0);
+    cudaEventDestroy(ev_start);
+
+    int64_t host_cap = 0;
+    if (!count_only && want_probe) {
+        host_cap = std::max<int64_t>(estimate_out_cap(h, n, pl), 1);
+        if (want_build) hp.hb = pinned_take(h, (size_t)host_cap * 8);
+        hp.hp = pinned_take(h, (size_t)host_cap * 4);
+    }
+    auto issue_h2d = [&](int64_t k) {
+        const int b = (int)(k & 1);
+        const int64_t lo = k * chunk, m = std::min(chunk, n - lo);
+        CU(cudaMemcpyAsync(hp.dk[b], (const char *)kc.values + (size_t)lo * kw, (size_t)m * kw, cudaMemcpyHostToDevice, h->copy_in));
+        if (kc.validity) {
+            const int64_t first = (kc.bit_offset + lo) >> 3, last = (kc.bit_offset + lo + m + 7) >> 3;
+            CU(cudaMemcpyAsync(hp.dv[b], kc.validity + first, (size_t)(last - first), cudaMemcpyHostToDevice, h->copy_in));
+        }
+        CU(cudaEventRecord(hp.ev_in[b], h->copy_in));
+    };
+    int64_t total = 0, bnull = 0;
+    issue_h2d(0);
+    for (int64_t k = 0; k < n_chunks; k++) {
+        const int b = (int)(k & 1);
+        const int64_t lo = k * chunk, m = std::min(chunk, n - lo);
+        // chunk k+1 goes into the other buffer, whose last reader (chunk k-1) finished before probe_device returned
+        if (k + 1 < n_chunks) issue_h2d(k + 1);
+        CU(cudaStreamWaitEvent(h->stream, hp.ev_in[b], 0));
+        h->probe_rid_base = (uint32_t)lo;
+        HostPipe::Pending pd;
+        int64_t bn = 0;
+        const int64_t cnt = probe_device(h, hp.dk[b], kc.validity ? (const uint8_t *)hp.dv[b] : nullptr, (kc.bit_offset + lo) & 7, m, pl,
+                                         count_only, &pd.ro, &bn);
+        h->probe_rid_base = 0;
+        bnull += bn;
+        if (count_only || !want_probe) {
+            if (pd.ro.build_idx) big_free(h, pd.ro.build_idx);
+            if (pd.ro.probe_idx) big_free(h, pd.ro.probe_idx);
+            total += cnt;
+            continue;
+        }
+        try {
+            if (cnt > 0 && lo > 0 && h->layout != B200J_LAYOUT_RADIX) {
+                add_base_u32_kernel<<<grid_for(h, cnt, 256, 8), 256, 0, h->stream>>>((uint32_t *)pd.ro.probe_idx, cnt, (uint32_t)lo);
+                h->st.kernel_launches++;
+                CU(cudaGetLastError());
+            }
+            if (total + cnt > host_cap) {
+                // duplicate build keys made the result larger than estimated: grow the pinned result (rare)
+                CU(cudaStreamSynchronize(h->copy_out));
+                const int64_t ncap = std::max<int64_t>((int64_t)((double)(total + cnt) * ((double)n / (double)(lo + m)) * 1.1) + 4096, total + cnt);
+                if (want_build) {
+                    void *nb = pinned_take(h, (size_t)ncap * 8);
+                    memcpy(nb, hp.hb, (size_t)total * 8);
+                    pinned_give(h, hp.hb);
+                    hp.hb = nb;
+                }
+                void *np = pinned_take(h, (size_t)ncap * 4);
+                memcpy(np, hp.hp, (size_t)total * 4);
+                pinned_give(h, hp.hp);
+                hp.hp = np;
+                host_cap = ncap;
+            }
+            // results of probe_device are complete (it synchronises the stream); a kernel may still be rebasing row ids
+            CU(cudaEventCreateWithFlags(&pd.done, cudaEventDisableTiming));
+            CU(cudaEventRecord(pd.done, h->stream));
+            CU(cudaStreamWaitEvent(h->copy_out, pd.done, 0));
+            if (cnt > 0) {
+                if (want_build)
+                    CU(cudaMemcpyAsync((char *)hp.hb + (size_t)total * 8, pd.ro.build_idx, (size_t)cnt * 8, cudaMemcpyDeviceToHost, h->copy_out));
+                CU(cudaMemcpyAsync((char *)hp.hp + (size_t)total * 4, pd.ro.probe_idx, (size_t)cnt * 4, cudaMemcpyDeviceToHost, h->copy_out));
+            }
+            CU(cudaEventRecord(pd.done, h->copy_out));
+        } catch (...) {
+            if (pd.done) cudaEventDestroy(pd.done);
+            if (pd.ro.build_idx) big_free(h, pd.ro.build_idx);
+            if (pd.ro.probe_idx) big_free(h, pd.ro.probe_idx);
+            throw;
+        }
+        hp.pending.push_back(pd);
+        total += cnt;
+        hp.retire(2);                 // at most two chunk results wait for PCIe: the loop runs at the speed of the D2H copies
+    }
+    CU(cudaStreamSynchronize(h->copy_out));
+    hp.retire(0);
+    *n_build_null = bnull;
+    if (!count_only && want_probe) {
+        ro->build_idx = hp.hb;
+        ro->probe_idx = hp.hp;
+        ro->mem = B200J_MEM_HOST;
+        hp.hb = hp.hp = nullptr;
+    }
+    return total;
+}
+
+void do_apply_pairs(H *h, int32_t partition, int64_t n_probe_rows, int32_t mem, int64_t n_pairs, const uint64_t *build_idx,
+                    const uint32_t *probe_idx, uint32_t want, b200j_result *out);
+
+// Composite keys (n_keys > 1), the reference's own order of operations on the device:
+//   calculate_hash over all key columns (shared.rs:11-16)            composite_hash_kernel
+//   get_matching_indices on the HASH (shared.rs:29-47)               probe_device on the row hashes, matches only
+//   equal_rows_arr on the candidate pairs (datafusion_private.rs)    equal_rows_kernel + compact_pairs_kernel
+//   join-type index algebra (datafusion_private.rs:85-185)           the same code path b200j_apply_pairs uses
+void do_probe_composite(H *h, int32_t partition, const b200j_batch *b, uint32_t want, b200j_result *out) {
+    const int64_t n = b->n_rows;
+    const int nk = h->cfg.n_keys;
+    std::vector<void *> temps;
+    ResultOwner cand;
+    try {
+        KeyCols pc{};
+        pc.n = nk;
+        for (int i = 0; i < nk && n > 0; i++) {
+            const int w = h->key_widths[i];
+            pc.c[i].width = w;
+            if (b->mem == B200J_MEM_DEVICE) {
+                pc.c[i].values = b->keys[i].values;
+                pc.c[i].validity = b->keys[i].validity;
+                pc.c[i].bit_offset = b->keys[i].bit_offset;
+            } else {
+                void *d = nullptr;
+                CU(big_alloc(h, &d, (size_t)n * w + 16));
+                temps.push_back(d);
+                CU(cudaMemcpyAsync(d, b->keys[i].values, (size_t)n * w, cudaMemcpyHostToDevice, h->stream));
+                pc.c[i].values = d;
+                int64_t boff = 0;
+                pc.c[i].validity = stage_validity(h, b->keys[i], n, B200J_MEM_HOST, temps, &boff);
+                pc.c[i].bit_offset = boff;
+            }
+        }
+        int64_t cnt = 0, bn = 0;
+        if (n > 0) {
+            void *dh = nullptr, *dok = nullptr;
+            CU(big_alloc(h, &dh, (size_t)n * 8 + 16));
+            temps.push_back(dh);
+            CU(big_alloc(h, &dok, (size_t)((n + 31) / 32 + 1) * 4));
+            temps.push_back(dok);
+            {
+                PhaseTimer tm(h, &h->st.ms_probe);
+                composite_hash_kernel<<<grid_for(h, n, 256, 8), 256, 0, h->stream>>>(pc, n, h->hk, (uint64_t *)dh, (uint32_t *)dok);
+                h->st.kernel_launches++;
+                CU(cudaGetLastError());
+                tm.stop();
+            }
+            cnt = probe_device(h, dh, (const uint8_t *)dok, 0, n, ProbePlan{PM_PAIRS, false}, false, &cand, &bn);
+            if (cnt > 0) {
+                // equality on the key VALUES: drops hash collisions
+                CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
+                const KeyCols bc = build_key_cols(h);
+                equal_rows_kernel<<<grid_for(h, cnt, 256, 8), 256, 0, h->stream>>>(bc, pc, (uint64_t *)cand.build_idx, (const uint32_t *)cand.probe_idx, cnt,
+                                                                                   &h->d_ctr->build_null_out);
+                h->st.kernel_launches++;
+                CU(cudaGetLastError());
+                CU(cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
+                CU(cudaStreamSynchronize(h->stream));
+                const int64_t failed = (int64_t)h->h_ctr->build_null_out;
+                if (failed > 0) {
+                    const int64_t keep = cnt - failed;
+                    void *ob2 = nullptr, *op2 = nullptr;
+                    CU(big_alloc(h, &ob2, (size_t)std::max<int64_t>(keep, 1) * 8));
+                    temps.push_back(ob2);
+                    CU(big_alloc(h, &op2, (size_t)std::max<int64_t>(keep, 1) * 4));
+                    temps.push_back(op2);
+                    CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
+                    compact_pairs_kernel<<<grid_for(h, cnt, CP_TILE, 8), CP_THREADS, 0, h->stream>>>((const uint64_t *)cand.build_idx, (const uint32_t *)cand.probe_idx,
+                                                                                                     (uint64_t)cnt, (uint64_t *)ob2, (uint32_t *)op2, &h->d_ctr->out_count);
+                    h->st.kernel_launches++;
+                    h->st.compact_launches++;
+                    CU(cudaGetLastError());
+                    std::swap(cand.build_idx, ob2);      // the unfiltered arrays are now the temps
+                    std::swap(cand.probe_idx, op2);
+                    temps[temps.size() - 2] = ob2;
+                    temps[temps.size() - 1] = op2;
+                    cnt = keep;
+                }
+            }
+        }
+        h->st.probe_rows += n;
+        if (want & B200J_OUT_MATCHES_ONLY) {
+            // the caller applies a JoinFilter and comes back through b200j_apply_pairs
+            ResultOwner *ro = new ResultOwner(cand);
+            cand = ResultOwner{};
+            try {
+                if (want & B200J_OUT_COUNT_ONLY) {
+                    if (ro->build_idx) big_free(h, ro->build_idx);
+                    if (ro->probe_idx) big_free(h, ro->probe_idx);
+                    ro->build_idx = ro->probe_idx = nullptr;
+                } else if (want & B200J_OUT_HOST) {
+                    move_result_to_host(h, ro, cnt);
+                }
+            } catch (...) {
+                release_owner(h, ro);
+                throw;
+            }
+            fill_result(out, ro, cnt, ro->mem);
+            out->n_build_null = 0;
+            out->n_probe_null = 0;
+            h->st.result_rows += cnt;
+        } else {
+            do_apply_pairs(h, partition, n, B200J_MEM_DEVICE, cnt, (const uint64_t *)cand.build_idx, (const uint32_t *)cand.probe_idx, want, out);
+        }
+        if (cand.build_idx) big_free(h, cand.build_idx);
+        if (cand.probe_idx) big_free(h, cand.probe_idx);
+        cand = ResultOwner{};
+        free_temps(h, temps);
+    } catch (...) {
+        if (cand.build_idx) big_free(h, cand.build_idx);
+        if (cand.probe_idx) big_free(h, cand.probe_idx);
+        free_temps(h, temps);
+        throw;
+    }
+}
+
 void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want, b200j_result *out) {
     REQUIRE(partition >= 0 && partition < h->cfg.n_partitions, B200J_ERR_INVALID, "partition out of range");
     REQUIRE(h->built, B200J_ERR_INVALID, "probe before every partition finished the build side");
@@ -865,6 +1169,10 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
     REQUIRE(out != nullptr && out->struct_size >= sizeof(b200j_result), B200J_ERR_INVALID, "result struct missing or too small");
     check_batch(h, b, h->cfg.n_probe_payload);
     REQUIRE(b->n_rows < 0xffff0000LL, B200J_ERR_UNSUPPORTED, "probe batch of more than 2^32 - 2^16 rows (probe indices are UInt32)");
+    if (h->composite) {
+        do_probe_composite(h, partition, b, want, out);
+        return;
+    }
     const ProbePlan pl = plan_for(h->cfg.join_type, (want & B200J_OUT_MATCHES_ONLY) != 0);
     const bool count_only = (want & B200J_OUT_COUNT_ONLY) != 0;
     const int kw = h->key_widths[0];
@@ -876,6 +1184,8 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
         if (b->mem == B200J_MEM_DEVICE || n == 0) {
             const b200j_column &kc = b->keys[0];
             total = probe_device(h, n ? kc.values : nullptr, n ? kc.validity : nullptr, n ? kc.bit_offset : 0, n, pl, count_only, ro, &n_bnull);
+        } else if (((want & B200J_OUT_HOST) || count_only) && n > host_chunk_rows() + host_chunk_rows() / 2) {
+            total = probe_host_pipelined(h, b->keys[0], n, pl, count_only, ro, &n_bnull);
         } else {
             const b200j_column &kc = b->keys[0];
             void *dk = nullptr;
@@ -890,7 +1200,7 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
             if (ro->build_idx) big_free(h, ro->build_idx);
             if (ro->probe_idx) big_free(h, ro->probe_idx);
             ro->build_idx = ro->probe_idx = nullptr;
-        } else if (want & B200J_OUT_HOST) {
+        } else if ((want & B200J_OUT_HOST) && ro->mem != B200J_MEM_HOST) {
             move_result_to_host(h, ro, total);
         }
         free_temps(h, temps);
@@ -1198,6 +1508,8 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
         if (!(k[0] | k[1] | k[2] | k[3])) keys_with_seed(0, k);
         h->hk = HashKeys{k[0], k[1], k[2], k[3], cfg->hash_flags, 0};
         h->timing = (cfg->flags & B200J_FLAG_TIMING) != 0;
+        h->composite = cfg->n_keys > 1;
+        h->table_kw = h->composite ? 8 : cfg->key_widths[0];
         cudaDeviceProp prop{};
         CU(cudaGetDeviceProperties(&prop, cfg->device));
         h->sm_count = prop.multiProcessorCount;

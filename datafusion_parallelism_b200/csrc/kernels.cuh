@@ -242,6 +242,56 @@ __global__ void __launch_bounds__(256) hash_keys_kernel(KeyCols cols, int64_t n,
     }
 }
 
+// Composite join keys (n_keys > 1): the table is keyed on the 64-bit ROW HASH, exactly like the reference's map
+// (version10 stores hashes, new_map_3.rs:250-303), and key equality is checked afterwards on the candidate pairs
+// (equal_rows_arr, datafusion_private.rs:40-80). This kernel produces the row hashes (create_hashes over all key
+// columns, combine_hashes from the second column on) and the "joinable" bitmap: a row with a NULL in ANY key column
+// can never match (null_equals_null = false, inner.rs:105-107), so it is kept out of the table / the lookup.
+__global__ void __launch_bounds__(256) composite_hash_kernel(KeyCols cols, int64_t n, HashKeys hk, uint64_t *__restrict__ out,
+                                                             uint32_t *__restrict__ joinable) {
+    const int lane = threadIdx.x & 31;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x - lane; i0 < n; i0 += stride) {
+        const int64_t i = i0 + lane;
+        bool ok = i < n;
+        uint64_t h = 0;
+        if (i < n) {
+            for (int c = 0; c < cols.n; c++) {
+                const KeyCol &kc = cols.c[c];
+                if (!bit_valid(kc.validity, kc.bit_offset + i)) { ok = false; continue; }
+                const uint64_t v = kc.width == 8 ? reinterpret_cast<const unsigned long long *>(kc.values)[i]
+                                                 : (uint64_t)reinterpret_cast<const uint32_t *>(kc.values)[i];
+                const uint64_t hv = hash_one(hk, v);
+                h = (c == 0) ? hv : combine_hashes(hv, h);
+            }
+            if (hk.flags & 2) h &= 0x3ffULL;       // B200J_HASH_TEST_COLLIDE: 1024 hash values, so equal_rows has work to do
+            out[i] = h;
+        }
+        const uint32_t w = __ballot_sync(0xffffffffu, ok);
+        if (lane == 0) joinable[i0 >> 5] = w;
+    }
+}
+
+// equal_rows_arr on candidate pairs: a pair survives when every key column is non-NULL and equal on both sides.
+// Failed pairs get build index ~0 (compacted away by compact_pairs_kernel); their number goes to *n_failed.
+__global__ void __launch_bounds__(256) equal_rows_kernel(KeyCols build, KeyCols probe, uint64_t *__restrict__ build_idx,
+                                                         const uint32_t *__restrict__ probe_idx, int64_t n, unsigned long long *n_failed) {
+    uint32_t failed = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t b = (int64_t)build_idx[i], p = (int64_t)probe_idx[i];
+        bool eq = true;
+        for (int c = 0; c < build.n && eq; c++) {
+            const KeyCol &bc = build.c[c], &pc = probe.c[c];
+            if (!bit_valid(bc.validity, bc.bit_offset + b) || !bit_valid(pc.validity, pc.bit_offset + p)) { eq = false; break; }
+            if (bc.width == 8) eq = reinterpret_cast<const unsigned long long *>(bc.values)[b] == reinterpret_cast<const unsigned long long *>(pc.values)[p];
+            else eq = reinterpret_cast<const uint32_t *>(bc.values)[b] == reinterpret_cast<const uint32_t *>(pc.values)[p];
+        }
+        if (!eq) { build_idx[i] = ~0ULL; failed++; }
+    }
+    const unsigned long long f = __reduce_add_sync(0xffffffffu, failed);
+    if ((threadIdx.x & 31) == 0 && f) atomicAdd(n_failed, f);
+}
+
 // ------------------------------------------------------------------------------------------------
 // a2: build — open addressing, atomicCAS claim on the key word, atomicAdd on the slot's count
 // ------------------------------------------------------------------------------------------------
@@ -782,6 +832,15 @@ __global__ void __launch_bounds__(256) fill_u64_kernel(uint64_t *p, int64_t n, u
 }
 __global__ void __launch_bounds__(256) fill_u32_kernel(uint32_t *p, int64_t n, uint32_t v) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
+}
+
+// Probe row ids of one chunk of a host batch -> row ids of the batch (direct layout; the radix layout's partition pass
+// adds the base while it writes the row-id array). NULL markers stay.
+__global__ void __launch_bounds__(256) add_base_u32_kernel(uint32_t *p, int64_t n, uint32_t base) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t v = p[i];
+        if (v != 0xffffffffu) p[i] = v + base;
+    }
 }
 
 // Validity concat for the build store: dst bits [dst_off, dst_off + n) <- src bits [src_off, src_off + n)

@@ -318,7 +318,10 @@ constexpr int PD_THREADS = 256;
 constexpr int PD_WARPS   = PD_THREADS / 32;
 constexpr int PD_ITEMS   = 4;
 constexpr int PD_WTILE   = 32 * PD_ITEMS;             // rows per warp iteration
-constexpr int PD_SUPER   = 16384;                     // rows per CTA claim (one global atomic)
+#ifndef B200J_PD_SUPER
+#define B200J_PD_SUPER 16384
+#endif
+constexpr int PD_SUPER   = B200J_PD_SUPER;             // rows per CTA claim (one global atomic)
 constexpr int PD_QCAP    = 32 + PD_WTILE;             // a queue holds < 32 entries between iterations
 
 struct PDShared {

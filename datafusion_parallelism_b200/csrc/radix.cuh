@@ -71,7 +71,7 @@ struct PartArgs {
     uint32_t           *out_rid;
     void               *dest_keys[RP_MAX_DEST + 1];    // DEST mode: output base per bin (may be peer memory)
     uint32_t           *dest_rid[RP_MAX_DEST + 1];
-    uint32_t            rid_base;         // DEST mode: added to the local row index (row ids of a chunked side)
+    uint32_t            rid_base;         // added to the local row index (row ids of a chunked side)
 };
 
 
@@ -409,7 +409,7 @@ __global__ void __launch_bounds__(SC_THREADS, 2) part_scatter_kernel(PartArgs a)
 
         // ---- write-out
         const uint32_t total = inner ? (uint32_t)SC_TILE : s_total;
-        const uint32_t rid0 = vbase - mis + (DEST ? a.rid_base : 0u);
+        const uint32_t rid0 = vbase - mis + a.rid_base;
 #pragma unroll 4
         for (uint32_t i = t; i < total; i += SC_THREADS) {
             const uint32_t pm = s_perm[i];

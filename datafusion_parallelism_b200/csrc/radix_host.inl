@@ -103,6 +103,7 @@ void radix_partition(H *h, const void *keys, const uint8_t *validity, int64_t bi
     PartPlan pl = part_plan(h, keys, validity, bit_offset, kw, n, bits, 0);
     pl.a.out_keys = out_keys;
     pl.a.out_rid = out_rid;
+    pl.a.rid_base = h->probe_rid_base;     // non-zero only while a host batch is probed chunk by chunk
     part_hist(h, pl, false);
     part_scatter(h, pl);
     tm.stop();

@@ -117,14 +117,18 @@ typedef struct {
     int32_t   n_partitions;           /* number of DataFusion partitions that will call build/probe   */
     int32_t   device;                 /* CUDA device ordinal                                          */
     int32_t   n_keys;
-    const int32_t *key_widths;        /* [n_keys] 4 or 8 (Int32/UInt32/Date32 | Int64/UInt64/Timestamp ...) */
+    const int32_t *key_widths;        /* [n_keys] 4 or 8 (Int32/UInt32/Date32 | Int64/UInt64/Timestamp ...). n_keys > 1
+                                         (composite key): the table is keyed on the row hash and key equality is checked
+                                         on the candidate pairs, as the reference does (datafusion_private.rs:40-80)      */
     int32_t   n_build_payload;
     const int32_t *build_payload_types;   /* [n_build_payload] width or B200J_T_UTF8                  */
     int32_t   n_probe_payload;
     const int32_t *probe_payload_types;
     uint64_t  hash_keys[4];           /* ahash RandomState keys; all zero => RandomState::with_seed(0) over the
                                          fixed PI seeds (shared.rs:14)                                */
-    int32_t   hash_flags;             /* bit0: 0 = `specialize` integer path (nightly, as the reference), 1 = stable */
+    int32_t   hash_flags;             /* bit0: 0 = `specialize` integer path (nightly, as the reference), 1 = stable;
+                                         bit1 (tests only): composite-key row hashes truncated to 10 bits, so that distinct
+                                         keys collide and the equal_rows filter is exercised                          */
     int32_t   layout;                 /* B200J_LAYOUT_*                                               */
     int32_t   radix_bits;             /* 0 = choose; else log2(number of radix partitions)            */
     float     load_factor;            /* 0 = default 0.5                                              */

@@ -95,6 +95,59 @@ def test_pairs_match_oracle(pkg, join_type, layout, radix_bits, dtype, null_frac
 
 
 @pytest.mark.parametrize("layout,radix_bits", LAYOUT_CASES)
+@pytest.mark.parametrize("join_type", JOIN_TYPES)
+def test_pipelined_host_probe(pkg, monkeypatch, join_type, layout, radix_bits):
+    """Host batch in, host pairs out: the library cuts the batch into chunks and overlaps H2D / kernels / D2H
+    (probe_host_pipelined). Chunk size shrunk so one batch is ~17 ragged chunks; NULLs with a non-zero bitmap offset;
+    duplicate build keys so the pinned result has to grow; the result must be that of the unchunked call."""
+    monkeypatch.setenv("B200J_HOST_CHUNK_ROWS", "3001")
+    rng = np.random.default_rng(hash((join_type, layout, "pipe")) & 0xFFFFFFFF)
+    bk, bv, pk, pv = gen_case(rng, 20_000, 50_003, 6_000, 0.07, np.int64)
+    probe = as_arrow(pk, pv, pa.int64()).slice(5)               # Arrow array offset 5: bitmap bit offset, unaligned keys
+    got, fins, stats = run_gpu(pkg, join_type, [as_arrow(bk, bv, pa.int64())], [probe], 8, layout, radix_bits)
+    want, want_fin = run_oracle(join_type, as_arrow(bk, bv, pa.int64()), [probe])
+    assert_pairs_equal(got[0], want[0], f"{join_type} pipelined")
+    assert_pairs_equal(fins[-1], want_fin, f"{join_type} finaliser")
+    with pkg.HashJoin(join_type, key_widths=(8,), layout=layout, radix_bits=radix_bits) as j:
+        j.build_push(0, [as_arrow(bk, bv, pa.int64())])
+        j.build_finish(0)
+        r = j.probe_batch(0, [probe], want=pkg.OUT_PAIRS | pkg.OUT_COUNT_ONLY)
+        assert r.n == len(want[0][1])
+        r.release()
+
+
+@pytest.mark.parametrize("layout,radix_bits", [("direct", 0), ("radix", 5)])
+@pytest.mark.parametrize("join_type", JOIN_TYPES)
+@pytest.mark.parametrize("collide", [0, 2])
+def test_composite_keys(pkg, join_type, layout, radix_bits, collide):
+    """Two key columns (Int64, Int32) with NULLs in either (TPC-H Q9's (ps_partkey, ps_suppkey) shape): the table is keyed on
+    the combined row hash, equality is checked on the candidate pairs. collide=2 truncates the row hash to 10 bits so that
+    almost every candidate is a hash collision the equality filter has to drop."""
+    rng = np.random.default_rng(hash((join_type, layout, collide, "comp")) & 0xFFFFFFFF)
+    nb, npr = 12_000, 30_000
+    b0, b1 = rng.integers(0, 300, nb).astype(np.int64), rng.integers(0, 40, nb).astype(np.int32)
+    p0, p1 = rng.integers(-20, 330, npr).astype(np.int64), rng.integers(0, 44, npr).astype(np.int32)
+    bv0, bv1 = rng.random(nb) >= 0.05, rng.random(nb) >= 0.05
+    pv0, pv1 = rng.random(npr) >= 0.05, rng.random(npr) >= 0.05
+    build = [as_arrow(b0, bv0, pa.int64()), as_arrow(b1, bv1, pa.int32())]
+    probes = [[as_arrow(p0[lo:lo + 11_000], pv0[lo:lo + 11_000], pa.int64()), as_arrow(p1[lo:lo + 11_000], pv1[lo:lo + 11_000], pa.int32())]
+              for lo in range(0, npr, 11_000)]
+    oj = oracle.OracleJoin(join_type, build)
+    with pkg.HashJoin(join_type, key_widths=(8, 4), layout=layout, radix_bits=radix_bits, hash_flags=collide) as j:
+        j.build_push(0, build)
+        j.build_finish(0)
+        for i, pb in enumerate(probes):
+            r = j.probe_batch(0, pb)
+            assert_pairs_equal(r.numpy(), oj.probe_batch(pb, len(pb[0])), f"{join_type} batch {i}")
+            r.release()
+        r = j.probe_finish(0)
+        assert_pairs_equal(r.numpy(), oj.finish(), f"{join_type} finaliser")
+        r.release()
+        if collide == 0:
+            assert np.array_equal(j.hash_keys(probes[0]), oracle.create_hashes(probes[0]))
+
+
+@pytest.mark.parametrize("layout,radix_bits", LAYOUT_CASES)
 def test_unique_keys_one_to_one(pkg, layout, radix_bits):
     """The BASELINE C1/C2 shape in miniature: unique build keys (a permutation), uniform probe, every probe row matches once."""
     n_build, n_probe = 1 << 18, 1 << 20
