@@ -8,7 +8,6 @@
 #include "kernels.cuh"
 #include "radix.cuh"
 #include "probe.cuh"
-#include "probe_dense.cuh"
 #include "gather.cuh"
 
 #include <algorithm>
@@ -116,8 +115,6 @@ struct b200j_handle {
     int probe_ctas_per_sm = 4;
     int dense_ctas_per_sm = 4;
     bool dense_ok = true;              // B200J_NO_DENSE=1 forces the staged probe kernel (tuning / tests)
-    bool dense_tma = true;             // B200J_DENSE_TMA=0: dense probe with LSU key loads / result stores (the first version)
-    int dense_tma_ctas_per_sm = 6;
     int64_t l2_bytes = 0;
     bool timing = false;
 
@@ -741,21 +738,11 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
                 a.out_probe = (uint32_t *)tr;
                 a.out_cap = (uint64_t)rows;
                 a.visited = (uint32_t *)h->visited.p;
-                a.part_off = h->rscratch.off;          // partition offsets of this batch's stream, left by radix_partition
                 a.ctr = h->d_ctr;
                 {
                     PhaseTimer tm(h, &h->st.ms_probe);
                     const int grid = grid_for(h, pn, PD_SUPER, h->dense_ctas_per_sm);
-                    if (h->dense_tma) {
-                        const int g2 = grid_for(h, pn, PW_TILE * PW_WARPS, h->dense_tma_ctas_per_sm);
-                        if (kw == 8) {
-                            if (pl.mark) probe_dense_tma_kernel<8, true><<<g2, PW_WARPS * 32, 0, h->stream>>>(a);
-                            else probe_dense_tma_kernel<8, false><<<g2, PW_WARPS * 32, 0, h->stream>>>(a);
-                        } else {
-                            if (pl.mark) probe_dense_tma_kernel<4, true><<<g2, PW_WARPS * 32, 0, h->stream>>>(a);
-                            else probe_dense_tma_kernel<4, false><<<g2, PW_WARPS * 32, 0, h->stream>>>(a);
-                        }
-                    } else if (kw == 8) {
+                    if (kw == 8) {
                         if (pl.mark) probe_dense_kernel<8, true><<<grid, PD_THREADS, 0, h->stream>>>(a);
                         else probe_dense_kernel<8, false><<<grid, PD_THREADS, 0, h->stream>>>(a);
                     } else {
@@ -1537,14 +1524,6 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
             else
                 cudaGetLastError();
             if (const char *e = getenv("B200J_NO_DENSE")) h->dense_ok = atoi(e) == 0;
-            if (const char *e = getenv("B200J_DENSE_TMA")) h->dense_tma = atoi(e) != 0;
-            for (auto f : {(const void *)probe_dense_tma_kernel<8, false>, (const void *)probe_dense_tma_kernel<8, true>,
-                           (const void *)probe_dense_tma_kernel<4, false>, (const void *)probe_dense_tma_kernel<4, true>})
-                if (cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared) != cudaSuccess) cudaGetLastError();
-            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, probe_dense_tma_kernel<8, false>, PW_WARPS * 32, 0) == cudaSuccess && occ > 0)
-                h->dense_tma_ctas_per_sm = occ;
-            else
-                cudaGetLastError();
         }
         h->l2_bytes = prop.l2CacheSize;
         if (cfg->stream) {

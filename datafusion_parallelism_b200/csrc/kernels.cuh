@@ -136,12 +136,7 @@ __device__ __forceinline__ void locate(const TableView &tv, uint32_t hp, uint32_
     }
 }
 
-// Home bucket of a key inside its (partition's) table. The reference hash (hash_one, bit-identical to ahash) selects the
-// radix partition and the destination GPU; INSIDE a table the placement function is free, and a Fibonacci multiply
-// (3 SASS instructions against 20 for hash_one) lets the dense probe drop the row hash altogether: its chunks know their
-// partition from their position in the partitioned stream.
-__device__ __forceinline__ uint32_t slot_hash(uint64_t key) { return (uint32_t)((key * 0x9E3779B97F4A7C15ULL) >> 32); }
-__device__ __forceinline__ uint32_t home_bucket(uint64_t key, uint32_t nb) { return __umulhi(slot_hash(key), nb); }
+__device__ __forceinline__ uint32_t home_bucket(uint64_t h, uint32_t nb) { return __umulhi((uint32_t)h, nb); }
 __device__ __forceinline__ uint32_t next_bucket(uint32_t b, uint32_t nb) { return b + 1u == nb ? 0u : b + 1u; }
 __device__ __forceinline__ Slot *bucket_ptr(const TableView &tv, uint32_t base, uint32_t b) {
     return tv.slots + 2ull * ((unsigned long long)base + b);
@@ -318,7 +313,7 @@ __device__ __forceinline__ Slot *find_or_claim(const TableView &tv, const HashKe
     const uint64_t h = hash_one(hk, key);
     uint32_t base, nb;
     locate<RADIX>(tv, (uint32_t)(h >> 32), base, nb);
-    uint32_t b = home_bucket(key, nb);
+    uint32_t b = home_bucket(h, nb);
     for (;;) {
         Slot *s = bucket_ptr(tv, base, b);      // slots of a bucket fill in order: even first
 #pragma unroll
@@ -457,7 +452,6 @@ struct ProbeArgs {
     uint32_t       *out_probe;
     uint64_t        out_cap;
     uint32_t       *visited;      // bitmap over build rows (MARK)
-    const unsigned long long *part_off;   // radix layout: first row of every partition in the partitioned probe stream (or null)
     Counters       *ctr;
 };
 
@@ -576,7 +570,7 @@ __device__ __forceinline__ void probe_tile(const ProbeArgs &a, uint32_t tile, in
             uint32_t base, nb;
             hp[q] = (uint32_t)(h >> 32);
             locate<RADIX>(a.tv, hp[q], base, nb);
-            idx[q] = home_bucket(key[q], nb);
+            idx[q] = home_bucket(h, nb);
             const Slot *p = key[q] ? bucket_ptr(a.tv, base, idx[q]) : a.tv.zero_slot;
             k0[q] = v0[q] = k1[q] = v1[q] = 0ULL;
             if (!GUARD || ((pending >> q) & 1u)) load_bucket(p, k0[q], v0[q], k1[q], v1[q]);

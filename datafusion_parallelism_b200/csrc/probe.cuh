@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(PF_THREADS) probe_fast_kernel(ProbeArgs a) {
                 const uint64_t h = hash_one(a.hk, key[q]);
                 uint32_t base, nb;
                 locate<RADIX>(a.tv, (uint32_t)(h >> 32), base, nb);
-                const Slot *p = key[q] ? bucket_ptr(a.tv, base, home_bucket(key[q], nb)) : a.tv.zero_slot;
+                const Slot *p = key[q] ? bucket_ptr(a.tv, base, home_bucket(h, nb)) : a.tv.zero_slot;
                 load_bucket(p, k0[q], v0[q], k1[q], v1[q]);
             }
             // ---- resolve from that bucket: hit, provable miss (bucket has a free slot; slots fill in order, so a free
@@ -229,7 +229,7 @@ __global__ void __launch_bounds__(PF_THREADS) probe_fast_kernel(ProbeArgs a) {
                 const uint64_t h = hash_one(a.hk, key);
                 uint32_t base, nb;
                 locate<RADIX>(a.tv, (uint32_t)(h >> 32), base, nb);
-                uint32_t idx = home_bucket(key, nb);
+                uint32_t idx = home_bucket(h, nb);
                 const Slot *p = key ? bucket_ptr(a.tv, base, idx) : a.tv.zero_slot;
                 for (;;) {
                     unsigned long long k0, v0, k1, v1;
@@ -341,7 +341,7 @@ __device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long lo
         const uint64_t h = hash_one(a.hk, key);
         uint32_t base, nb;
         locate<true>(a.tv, (uint32_t)(h >> 32), base, nb);
-        uint32_t b = next_bucket(home_bucket(key, nb), nb);        // the home bucket was full without the key
+        uint32_t b = next_bucket(home_bucket(h, nb), nb);          // the home bucket was full without the key
         unsigned long long res = ~0ULL;
         for (;;) {
             const uint32_t b2 = next_bucket(b, nb);
@@ -423,7 +423,7 @@ __global__ void __launch_bounds__(PD_THREADS) probe_dense_kernel(ProbeArgs a) {
                 const uint64_t h = hash_one(a.hk, key[q]);
                 uint32_t base, nb;
                 locate<true>(a.tv, (uint32_t)(h >> 32), base, nb);
-                const Slot *p = key[q] ? bucket_ptr(a.tv, base, home_bucket(key[q], nb)) : a.tv.zero_slot;
+                const Slot *p = key[q] ? bucket_ptr(a.tv, base, home_bucket(h, nb)) : a.tv.zero_slot;
                 load_bucket(p, k0[q], v0[q], k1[q], v1[q]);
             }
             // ---- resolve; unresolved lookups go to the warp's queue
