@@ -135,6 +135,7 @@ struct b200j_handle {
     uint64_t n_slots = 0;
     DevBuf zero_slot;
     DevBuf rowids;
+    DevBuf bigruns;                    // BigRun list of the probe launch in flight (allocated when the build has long duplicate runs)
     DevBuf visited;
     DevBuf parts;                      // radix layout: PartEnt per partition
     RadixScratch rscratch;
@@ -832,6 +833,12 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
             a.out_cap = (uint64_t)cap;
             a.visited = (uint32_t *)h->visited.p;
             a.ctr = h->d_ctr;
+            constexpr uint32_t BIG_CAP = 1u << 18;
+            if (h->st.duplicate_rows >= (int64_t)BIG_RUN_ROWS && (cap > 0 || pl.mark)) {
+                dev_alloc(h, h->bigruns, (size_t)BIG_CAP * sizeof(BigRun));
+                a.big_runs = (BigRun *)h->bigruns.p;
+                a.big_cap = BIG_CAP;
+            }
             if (pn > 0) {
                 PhaseTimer tm(h, &h->st.ms_probe);
                 launch_probe(h, pl, a, kw, radix);
@@ -843,6 +850,21 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
             const int64_t total = (int64_t)h->h_ctr->out_count;
             *n_build_null = (int64_t)h->h_ctr->build_null_out + extra;
             if (count_only || total + extra <= cap) {
+                const uint32_t n_big = a.big_runs ? std::min<uint32_t>(h->h_ctr->big_count, a.big_cap) : 0u;
+                if (n_big > 0) {
+                    // heavy-hitter runs the probe kernel only reserved room for: the whole grid copies them (marking is
+                    // idempotent, so a retried launch that deferred them twice is harmless)
+                    PhaseTimer tm(h, &h->st.ms_probe);
+                    const int grid = h->sm_count * 8;
+                    const bool emit = want_build && !count_only;
+                    if (emit && pl.mark) expand_runs_kernel<true, true><<<grid, 256, 0, h->stream>>>(a.big_runs, n_big, a.tv.rowids, a.out_build, a.out_probe, a.out_cap, a.visited);
+                    else if (emit) expand_runs_kernel<true, false><<<grid, 256, 0, h->stream>>>(a.big_runs, n_big, a.tv.rowids, a.out_build, a.out_probe, a.out_cap, a.visited);
+                    else if (pl.mark) expand_runs_kernel<false, true><<<grid, 256, 0, h->stream>>>(a.big_runs, n_big, a.tv.rowids, a.out_build, a.out_probe, a.out_cap, a.visited);
+                    h->st.kernel_launches++;
+                    CU(cudaGetLastError());
+                    tm.stop();
+                    CU(cudaStreamSynchronize(h->stream));
+                }
                 if (extra > 0 && !count_only) {
                     emit_null_rows_kernel<<<grid_for(h, extra, 256, 8), 256, 0, h->stream>>>(prid + pn, extra, (uint64_t *)ob, (uint32_t *)op,
                                                                                              (uint64_t)total);
@@ -1575,7 +1597,7 @@ int32_t b200j_destroy(b200j_handle *h) {
     for (auto *v : {&h->bkeys, &h->bpayload})
         for (auto &c : *v) { fr(c.values); fr(c.offsets); fr(c.validity); }
     radix_release(h);
-    fr(h->slots); fr(h->zero_slot); fr(h->rowids); fr(h->visited); fr(h->parts);
+    fr(h->slots); fr(h->zero_slot); fr(h->rowids); fr(h->bigruns); fr(h->visited); fr(h->parts);
     cudaStreamSynchronize(h->stream);
     for (auto &b : h->blocks) cudaFreeAsync(b.p, h->stream);
     h->blocks.clear();

@@ -97,7 +97,7 @@ struct Counters {
     unsigned long long out_count;     // rows produced (may exceed capacity: then nothing past capacity is written)
     unsigned long long build_null_out;
     unsigned int       next_tile;     // dynamic tile scheduler
-    unsigned int       _pad;
+    unsigned int       big_count;     // duplicate runs deferred to expand_runs_kernel (may exceed the list's capacity)
     // build
     unsigned long long distinct;
     unsigned long long dup_rows;
@@ -438,6 +438,19 @@ enum ProbeMode : int {
     PM_MARK  = 4,   // LeftSemi / LeftAnti: only mark visited build rows
 };
 
+// A duplicate run too long for one warp (a heavy-hitter key: C3's Zipf build side has runs of millions of rows). The probe
+// kernel reserves the run's output range as usual but leaves the copy to expand_runs_kernel, where the whole grid shares
+// it: with the copy inside the probe kernel, ONE warp walked a 2.7 M-row run for every probe row that hit the key and the
+// launch took 135 ms for 1 B probe rows; deferred, it is bounded by the output bandwidth.
+struct BigRun {
+    unsigned long long pos;       // first output row of the run's (build, probe) pairs
+    uint32_t           run;       // start of the run in rowids[]
+    uint32_t           cnt;
+    uint32_t           prow;      // the probe row
+    uint32_t           _pad;
+};
+constexpr uint32_t BIG_RUN_ROWS = 4096;
+
 struct ProbeArgs {
     const void     *keys;
     const uint8_t  *validity;
@@ -452,6 +465,9 @@ struct ProbeArgs {
     uint32_t       *out_probe;
     uint64_t        out_cap;
     uint32_t       *visited;      // bitmap over build rows (MARK)
+    struct BigRun  *big_runs;     // list for duplicate runs too long for one warp (or null)
+    uint32_t        big_cap;
+    uint32_t        _pad2;
     Counters       *ctr;
 };
 
@@ -469,6 +485,55 @@ __device__ __forceinline__ void mark_visited(uint32_t *visited, uint32_t row) {
     uint32_t *w = visited + (row >> 5);
     const uint32_t bit = 1u << (row & 31);
     if (!(__ldcg(w) & bit)) atomicOr(w, bit);
+}
+
+// One long duplicate run (>= 32 rows), called by the whole warp with warp-uniform arguments: deferred to the grid-wide
+// expansion when it is a heavy hitter, else copied here, coalesced.
+template <bool EMIT, bool MARK>
+__device__ __forceinline__ void copy_long_run(const ProbeArgs &a, unsigned long long pos, uint32_t cnt, uint32_t rb, uint32_t pr, int lane) {
+    if (cnt >= BIG_RUN_ROWS && a.big_runs != nullptr) {
+        uint32_t slot = 0;
+        if (lane == 0) slot = atomicAdd(&a.ctr->big_count, 1u);
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        if (slot < a.big_cap) {
+            if (lane == 0) a.big_runs[slot] = BigRun{pos, rb, cnt, pr, 0u};
+            return;
+        }
+    }
+    for (uint32_t k = lane; k < cnt; k += 32) {
+        const uint32_t br = __ldcg(a.tv.rowids + rb + k);
+        if (EMIT && pos + k < a.out_cap) {
+            a.out_build[pos + k] = (uint64_t)br;
+            a.out_probe[pos + k] = pr;
+        }
+        if (MARK) mark_visited(a.visited, br);
+    }
+}
+
+// The deferred runs, shared out over the grid in chunks of EXPAND_CHUNK rows (global chunk g goes to CTA g % gridDim.x).
+constexpr uint32_t EXPAND_CHUNK = 2048;
+template <bool EMIT, bool MARK>
+__global__ void __launch_bounds__(256) expand_runs_kernel(const BigRun *__restrict__ runs, uint32_t n_runs, const uint32_t *__restrict__ rowids,
+                                                          uint64_t *__restrict__ out_build, uint32_t *__restrict__ out_probe, uint64_t out_cap,
+                                                          uint32_t *visited) {
+    unsigned long long before = 0;                       // chunks of the runs in front of this one
+    for (uint32_t d = 0; d < n_runs; d++) {
+        const BigRun r = runs[d];
+        const uint32_t chunks = (r.cnt + EXPAND_CHUNK - 1) / EXPAND_CHUNK;
+        const uint32_t first = (uint32_t)((blockIdx.x + gridDim.x - (uint32_t)(before % gridDim.x)) % gridDim.x);
+        for (uint32_t c = first; c < chunks; c += gridDim.x) {
+            const uint32_t k1 = min(r.cnt, (c + 1u) * EXPAND_CHUNK);
+            for (uint32_t k = c * EXPAND_CHUNK + threadIdx.x; k < k1; k += blockDim.x) {
+                const uint32_t br = __ldcs(rowids + r.run + k);
+                if (EMIT && r.pos + k < out_cap) {
+                    __stcs(reinterpret_cast<unsigned long long *>(out_build) + r.pos + k, (unsigned long long)br);
+                    __stcs(out_probe + r.pos + k, r.prow);
+                }
+                if (MARK) mark_visited(visited, br);
+            }
+        }
+        before += chunks;
+    }
 }
 
 // Keys of one tile. GUARD = false: the tile lies fully inside the batch and there is no validity bitmap, so
@@ -699,14 +764,7 @@ __device__ __forceinline__ void probe_tile(const ProbeArgs &a, uint32_t tile, in
                 const uint32_t cnt = __shfl_sync(FULL, scnt[q], src);
                 const uint32_t rb = __shfl_sync(FULL, srow[q], src);
                 const uint32_t pr = __shfl_sync(FULL, prow, src);
-                for (uint32_t k = lane; k < cnt; k += 32) {
-                    const uint32_t br = __ldcg(a.tv.rowids + rb + k);
-                    if (emit && pos + k < a.out_cap) {
-                        a.out_build[pos + k] = (uint64_t)br;
-                        a.out_probe[pos + k] = pr;
-                    }
-                    if (MARK) mark_visited(a.visited, br);
-                }
+                copy_long_run<(MODE == PM_PAIRS || MODE == PM_OUTER), MARK>(a, pos, cnt, rb, pr, lane);
             }
         }
     }

@@ -75,14 +75,7 @@ __device__ __forceinline__ void emit_runs(const ProbeArgs &a, bool mine, uint32_
         const uint32_t cnt = __shfl_sync(FULL, scnt, src);
         const uint32_t rb = __shfl_sync(FULL, srow, src);
         const uint32_t pr = __shfl_sync(FULL, prow, src);
-        for (uint32_t k = lane; k < cnt; k += 32) {
-            const uint32_t br = __ldcg(a.tv.rowids + rb + k);
-            if (emit && pos + k < a.out_cap) {
-                a.out_build[pos + k] = (uint64_t)br;
-                a.out_probe[pos + k] = pr;
-            }
-            if (MARK) mark_visited(a.visited, br);
-        }
+        copy_long_run<emit, MARK>(a, pos, cnt, rb, pr, lane);
     }
 }
 

@@ -38,8 +38,26 @@ constexpr int RP_THREADS = B200J_RP_THREADS;
 constexpr int RP_ITEMS   = B200J_RP_ITEMS;
 constexpr int RP_CTAS    = B200J_RP_CTAS;            // resident CTAs per SM the kernels are tuned for
 constexpr int RP_TILE    = RP_THREADS * RP_ITEMS;      // rows per iteration of the histogram kernel
-constexpr int SC_THREADS = 512;                        // scatter kernel
-constexpr int SC_TILE    = 4096;                       // rows per iteration of the scatter kernel; a CTA owns tiles_per_cta of them
+#ifndef B200J_SC_THREADS
+#define B200J_SC_THREADS 256
+#endif
+#ifndef B200J_SC_TILE
+#define B200J_SC_TILE 4096
+#endif
+#ifndef B200J_SC_CTAS
+#define B200J_SC_CTAS 3
+#endif
+constexpr int SC_THREADS = B200J_SC_THREADS;           // scatter kernel
+constexpr int SC_TILE    = B200J_SC_TILE;              // rows per iteration of the scatter kernel; a CTA owns tiles_per_cta of them
+#ifndef B200J_SC_NBUF
+#define B200J_SC_NBUF 1
+#endif
+constexpr int SC_NBUF    = B200J_SC_NBUF;              // key staging buffers: 2 = the next tile streams in while this one is processed.
+// Measured on B200, 1 B rows, 2^7 bins, histogram + scatter: 512 thr x 4096 rows x 2 CTAs x 2 buffers 7.95 ms; 256 x 4096 x 3 x 1 buffer
+// 7.55 ms (the third CTA hides the un-prefetched tile better than a second buffer does); 2048-row tiles 10.0 ms and 8192-row
+// tiles at one CTA per SM 8.6 ms: the run a tile appends to a bin (tile / bins rows) must stay long AND several CTAs must
+// overlap their barrier phases.
+constexpr int SC_CTAS    = B200J_SC_CTAS;              // resident CTAs per SM the scatter kernel (and the grid of both passes) is sized for
 static_assert(SC_TILE % RP_TILE == 0, "a scatter tile must be a whole number of histogram tiles");
 constexpr int RP_MAX_BITS = 12;
 constexpr int RP_MAX_DEST = 16;
@@ -258,7 +276,7 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 
 __host__ __device__ inline size_t part_scatter_smem(int kw, uint32_t n_bins) {
     const size_t P1 = (size_t)n_bins + 1;
-    return 2 * (size_t)SC_TILE * kw + (size_t)SC_TILE * 4 + P1 * 16 + 128;
+    return (size_t)SC_NBUF * SC_TILE * kw + (size_t)SC_TILE * 4 + P1 * 16 + 128;
 }
 
 // Scatter of one CTA's row range. Key tiles are double-buffered in shared memory by bulk-async copies (the next tile
@@ -267,7 +285,7 @@ __host__ __device__ inline size_t part_scatter_smem(int kw, uint32_t n_bins) {
 // and the write-out walks that permutation: consecutive threads -> consecutive elements of a bin's run -> consecutive
 // global addresses, appended at the CTA's own cursor of that bin (cursors live in shared memory: no global atomics).
 template <int KW, bool DEST>
-__global__ void __launch_bounds__(SC_THREADS, 2) part_scatter_kernel(PartArgs a) {
+__global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartArgs a) {
     using KeyT = typename std::conditional<KW == 8, unsigned long long, uint32_t>::type;
     constexpr int PER_VEC = 16 / KW;
     constexpr int ITEMS = SC_TILE / SC_THREADS;
@@ -276,8 +294,8 @@ __global__ void __launch_bounds__(SC_THREADS, 2) part_scatter_kernel(PartArgs a)
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const uint32_t P1 = a.n_bins + 1;
     KeyT *s_stage0 = reinterpret_cast<KeyT *>(smem_raw);
-    KeyT *s_stage1 = reinterpret_cast<KeyT *>(smem_raw + TILE_BYTES);
-    uint32_t *s_perm = reinterpret_cast<uint32_t *>(smem_raw + 2 * TILE_BYTES);     // (bin << 16 | source index), bin by bin
+    KeyT *s_stage1 = reinterpret_cast<KeyT *>(smem_raw + (SC_NBUF - 1) * TILE_BYTES);
+    uint32_t *s_perm = reinterpret_cast<uint32_t *>(smem_raw + SC_NBUF * TILE_BYTES);     // (bin << 16 | source index), bin by bin
     uint32_t *s_cnt = s_perm + SC_TILE;
     uint32_t *s_off = s_cnt + P1;        // position of the bin's run inside the permuted tile
     uint32_t *s_cur = s_off + P1;        // this CTA's append cursor inside the bin's output
@@ -328,11 +346,11 @@ __global__ void __launch_bounds__(SC_THREADS, 2) part_scatter_kernel(PartArgs a)
     uint32_t n_bulk[2] = {0, 0};         // bulk copies issued so far per buffer (mbarrier phase parity)
     fetch(t0, 0);
     for (uint32_t tile = t0; tile < t1; tile++) {
-        const int buf = (int)((tile - t0) & 1u);
+        const int buf = SC_NBUF == 2 ? (int)((tile - t0) & 1u) : 0;
         const KeyT *stage = buf ? s_stage1 : s_stage0;
         const bool inner = is_inner(tile);
         // the other buffer was last read in the write-out of tile - 1, which ended with a block barrier: refill it now
-        if (tile + 1 < t1) fetch(tile + 1, buf ^ 1);
+        if (SC_NBUF == 2 && tile + 1 < t1) fetch(tile + 1, buf ^ 1);
         if (inner) { mbar_wait(&s_bar[buf], n_bulk[buf] & 1u); n_bulk[buf]++; }
         else __syncthreads();
         // note: n_bulk of the buffer being prefetched is advanced when that tile is consumed
@@ -424,6 +442,7 @@ __global__ void __launch_bounds__(SC_THREADS, 2) part_scatter_kernel(PartArgs a)
             }
         }
         __syncthreads();
+        if (SC_NBUF == 1 && tile + 1 < t1) fetch(tile + 1, 0);
     }
 }
 

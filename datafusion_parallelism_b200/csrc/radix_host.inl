@@ -44,7 +44,7 @@ PartPlan part_plan(H *h, const void *keys, const uint8_t *validity, int64_t bit_
     a.n_bins = pl.dest ? (uint32_t)n_dest : (1u << bits);
     a.hk = h->hk;
     const int64_t n_tiles = (n + a.mis + SC_TILE - 1) / SC_TILE;
-    pl.grid = (int)std::max<int64_t>(1, std::min<int64_t>(n_tiles, (int64_t)h->sm_count * 2));
+    pl.grid = (int)std::max<int64_t>(1, std::min<int64_t>(n_tiles, (int64_t)h->sm_count * SC_CTAS));
     a.tiles_per_cta = (uint32_t)((n_tiles + pl.grid - 1) / pl.grid);
     radix_ensure(h, (int)a.n_bins + 1, pl.grid);
     a.cta_hist = h->rscratch.cta_hist;
@@ -78,7 +78,7 @@ template <int KW, bool DEST>
 void part_scatter_launch(H *h, PartPlan &pl) {
     static bool attr = false;
     if (!attr) {
-        CU(cudaFuncSetAttribute(part_scatter_kernel<KW, DEST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        CU(cudaFuncSetAttribute(part_scatter_kernel<KW, DEST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr = true;
     }
     part_scatter_kernel<KW, DEST><<<pl.grid, SC_THREADS, part_scatter_smem(KW, pl.a.n_bins), h->stream>>>(pl.a);
