@@ -544,6 +544,12 @@ void run_build(H *h) {
         a.n = n;
         a.mis = 0;      // the build store is 256 B aligned
         a.tv = h->view();
+        void *slot_of = nullptr;
+        struct SlotOfGuard { H *h; void **p; ~SlotOfGuard() { if (*p) big_free(h, *p); } } slot_of_guard{h, &slot_of};
+        if (n > 0 && direct_slots < 0xffffffffULL) {
+            CU(big_alloc(h, &slot_of, (size_t)n * 4 + 16));
+            a.slot_of = (uint32_t *)slot_of;
+        }
         if (n > 0) {
             const int grid = grid_for(h, n, TILE_ROWS, 8);
             launch_by_kw(kw, [&](auto KW) { build_insert_kernel<decltype(KW)::value, false><<<grid, TILE_THREADS, 0, h->stream>>>(a); });

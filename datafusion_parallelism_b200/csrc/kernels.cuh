@@ -305,6 +305,7 @@ struct BuildArgs {
     TableView       tv;
     HashKeys        hk;
     Counters       *ctr;
+    uint32_t       *slot_of;      // [n] slot index every row went to (0xffffffff = the zero-key side slot), for csr_fill; may be null
 };
 
 template <bool RADIX>
@@ -350,8 +351,23 @@ __global__ void __launch_bounds__(TILE_THREADS) build_insert_kernel(BuildArgs a)
             if (row[q] < 0 || row[q] >= a.n) continue;
             if (!bit_valid(a.validity, row[q])) { nulls++; continue; }
             const uint32_t r = a.rowid ? __ldcs(a.rowid + row[q]) : (uint32_t)row[q];
+            const uint32_t d0 = distinct;
             Slot *s = find_or_claim<RADIX>(a.tv, a.hk, key[q], distinct);
-            const uint32_t pos = atomicAdd(&s->count, 1u);
+            if (a.slot_of) a.slot_of[row[q]] = key[q] ? (uint32_t)(s - a.tv.slots) : 0xffffffffu;
+            // Rows that found their key already present may be many rows of ONE key (a heavy hitter fills most of its radix
+            // partition's tiles): lanes on the same slot add up first and send one atomic. Unique keys never take this path.
+            uint32_t pos;
+            const unsigned am = __activemask();
+            if (__any_sync(am, distinct == d0)) {
+                const unsigned peers = __match_any_sync(am, (unsigned long long)s);
+                const int leader = __ffs(peers) - 1;
+                uint32_t base = 0;
+                if ((t & 31) == leader) base = atomicAdd(&s->count, (uint32_t)__popc(peers));
+                base = __shfl_sync(peers, base, leader);
+                pos = base + __popc(peers & ((1u << (t & 31)) - 1u));
+            } else {
+                pos = atomicAdd(&s->count, 1u);
+            }
             if (pos == 0) {
                 s->row = r;
                 if (key[q] == 0) distinct++;
@@ -416,13 +432,24 @@ __global__ void __launch_bounds__(TILE_THREADS) csr_fill_kernel(BuildArgs a) {
             if (row[q] < 0 || row[q] >= a.n) continue;
             if (!bit_valid(a.validity, row[q])) continue;
             const uint32_t r = a.rowid ? __ldcs(a.rowid + row[q]) : (uint32_t)row[q];
-            uint32_t dummy = 0;
-            Slot *s = find_or_claim<RADIX>(a.tv, a.hk, key[q], dummy);      // key is present: never claims
+            Slot *s;
+            if (a.slot_of) {                                                 // the insert pass remembered where the row went
+                const uint32_t si = __ldcs(a.slot_of + row[q]);
+                s = si == 0xffffffffu ? a.tv.zero_slot : a.tv.slots + si;
+            } else {
+                uint32_t dummy = 0;
+                s = find_or_claim<RADIX>(a.tv, a.hk, key[q], dummy);         // key is present: never claims
+            }
             const Slot v = load_slot(s);
             if (v.count < 2) continue;
             if (__ldcg(a.tv.rowids + v.row) == r) continue;                  // the run's first row is already placed
-            const uint32_t p = atomicAdd(a.tv.rowids + v.row - 1, 1u);
-            a.tv.rowids[v.row + p] = r;
+            const unsigned am = __activemask();                              // lanes of the same run: one cursor atomic
+            const unsigned peers = __match_any_sync(am, v.row);
+            const int leader = __ffs(peers) - 1;
+            uint32_t base = 0;
+            if ((t & 31) == leader) base = atomicAdd(a.tv.rowids + v.row - 1, (uint32_t)__popc(peers));
+            base = __shfl_sync(peers, base, leader);
+            a.tv.rowids[v.row + base + __popc(peers & ((1u << (t & 31)) - 1u))] = r;
         }
     }
 }

@@ -164,6 +164,12 @@ void radix_build(H *h, const void *keys, const uint8_t *validity, int kw, int64_
         a.n = n_valid;
         a.mis = 0;
         a.tv = h->view();
+        if (n_valid > 0 && total < 0xffffffffULL) {          // slot indices fit 32 bits: remember them for the duplicate-run pass
+            void *so = nullptr;
+            CU(big_alloc(h, &so, (size_t)n_valid * 4 + 16));
+            temps.push_back(so);
+            a.slot_of = (uint32_t *)so;
+        }
         if (n_valid > 0) {
             const int grid = grid_for(h, n_valid, TILE_ROWS, 8);
             launch_by_kw(kw, [&](auto KW) { build_insert_kernel<decltype(KW)::value, true><<<grid, TILE_THREADS, 0, h->stream>>>(a); });
