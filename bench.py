@@ -61,6 +61,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-probe-sample", type=int, default=250_000_000)
+    ap.add_argument("--exchange-chunk-rows", type=int, default=0, help="N>1: > 0 = probe rows per exchange / local-join pipeline stage (DistributedJoin.probe_chunks)")
     ap.add_argument("--shuffle", default="p2p", choices=["p2p", "nccl"], help="N>1: fused peer-store scatter or NCCL all-to-all")
     return ap.parse_args()
 
@@ -182,7 +183,8 @@ def workload_config(args, n_gpus):
     return {"workload": f"C2: {args.build_rows}-row int64 unique-key build x {args.probe_rows}-row uniform probe, 1:1 matches, "
                         f"inner join, (build_idx u64, probe_idx u32) pairs out" + (f"; per GPU, {n_gpus} GPUs, key space x{n_gpus}, "
                         "hash-partition + NVLink exchange of both sides" if n_gpus > 1 else ""),
-            "build_rows_per_gpu": args.build_rows, "probe_rows_per_gpu": args.probe_rows, "probe_chunk_rows": args.chunk_rows,
+            "build_rows_per_gpu": args.build_rows, "probe_rows_per_gpu": args.probe_rows,
+            "probe_chunk_rows": args.chunk_rows if (n_gpus == 1 or args.exchange_chunk_rows <= 0) else min(args.chunk_rows, args.exchange_chunk_rows),
             "l2": "inputs (8 GB probe keys per step) are far larger than the 126 MB L2; no flush needed"}
 
 
@@ -240,6 +242,15 @@ def run_b200(args):
         join.build_push(0, [bk])
         join.build_finish(0)
         tot = 0
+        if world > 1 and args.exchange_chunk_rows > 0:
+            # optional: sub-chunks, the NVLink exchange of chunk k+1 overlapping the local join of chunk k. OFF by default:
+            # measured on 2 x B200 it is slower (35.4 -> 50.7 ms/step at 128 M-row chunks) because the exchange kernels'
+            # streams evict the radix partition's table from L2 under the probe kernel (ms_probe 7.0 -> 19 ms)
+            sub = min(chunk, args.exchange_chunk_rows)
+            for r in join.probe_chunks(0, [pk[lo:lo + sub] for lo in range(0, n_probe, sub)], want=d.OUT_PAIRS):
+                tot += r.n
+                r.release()
+            return tot
         for lo in range(0, n_probe, chunk):
             r = join.probe_batch(0, [pk[lo:lo + chunk]], want=d.OUT_PAIRS)
             tot += r.n

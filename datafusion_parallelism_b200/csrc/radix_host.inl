@@ -44,7 +44,14 @@ PartPlan part_plan(H *h, const void *keys, const uint8_t *validity, int64_t bit_
     a.n_bins = pl.dest ? (uint32_t)n_dest : (1u << bits);
     a.hk = h->hk;
     const int64_t n_tiles = (n + a.mis + SC_TILE - 1) / SC_TILE;
-    pl.grid = (int)std::max<int64_t>(1, std::min<int64_t>(n_tiles, (int64_t)h->sm_count * SC_CTAS));
+    // DEST mode (multi-GPU exchange): the scatter's stores cross NVLink and its CTAs mostly wait; a smaller grid leaves the
+    // SMs' registers and shared memory to the local join running beside it on the other stream (B200J_DEST_CTAS per SM)
+    int ctas = SC_CTAS;
+    if (pl.dest) {
+        const char *e = getenv("B200J_DEST_CTAS");
+        ctas = e ? std::max(1, std::min(SC_CTAS, atoi(e))) : SC_CTAS;
+    }
+    pl.grid = (int)std::max<int64_t>(1, std::min<int64_t>(n_tiles, (int64_t)h->sm_count * ctas));
     a.tiles_per_cta = (uint32_t)((n_tiles + pl.grid - 1) / pl.grid);
     radix_ensure(h, (int)a.n_bins + 1, pl.grid);
     a.cta_hist = h->rscratch.cta_hist;

@@ -131,7 +131,14 @@ class DistributedJoin:
         self.stream = stream if stream is not None else torch.cuda.current_stream()
         join_kwargs.setdefault("device", torch.cuda.current_device())     # one process per GPU: the handle lives on this rank's device
         self.join = HashJoin(join_type, key_widths=(key_width,), stream=self.stream.cuda_stream, **join_kwargs)
-        self.build, self.probe = _Side(), _Side()
+        # a second handle on its own stream does the partition + exchange kernels of probe chunk k+1 while the first one
+        # joins chunk k (probe_chunks): two receive-buffer sets for the probe side
+        self.xstream = torch.cuda.Stream(device=join_kwargs["device"])
+        xkw = {k: v for k, v in join_kwargs.items() if k in ("device", "hash_keys", "hash_flags")}
+        self.xjoin = HashJoin(join_type, key_widths=(key_width,), stream=self.xstream.cuda_stream, **xkw)
+        self.build = _Side()
+        self.probe_sides = [_Side(), _Side()]
+        self.probe = self.probe_sides[0]
         self.ms_exchange = {"build": 0.0, "probe": 0.0}
         self.build_rows_local = 0
         self._key_dtype = torch.int64 if key_width == 8 else torch.int32
@@ -147,21 +154,25 @@ class DistributedJoin:
             for b in (side.keys, side.rid):
                 if b is not None:
                     b.close(self.dist)
-            side.keys = _PeerBuffer(self.join, self.dist, cap * self.kw + 64)
-            side.rid = _PeerBuffer(self.join, self.dist, cap * 4 + 64)
+            # allocated through the exchange handle: the join handle may be busy with a local probe (probe_chunks)
+            side.keys = _PeerBuffer(self.xjoin, self.dist, cap * self.kw + 64)
+            side.rid = _PeerBuffer(self.xjoin, self.dist, cap * 4 + 64)
         else:
             dev = torch.device("cuda", torch.cuda.current_device())
             side.keys = torch.empty(cap, dtype=self._key_dtype, device=dev)
             side.rid = torch.empty(cap, dtype=torch.int32, device=dev)
         side.cap = cap
 
-    def _exchange(self, side: _Side, keys, rowid_base: int = 0) -> int:
-        """Partition `keys` by destination rank and deliver them; returns the rows this rank received."""
+    def _exchange(self, side: _Side, keys, rowid_base: int = 0, overlapped: bool = False) -> int:
+        """Partition `keys` by destination rank and deliver them; returns the rows this rank received.
+        overlapped: run on the exchange handle / stream (called from the exchange thread of probe_chunks)."""
         torch, dist = self.torch, self.dist
         W = self.world
         n = int(keys.shape[0])
-        counts = shuffle_count(self.join, keys, W)
-        with torch.cuda.stream(self.stream):
+        xj = self.xjoin if overlapped else self.join
+        xs = self.xstream if overlapped else self.stream
+        counts = shuffle_count(xj, keys, W)
+        with torch.cuda.stream(xs):
             mine = torch.from_numpy(counts[:W].copy()).to(keys.device)
             allc = torch.empty(W * W, dtype=torch.int64, device=keys.device)
             dist.all_gather_into_tensor(allc, mine, group=self.group)
@@ -177,9 +188,9 @@ class DistributedJoin:
             nk, nr = side.null_keys.data_ptr(), side.null_rid.data_ptr()
         if self.mode == "p2p":
             # the count all-gather above doubles as the "everyone is done with the previous contents" barrier
-            shuffle_scatter(self.join, W, list(side.keys.ptrs) + [nk], list(side.rid.ptrs) + [nr],
+            shuffle_scatter(xj, W, list(side.keys.ptrs) + [nk], list(side.rid.ptrs) + [nr],
                             list(plan.dest_offset) + [0], rowid_base)
-            self.join.synchronize()
+            xj.synchronize()
             dist.barrier(group=self.group)          # every peer's stores have landed in my receive buffer
             recv_keys_ptr, recv_rid_ptr = side.keys.local, side.rid.local
         else:
@@ -187,13 +198,13 @@ class DistributedJoin:
                 side.send_keys = torch.empty(int(n * 1.1) + 4096, dtype=self._key_dtype, device=keys.device)
                 side.send_rid = torch.empty(int(n * 1.1) + 4096, dtype=torch.int32, device=keys.device)
             sk, sr = side.send_keys.data_ptr(), side.send_rid.data_ptr()
-            shuffle_scatter(self.join, W, [sk] * W + [nk], [sr] * W + [nr], list(plan.send_offset[:W]) + [0], rowid_base)
+            shuffle_scatter(xj, W, [sk] * W + [nk], [sr] * W + [nr], list(plan.send_offset[:W]) + [0], rowid_base)
             n_recv = int(plan.recv_rows[self.rank])
             n_send = int(plan.send_offset[W])
-            with torch.cuda.stream(self.stream):
+            with torch.cuda.stream(xs):
                 dist.all_to_all_single(side.keys[:n_recv], side.send_keys[:n_send], plan.recv_split, plan.send_split, group=self.group)
                 dist.all_to_all_single(side.rid[:n_recv], side.send_rid[:n_send], plan.recv_split, plan.send_split, group=self.group)
-            self.stream.synchronize()
+            xs.synchronize()
             recv_keys_ptr, recv_rid_ptr = side.keys.data_ptr(), side.rid.data_ptr()
         side.recv_keys_ptr, side.recv_rid_ptr = recv_keys_ptr, recv_rid_ptr
         return int(plan.recv_rows[self.rank])
@@ -232,6 +243,52 @@ class DistributedJoin:
         res = self.join.probe_batch(partition, [_dev_column(self.probe.recv_keys_ptr, n_recv, self.kw, keep=(self.probe.keys,))], want=want)
         res.exchange_plan = self.probe.plan
         return res
+
+    def probe_chunks(self, partition: int, key_chunks: Sequence, want: int = OUT_PAIRS):
+        """Generator over the results of a sequence of probe chunks (device key tensors), with the partition + exchange
+        of chunk k+1 running on the exchange stream while chunk k is joined locally ("chunked and
+        overlapped"). Every rank must iterate over the same number of chunks. The exchange of chunk k+2 overwrites the
+        receive buffers of chunk k: it is started only after chunk k's local join has returned, and its count all-gather
+        (every rank's exchange thread takes part) keeps any peer from storing into buffers a slower rank still reads."""
+        import threading
+        torch = self.torch
+        chunks = list(key_chunks)
+        dev = torch.cuda.current_device()
+        box = {}
+
+        def run_exchange(k):
+            try:
+                torch.cuda.set_device(dev)                      # the CUDA device is per thread
+                side = self.probe_sides[k & 1]
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(self.xstream)
+                n_recv = self._exchange(side, chunks[k], rowid_base=0, overlapped=True)
+                e1.record(self.xstream)
+                e1.synchronize()
+                self.ms_exchange["probe"] += e0.elapsed_time(e1)
+                box[k] = n_recv
+            except BaseException as exc:                        # surfaces in the consuming thread
+                box[k] = exc
+
+        def start(k):
+            th = threading.Thread(target=run_exchange, args=(k,), daemon=True)
+            th.start()
+            return th
+
+        if not chunks:
+            return
+        th = start(0)
+        for k in range(len(chunks)):
+            th.join()
+            got = box.pop(k)
+            if isinstance(got, BaseException):
+                raise got
+            th = start(k + 1) if k + 1 < len(chunks) else None
+            side = self.probe_sides[k & 1]
+            self.probe = side
+            res = self.join.probe_batch(partition, [_dev_column(side.recv_keys_ptr, got, self.kw, keep=(side.keys,))], want=want)
+            res.exchange_plan = side.plan
+            yield res
 
     def probe_finish(self, partition: int, want: int = OUT_PAIRS):
         return self.join.probe_finish(partition, want=want)
@@ -272,11 +329,12 @@ class DistributedJoin:
 
     def close(self):
         if self.mode == "p2p":
-            for side in (self.build, self.probe):
+            for side in [self.build] + self.probe_sides:
                 for b in (side.keys, side.rid):
                     if b is not None:
                         b.close(self.dist)
                 side.keys = side.rid = None
+        self.xjoin.close()
         self.join.close()
 
 

@@ -1,0 +1,54 @@
+"""torchrun check of DistributedJoin.probe_chunks on real GPUs (one rank per GPU): every pair of every chunk must join equal
+keys (checked on the rank that produced it, against the rows it received), and the pair count over all ranks must be the
+1:1 workload's probe row count.  torchrun --nproc-per-node N scripts/check_dist.py [--mode p2p|nccl]"""
+import argparse, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+import datafusion_parallelism_b200 as d
+from datafusion_parallelism_b200.exchange import DistributedJoin, _RawCudaArray
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--mode", default="p2p")
+ap.add_argument("--build", type=int, default=5_000_000)
+ap.add_argument("--probe", type=int, default=40_000_000)
+ap.add_argument("--chunk", type=int, default=6_000_000)
+a = ap.parse_args()
+rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(lr)
+dev = torch.device("cuda", lr)
+os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+dist.init_process_group("nccl", device_id=dev)
+g = torch.Generator(device=dev)
+g.manual_seed(11 + rank)
+bk = torch.randperm(a.build, device=dev, generator=g, dtype=torch.int64) * world + rank       # unique over all ranks
+pk = torch.randint(0, a.build * world, (a.probe,), device=dev, generator=g, dtype=torch.int64)
+stream = torch.cuda.Stream(device=dev)
+j = DistributedJoin("inner", key_width=8, stream=stream, mode=a.mode, layout="radix", radix_bits=5)
+for rep in range(2):                                    # second pass re-uses the receive buffers
+    j.reset()
+    j.build_push(0, [bk])
+    j.build_finish(0)
+    n_b = j.build_rows_local
+    bkeys = torch.as_tensor(_RawCudaArray(j.build.recv_keys_ptr, n_b, "<i8"), device=dev).clone()
+    tot = 0
+    for r in j.probe_chunks(0, [pk[lo:lo + a.chunk] for lo in range(0, a.probe, a.chunk)], want=d.OUT_PAIRS):
+        side = j.probe
+        n_recv = int(side.plan.recv_rows[rank])
+        pkeys = torch.as_tensor(_RawCudaArray(side.recv_keys_ptr, n_recv, "<i8"), device=dev)
+        b_, p_ = r.device_arrays()
+        bi = torch.as_tensor(b_, device=dev).to(torch.int64)
+        pi = torch.as_tensor(p_, device=dev).to(torch.int64) & 0xffffffff
+        assert r.n == n_recv, (r.n, n_recv)
+        assert bool((bkeys[bi] == pkeys[pi]).all()), "a pair joins different keys"
+        assert int(torch.unique(pi).numel()) == n_recv, "a probe row is missing or doubled"
+        tot += r.n
+        r.release()
+    t = torch.tensor([tot], device=dev, dtype=torch.int64)
+    dist.all_reduce(t)
+    assert int(t.item()) == a.probe * world, (int(t.item()), a.probe * world)
+if rank == 0:
+    print(f"check_dist ok: {world} ranks, mode {a.mode}, {a.probe * world} pairs, every pair key-equal")
+j.close()
+dist.barrier()
+dist.destroy_process_group()
