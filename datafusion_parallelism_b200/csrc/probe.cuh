@@ -35,8 +35,9 @@ struct PFShared {
     uint32_t           brow[PF_STAGE];                // staged single-row results (0xffffffff = NULL build side)
     uint32_t           prow[PF_STAGE];
     unsigned long long gbase;
-    uint32_t           count, qcount, next;
+    uint32_t           count, qcount, next, mcount;
 };
+constexpr uint32_t PF_SHORT = 8;                      // duplicate runs up to this length are staged like single rows
 
 // Copies the duplicate-key runs of one warp's lanes (one run per lane, `mine` lanes only) to the output and/or marks
 // them visited. Short runs are copied by their lane, long runs by the whole warp (coalesced).
@@ -92,7 +93,7 @@ __global__ void __launch_bounds__(PF_THREADS) probe_fast_kernel(ProbeArgs a) {
     const uint32_t n_super = (n_tiles + PF_SUB - 1) / PF_SUB;
     uint32_t null_build_out = 0;
 
-    if (t == 0) { sh.count = 0; sh.qcount = 0; sh.next = atomicAdd(&a.ctr->next_tile, 1u); }
+    if (t == 0) { sh.count = 0; sh.qcount = 0; sh.mcount = 0; sh.next = atomicAdd(&a.ctr->next_tile, 1u); }
     __syncthreads();
     for (;;) {
         const uint32_t sup = sh.next;
@@ -217,6 +218,7 @@ __global__ void __launch_bounds__(PF_THREADS) probe_fast_kernel(ProbeArgs a) {
             const bool act = i < qn;
             const uint64_t key = act ? sh.qkey[i] : 0ULL;
             const uint32_t prow = act ? sh.qrow[i] : 0u;
+            __syncthreads();          // every entry of this round is in registers: the duplicate-run list below may reuse the queue
             uint32_t srow = 0, scnt = 0;
             if (act) {
                 const uint64_t h = hash_one(a.hk, key);
@@ -260,7 +262,62 @@ __global__ void __launch_bounds__(PF_THREADS) probe_fast_kernel(ProbeArgs a) {
                 }
             }
             if (MODE == PM_PAIRS || MODE == PM_OUTER || MARK) {
-                if (__any_sync(FULL, multi)) emit_runs<MODE, MARK>(a, multi, scnt, srow, prow, lane);
+                // duplicate runs wait until every single row of the super-tile is staged: (run start, length, probe row) goes
+                // back into the queue arrays, compacted (position < number of entries already read, see the barrier above)
+                const uint32_t bm = __ballot_sync(FULL, multi);
+                uint32_t mbase = 0;
+                if (lane == 0 && bm) mbase = atomicAdd(&sh.mcount, (uint32_t)__popc(bm));
+                mbase = __shfl_sync(FULL, mbase, 0);
+                if (multi) {
+                    const uint32_t j = mbase + __popc(bm & lt_mask);
+                    sh.qkey[j] = (unsigned long long)srow | ((unsigned long long)scnt << 32);
+                    sh.qrow[j] = prow;
+                }
+            }
+        }
+        __syncthreads();
+        // ---- duplicate runs. Short ones are staged like single rows while the stage has room (their pairs then leave in the
+        //      coalesced flush: a per-lane copy straight to global memory costs two L2 sectors per output row); long ones, and
+        //      whatever does not fit, reserve their own output range per warp (emit_runs).
+        if (MODE == PM_PAIRS || MODE == PM_OUTER || MARK) {
+            const uint32_t mn = sh.mcount;
+            for (uint32_t j0 = 0; j0 < mn; j0 += PF_THREADS) {
+                const uint32_t j = j0 + t;
+                const bool act = j < mn;
+                const unsigned long long v = act ? sh.qkey[j] : 0ULL;
+                const uint32_t srow = (uint32_t)v, scnt = (uint32_t)(v >> 32);
+                const uint32_t prow = act ? sh.qrow[j] : 0u;
+                bool staged = false;
+                if (MODE == PM_PAIRS || MODE == PM_OUTER) {
+                    const bool shortrun = act && scnt <= PF_SHORT;
+                    const uint32_t need = shortrun ? scnt : 0u;
+                    uint32_t incl = need;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += y; }
+                    const uint32_t wtot = __shfl_sync(FULL, incl, 31);
+                    uint32_t wbase = 0xffffffffu;
+                    if (lane == 0 && wtot) {
+                        uint32_t old = *reinterpret_cast<volatile uint32_t *>(&sh.count);
+                        while (old + wtot <= (uint32_t)PF_STAGE) {
+                            const uint32_t prev = atomicCAS(&sh.count, old, old + wtot);
+                            if (prev == old) { wbase = old; break; }
+                            old = prev;
+                        }
+                    }
+                    wbase = __shfl_sync(FULL, wbase, 0);
+                    staged = shortrun && wbase != 0xffffffffu;
+                    if (staged) {
+                        const uint32_t pos = wbase + incl - need;
+                        for (uint32_t k = 0; k < scnt; k++) {
+                            const uint32_t br = __ldcg(a.tv.rowids + srow + k);
+                            sh.brow[pos + k] = br;
+                            sh.prow[pos + k] = prow;
+                            if (MARK) mark_visited(a.visited, br);
+                        }
+                    }
+                }
+                const bool rest = act && !staged;
+                if (__any_sync(FULL, rest)) emit_runs<MODE, MARK>(a, rest, scnt, srow, prow, lane);
             }
         }
         __syncthreads();
@@ -285,7 +342,7 @@ __global__ void __launch_bounds__(PF_THREADS) probe_fast_kernel(ProbeArgs a) {
             }
         }
         __syncthreads();
-        if (t == 0) { sh.count = 0; sh.qcount = 0; sh.next = atomicAdd(&a.ctr->next_tile, 1u); }
+        if (t == 0) { sh.count = 0; sh.qcount = 0; sh.mcount = 0; sh.next = atomicAdd(&a.ctr->next_tile, 1u); }
         __syncthreads();
     }
     if (MODE == PM_OUTER || MODE == PM_SEMI || MODE == PM_ANTI) {

@@ -19,7 +19,7 @@ import oracle
 ap = argparse.ArgumentParser()
 ap.add_argument("--build", type=int, default=100_000_000)
 ap.add_argument("--probe", type=int, default=1_000_000_000)
-ap.add_argument("--chunk", type=int, default=1 << 28)
+ap.add_argument("--chunk", type=int, default=0, help="probe rows per call; 0 = whole probe side (zipf-b: 2^28, its pair buffer is sized for 5.5 pairs per probe row)")
 ap.add_argument("--workloads", default="exp,zipf-b,zipf-p")
 ap.add_argument("--reps", type=int, default=2)
 ap.add_argument("--join", default="inner")
@@ -80,6 +80,7 @@ def expected_rows(bk, pk, key_space):
 for wl in a.workloads.split(","):
     bk, pk = make(wl, a.build, a.probe)
     want, top = expected_rows(bk, pk, a.build)
+    chunk = a.chunk if a.chunk > 0 else ((1 << 28) if wl == "zipf-b" else a.probe)
     torch.cuda.synchronize()
     best = None
     for rep in range(a.reps + 1):
@@ -88,8 +89,8 @@ for wl in a.workloads.split(","):
             j.build_push(0, [bk])
             j.build_finish(0)
             tot = 0
-            for lo in range(0, a.probe, a.chunk):
-                r = j.probe_batch(0, [pk[lo:lo + a.chunk]], want=d.OUT_PAIRS)
+            for lo in range(0, a.probe, chunk):
+                r = j.probe_batch(0, [pk[lo:lo + chunk]], want=d.OUT_PAIRS)
                 tot += r.n
                 r.release()
             wall = (time.perf_counter() - t0) * 1e3
@@ -97,7 +98,7 @@ for wl in a.workloads.split(","):
         assert tot == want, f"{wl}: {tot} result rows, expected {want}"
         bms = st["ms_build_copy"] + st["ms_build_partition"] + st["ms_build_insert"]
         pms = st["ms_probe_partition"] + st["ms_probe"]
-        line = {"workload": wl, "build_rows": a.build, "probe_rows": a.probe, "key": "int32", "join": a.join, "result_rows": tot,
+        line = {"workload": wl, "build_rows": a.build, "probe_rows": a.probe, "probe_chunk_rows": chunk, "key": "int32", "join": a.join, "result_rows": tot,
                 "longest_duplicate_run": top, "distinct_keys": st["distinct_keys"], "duplicate_rows": st["duplicate_rows"],
                 "layout": st["layout"], "radix_bits": st["radix_bits"], "build_ms": bms, "probe_ms": pms, "wall_ms": wall,
                 "build_Gtps": a.build / bms / 1e6, "probe_Gtps": a.probe / pms / 1e6,
