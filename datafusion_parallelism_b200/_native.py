@@ -111,6 +111,7 @@ SIGNATURES = {
     "b200j_gathered_release": (C.c_int32, [C.c_void_p, C.POINTER(Gathered)]),
     "b200j_hash_keys": (C.c_int32, [C.c_void_p, C.POINTER(Batch), C.c_void_p]),
     "b200j_shuffle_count": (C.c_int32, [C.c_void_p, C.POINTER(Batch), C.c_int32, C.POINTER(C.c_int64)]),
+    "b200j_shuffle_set_hot": (C.c_int32, [C.c_void_p, C.POINTER(C.c_uint64), C.c_int32]),
     "b200j_shuffle_scatter": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.c_uint32]),
     "b200j_ipc_alloc": (C.c_int32, [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]),
     "b200j_ipc_open": (C.c_int32, [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p)]),

@@ -135,6 +135,9 @@ struct b200j_handle {
     uint64_t n_slots = 0;
     DevBuf zero_slot;
     DevBuf rowids;
+    DevBuf hot_table;                  // heavy-hitter key set of the exchange (b200j_shuffle_set_hot)
+    uint32_t hot_mask = 0;
+    int hot_n = 0;
     DevBuf bigruns;                    // BigRun list of the probe launch in flight (allocated when the build has long duplicate runs)
     DevBuf visited;
     DevBuf parts;                      // radix layout: PartEnt per partition
@@ -1438,6 +1441,7 @@ void do_hash_keys(H *h, const b200j_batch *b, uint64_t *out) {
 }
 
 void do_shuffle_count(H *h, const b200j_batch *b, int32_t n_dest, int64_t *counts);
+void do_shuffle_set_hot(H *h, const uint64_t *keys, int32_t n);
 void do_shuffle_scatter(H *h, int32_t n_dest, void *const *dest_keys, uint32_t *const *dest_rowid, const int64_t *dest_offset, uint32_t rowid_base);
 
 template <typename F>
@@ -1603,7 +1607,7 @@ int32_t b200j_destroy(b200j_handle *h) {
     for (auto *v : {&h->bkeys, &h->bpayload})
         for (auto &c : *v) { fr(c.values); fr(c.offsets); fr(c.validity); }
     radix_release(h);
-    fr(h->slots); fr(h->zero_slot); fr(h->rowids); fr(h->bigruns); fr(h->visited); fr(h->parts);
+    fr(h->slots); fr(h->zero_slot); fr(h->rowids); fr(h->bigruns); fr(h->hot_table); fr(h->visited); fr(h->parts);
     cudaStreamSynchronize(h->stream);
     for (auto &b : h->blocks) cudaFreeAsync(b.p, h->stream);
     h->blocks.clear();
@@ -1700,6 +1704,9 @@ int32_t b200j_hash_keys(b200j_handle *h, const b200j_batch *batch, uint64_t *out
 
 int32_t b200j_shuffle_count(b200j_handle *h, const b200j_batch *batch, int32_t n_dest, int64_t *counts) {
     return guarded(h, [&] { do_shuffle_count(h, batch, n_dest, counts); });
+}
+int32_t b200j_shuffle_set_hot(b200j_handle *h, const uint64_t *keys, int32_t n) {
+    return guarded(h, [&] { do_shuffle_set_hot(h, keys, n); });
 }
 int32_t b200j_shuffle_scatter(b200j_handle *h, int32_t n_dest, void *const *dest_keys, uint32_t *const *dest_rowid, const int64_t *dest_offset,
                               uint32_t rowid_base) {

@@ -87,15 +87,33 @@ struct PartArgs {
     const uint32_t     *bin_base;
     void               *out_keys;         // radix mode
     uint32_t           *out_rid;
-    void               *dest_keys[RP_MAX_DEST + 1];    // DEST mode: output base per bin (may be peer memory)
-    uint32_t           *dest_rid[RP_MAX_DEST + 1];
+    void               *dest_keys[RP_MAX_DEST + 2];    // DEST mode: output base per bin (may be peer memory)
+    uint32_t           *dest_rid[RP_MAX_DEST + 2];
+    const unsigned long long *hot_keys;   // DEST mode: open-addressing set of heavy-hitter key values (0 = empty slot) or null
+    uint32_t            hot_mask;         // its size - 1
     uint32_t            rid_base;         // added to the local row index (row ids of a chunked side)
 };
 
 
+// Heavy-hitter routing of the multi-GPU exchange (SURVEY §8e "skew"): rows whose key is in the hot set are NOT sent to the
+// key's owner but kept on this GPU (bin n_dest), where they are joined against the broadcast build rows of the hot keys.
+__device__ __forceinline__ bool part_is_hot(const PartArgs &a, uint64_t key) {
+    if (key == 0ULL) return false;
+    uint32_t i = (uint32_t)((key * 0x9E3779B97F4A7C15ULL) >> 32) & a.hot_mask;
+    for (;;) {
+        const unsigned long long k = __ldg(a.hot_keys + i);
+        if (k == key) return true;
+        if (k == 0ULL) return false;
+        i = (i + 1u) & a.hot_mask;
+    }
+}
+
 template <bool DEST>
-__device__ __forceinline__ uint32_t part_bin(const PartArgs &a, uint64_t h) {
-    if (DEST) return (uint32_t)((((uint32_t)(h >> 32) & 0xfffffu) * (uint32_t)a.n_dest) >> 20);
+__device__ __forceinline__ uint32_t part_bin(const PartArgs &a, uint64_t h, uint64_t key) {
+    if (DEST) {
+        if (a.hot_keys != nullptr && part_is_hot(a, key)) return (uint32_t)a.n_dest;
+        return (uint32_t)((((uint32_t)(h >> 32) & 0xfffffu) * (uint32_t)a.n_dest) >> 20);
+    }
     return (uint32_t)(h >> (64 - a.radix_bits));
 }
 
@@ -158,7 +176,7 @@ __device__ __forceinline__ void part_tile_bins(const PartArgs &a, uint32_t tile,
     part_load_tile<KW, GUARD>(a, tile, t, key, row, in);
 #pragma unroll
     for (int q = 0; q < RP_ITEMS; q++) {
-        bin[q] = part_bin<DEST>(a, hash_one(a.hk, key[q]));
+        bin[q] = part_bin<DEST>(a, hash_one(a.hk, key[q]), key[q]);
         if (GUARD) {
             if (!((in >> q) & 1u)) bin[q] = 0xffffffffu;
             else if (a.validity != nullptr && !bit_valid(a.validity, a.bit_offset + (int64_t)row[q])) bin[q] = a.n_bins;
@@ -303,8 +321,8 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
     __shared__ __align__(8) uint64_t s_bar[2];
     __shared__ uint32_t s_wsum[SC_THREADS / 32];
     __shared__ uint32_t s_total;
-    __shared__ KeyT *s_dkeys[RP_MAX_DEST + 1];
-    __shared__ uint32_t *s_drid[RP_MAX_DEST + 1];
+    __shared__ KeyT *s_dkeys[RP_MAX_DEST + 2];
+    __shared__ uint32_t *s_drid[RP_MAX_DEST + 2];
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const uint32_t mis = a.mis;
@@ -315,7 +333,7 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
         s_cnt[p] = 0;
         s_cur[p] = a.bin_base[p] + a.cta_hist[(size_t)p * gridDim.x + blockIdx.x];
     }
-    if (DEST && t <= RP_MAX_DEST) { s_dkeys[t] = reinterpret_cast<KeyT *>(a.dest_keys[t]); s_drid[t] = a.dest_rid[t]; }
+    if (DEST && t <= RP_MAX_DEST + 1) { s_dkeys[t] = reinterpret_cast<KeyT *>(a.dest_keys[t]); s_drid[t] = a.dest_rid[t]; }
     if (t == 0) { mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
@@ -371,7 +389,7 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
             }
 #pragma unroll
             for (int j = 0; j < PER_VEC; j++) {
-                uint32_t bin = part_bin<DEST>(a, hash_one(a.hk, (uint64_t)k[j]));
+                uint32_t bin = part_bin<DEST>(a, hash_one(a.hk, (uint64_t)k[j]), (uint64_t)k[j]);
                 bool in = true;
                 if (!inner) {
                     const uint32_t vrow = vbase + src0 + j;

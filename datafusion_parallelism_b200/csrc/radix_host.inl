@@ -41,7 +41,10 @@ PartPlan part_plan(H *h, const void *keys, const uint8_t *validity, int64_t bit_
     a.mis = (uint32_t)(((uintptr_t)keys & 15) / (uintptr_t)kw);
     a.radix_bits = bits;
     a.n_dest = n_dest;
-    a.n_bins = pl.dest ? (uint32_t)n_dest : (1u << bits);
+    const bool hot = pl.dest && h->hot_n > 0;          // DEST mode bins: [ranks][hot, kept local][NULL keys]
+    a.hot_keys = hot ? (const unsigned long long *)h->hot_table.p : nullptr;
+    a.hot_mask = hot ? h->hot_mask : 0u;
+    a.n_bins = pl.dest ? (uint32_t)n_dest + (hot ? 1u : 0u) : (1u << bits);
     a.hk = h->hk;
     const int64_t n_tiles = (n + a.mis + SC_TILE - 1) / SC_TILE;
     // DEST mode (multi-GPU exchange): the scatter's stores cross NVLink and its CTAs mostly wait; a smaller grid leaves the
@@ -213,7 +216,8 @@ void do_shuffle_count(H *h, const b200j_batch *b, int32_t n_dest, int64_t *count
     REQUIRE(counts != nullptr, B200J_ERR_INVALID, "counts is NULL");
     REQUIRE(b->mem == B200J_MEM_DEVICE || b->n_rows == 0, B200J_ERR_UNSUPPORTED, "the exchange takes device-resident batches");
     h->shuffle_armed = false;
-    for (int d = 0; d <= n_dest; d++) counts[d] = 0;
+    const bool hot = h->hot_n > 0;
+    for (int d = 0; d <= n_dest + (hot ? 1 : 0); d++) counts[d] = 0;
     if (b->n_rows == 0) {
         h->shuffle_n = 0;
         h->shuffle_armed = true;
@@ -225,7 +229,13 @@ void do_shuffle_count(H *h, const b200j_batch *b, int32_t n_dest, int64_t *count
     part_hist(h, h->shuffle_plan, true);
     tm.stop();
     const unsigned long long *off = h->rscratch.h_off;
-    for (int d = 0; d <= n_dest; d++) counts[d] = (int64_t)(off[d + 1] - off[d]);
+    for (int d = 0; d < n_dest; d++) counts[d] = (int64_t)(off[d + 1] - off[d]);
+    if (hot) {      // internal bin order [ranks][hot][NULL] -> API order [ranks][NULL][hot]
+        counts[n_dest + 1] = (int64_t)(off[n_dest + 1] - off[n_dest]);
+        counts[n_dest] = (int64_t)(off[n_dest + 2] - off[n_dest + 1]);
+    } else {
+        counts[n_dest] = (int64_t)(off[n_dest + 1] - off[n_dest]);
+    }
     h->shuffle_n = b->n_rows;
     h->shuffle_armed = true;
 }
@@ -237,20 +247,51 @@ void do_shuffle_scatter(H *h, int32_t n_dest, void *const *dest_keys, uint32_t *
     PartPlan &pl = h->shuffle_plan;
     REQUIRE(n_dest == pl.a.n_dest, B200J_ERR_INVALID, "n_dest differs from the b200j_shuffle_count call");
     REQUIRE(dest_keys && dest_rowid && dest_offset, B200J_ERR_INVALID, "destination arrays missing");
-    uint32_t base[B200J_MAX_DEST + 1];
+    uint32_t base[B200J_MAX_DEST + 2];
     const unsigned long long *off = h->rscratch.h_off;
-    for (int d = 0; d <= n_dest; d++) {
-        const bool used = off[d + 1] > off[d];
+    const bool hot = pl.a.hot_keys != nullptr;
+    REQUIRE(hot == (h->hot_n > 0), B200J_ERR_STATE, "the hot-key set changed between b200j_shuffle_count and b200j_shuffle_scatter");
+    const int n_api = n_dest + 1 + (hot ? 1 : 0);
+    for (int d = 0; d < n_api; d++) {
+        // API order [ranks][NULL][hot] -> internal bin order [ranks][hot][NULL]
+        const int bin = d < n_dest ? d : (hot ? (d == n_dest ? n_dest + 1 : n_dest) : n_dest);
+        const bool used = off[bin + 1] > off[bin];
         REQUIRE(!used || (dest_keys[d] && dest_rowid[d]), B200J_ERR_INVALID, "destination buffer missing for a non-empty destination");
         REQUIRE(dest_offset[d] >= 0 && dest_offset[d] < 0xffff0000LL, B200J_ERR_INVALID, "destination offset out of range");
-        base[d] = (uint32_t)dest_offset[d];
-        pl.a.dest_keys[d] = dest_keys[d];
-        pl.a.dest_rid[d] = dest_rowid[d];
+        base[bin] = (uint32_t)dest_offset[d];
+        pl.a.dest_keys[bin] = dest_keys[d];
+        pl.a.dest_rid[bin] = dest_rowid[d];
     }
     pl.a.rid_base = rowid_base;
     PhaseTimer tm(h, &h->st.ms_exchange_partition);
-    CU(cudaMemcpyAsync(h->rscratch.bin_base, base, (size_t)(n_dest + 1) * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemcpyAsync(h->rscratch.bin_base, base, (size_t)n_api * 4, cudaMemcpyHostToDevice, h->stream));
     CU(cudaStreamSynchronize(h->stream));      // `base` is a stack array
     part_scatter(h, pl);
     tm.stop();
+}
+
+// Heavy-hitter key set of the exchange: rows with these keys stay on the rank that holds them (see part_is_hot).
+void do_shuffle_set_hot(H *h, const uint64_t *keys, int32_t n) {
+    REQUIRE(n >= 0 && n <= 65536, B200J_ERR_INVALID, "hot key count must be in 0..65536");
+    REQUIRE(n == 0 || keys != nullptr, B200J_ERR_INVALID, "hot keys missing");
+    REQUIRE(!h->shuffle_armed, B200J_ERR_STATE, "b200j_shuffle_set_hot between b200j_shuffle_count and b200j_shuffle_scatter");
+    h->hot_n = 0;
+    if (n == 0) return;
+    uint32_t size = 64;
+    while (size < (uint32_t)n * 4u) size <<= 1;
+    std::vector<unsigned long long> tab(size, 0ULL);
+    int kept = 0;
+    for (int i = 0; i < n; i++) {
+        const unsigned long long k = keys[i];
+        if (k == 0ULL) continue;                       // the key value 0 marks an empty slot: it is never routed as hot
+        uint32_t j = (uint32_t)((k * 0x9E3779B97F4A7C15ULL) >> 32) & (size - 1);
+        while (tab[j] != 0ULL && tab[j] != k) j = (j + 1) & (size - 1);
+        if (tab[j] == 0ULL) { tab[j] = k; kept++; }
+    }
+    if (kept == 0) return;
+    dev_alloc(h, h->hot_table, (size_t)size * 8);
+    CU(cudaMemcpyAsync(h->hot_table.p, tab.data(), (size_t)size * 8, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));              // `tab` is a stack-owned vector
+    h->hot_mask = size - 1;
+    h->hot_n = kept;
 }

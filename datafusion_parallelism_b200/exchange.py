@@ -87,10 +87,18 @@ def _dev_column(ptr: int, n_rows: int, width: int, keep=None):
     return ColumnRef(ptr or None, None, None, 0, n_rows, MEM_DEVICE, width, keep)
 
 
-def shuffle_count(join: HashJoin, keys, n_dest: int) -> np.ndarray:
-    """b200j_shuffle_count: rows of `keys` (device column) per destination rank; [n_dest] = NULL-key rows."""
+def shuffle_set_hot(join: HashJoin, hot_keys) -> None:
+    """b200j_shuffle_set_hot: key values whose rows stay on the rank that holds them (empty / None = off)."""
+    hk = np.ascontiguousarray(np.asarray(hot_keys if hot_keys is not None else [], dtype=np.uint64))
+    ptr = hk.ctypes.data_as(C.POINTER(C.c_uint64)) if hk.size else None
+    join._check(N.lib().b200j_shuffle_set_hot(join._h, ptr, int(hk.size)))
+
+
+def shuffle_count(join: HashJoin, keys, n_dest: int, hot: bool = False) -> np.ndarray:
+    """b200j_shuffle_count: rows of `keys` (device column) per destination rank; [n_dest] = NULL-key rows,
+    [n_dest + 1] = rows of hot keys (only with a hot set)."""
     b, keep = make_batch([keys])
-    counts = (C.c_int64 * (n_dest + 1))()
+    counts = (C.c_int64 * (n_dest + 2))()
     join._check(N.lib().b200j_shuffle_count(join._h, C.byref(b), n_dest, counts))
     return np.array(list(counts), dtype=np.int64)
 
@@ -98,9 +106,10 @@ def shuffle_count(join: HashJoin, keys, n_dest: int) -> np.ndarray:
 def shuffle_scatter(join: HashJoin, n_dest: int, dest_keys: Sequence[int], dest_rowid: Sequence[int], dest_offset: Sequence[int],
                     rowid_base: int = 0):
     """b200j_shuffle_scatter: write every (key, row id) of the counted batch to its destination buffer."""
-    dk = (C.c_void_p * (n_dest + 1))(*[C.c_void_p(int(p) if p else None) for p in dest_keys])
-    dr = (C.c_void_p * (n_dest + 1))(*[C.c_void_p(int(p) if p else None) for p in dest_rowid])
-    do = (C.c_int64 * (n_dest + 1))(*[int(x) for x in dest_offset])
+    m = len(dest_keys)                      # n_dest + 1, or n_dest + 2 with a hot set
+    dk = (C.c_void_p * m)(*[C.c_void_p(int(p) if p else None) for p in dest_keys])
+    dr = (C.c_void_p * m)(*[C.c_void_p(int(p) if p else None) for p in dest_rowid])
+    do = (C.c_int64 * m)(*[int(x) for x in dest_offset])
     join._check(N.lib().b200j_shuffle_scatter(join._h, n_dest, dk, dr, do, rowid_base))
 
 
@@ -116,6 +125,9 @@ class _Side:
         self.plan: Optional[ExchangePlan] = None
         self.null_keys = None
         self.null_rid = None
+        self.hot_keys = None    # rows of hot keys, kept on this rank (heavy-hitter routing)
+        self.hot_rid = None
+        self.n_hot = 0
 
 
 class DistributedJoin:
@@ -140,6 +152,10 @@ class DistributedJoin:
         self.probe_sides = [_Side(), _Side()]
         self.probe = self.probe_sides[0]
         self.ms_exchange = {"build": 0.0, "probe": 0.0}
+        self.join_type = join_type
+        self.hot = None                 # numpy uint64 hot key values, or None
+        self.hot_join: Optional[HashJoin] = None
+        self.hot_build_keys = self.hot_owner = self.hot_bidx = None
         self.build_rows_local = 0
         self._key_dtype = torch.int64 if key_width == 8 else torch.int32
 
@@ -171,7 +187,10 @@ class DistributedJoin:
         n = int(keys.shape[0])
         xj = self.xjoin if overlapped else self.join
         xs = self.xstream if overlapped else self.stream
-        counts = shuffle_count(xj, keys, W)
+        hot = self.hot is not None and side is not self.build        # the build side is never routed: its rows go to their owners
+        if self.hot is not None:
+            shuffle_set_hot(xj, self.hot if hot else None)
+        counts = shuffle_count(xj, keys, W, hot)
         with torch.cuda.stream(xs):
             mine = torch.from_numpy(counts[:W].copy()).to(keys.device)
             allc = torch.empty(W * W, dtype=torch.int64, device=keys.device)
@@ -186,10 +205,17 @@ class DistributedJoin:
             side.null_keys = torch.empty(n_null, dtype=self._key_dtype, device=keys.device)
             side.null_rid = torch.empty(n_null, dtype=torch.int32, device=keys.device)
             nk, nr = side.null_keys.data_ptr(), side.null_rid.data_ptr()
+        extra_k, extra_r, extra_o = [nk], [nr], [0]
+        side.n_hot = 0
+        if hot:
+            side.n_hot = int(counts[W + 1])
+            side.hot_keys = torch.empty(max(side.n_hot, 1), dtype=self._key_dtype, device=keys.device)
+            side.hot_rid = torch.empty(max(side.n_hot, 1), dtype=torch.int32, device=keys.device)
+            extra_k, extra_r, extra_o = [nk, side.hot_keys.data_ptr()], [nr, side.hot_rid.data_ptr()], [0, 0]
         if self.mode == "p2p":
             # the count all-gather above doubles as the "everyone is done with the previous contents" barrier
-            shuffle_scatter(xj, W, list(side.keys.ptrs) + [nk], list(side.rid.ptrs) + [nr],
-                            list(plan.dest_offset) + [0], rowid_base)
+            shuffle_scatter(xj, W, list(side.keys.ptrs) + extra_k, list(side.rid.ptrs) + extra_r,
+                            list(plan.dest_offset) + extra_o, rowid_base)
             xj.synchronize()
             dist.barrier(group=self.group)          # every peer's stores have landed in my receive buffer
             recv_keys_ptr, recv_rid_ptr = side.keys.local, side.rid.local
@@ -198,7 +224,7 @@ class DistributedJoin:
                 side.send_keys = torch.empty(int(n * 1.1) + 4096, dtype=self._key_dtype, device=keys.device)
                 side.send_rid = torch.empty(int(n * 1.1) + 4096, dtype=torch.int32, device=keys.device)
             sk, sr = side.send_keys.data_ptr(), side.send_rid.data_ptr()
-            shuffle_scatter(xj, W, [sk] * W + [nk], [sr] * W + [nr], list(plan.send_offset[:W]) + [0], rowid_base)
+            shuffle_scatter(xj, W, [sk] * W + extra_k, [sr] * W + extra_r, list(plan.send_offset[:W]) + extra_o, rowid_base)
             n_recv = int(plan.recv_rows[self.rank])
             n_send = int(plan.send_offset[W])
             with torch.cuda.stream(xs):
@@ -223,6 +249,12 @@ class DistributedJoin:
     def reset(self):
         self.join.reset()
         self.build_rows_local = 0
+        if self.hot_join is not None:
+            self.hot_join.close()
+        self.hot = None
+        self.hot_join = None
+        for jh in (self.join, self.xjoin):
+            shuffle_set_hot(jh, None)
 
     def build_push(self, partition: int, keys: Sequence):
         """Exchange this rank's build rows, then append what this rank received to its local build side."""
@@ -234,6 +266,83 @@ class DistributedJoin:
     def build_finish(self, partition: int):
         self.join.build_finish(partition)
 
+    # ---- heavy hitters (SURVEY §8e "skew") ------------------------------------------------------------------------
+    HOT_JOIN_TYPES = ("inner", "right", "right_semi", "right_anti")   # left-side marks would have to travel back to the owners
+
+    def enable_hot_routing(self, sample_keys, hot_fraction: Optional[float] = None, sample_rows: int = 1 << 20, max_hot: int = 256):
+        """Collective, after build_finish. Finds the heavy-hitter probe keys from a sample of this rank's probe keys, agrees
+        on their union over all ranks, BROADCASTS the build rows of those keys (every rank looks the hot keys up in its own
+        table; the matches are all-gathered and loaded into a small local join), and tells the exchange kernels to keep rows
+        with these keys where they are. A key holding the fraction f of all probe rows would otherwise send f * N rows to one
+        GPU whose fair share is N / G. Returns the number of hot keys (0: routing stays off)."""
+        torch, dist = self.torch, self.dist
+        if self.join_type not in self.HOT_JOIN_TYPES:
+            raise ValueError(f"heavy-hitter routing supports {self.HOT_JOIN_TYPES}, not {self.join_type}")
+        W = self.world
+        if hot_fraction is None:
+            hot_fraction = 1.0 / (32.0 * W)
+        n = int(sample_keys.shape[0])
+        stride = max(1, n // sample_rows)
+        samp = sample_keys[::stride][:sample_rows]
+        uniq, cnt = torch.unique(samp, return_counts=True)
+        sel = cnt.to(torch.float64) >= hot_fraction * float(samp.shape[0])
+        uniq, cnt = uniq[sel], cnt[sel]
+        if int(uniq.shape[0]) > max_hot:
+            top = torch.topk(cnt, max_hot).indices
+            uniq = uniq[top]
+        mine = torch.zeros(max_hot, dtype=torch.int64, device=sample_keys.device)          # 0 = padding (never hot)
+        mine[: int(uniq.shape[0])] = uniq.to(torch.int64) if self.kw == 8 else (uniq.to(torch.int64) & 0xFFFFFFFF)
+        allk = torch.empty(W * max_hot, dtype=torch.int64, device=sample_keys.device)
+        dist.all_gather_into_tensor(allk, mine, group=self.group)
+        hot = torch.unique(allk)
+        hot = hot[hot != 0]
+        self.hot = None
+        self.hot_join = None
+        if int(hot.shape[0]) == 0:
+            for jh in (self.join, self.xjoin):
+                shuffle_set_hot(jh, None)
+            return 0
+        # the owners' build rows of the hot keys -> everyone
+        hk_dev = hot if self.kw == 8 else hot.to(torch.int32)
+        from .join import OUT_MATCHES_ONLY
+        res = self.join.probe_batch(0, [hk_dev], want=OUT_PAIRS | OUT_MATCHES_ONLY)
+        b_, p_ = res.device_arrays()
+        if res.n:
+            bi = torch.as_tensor(b_, device=hot.device).cpu().numpy().astype(np.int64)
+            pi = torch.as_tensor(p_, device=hot.device).cpu().numpy().astype(np.int64) & 0xFFFFFFFF
+        else:
+            bi = pi = np.zeros(0, dtype=np.int64)
+        res.release()
+        hot_np = hot.cpu().numpy()
+        parts: List = [None] * W
+        dist.all_gather_object(parts, (hot_np[pi], bi), group=self.group)
+        keys_all = np.concatenate([p[0] for p in parts]).astype(np.int64)
+        self.hot_owner = np.concatenate([np.full(len(p[0]), r, dtype=np.int32) for r, p in enumerate(parts)])
+        self.hot_bidx = np.concatenate([p[1] for p in parts]).astype(np.int64)
+        self.hot_build_keys = torch.from_numpy(keys_all).to(hot.device)
+        if self.kw == 4:
+            self.hot_build_keys = self.hot_build_keys.to(torch.int32)
+        self.hot_join = HashJoin(self.join_type, key_widths=(self.kw,), stream=self.stream.cuda_stream,
+                                 device=torch.cuda.current_device())
+        self.hot_join.build_push(0, [self.hot_build_keys])
+        self.hot_join.build_finish(0)
+        self.hot = hot_np.astype(np.uint64)
+        return int(self.hot.shape[0])
+
+    def _probe_hot(self, side: _Side, res, want: int):
+        """Rows of hot keys never left this rank: join them against the broadcast build rows. res.hot = PairResult whose
+        build_idx indexes hot_build_keys / hot_owner / hot_bidx (owner rank and its local build row) and whose probe_idx
+        indexes side.hot_rid (the row's index in this rank's probe batch)."""
+        res.hot = None
+        res.n_hot = 0
+        if self.hot_join is None:
+            return res
+        hk = side.hot_keys[: side.n_hot]
+        res.hot = self.hot_join.probe_batch(0, [hk], want=want)
+        res.n_hot = res.hot.n
+        res.hot_rid = side.hot_rid[: side.n_hot]
+        return res
+
     def probe_batch(self, partition: int, keys: Sequence, want: int = OUT_PAIRS):
         """Exchange one probe batch, probe the received rows locally. The result's indices are LOCAL: build_idx counts
         the build rows this rank received (in arrival order), probe_idx the rows of the received probe batch; map them to
@@ -242,7 +351,7 @@ class DistributedJoin:
         n_recv = self._timed("probe", lambda: self._exchange(self.probe, k, rowid_base=0))
         res = self.join.probe_batch(partition, [_dev_column(self.probe.recv_keys_ptr, n_recv, self.kw, keep=(self.probe.keys,))], want=want)
         res.exchange_plan = self.probe.plan
-        return res
+        return self._probe_hot(self.probe, res, want)
 
     def probe_chunks(self, partition: int, key_chunks: Sequence, want: int = OUT_PAIRS):
         """Generator over the results of a sequence of probe chunks (device key tensors), with the partition + exchange
@@ -288,7 +397,7 @@ class DistributedJoin:
             self.probe = side
             res = self.join.probe_batch(partition, [_dev_column(side.recv_keys_ptr, got, self.kw, keep=(side.keys,))], want=want)
             res.exchange_plan = side.plan
-            yield res
+            yield self._probe_hot(side, res, want)
 
     def probe_finish(self, partition: int, want: int = OUT_PAIRS):
         return self.join.probe_finish(partition, want=want)
@@ -334,6 +443,8 @@ class DistributedJoin:
                     if b is not None:
                         b.close(self.dist)
                 side.keys = side.rid = None
+        if self.hot_join is not None:
+            self.hot_join.close()
         self.xjoin.close()
         self.join.close()
 

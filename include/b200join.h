@@ -253,10 +253,16 @@ int32_t b200j_gathered_release(b200j_handle *h, b200j_gathered *g);
  * No other call on the handle may come between the two. Rows whose key is NULL are counted in
  * counts[n_dest] and written to destination n_dest (keep that one local: NULL keys never match). */
 #define B200J_MAX_DEST 16
-int32_t b200j_shuffle_count(b200j_handle *h, const b200j_batch *batch, int32_t n_dest, int64_t *counts /* [n_dest + 1] */);
+int32_t b200j_shuffle_count(b200j_handle *h, const b200j_batch *batch, int32_t n_dest, int64_t *counts /* [n_dest + 1], [n_dest + 2] with a hot set */);
 int32_t b200j_shuffle_scatter(b200j_handle *h, int32_t n_dest, void *const *dest_keys /* [n_dest + 1] */,
                               uint32_t *const *dest_rowid /* [n_dest + 1] */, const int64_t *dest_offset /* [n_dest + 1] first row to
                               write in each destination buffer */, uint32_t rowid_base /* added to the batch-local row index */);
+/* Heavy-hitter routing (SURVEY §8e "skew"). Rows whose key is in the hot set are NOT sent to the key's owner: they go
+ * to one extra, rank-local destination, to be joined there against the build rows of the hot keys, which the caller
+ * broadcasts (a hot key would otherwise deliver its whole probe volume to one GPU). With a non-empty hot set the count /
+ * scatter calls take n_dest + 2 entries: [0, n_dest) ranks, [n_dest] NULL keys, [n_dest + 1] hot keys. `keys`: host array
+ * of key values (32-bit keys zero-extended); the value 0 is ignored; n = 0 switches the routing off. */
+int32_t b200j_shuffle_set_hot(b200j_handle *h, const uint64_t *keys, int32_t n);
 /* Device buffers that peers on the same node can map (cudaIpc): `handle_out` is 64 opaque bytes to send to the peers. */
 #define B200J_IPC_HANDLE_BYTES 64
 int32_t b200j_ipc_alloc(b200j_handle *h, size_t bytes, void **ptr, uint8_t *handle_out);

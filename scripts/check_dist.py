@@ -13,6 +13,8 @@ ap.add_argument("--mode", default="p2p")
 ap.add_argument("--build", type=int, default=5_000_000)
 ap.add_argument("--probe", type=int, default=40_000_000)
 ap.add_argument("--chunk", type=int, default=6_000_000)
+ap.add_argument("--hot-share", type=float, default=0.0, help="this fraction of every rank's probe rows carries ONE key (extreme heavy hitter)")
+ap.add_argument("--zipf", action="store_true", help="Zipf(1) probe keys: heavy hitters, routed with enable_hot_routing on the second pass")
 a = ap.parse_args()
 rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(lr)
@@ -23,6 +25,16 @@ g = torch.Generator(device=dev)
 g.manual_seed(11 + rank)
 bk = torch.randperm(a.build, device=dev, generator=g, dtype=torch.int64) * world + rank       # unique over all ranks
 pk = torch.randint(0, a.build * world, (a.probe,), device=dev, generator=g, dtype=torch.int64)
+if a.zipf:
+    import math
+    u = torch.rand(a.probe, device=dev, generator=g, dtype=torch.float64)
+    ks = a.build * world
+    pk = (torch.exp(u * math.log(ks + 0.5)) - 0.5).clamp_(0, ks - 1).to(torch.int64)
+    pk = (pk * 2654435761) % ks                       # hot keys spread over the key space (and over the owners)
+if a.hot_share > 0:
+    m = torch.rand(a.probe, device=dev, generator=g) < a.hot_share
+    pk = torch.where(m, torch.full_like(pk, 12345 * world + 1), pk)
+    a.zipf = True                                     # second pass routes the heavy hitter
 stream = torch.cuda.Stream(device=dev)
 j = DistributedJoin("inner", key_width=8, stream=stream, mode=a.mode, layout="radix", radix_bits=5)
 for rep in range(2):                                    # second pass re-uses the receive buffers
@@ -31,7 +43,12 @@ for rep in range(2):                                    # second pass re-uses th
     j.build_finish(0)
     n_b = j.build_rows_local
     bkeys = torch.as_tensor(_RawCudaArray(j.build.recv_keys_ptr, n_b, "<i8"), device=dev).clone()
-    tot = 0
+    lo_of = [0]
+    n_hot_keys = j.enable_hot_routing(pk) if (a.zipf and rep == 1) else 0
+    tot, recv_rows, hot_rows = 0, 0, 0
+    torch.cuda.synchronize(); dist.barrier()
+    import time
+    t_start = time.perf_counter()
     for r in j.probe_chunks(0, [pk[lo:lo + a.chunk] for lo in range(0, a.probe, a.chunk)], want=d.OUT_PAIRS):
         side = j.probe
         n_recv = int(side.plan.recv_rows[rank])
@@ -43,10 +60,31 @@ for rep in range(2):                                    # second pass re-uses th
         assert bool((bkeys[bi] == pkeys[pi]).all()), "a pair joins different keys"
         assert int(torch.unique(pi).numel()) == n_recv, "a probe row is missing or doubled"
         tot += r.n
+        recv_rows += n_recv
+        if r.hot is not None:
+            hb_, hp_ = r.hot.device_arrays()
+            if r.hot.n:
+                hb = torch.as_tensor(hb_, device=dev).to(torch.int64)
+                hp = torch.as_tensor(hp_, device=dev).to(torch.int64) & 0xffffffff
+                assert bool((j.hot_build_keys[hb] == side.hot_keys[: side.n_hot][hp]).all()), "a hot pair joins different keys"
+                assert int(torch.unique(hp).numel()) == side.n_hot == r.hot.n, "a hot probe row is missing or doubled"
+                assert bool((pk[lo_of[0] + r.hot_rid.to(torch.int64)[hp]] == side.hot_keys[: side.n_hot][hp]).all()), "hot row id does not point at its row"
+            tot += r.hot.n
+            hot_rows += r.hot.n
+            r.hot.release()
+        lo_of[0] += a.chunk
         r.release()
+    torch.cuda.synchronize(); dist.barrier()
+    ms = (time.perf_counter() - t_start) * 1e3
     t = torch.tensor([tot], device=dev, dtype=torch.int64)
     dist.all_reduce(t)
     assert int(t.item()) == a.probe * world, (int(t.item()), a.probe * world)
+    rr = torch.tensor([recv_rows + hot_rows], device=dev, dtype=torch.int64)
+    allr = [torch.zeros_like(rr) for _ in range(world)]
+    dist.all_gather(allr, rr)
+    if rank == 0:
+        loads = [int(x.item()) for x in allr]
+        print(f"pass {rep}: hot keys {n_hot_keys}, rows joined per rank {loads} (max/mean {max(loads) / (sum(loads) / world):.3f}), probe side {ms:.1f} ms wall")
 if rank == 0:
     print(f"check_dist ok: {world} ranks, mode {a.mode}, {a.probe * world} pairs, every pair key-equal")
 j.close()

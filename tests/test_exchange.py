@@ -128,3 +128,51 @@ def test_emulated_ranks_join_matches_oracle(world, dtype):
     o1 = np.lexsort((got_b, got_p))
     o2 = np.lexsort((ob, op.astype(np.uint64)))
     assert np.array_equal(got_b[o1], ob[o2]) and np.array_equal(got_p[o1], op.astype(np.uint64)[o2])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [np.int64, np.int32])
+def test_hot_keys_stay_local(dtype):
+    """Heavy-hitter routing of the exchange kernels (b200j_shuffle_set_hot): rows whose key is in the hot set are counted in,
+    and scattered to, the extra rank-local destination; every other row goes where it went without a hot set."""
+    import torch
+    import datafusion_parallelism_b200 as d
+    from datafusion_parallelism_b200.exchange import shuffle_count, shuffle_scatter, shuffle_set_hot
+    rng = np.random.default_rng(9)
+    kw, world, n = np.dtype(dtype).itemsize, 3, 200_000
+    tdt = torch.int64 if kw == 8 else torch.int32
+    keys = rng.integers(1, 40_000, n).astype(dtype)
+    hot_vals = np.array([7, 31_337, 0xF0000001 if kw == 4 else 123_456_789_012], dtype=np.uint64)
+    keys[rng.random(n) < 0.2] = dtype(7)
+    keys[rng.random(n) < 0.05] = np.array([hot_vals[2]], dtype=np.uint64).astype(dtype)[0]
+    is_hot = np.isin(keys.astype(np.uint64) & (0xFFFFFFFF if kw == 4 else 0xFFFFFFFFFFFFFFFF), hot_vals)
+    with d.HashJoin("inner", key_widths=(kw,)) as j:
+        dev = torch.from_numpy(keys).cuda()
+        plain = shuffle_count(j, dev, world)
+        # discard the armed count (a count must be followed by its scatter): scatter into scratch buffers
+        sk = [torch.empty(n, dtype=tdt, device="cuda") for _ in range(world + 2)]
+        sr = [torch.empty(n, dtype=torch.int32, device="cuda") for _ in range(world + 2)]
+        shuffle_scatter(j, world, [t.data_ptr() for t in sk[: world + 1]], [t.data_ptr() for t in sr[: world + 1]], [0] * (world + 1))
+        j.synchronize()
+        dest_plain = np.full(n, -1)
+        for r in range(world):
+            dest_plain[sr[r][: int(plain[r])].cpu().numpy().view(np.uint32)] = r
+        assert (dest_plain >= 0).all()
+
+        shuffle_set_hot(j, hot_vals)
+        c = shuffle_count(j, dev, world, hot=True)
+        assert int(c[world + 1]) == int(is_hot.sum()) and int(c[world]) == 0
+        for r in range(world):
+            assert int(c[r]) == int(((dest_plain == r) & ~is_hot).sum())
+        shuffle_scatter(j, world, [t.data_ptr() for t in sk], [t.data_ptr() for t in sr], [0] * (world + 2))
+        j.synchronize()
+        hot_rows = sr[world + 1][: int(c[world + 1])].cpu().numpy().view(np.uint32)
+        assert np.array_equal(np.sort(hot_rows), np.flatnonzero(is_hot))
+        assert np.array_equal(sk[world + 1][: int(c[world + 1])].cpu().numpy(), keys[hot_rows])
+        for r in range(world):
+            rows = sr[r][: int(c[r])].cpu().numpy().view(np.uint32)
+            assert not is_hot[rows].any() and (dest_plain[rows] == r).all()
+            assert np.array_equal(sk[r][: int(c[r])].cpu().numpy(), keys[rows])
+        shuffle_set_hot(j, None)
+        assert np.array_equal(shuffle_count(j, dev, world)[: world + 1], plain[: world + 1])
+        shuffle_scatter(j, world, [t.data_ptr() for t in sk[: world + 1]], [t.data_ptr() for t in sr[: world + 1]], [0] * (world + 1))
