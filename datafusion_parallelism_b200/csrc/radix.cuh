@@ -26,26 +26,26 @@
 namespace b200j {
 
 #ifndef B200J_RP_THREADS
-#define B200J_RP_THREADS 256
+#define B200J_RP_THREADS 512
 #endif
 #ifndef B200J_RP_ITEMS
 #define B200J_RP_ITEMS 8
 #endif
 #ifndef B200J_RP_CTAS
-#define B200J_RP_CTAS 4
+#define B200J_RP_CTAS 2
 #endif
 constexpr int RP_THREADS = B200J_RP_THREADS;
 constexpr int RP_ITEMS   = B200J_RP_ITEMS;
 constexpr int RP_CTAS    = B200J_RP_CTAS;            // resident CTAs per SM the kernels are tuned for
 constexpr int RP_TILE    = RP_THREADS * RP_ITEMS;      // rows per iteration of the histogram kernel
 #ifndef B200J_SC_THREADS
-#define B200J_SC_THREADS 256
+#define B200J_SC_THREADS 512
 #endif
 #ifndef B200J_SC_TILE
-#define B200J_SC_TILE 4096
+#define B200J_SC_TILE 8192
 #endif
 #ifndef B200J_SC_CTAS
-#define B200J_SC_CTAS 3
+#define B200J_SC_CTAS 2
 #endif
 constexpr int SC_THREADS = B200J_SC_THREADS;           // scatter kernel
 constexpr int SC_TILE    = B200J_SC_TILE;              // rows per iteration of the scatter kernel; a CTA owns tiles_per_cta of them
@@ -53,10 +53,13 @@ constexpr int SC_TILE    = B200J_SC_TILE;              // rows per iteration of 
 #define B200J_SC_NBUF 1
 #endif
 constexpr int SC_NBUF    = B200J_SC_NBUF;              // key staging buffers: 2 = the next tile streams in while this one is processed.
-// Measured on B200, 1 B rows, 2^7 bins, histogram + scatter: 512 thr x 4096 rows x 2 CTAs x 2 buffers 7.95 ms; 256 x 4096 x 3 x 1 buffer
-// 7.55 ms (the third CTA hides the un-prefetched tile better than a second buffer does); 2048-row tiles 10.0 ms and 8192-row
-// tiles at one CTA per SM 8.6 ms: the run a tile appends to a bin (tile / bins rows) must stay long AND several CTAs must
-// overlap their barrier phases.
+// Measured on B200, 1 B rows, 2^7 bins, histogram + scatter (threads x tile rows x CTAs/SM x staging buffers):
+//   512 x 4096 x 2 x 2   7.95 ms   (first version: the next tile streams in while this one is processed)
+//   256 x 4096 x 3 x 1   7.55 ms   (a third CTA hides the un-prefetched tile better than a second buffer does)
+//   256 x 2048 x 4 x 1  10.0  ms   1024 x 8192 x 1 x 2   8.6 ms   1024 x 16384 x 1 x 1   9.8 ms
+//   512 x 8192 x 2 x 1   7.06 ms   and with 512-thread histogram CTAs (2 per SM, same row ranges) 6.78 ms   <- current
+// The run a tile appends to a bin (tile / bins = 64 rows = 512 B of keys) must be long for DRAM write locality AND at least
+// two CTAs per SM must overlap their barrier phases.
 constexpr int SC_CTAS    = B200J_SC_CTAS;              // resident CTAs per SM the scatter kernel (and the grid of both passes) is sized for
 static_assert(SC_TILE % RP_TILE == 0, "a scatter tile must be a whole number of histogram tiles");
 constexpr int RP_MAX_BITS = 12;
