@@ -61,6 +61,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-probe-sample", type=int, default=250_000_000)
+    ap.add_argument("--host-chunk-rows", type=int, default=1 << 27, help="N>1 e2e: probe rows per pipelined host chunk (DistributedJoin.probe_host_chunks)")
     ap.add_argument("--exchange-chunk-rows", type=int, default=0, help="N>1: > 0 = probe rows per exchange / local-join pipeline stage (DistributedJoin.probe_chunks)")
     ap.add_argument("--shuffle", default="p2p", choices=["p2p", "nccl"], help="N>1: fused peer-store scatter or NCCL all-to-all")
     return ap.parse_args()
@@ -374,13 +375,7 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
     steps = max(1, min(args.e2e_steps, args.steps))
     checksum = 0
 
-    if world > 1:
-        # N > 1: the distributed join takes device batches; the host<->device copies are explicit here and inside the timed region
-        bdev = torch.empty_like(bk)
-        pdev = torch.empty(min(chunk, n_probe), dtype=torch.int64, device=dev)
-        out_b = torch.empty(int(min(chunk, n_probe) * 1.3) + 4096, dtype=torch.int64).pin_memory()
-        out_p = torch.empty(int(min(chunk, n_probe) * 1.3) + 4096, dtype=torch.int32).pin_memory()
-        hb_t, hp_t = torch.from_numpy(hb.array), torch.from_numpy(hp.array)
+    host_chunk = min(chunk, args.host_chunk_rows)
 
     def step_host():
         if world > 1:
@@ -391,25 +386,18 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
     def step_host_inner():
         nonlocal checksum
         join.reset()
-        if world > 1:
-            bdev.copy_(hb_t, non_blocking=True)
-            join.build_push(0, [bdev])
-        else:
-            join.build_push(0, [hb.array])
-        join.build_finish(0)
         tot = 0
+        if world > 1:
+            # N > 1: DistributedJoin's host-batch calls; H2D of chunk k+1 and D2H of chunk k-1's pairs overlap chunk k's exchange + join
+            join.build_push_host(0, hb.array)
+            join.build_finish(0)
+            for r in join.probe_host_chunks(0, hp.array, chunk_rows=host_chunk, want=d.OUT_PAIRS):
+                tot += r.n
+            return tot
+        join.build_push(0, [hb.array])
+        join.build_finish(0)
         for lo in range(0, n_probe, chunk):
-            if world > 1:
-                m = min(chunk, n_probe - lo)
-                pdev[:m].copy_(hp_t[lo:lo + m], non_blocking=True)
-                r = join.probe_batch(0, [pdev[:m]], want=d.OUT_PAIRS)
-                b_, p_ = r.device_arrays()
-                if r.n:
-                    out_b[:r.n].copy_(torch.as_tensor(b_, device=dev), non_blocking=True)
-                    out_p[:r.n].copy_(torch.as_tensor(p_, device=dev), non_blocking=True)
-                    torch.cuda.synchronize()
-            else:
-                r = join.probe_batch(0, [hp.array[lo:lo + chunk]], want=d.OUT_PAIRS | d.OUT_HOST)
+            r = join.probe_batch(0, [hp.array[lo:lo + chunk]], want=d.OUT_PAIRS | d.OUT_HOST)
             tot += r.n
             r.release()
         return tot
@@ -429,7 +417,8 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
     hp.free()
     return {"value": (n_build + n_probe) * world / (dt / steps), "unit": UNIT, "h2d_bytes_per_step": 8 * (n_build + n_probe),
             "d2h_bytes_per_step": 12 * tot, "steps": steps, "ms_per_step": dt / steps * 1e3,
-            "api": "HashJoin.build_push/probe_batch(host numpy over b200j_host_alloc pinned buffers, OUT_PAIRS|OUT_HOST) -> b200j_* C ABI"}
+            "api": ("HashJoin.build_push/probe_batch(host numpy over b200j_host_alloc pinned buffers, OUT_PAIRS|OUT_HOST) -> b200j_* C ABI" if world == 1 else
+                    f"DistributedJoin.build_push_host/probe_host_chunks(pinned numpy in, pinned pairs out, {host_chunk}-row chunks) -> b200j_* C ABI")}
 
 
 def main():

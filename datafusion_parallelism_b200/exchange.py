@@ -399,6 +399,96 @@ class DistributedJoin:
             res.exchange_plan = side.plan
             yield self._probe_hot(side, res, want)
 
+    # ---- host batches (pinned numpy in, pinned index pairs out), copies pipelined around the exchange + join ------------
+    def _host_state(self, chunk_rows: int, out_rows: int):
+        """Device staging buffers (two chunks of keys), copy streams and the pinned result arrays; grown, never shrunk."""
+        torch = self.torch
+        hs = getattr(self, "_hs", None)
+        if hs is None:
+            dev = torch.cuda.current_device()
+            hs = self._hs = {"in": torch.cuda.Stream(device=dev), "out": torch.cuda.Stream(device=dev), "chunk": 0, "cap": 0}
+        if chunk_rows > hs["chunk"]:
+            hs["dbuf"] = [torch.empty(chunk_rows, dtype=self._key_dtype, device="cuda") for _ in range(2)]
+            hs["chunk"] = chunk_rows
+        if out_rows > hs["cap"]:
+            ob = torch.empty(out_rows, dtype=torch.int64).pin_memory()
+            op = torch.empty(out_rows, dtype=torch.int32).pin_memory()
+            if hs["cap"]:
+                hs["out"].synchronize()
+                ob[: hs["cap"]].copy_(hs["out_b"])
+                op[: hs["cap"]].copy_(hs["out_p"])
+            hs["out_b"], hs["out_p"], hs["cap"] = ob, op, out_rows
+        return hs
+
+    def build_push_host(self, partition: int, host_keys: np.ndarray):
+        """build_push for a host (ideally pinned) key array: one H2D copy on the join's stream, then the exchange."""
+        torch = self.torch
+        with torch.cuda.stream(self.stream):
+            k = torch.from_numpy(host_keys).to("cuda", non_blocking=True)
+            self.build_push(partition, [k])
+
+    def probe_host_chunks(self, partition: int, host_keys: np.ndarray, chunk_rows: int = 1 << 27, want: int = OUT_PAIRS):
+        """Generator over the chunks of ONE host probe batch (a pinned numpy key array): the H2D copy of chunk k+1 and
+        the D2H copy of chunk k-1's pairs run on their own streams while chunk k is exchanged and joined, so that the
+        PCIe link works in both directions for the whole batch (the multi-GPU counterpart of the C ABI's pipelined host
+        probe). Yields, for every chunk in order, the probe result with `host_build_idx` / `host_probe_idx` set to numpy
+        views of this rank's pinned result arrays (valid until the next call of this method) and `side` = the receive
+        buffers the chunk's LOCAL indices refer to (`origin_probe(idx, side=res.side)`; they survive one more chunk).
+        Every rank must call with the same number of chunks."""
+        torch = self.torch
+        hk = torch.from_numpy(host_keys)
+        n = int(hk.shape[0])
+        chunk_rows = max(1, min(chunk_rows, n))
+        hs = self._host_state(chunk_rows, int(n * 1.05) + 4096)
+        s_in, s_out = hs["in"], hs["out"]
+        bounds = [(lo, min(chunk_rows, n - lo)) for lo in range(0, n, chunk_rows)]
+        ev_in = [torch.cuda.Event(), torch.cuda.Event()]
+
+        def stage(k):
+            lo, m = bounds[k]
+            with torch.cuda.stream(s_in):
+                hs["dbuf"][k & 1][:m].copy_(hk[lo:lo + m], non_blocking=True)
+                ev_in[k & 1].record(s_in)
+
+        def finish(item):
+            res, ev, off = item
+            ev.synchronize()
+            res.host_build_idx = hs["out_b"][off:off + res.n].numpy().view(np.uint64)
+            res.host_probe_idx = hs["out_p"][off:off + res.n].numpy().view(np.uint32)
+            res.release()
+            return res
+
+        if not bounds:
+            return
+        stage(0)
+        pending, off = None, 0
+        for k, (lo, m) in enumerate(bounds):
+            # probe_batch(k-1) returned with its result counted: the staging buffer of chunk k-1 is consumed, chunk k+1 may land in it
+            if k + 1 < len(bounds):
+                stage(k + 1)
+            self.stream.wait_event(ev_in[k & 1])
+            self.probe = self.probe_sides[k & 1]
+            with torch.cuda.stream(self.stream):
+                res = self.probe_batch(partition, [hs["dbuf"][k & 1][:m]], want=want)
+            res.side, res.chunk_lo = self.probe, lo
+            if off + res.n > hs["cap"]:
+                hs = self._host_state(chunk_rows, int((off + res.n) * 1.5) + 4096)
+            done = torch.cuda.Event()
+            done.record(self.stream)
+            ev_out = torch.cuda.Event()
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(done)
+                if res.n:
+                    b_, p_ = res.device_arrays()
+                    hs["out_b"][off:off + res.n].copy_(torch.as_tensor(b_, device="cuda").view(torch.int64), non_blocking=True)
+                    hs["out_p"][off:off + res.n].copy_(torch.as_tensor(p_, device="cuda").view(torch.int32), non_blocking=True)
+                ev_out.record(s_out)
+            if pending is not None:
+                yield finish(pending)
+            pending = (res, ev_out, off)
+            off += res.n
+        yield finish(pending)
+
     def probe_finish(self, partition: int, want: int = OUT_PAIRS):
         return self.join.probe_finish(partition, want=want)
 
@@ -423,8 +513,8 @@ class DistributedJoin:
     def origin_build(self, build_idx):
         return self._origin(self.build, build_idx)
 
-    def origin_probe(self, probe_idx):
-        return self._origin(self.probe, probe_idx)
+    def origin_probe(self, probe_idx, side: Optional[_Side] = None):
+        return self._origin(side if side is not None else self.probe, probe_idx)
 
     def stats(self) -> dict:
         st = self.join.stats()

@@ -85,6 +85,33 @@ for rep in range(2):                                    # second pass re-uses th
     if rank == 0:
         loads = [int(x.item()) for x in allr]
         print(f"pass {rep}: hot keys {n_hot_keys}, rows joined per rank {loads} (max/mean {max(loads) / (sum(loads) / world):.3f}), probe side {ms:.1f} ms wall")
+# host batches: pinned keys in, pinned pairs out, copies pipelined around the exchange + join (probe_host_chunks)
+j.reset()
+hbk = torch.empty(a.build, dtype=torch.int64).pin_memory(); hbk.copy_(bk)
+hpk = torch.empty(a.probe, dtype=torch.int64).pin_memory(); hpk.copy_(pk)
+with torch.cuda.stream(stream):
+    j.build_push_host(0, hbk.numpy())
+    j.build_finish(0)
+    bkeys_h = torch.as_tensor(_RawCudaArray(j.build.recv_keys_ptr, j.build_rows_local, "<i8"), device=dev).cpu().numpy()
+    tot = 0
+    for r in j.probe_host_chunks(0, hpk.numpy(), chunk_rows=a.chunk, want=d.OUT_PAIRS):
+        side = r.side
+        n_recv = int(side.plan.recv_rows[rank])
+        pkeys_h = torch.as_tensor(_RawCudaArray(side.recv_keys_ptr, n_recv, "<i8"), device=dev).cpu().numpy()
+        assert r.n == n_recv == r.host_build_idx.shape[0] == r.host_probe_idx.shape[0]
+        assert (bkeys_h[r.host_build_idx.astype("int64")] == pkeys_h[r.host_probe_idx.astype("int64")]).all(), "host pair joins different keys"
+        src_rank, src_row = j.origin_probe(r.host_probe_idx[:1000], side=side)
+        for sr in range(world):                      # a pair's origin row on THIS rank really holds that key
+            if sr == rank:
+                m = src_rank == sr
+                rows = r.chunk_lo + src_row[m].astype("int64")
+                assert (hpk.numpy()[rows] == pkeys_h[r.host_probe_idx[:1000].astype("int64")][m]).all(), "origin_probe points at the wrong row"
+        tot += r.n
+t = torch.tensor([tot], device=dev, dtype=torch.int64)
+dist.all_reduce(t)
+assert int(t.item()) == a.probe * world, (int(t.item()), a.probe * world)
+if rank == 0:
+    print(f"host chunks ok: {int(t.item())} pairs")
 if rank == 0:
     print(f"check_dist ok: {world} ranks, mode {a.mode}, {a.probe * world} pairs, every pair key-equal")
 j.close()
