@@ -364,7 +364,8 @@ void check_batch(H *h, const b200j_batch *b, int n_payload_expected) {
     REQUIRE(b->mem == B200J_MEM_HOST || b->mem == B200J_MEM_DEVICE, B200J_ERR_INVALID, "batch.mem invalid");
     if (b->n_rows > 0) {
         REQUIRE(b->keys != nullptr, B200J_ERR_INVALID, "batch.keys is NULL");
-        for (int i = 0; i < b->n_keys; i++) REQUIRE(b->keys[i].values != nullptr, B200J_ERR_INVALID, "key column without values buffer");
+        for (int i = 0; i < b->n_keys; i++)       // a Utf8 column of empty / NULL strings only may come without a data buffer
+            REQUIRE(b->keys[i].values != nullptr || h->key_widths[i] == B200J_T_UTF8, B200J_ERR_INVALID, "key column without values buffer");
     }
 }
 
@@ -389,6 +390,49 @@ const uint8_t *stage_validity(H *h, const b200j_column &c, int64_t n_rows, int m
 void free_temps(H *h, std::vector<void *> &temps) {
     for (void *p : temps) big_free(h, p);
     temps.clear();
+}
+
+// The key columns of a batch as the kernels' KeyCols descriptor; host columns are copied to the device (temps).
+// Utf8 keys (width 0): 32-bit Arrow offsets + data bytes; only the bytes the batch's rows refer to are copied.
+KeyCols stage_key_cols(H *h, const b200j_batch *b, int64_t n, std::vector<void *> &temps) {
+    KeyCols kc{};
+    kc.n = h->cfg.n_keys;
+    for (int i = 0; i < kc.n && n > 0; i++) {
+        const int w = h->key_widths[i];
+        const b200j_column &c = b->keys[i];
+        kc.c[i].width = w;
+        kc.c[i].off_width = 4;
+        if (w == B200J_T_UTF8) REQUIRE(c.offsets != nullptr, B200J_ERR_INVALID, "Utf8 key column without offsets buffer");
+        if (b->mem == B200J_MEM_DEVICE) {
+            kc.c[i].values = c.values;
+            kc.c[i].offsets = c.offsets;
+            kc.c[i].validity = c.validity;
+            kc.c[i].bit_offset = c.bit_offset;
+            continue;
+        }
+        void *d = nullptr;
+        if (w == B200J_T_UTF8) {
+            const int64_t o0 = c.offsets[0], nbytes = (int64_t)c.offsets[n] - o0;
+            void *doff = nullptr;
+            CU(big_alloc(h, &doff, (size_t)(n + 1) * 4 + 16));
+            temps.push_back(doff);
+            CU(cudaMemcpyAsync(doff, c.offsets, (size_t)(n + 1) * 4, cudaMemcpyHostToDevice, h->stream));
+            CU(big_alloc(h, &d, (size_t)nbytes + 16));
+            temps.push_back(d);
+            if (nbytes) CU(cudaMemcpyAsync(d, (const char *)c.values + o0, (size_t)nbytes, cudaMemcpyHostToDevice, h->stream));
+            kc.c[i].values = (const char *)d - o0;          // the offsets keep counting from the host buffer's start
+            kc.c[i].offsets = doff;
+        } else {
+            CU(big_alloc(h, &d, (size_t)n * w + 16));
+            temps.push_back(d);
+            CU(cudaMemcpyAsync(d, c.values, (size_t)n * w, cudaMemcpyHostToDevice, h->stream));
+            kc.c[i].values = d;
+        }
+        int64_t boff = 0;
+        kc.c[i].validity = stage_validity(h, c, n, B200J_MEM_HOST, temps, &boff);
+        kc.c[i].bit_offset = boff;
+    }
+    return kc;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -489,6 +533,8 @@ KeyCols build_key_cols(H *h) {
         kc.c[i].validity = h->bkeys[i].has_nulls ? (const uint8_t *)h->bkeys[i].validity.p : nullptr;
         kc.c[i].bit_offset = 0;
         kc.c[i].width = h->key_widths[i];
+        kc.c[i].offsets = h->bkeys[i].offsets.p;           // Utf8: the store's 64-bit offsets
+        kc.c[i].off_width = 8;
     }
     return kc;
 }
@@ -1090,26 +1136,7 @@ void do_probe_composite(H *h, int32_t partition, const b200j_batch *b, uint32_t 
     std::vector<void *> temps;
     ResultOwner cand;
     try {
-        KeyCols pc{};
-        pc.n = nk;
-        for (int i = 0; i < nk && n > 0; i++) {
-            const int w = h->key_widths[i];
-            pc.c[i].width = w;
-            if (b->mem == B200J_MEM_DEVICE) {
-                pc.c[i].values = b->keys[i].values;
-                pc.c[i].validity = b->keys[i].validity;
-                pc.c[i].bit_offset = b->keys[i].bit_offset;
-            } else {
-                void *d = nullptr;
-                CU(big_alloc(h, &d, (size_t)n * w + 16));
-                temps.push_back(d);
-                CU(cudaMemcpyAsync(d, b->keys[i].values, (size_t)n * w, cudaMemcpyHostToDevice, h->stream));
-                pc.c[i].values = d;
-                int64_t boff = 0;
-                pc.c[i].validity = stage_validity(h, b->keys[i], n, B200J_MEM_HOST, temps, &boff);
-                pc.c[i].bit_offset = boff;
-            }
-        }
+        const KeyCols pc = stage_key_cols(h, b, n, temps);
         int64_t cnt = 0, bn = 0;
         if (n > 0) {
             void *dh = nullptr, *dok = nullptr;
@@ -1401,26 +1428,7 @@ void do_hash_keys(H *h, const b200j_batch *b, uint64_t *out) {
     if (n == 0) return;
     std::vector<void *> temps;
     try {
-        KeyCols kc{};
-        kc.n = h->cfg.n_keys;
-        for (int i = 0; i < kc.n; i++) {
-            const int w = h->key_widths[i];
-            kc.c[i].width = w;
-            if (b->mem == B200J_MEM_DEVICE) {
-                kc.c[i].values = b->keys[i].values;
-                kc.c[i].validity = b->keys[i].validity;
-                kc.c[i].bit_offset = b->keys[i].bit_offset;
-            } else {
-                void *d = nullptr;
-                CU(big_alloc(h, &d, (size_t)n * w));
-                temps.push_back(d);
-                CU(cudaMemcpyAsync(d, b->keys[i].values, (size_t)n * w, cudaMemcpyHostToDevice, h->stream));
-                kc.c[i].values = d;
-                int64_t boff = 0;
-                kc.c[i].validity = stage_validity(h, b->keys[i], n, B200J_MEM_HOST, temps, &boff);
-                kc.c[i].bit_offset = boff;
-            }
-        }
+        const KeyCols kc = stage_key_cols(h, b, n, temps);
         uint64_t *d_out = out;
         if (b->mem == B200J_MEM_HOST) {
             void *d = nullptr;
@@ -1508,7 +1516,8 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
         REQUIRE(cfg->n_keys >= 1 && cfg->n_keys <= MAX_KEYS, B200J_ERR_INVALID, "n_keys must be in 1..8");
         REQUIRE(cfg->key_widths != nullptr, B200J_ERR_INVALID, "key_widths is NULL");
         for (int i = 0; i < cfg->n_keys; i++)
-            REQUIRE(cfg->key_widths[i] == 4 || cfg->key_widths[i] == 8, B200J_ERR_UNSUPPORTED, "key columns must be 4 or 8 bytes wide");
+            REQUIRE(cfg->key_widths[i] == 4 || cfg->key_widths[i] == 8 || cfg->key_widths[i] == B200J_T_UTF8, B200J_ERR_UNSUPPORTED,
+                    "key columns must be 4 or 8 bytes wide, or B200J_T_UTF8");
         REQUIRE(cfg->n_build_payload >= 0 && cfg->n_probe_payload >= 0, B200J_ERR_INVALID, "negative payload count");
         REQUIRE(cfg->n_build_payload == 0 || cfg->build_payload_types, B200J_ERR_INVALID, "build_payload_types is NULL");
         REQUIRE(cfg->n_probe_payload == 0 || cfg->probe_payload_types, B200J_ERR_INVALID, "probe_payload_types is NULL");
@@ -1541,6 +1550,7 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
         h->hk = HashKeys{k[0], k[1], k[2], k[3], cfg->hash_flags, 0};
         h->timing = (cfg->flags & B200J_FLAG_TIMING) != 0;
         h->composite = cfg->n_keys > 1;
+        for (int i = 0; i < cfg->n_keys; i++) h->composite |= cfg->key_widths[i] == B200J_T_UTF8;     // Utf8 keys: row-hash table + equal_rows
         h->table_kw = h->composite ? 8 : cfg->key_widths[0];
         cudaDeviceProp prop{};
         CU(cudaGetDeviceProperties(&prop, cfg->device));

@@ -55,6 +55,38 @@ __host__ __device__ __forceinline__ uint64_t hash_one(const HashKeys &k, uint64_
     return (k.flags & 1) ? rotl64(h, (unsigned)(buffer & 63u)) : h;
 }
 
+// hash_one of a Utf8 value: std's `Hash for str` (write(bytes), write_u8(0xff)) over ahash's fallback AHasher
+// {buffer: k1, pad: k0, extra: [k2, k3]} -- restated in oracle/join_oracle.c orc_hash_bytes, which this must equal
+// bit for bit. Unaligned little-endian reads are assembled from bytes (strings start at any offset).
+__device__ __forceinline__ uint64_t load_le(const uint8_t *p, int n) {
+    uint64_t v = 0;
+    for (int i = 0; i < n; i++) v |= (uint64_t)p[i] << (8 * i);
+    return v;
+}
+__device__ __forceinline__ uint64_t ah_large_update(const HashKeys &k, uint64_t buffer, uint64_t a, uint64_t b) {
+    return rotl64((buffer + k.k0) ^ folded_multiply(a ^ k.k2, b ^ k.k3), 23u);
+}
+__device__ inline uint64_t hash_bytes(const HashKeys &k, const uint8_t *d, uint64_t len) {
+    uint64_t buffer = (k.k1 + len) * AHASH_MULTIPLE;
+    if (len > 8) {
+        if (len > 16) {
+            buffer = ah_large_update(k, buffer, load_le(d + len - 16, 8), load_le(d + len - 8, 8));
+            for (uint64_t off = 0; len - off > 16; off += 16)
+                buffer = ah_large_update(k, buffer, load_le(d + off, 8), load_le(d + off + 8, 8));
+        } else {
+            buffer = ah_large_update(k, buffer, load_le(d, 8), load_le(d + len - 8, 8));
+        }
+    } else {
+        uint64_t a = 0, b = 0;
+        if (len >= 4) { a = load_le(d, 4); b = load_le(d + len - 4, 4); }
+        else if (len >= 2) { a = load_le(d, 2); b = d[len - 1]; }
+        else if (len == 1) { a = d[0]; b = d[0]; }
+        buffer = ah_large_update(k, buffer, a, b);
+    }
+    buffer = folded_multiply(0xffULL ^ buffer, AHASH_MULTIPLE);
+    return rotl64(folded_multiply(buffer, k.k0), (unsigned)(buffer & 63u));
+}
+
 // datafusion-common hash_utils::combine_hashes
 __host__ __device__ __forceinline__ uint64_t combine_hashes(uint64_t l, uint64_t r) {
     return ((uint64_t)(17 * 37) + l) * 37ULL + r;
@@ -66,11 +98,12 @@ __host__ __device__ __forceinline__ uint64_t combine_hashes(uint64_t l, uint64_t
 constexpr int MAX_KEYS = 8;
 
 struct KeyCol {
-    const void    *values;
+    const void    *values;     // fixed-width values, or the Utf8 data bytes
     const uint8_t *validity;   // LSB-first bitmap, may be null
     int64_t        bit_offset;
-    int32_t        width;      // 4 or 8
-    int32_t        _pad;
+    int32_t        width;      // 4 or 8; 0 = Utf8
+    int32_t        off_width;  // Utf8: 4 (Arrow int32 offsets of a batch) or 8 (the build store's int64 offsets)
+    const void    *offsets;    // Utf8: n + 1 offsets into `values`
 };
 
 struct KeyCols {
@@ -81,6 +114,21 @@ struct KeyCols {
 
 __device__ __forceinline__ bool bit_valid(const uint8_t *bm, int64_t i) {
     return bm == nullptr || ((bm[i >> 3] >> (i & 7)) & 1);
+}
+
+__device__ __forceinline__ int64_t utf8_offset(const KeyCol &kc, int64_t i) {
+    return kc.off_width == 8 ? reinterpret_cast<const int64_t *>(kc.offsets)[i] : (int64_t)reinterpret_cast<const int32_t *>(kc.offsets)[i];
+}
+
+// hash_one of row i of one key column (the value is known to be non-NULL)
+__device__ __forceinline__ uint64_t hash_col_value(const HashKeys &hk, const KeyCol &kc, int64_t i) {
+    if (kc.width == 0) {
+        const int64_t o0 = utf8_offset(kc, i), o1 = utf8_offset(kc, i + 1);
+        return hash_bytes(hk, reinterpret_cast<const uint8_t *>(kc.values) + o0, (uint64_t)(o1 - o0));
+    }
+    const uint64_t v = kc.width == 8 ? reinterpret_cast<const unsigned long long *>(kc.values)[i]
+                                     : (uint64_t)reinterpret_cast<const uint32_t *>(kc.values)[i];
+    return hash_one(hk, v);
 }
 
 // Table slot: 16 B, two per 32 B sector. key == 0 marks an empty slot (the key value 0 lives in a side slot).
@@ -233,9 +281,7 @@ __global__ void __launch_bounds__(256) hash_keys_kernel(KeyCols cols, int64_t n,
         for (int c = 0; c < cols.n; c++) {
             const KeyCol &kc = cols.c[c];
             if (!bit_valid(kc.validity, kc.bit_offset + i)) continue;     // NULL leaves the running hash unchanged
-            const uint64_t v = kc.width == 8 ? reinterpret_cast<const unsigned long long *>(kc.values)[i]
-                                             : (uint64_t)reinterpret_cast<const uint32_t *>(kc.values)[i];
-            const uint64_t hv = hash_one(hk, v);
+            const uint64_t hv = hash_col_value(hk, kc, i);
             h = (c == 0) ? hv : combine_hashes(hv, h);
         }
         out[i] = h;
@@ -259,9 +305,7 @@ __global__ void __launch_bounds__(256) composite_hash_kernel(KeyCols cols, int64
             for (int c = 0; c < cols.n; c++) {
                 const KeyCol &kc = cols.c[c];
                 if (!bit_valid(kc.validity, kc.bit_offset + i)) { ok = false; continue; }
-                const uint64_t v = kc.width == 8 ? reinterpret_cast<const unsigned long long *>(kc.values)[i]
-                                                 : (uint64_t)reinterpret_cast<const uint32_t *>(kc.values)[i];
-                const uint64_t hv = hash_one(hk, v);
+                const uint64_t hv = hash_col_value(hk, kc, i);
                 h = (c == 0) ? hv : combine_hashes(hv, h);
             }
             if (hk.flags & 2) h &= 0x3ffULL;       // B200J_HASH_TEST_COLLIDE: 1024 hash values, so equal_rows has work to do
@@ -283,7 +327,13 @@ __global__ void __launch_bounds__(256) equal_rows_kernel(KeyCols build, KeyCols 
         for (int c = 0; c < build.n && eq; c++) {
             const KeyCol &bc = build.c[c], &pc = probe.c[c];
             if (!bit_valid(bc.validity, bc.bit_offset + b) || !bit_valid(pc.validity, pc.bit_offset + p)) { eq = false; break; }
-            if (bc.width == 8) eq = reinterpret_cast<const unsigned long long *>(bc.values)[b] == reinterpret_cast<const unsigned long long *>(pc.values)[p];
+            if (bc.width == 0) {
+                const int64_t bo = utf8_offset(bc, b), bl = utf8_offset(bc, b + 1) - bo;
+                const int64_t po = utf8_offset(pc, p), pl = utf8_offset(pc, p + 1) - po;
+                eq = bl == pl;
+                const uint8_t *x = reinterpret_cast<const uint8_t *>(bc.values) + bo, *y = reinterpret_cast<const uint8_t *>(pc.values) + po;
+                for (int64_t j = 0; j < bl && eq; j++) eq = x[j] == y[j];
+            } else if (bc.width == 8) eq = reinterpret_cast<const unsigned long long *>(bc.values)[b] == reinterpret_cast<const unsigned long long *>(pc.values)[p];
             else eq = reinterpret_cast<const uint32_t *>(bc.values)[b] == reinterpret_cast<const uint32_t *>(pc.values)[p];
         }
         if (!eq) { build_idx[i] = ~0ULL; failed++; }

@@ -215,6 +215,7 @@ void do_shuffle_count(H *h, const b200j_batch *b, int32_t n_dest, int64_t *count
     REQUIRE(n_dest >= 1 && n_dest <= B200J_MAX_DEST, B200J_ERR_INVALID, "n_dest must be in 1..16");
     REQUIRE(counts != nullptr, B200J_ERR_INVALID, "counts is NULL");
     REQUIRE(b->mem == B200J_MEM_DEVICE || b->n_rows == 0, B200J_ERR_UNSUPPORTED, "the exchange takes device-resident batches");
+    REQUIRE(h->cfg.n_keys == 1 && h->key_widths[0] != B200J_T_UTF8, B200J_ERR_UNSUPPORTED, "the exchange partitions one fixed-width key column");
     h->shuffle_armed = false;
     const bool hot = h->hot_n > 0;
     for (int d = 0; d <= n_dest + (hot ? 1 : 0); d++) counts[d] = 0;

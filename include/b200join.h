@@ -117,9 +117,11 @@ typedef struct {
     int32_t   n_partitions;           /* number of DataFusion partitions that will call build/probe   */
     int32_t   device;                 /* CUDA device ordinal                                          */
     int32_t   n_keys;
-    const int32_t *key_widths;        /* [n_keys] 4 or 8 (Int32/UInt32/Date32 | Int64/UInt64/Timestamp ...). n_keys > 1
-                                         (composite key): the table is keyed on the row hash and key equality is checked
-                                         on the candidate pairs, as the reference does (datafusion_private.rs:40-80)      */
+    const int32_t *key_widths;        /* [n_keys] 4 or 8 (Int32/UInt32/Date32 | Int64/UInt64/Timestamp ...) or B200J_T_UTF8
+                                         (Utf8: b200j_column.offsets = 32-bit Arrow offsets, .values = data bytes).
+                                         n_keys > 1 (composite key) or a Utf8 key: the table is keyed on the row hash
+                                         (create_hashes, shared.rs:11-16) and key equality is checked on the candidate
+                                         pairs, as the reference does (equal_rows_arr, datafusion_private.rs:40-80)      */
     int32_t   n_build_payload;
     const int32_t *build_payload_types;   /* [n_build_payload] width or B200J_T_UTF8                  */
     int32_t   n_probe_payload;

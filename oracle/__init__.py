@@ -40,7 +40,7 @@ def build(force: bool = False) -> str:
 
 
 class _Col(C.Structure):
-    _fields_ = [("values", C.c_void_p), ("validity", C.c_void_p), ("width", C.c_int32), ("_pad", C.c_int32)]
+    _fields_ = [("values", C.c_void_p), ("validity", C.c_void_p), ("width", C.c_int32), ("_pad", C.c_int32), ("offsets", C.c_void_p)]
 
 
 _lib = None
@@ -135,8 +135,15 @@ class _ColSet:
         self.arr = (_Col * max(1, len(cols)))()
         self.n = len(cols)
         for i, col in enumerate(cols):
-            values, validity, width, n = self._split(col)
-            self.keep += [values, validity]
+            offsets = None
+            if isinstance(col, pa.ChunkedArray):
+                col = col.combine_chunks()
+            if isinstance(col, pa.Array) and (pa.types.is_string(col.type) or pa.types.is_binary(col.type)):
+                values, offsets, validity, width, n = self._split_utf8(col)
+            else:
+                values, validity, width, n = self._split(col)
+            self.keep += [values, validity, offsets]
+            self.arr[i].offsets = offsets.ctypes.data if offsets is not None else None
             if self.n_rows is None:
                 self.n_rows = n
             assert self.n_rows == n, "key columns differ in length"
@@ -145,6 +152,21 @@ class _ColSet:
             self.arr[i].width = width
         if self.n_rows is None:
             self.n_rows = 0
+
+    @staticmethod
+    def _split_utf8(col):
+        """Arrow Utf8: data bytes + n + 1 int32 offsets (rebased to 0); width 0 marks the column as Utf8."""
+        n = len(col)
+        validity = None
+        if col.null_count:
+            validity = np.packbits(np.asarray(col.is_valid()).astype(np.uint8), bitorder="little")
+        bufs = col.buffers()
+        off = np.frombuffer(bufs[1], dtype=np.int32)[col.offset: col.offset + n + 1].copy()
+        data = np.frombuffer(bufs[2], dtype=np.uint8)[int(off[0]): int(off[-1])].copy() if bufs[2] is not None and n else np.zeros(0, np.uint8)
+        off -= off[0]
+        if data.size == 0:
+            data = np.zeros(1, np.uint8)
+        return data, off, validity, 0, n
 
     @staticmethod
     def _split(col):

@@ -35,12 +35,13 @@
 enum { ORC_INNER = 0, ORC_LEFT = 1, ORC_RIGHT = 2, ORC_FULL = 3,
        ORC_LEFT_SEMI = 4, ORC_RIGHT_SEMI = 5, ORC_LEFT_ANTI = 6, ORC_RIGHT_ANTI = 7 };
 
-/* One Arrow primitive key column: values buffer, optional LSB-first validity bitmap. */
+/* One Arrow key column: values buffer, optional LSB-first validity bitmap; Utf8 adds 32-bit offsets. */
 typedef struct {
-    const void    *values;
+    const void    *values;     /* fixed-width values, or the Utf8 data bytes */
     const uint8_t *validity;   /* NULL => all valid */
-    int32_t        width;      /* 4 (Int32/UInt32/Date32) or 8 (Int64/UInt64/…) */
+    int32_t        width;      /* 4 (Int32/UInt32/Date32), 8 (Int64/UInt64/…) or 0 = Utf8 */
     int32_t        _pad;
+    const int32_t *offsets;    /* Utf8: n_rows + 1 offsets into values */
 } orc_col;
 
 /* ------------------------------------------------------------------------------------------ */
@@ -96,6 +97,41 @@ uint64_t orc_hash_u64(const uint64_t k[4], uint64_t v, int flags) {
     return (flags & 1) ? rotl64(h, (unsigned)(buffer & 63)) : h;
 }
 
+/* hash_one for a Utf8 value (datafusion-common 40 hash_utils: `impl HashValue for str` -> state.hash_one(&str)).
+ * [recalled, unpinned] std's `Hash for str` is write(bytes) then write_u8(0xff); ahash 0.8.11 fallback_hash.rs:
+ *   write(bytes): buffer = (buffer + len) * MULTIPLE; then
+ *       len <= 8 : large_update(read_small(bytes));  9..16: large_update([first u64, last u64]);
+ *       len > 16 : large_update(last 16 bytes), then large_update(every leading 16-byte block while > 16 bytes remain)
+ *   large_update([a, b]): buffer = rotl((buffer + pad) ^ folded_multiply(a ^ extra[0], b ^ extra[1]), 23)
+ *   write_u8(x) = update(x): buffer = folded_multiply(x ^ buffer, MULTIPLE);  finish rotates by buffer & 63.
+ * AHasher::from_random_state: buffer = k1, pad = k0, extra = [k2, k3]. Join RESULTS do not depend on this value
+ * (equal_rows_arr compares the strings); the GPU hash is checked bit for bit against this function. */
+static inline uint64_t rd_le(const uint8_t *p, int n) { uint64_t v = 0; memcpy(&v, p, (size_t)n); return v; }
+uint64_t orc_hash_bytes(const uint64_t k[4], const uint8_t *d, uint64_t len) {
+    uint64_t buffer = k[1];
+    const uint64_t pad = k[0];
+    buffer = (buffer + len) * ORC_MULTIPLE;
+#define ORC_LARGE(a, b) buffer = rotl64((buffer + pad) ^ folded_multiply((a) ^ k[2], (b) ^ k[3]), 23)
+    if (len > 8) {
+        if (len > 16) {
+            ORC_LARGE(rd_le(d + len - 16, 8), rd_le(d + len - 8, 8));
+            uint64_t off = 0;
+            while (len - off > 16) { ORC_LARGE(rd_le(d + off, 8), rd_le(d + off + 8, 8)); off += 16; }
+        } else {
+            ORC_LARGE(rd_le(d, 8), rd_le(d + len - 8, 8));
+        }
+    } else {
+        uint64_t a = 0, b = 0;                                    /* read_small */
+        if (len >= 4) { a = rd_le(d, 4); b = rd_le(d + len - 4, 4); }
+        else if (len >= 2) { a = rd_le(d, 2); b = d[len - 1]; }
+        else if (len == 1) { a = d[0]; b = d[0]; }
+        ORC_LARGE(a, b);
+    }
+#undef ORC_LARGE
+    buffer = folded_multiply(0xffULL ^ buffer, ORC_MULTIPLE);      /* write_u8(0xff) of Hash for str */
+    return rotl64(folded_multiply(buffer, pad), (unsigned)(buffer & 63));
+}
+
 /* datafusion-common hash_utils::combine_hashes. */
 static inline uint64_t combine_hashes(uint64_t l, uint64_t r) {
     uint64_t h = (uint64_t)(17 * 37) + l;
@@ -119,7 +155,9 @@ void orc_create_hashes(int32_t n_cols, const orc_col *cols, uint64_t n_rows,
     for (int32_t c = 0; c < n_cols; c++) {
         for (uint64_t i = 0; i < n_rows; i++) {
             if (!col_valid(&cols[c], i)) continue;
-            uint64_t h = orc_hash_u64(k, col_bits(&cols[c], i), flags);
+            uint64_t h = cols[c].width == 0
+                ? orc_hash_bytes(k, (const uint8_t *)cols[c].values + cols[c].offsets[i], (uint64_t)(cols[c].offsets[i + 1] - cols[c].offsets[i]))
+                : orc_hash_u64(k, col_bits(&cols[c], i), flags);
             out[i] = (c == 0) ? h : combine_hashes(h, out[i]);
         }
     }
@@ -299,7 +337,11 @@ void orc_equal_rows(const orc_pairs *in, int32_t n_cols, const orc_col *build_co
         for (int32_t c = 0; c < n_cols && eq; c++) {
             if (!col_valid(&build_cols[c], b) || !col_valid(&probe_cols[c], p)) { eq = 0; break; }
             if (build_cols[c].width != probe_cols[c].width) { eq = 0; break; }
-            if (col_bits(&build_cols[c], b) != col_bits(&probe_cols[c], p)) eq = 0;
+            if (build_cols[c].width == 0) {
+                const int32_t bo = build_cols[c].offsets[b], bl = build_cols[c].offsets[b + 1] - bo;
+                const int32_t po = probe_cols[c].offsets[p], pl = probe_cols[c].offsets[p + 1] - po;
+                if (bl != pl || memcmp((const char *)build_cols[c].values + bo, (const char *)probe_cols[c].values + po, (size_t)bl) != 0) eq = 0;
+            } else if (col_bits(&build_cols[c], b) != col_bits(&probe_cols[c], p)) eq = 0;
         }
         if (eq) orc_pairs_push(out, b, p);
     }

@@ -147,6 +147,76 @@ def test_composite_keys(pkg, join_type, layout, radix_bits, collide):
             assert np.array_equal(j.hash_keys(probes[0]), oracle.create_hashes(probes[0]))
 
 
+UTF8_WORDS = ["", "a", "ab", "abc", "abcd", "abcde", "abcdefg", "abcdefgh", "abcdefghi", "0123456789abcdef", "0123456789abcdefg",
+              "x" * 31, "y" * 32, "z" * 33, "naïve", "日本語のキー"] + [f"customer#{i:09d}" for i in range(400)]
+
+
+def utf8_array(rng, n, null_rate=0.05, hi=None):
+    idx = rng.integers(0, hi or len(UTF8_WORDS), n)
+    return pa.array([UTF8_WORDS[i] for i in idx], type=pa.string(), mask=rng.random(n) < null_rate)
+
+
+@pytest.mark.parametrize("layout,radix_bits", [("direct", 0), ("radix", 5)])
+@pytest.mark.parametrize("join_type", JOIN_TYPES)
+@pytest.mark.parametrize("collide", [0, 2])
+def test_utf8_keys(pkg, join_type, layout, radix_bits, collide):
+    """Utf8 join key ("hash on device, equality via offsets"): key_widths = (B200J_T_UTF8,). The table is
+    keyed on the string's row hash, equal_rows compares the bytes; duplicates and NULLs on both sides, probe words the build
+    side does not have, sliced (offset != 0) probe batches."""
+    rng = np.random.default_rng(hash((join_type, layout, collide, "utf8")) & 0xFFFFFFFF)
+    nb, npr = 6_000, 20_000
+    build = [utf8_array(rng, nb, hi=300)]
+    whole = utf8_array(rng, npr)
+    probes = [[whole.slice(lo, 7_000)] for lo in range(0, npr, 7_000)]
+    oj = oracle.OracleJoin(join_type, build)
+    with pkg.HashJoin(join_type, key_widths=(pkg.T_UTF8,), layout=layout, radix_bits=radix_bits, hash_flags=collide) as j:
+        j.build_push(0, [build[0].slice(0, 2_500)])
+        j.build_push(0, [build[0].slice(2_500)])
+        j.build_finish(0)
+        for i, pb in enumerate(probes):
+            r = j.probe_batch(0, pb)
+            assert_pairs_equal(r.numpy(), oj.probe_batch(pb, len(pb[0])), f"{join_type} batch {i}")
+            r.release()
+        r = j.probe_finish(0)
+        assert_pairs_equal(r.numpy(), oj.finish(), f"{join_type} finaliser")
+        r.release()
+        if collide == 0:
+            for pb in probes[:2]:
+                assert np.array_equal(j.hash_keys(pb), oracle.create_hashes(pb))
+
+
+def test_utf8_with_int_key_device_batches(pkg):
+    """(Utf8, Int32) composite key from DEVICE buffers: data bytes, int32 offsets and the bitmap live in HBM."""
+    import torch
+    rng = np.random.default_rng(77)
+    nb, npr = 3_000, 9_000
+
+    def side(n):
+        s = utf8_array(rng, n, hi=120)
+        k2 = pa.array(rng.integers(0, 4, n).astype(np.int32), mask=rng.random(n) < 0.03)
+        return s, k2
+    bs, b2 = side(nb)
+    ps, p2 = side(npr)
+    want = oracle.OracleJoin("inner", [bs, b2])
+
+    def dev_cols(s, k2):
+        bufs = s.buffers()
+        n = len(s)
+        off = torch.from_numpy(np.frombuffer(bufs[1], dtype=np.int32)[: n + 1].copy()).cuda()
+        data = torch.from_numpy(np.frombuffer(bufs[2], dtype=np.uint8).copy()).cuda()
+        val = torch.from_numpy(np.packbits(np.asarray(s.is_valid()).astype(np.uint8), bitorder="little")).cuda()
+        c0 = pkg.ColumnRef(data.data_ptr(), off.data_ptr(), val.data_ptr(), 0, n, pkg.MEM_DEVICE, pkg.T_UTF8, (off, data, val))
+        v2 = torch.from_numpy(np.packbits(np.asarray(k2.is_valid()).astype(np.uint8), bitorder="little")).cuda()
+        c1 = pkg.column(torch.from_numpy(k2.fill_null(0).to_numpy(zero_copy_only=False).astype(np.int32)).cuda(), validity=v2)
+        return [c0, c1]
+    with pkg.HashJoin("inner", key_widths=(pkg.T_UTF8, 4), layout="direct") as j:
+        j.build_push(0, dev_cols(bs, b2))
+        j.build_finish(0)
+        r = j.probe_batch(0, dev_cols(ps, p2), want=pkg.OUT_PAIRS | pkg.OUT_HOST)
+        assert_pairs_equal(r.numpy(), want.probe_batch([ps, p2], npr), "utf8+int32 device")
+        r.release()
+
+
 @pytest.mark.parametrize("layout,radix_bits", LAYOUT_CASES)
 def test_unique_keys_one_to_one(pkg, layout, radix_bits):
     """The BASELINE C1/C2 shape in miniature: unique build keys (a permutation), uniform probe, every probe row matches once."""

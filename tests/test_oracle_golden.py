@@ -176,6 +176,95 @@ def test_oracle_vs_acero(join_type, seed, key_type):
     assert rows_multiset(got) == exp_rows
 
 
+UTF8_WORDS = ["", "a", "ab", "abc", "abcd", "abcde", "abcdefg", "abcdefgh", "abcdefghi", "0123456789abcdef", "0123456789abcdefg",
+              "x" * 31, "y" * 32, "z" * 33, "naïve", "日本語のキー", "key-000017", "key-000018"] + [f"customer#{i:09d}" for i in range(40)]
+
+
+def utf8_tables(rng, nb, npb, with_second_key=False):
+    def mk(n, base):
+        k = [UTF8_WORDS[i] for i in rng.integers(0, len(UTF8_WORDS), n)]
+        nulls = rng.random(n) < 0.1
+        cols = [pa.array(k, type=pa.string(), mask=nulls)]
+        names = ["k"]
+        if with_second_key:
+            cols.append(pa.array(rng.integers(0, 3, n), type=pa.int32()))
+            names.append("k2")
+        cols.append(pa.array(np.arange(n, dtype=np.int64) + base))
+        names.append("payload")
+        return pa.Table.from_arrays(cols, names=names)
+    return mk(nb, 0), mk(npb, 10_000)
+
+
+@pytest.mark.parametrize("join_type", list(ACERO))
+def test_utf8_keys_vs_acero(join_type):
+    """Utf8 join keys: equality on the string VALUES, NULL never matches; against Acero."""
+    build, probe = utf8_tables(np.random.default_rng(3), 300, 700)
+    got = oracle.join_tables(build, [probe.slice(i, 97) for i in range(0, 700, 97)], [("k", "k")], join_type, build_batch_rows=64)
+    exp = build.join(probe, keys="k", right_keys="k", join_type=ACERO[join_type], left_suffix="_l", right_suffix="_r",
+                     coalesce_keys=False, use_threads=False)
+    if join_type in ("left_semi", "left_anti", "right_semi", "right_anti"):
+        exp_rows = rows_multiset(exp)
+    else:
+        exp_rows = rows_multiset([exp.column(c).to_pylist() for c in ("k_l", "payload_l", "k_r", "payload_r")])
+    assert rows_multiset(got) == exp_rows
+
+
+def test_utf8_hash_restatement():
+    """orc_hash_bytes against a pure-Python restatement of ahash's fallback write(bytes) + write_u8(0xff) + finish for
+    every length class (0, 1, 2-3, 4-8, 9-16, > 16 incl. exact multiples of 16). Parity with a real ahash build: unpinned."""
+    keys = oracle.keys_with_seed(0)
+    k = [int(x) for x in keys]
+    mask, MULT = (1 << 64) - 1, 6364136223846793005
+
+    def fm(s, by):
+        r = s * by
+        return (r & mask) ^ (r >> 64)
+
+    def rotl(x, r):
+        r &= 63
+        return ((x << r) | (x >> (64 - r))) & mask if r else x
+
+    def le(b):
+        return int.from_bytes(b, "little")
+
+    def ref(d: bytes):
+        buf, pad = k[1], k[0]
+        buf = ((buf + len(d)) * MULT) & mask
+
+        def large(buf, a, b):
+            return rotl(((buf + pad) & mask) ^ fm(a ^ k[2], b ^ k[3]), 23)
+        n = len(d)
+        if n > 8:
+            if n > 16:
+                buf = large(buf, le(d[n - 16:n - 8]), le(d[n - 8:]))
+                rest = d
+                while len(rest) > 16:
+                    buf = large(buf, le(rest[:8]), le(rest[8:16]))
+                    rest = rest[16:]
+            else:
+                buf = large(buf, le(d[:8]), le(d[n - 8:]))
+        else:
+            if n >= 4:
+                a, b = le(d[:4]), le(d[n - 4:])
+            elif n >= 2:
+                a, b = le(d[:2]), d[n - 1]
+            elif n == 1:
+                a, b = d[0], d[0]
+            else:
+                a, b = 0, 0
+            buf = large(buf, a, b)
+        buf = fm(0xff ^ buf, MULT)
+        return rotl(fm(buf, pad), buf & 63)
+
+    col = pa.array(UTF8_WORDS + [None], type=pa.string())
+    h = oracle.create_hashes([col], keys)
+    for w, got in zip(UTF8_WORDS, h[:-1]):
+        assert int(got) == ref(w.encode()), w
+    assert h[-1] == 0                                  # NULL leaves the running hash at 0
+    # a sliced array (non-zero offset) hashes like its copy
+    assert (oracle.create_hashes([col.slice(5, 20)], keys) == h[5:25]).all()
+
+
 def test_two_key_columns_vs_acero():
     rng = np.random.default_rng(7)
     n = 500
