@@ -775,9 +775,16 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
         const int64_t extra = (pl.mode == PM_OUTER || pl.mode == PM_ANTI) ? n_null_rows : 0;
         // Dense path (probe.cuh): unique build keys behind the partition pass. The partitioned row-id array becomes the
         // result's probe-index column as it is; the kernel writes one build index (or NULL) per partitioned row.
-        if (radix && !count_only && h->dense_ok && h->st.duplicate_rows == 0 && pn > 0 && (pl.mode == PM_PAIRS || pl.mode == PM_OUTER)) {
-            void *tr = temps.back();              // the row-id array: owned by the result from here on
-            temps.pop_back();
+        // Direct layout: same kernel over the caller's keys when they can be read as 16 B vectors and carry no bitmap.
+        const bool dense_direct = !radix && pvalid == nullptr && ((uintptr_t)pkeys & 15) == 0;
+        if ((radix || dense_direct) && !count_only && h->dense_ok && h->st.duplicate_rows == 0 && pn > 0 && (pl.mode == PM_PAIRS || pl.mode == PM_OUTER)) {
+            void *tr = nullptr;
+            if (radix) {
+                tr = temps.back();                // the row-id array: owned by the result from here on
+                temps.pop_back();
+            } else {
+                CU(big_alloc(h, &tr, (size_t)n * 4 + 16));
+            }
             void *ob = nullptr;
             try {
                 const int64_t rows = pl.mode == PM_OUTER ? n : pn;
@@ -798,12 +805,16 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
                 {
                     PhaseTimer tm(h, &h->st.ms_probe);
                     const int grid = grid_for(h, pn, PD_SUPER, h->dense_ctas_per_sm);
+                    auto launch = [&](auto KW, auto MARK) {
+                        if (radix) probe_dense_kernel<decltype(KW)::value, decltype(MARK)::value, true><<<grid, PD_THREADS, 0, h->stream>>>(a);
+                        else probe_dense_kernel<decltype(KW)::value, decltype(MARK)::value, false><<<grid, PD_THREADS, 0, h->stream>>>(a);
+                    };
                     if (kw == 8) {
-                        if (pl.mark) probe_dense_kernel<8, true><<<grid, PD_THREADS, 0, h->stream>>>(a);
-                        else probe_dense_kernel<8, false><<<grid, PD_THREADS, 0, h->stream>>>(a);
+                        if (pl.mark) launch(std::integral_constant<int, 8>{}, std::true_type{});
+                        else launch(std::integral_constant<int, 8>{}, std::false_type{});
                     } else {
-                        if (pl.mark) probe_dense_kernel<4, true><<<grid, PD_THREADS, 0, h->stream>>>(a);
-                        else probe_dense_kernel<4, false><<<grid, PD_THREADS, 0, h->stream>>>(a);
+                        if (pl.mark) launch(std::integral_constant<int, 4>{}, std::true_type{});
+                        else launch(std::integral_constant<int, 4>{}, std::false_type{});
                     }
                     h->st.kernel_launches++;
                     h->st.probe_launches++;
@@ -1561,7 +1572,7 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
                 h->probe_ctas_per_sm = occ;
             else
                 cudaGetLastError();
-            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, probe_dense_kernel<8, false>, PD_THREADS, 0) == cudaSuccess && occ > 0)
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, probe_dense_kernel<8, false, true>, PD_THREADS, 0) == cudaSuccess && occ > 0)
                 h->dense_ctas_per_sm = occ;
             else
                 cudaGetLastError();

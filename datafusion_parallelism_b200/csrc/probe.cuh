@@ -353,7 +353,9 @@ __global__ void __launch_bounds__(PF_THREADS) probe_fast_kernel(ProbeArgs a) {
 
 
 // =====================================================================================================================
-// Dense probe (radix layout, build keys unique): the output is NOT compacted. Row i of the partitioned probe stream
+// Dense probe (build keys unique): the output is NOT compacted. RADIX = false is the same kernel over the caller's own key
+// buffer (direct layout, 16 B-aligned keys without a validity bitmap); it also writes the probe-index column (row i -> i).
+// Radix layout: Row i of the partitioned probe stream
 // writes out_build[i] = its build row or NULL; the partition pass's row-id array IS the probe-index column of the
 // result, so this kernel neither reads nor writes it: 8 B key in, 8 B build index out per probe row (16 B/row of HBM
 // traffic instead of 24 B), no shared-memory staging, no block barrier on the hot path, no output atomics.
@@ -380,7 +382,7 @@ struct PDShared {
     uint32_t           next;
 };
 
-template <bool MARK>
+template <bool MARK, bool RADIX>
 __device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long long *qkey, uint32_t *qidx, uint32_t first, uint32_t cnt,
                                             int lane, uint32_t &misses) {
     // entries [first, first + cnt) of the warp's queue, one per lane (cnt <= 32)
@@ -390,7 +392,7 @@ __device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long lo
     if (act) {
         const uint64_t h = hash_one(a.hk, key);
         uint32_t base, nb;
-        locate<true>(a.tv, (uint32_t)(h >> 32), base, nb);
+        locate<RADIX>(a.tv, (uint32_t)(h >> 32), base, nb);
         uint32_t b = next_bucket(home_bucket(h, nb), nb);          // the home bucket was full without the key
         unsigned long long res = ~0ULL;
         for (;;) {
@@ -412,7 +414,7 @@ __device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long lo
     }
 }
 
-template <int KW, bool MARK>
+template <int KW, bool MARK, bool RADIX>
 __global__ void __launch_bounds__(PD_THREADS) probe_dense_kernel(ProbeArgs a) {
     constexpr int PER_VEC = 16 / KW;
     constexpr int NVEC = PD_ITEMS / PER_VEC;
@@ -472,7 +474,7 @@ __global__ void __launch_bounds__(PD_THREADS) probe_dense_kernel(ProbeArgs a) {
             for (int q = 0; q < PD_ITEMS; q++) {
                 const uint64_t h = hash_one(a.hk, key[q]);
                 uint32_t base, nb;
-                locate<true>(a.tv, (uint32_t)(h >> 32), base, nb);
+                locate<RADIX>(a.tv, (uint32_t)(h >> 32), base, nb);
                 const Slot *p = key[q] ? bucket_ptr(a.tv, base, home_bucket(h, nb)) : a.tv.zero_slot;
                 load_bucket(p, k0[q], v0[q], k1[q], v1[q]);
             }
@@ -517,6 +519,24 @@ __global__ void __launch_bounds__(PD_THREADS) probe_dense_kernel(ProbeArgs a) {
                     }
                 }
             }
+            // ---- direct layout: no partition pass wrote the probe-index column, so it is written here (row i -> i)
+            if (!RADIX) {
+#pragma unroll
+                for (int v = 0; v < NVEC; v++) {
+                    uint32_t *o = a.out_probe + idx0[v];
+                    if (KW == 8) {
+                        if (inb[2 * v + 1]) __stcs(reinterpret_cast<uint2 *>(o), make_uint2(idx0[v], idx0[v] + 1u));
+                        else if (inb[2 * v]) __stcs(o, idx0[v]);
+                    } else {
+                        if (inb[4 * v + 3]) __stcs(reinterpret_cast<uint4 *>(o), make_uint4(idx0[v], idx0[v] + 1u, idx0[v] + 2u, idx0[v] + 3u));
+                        else {
+#pragma unroll
+                            for (int q = 0; q < 4; q++)
+                                if (inb[4 * v + q]) __stcs(o + q, idx0[v] + (uint32_t)q);
+                        }
+                    }
+                }
+            }
             // ---- queue the pending ones (warp-private: ballots, no atomics)
             const uint32_t b0 = __ballot_sync(FULL, n_pend & 1u), b1 = __ballot_sync(FULL, n_pend & 2u), b2 = __ballot_sync(FULL, n_pend & 4u);
             const uint32_t wtot = __popc(b0) + 2u * __popc(b1) + 4u * __popc(b2);
@@ -534,13 +554,13 @@ __global__ void __launch_bounds__(PD_THREADS) probe_dense_kernel(ProbeArgs a) {
                 __syncwarp();
                 while (qn >= 32u) {
                     qn -= 32u;
-                    dense_drain<MARK>(a, qkey, qidx, qn, 32u, lane, misses);
+                    dense_drain<MARK, RADIX>(a, qkey, qidx, qn, 32u, lane, misses);
                     __syncwarp();
                 }
             }
         }
     }
-    if (qn) dense_drain<MARK>(a, qkey, qidx, 0u, qn, lane, misses);
+    if (qn) dense_drain<MARK, RADIX>(a, qkey, qidx, 0u, qn, lane, misses);
     const unsigned long long z = warp_sum_u32(misses);
     if (lane == 0 && z) atomicAdd(&a.ctr->build_null_out, z);
 }
