@@ -546,7 +546,8 @@ void run_build(H *h) {
 
     // ---- layout choice: direct while the table fits the L2 budget
     const uint64_t direct_slots = table_slots_for(n, lf);
-    const int64_t budget = h->cfg.l2_budget_bytes > 0 ? h->cfg.l2_budget_bytes : h->l2_bytes / 2;
+    // measured on B200 (profiles/r1_i_sizing_sweep.txt): the un-partitioned probe beats partition + probe up to a ~130 MB table
+    const int64_t budget = h->cfg.l2_budget_bytes > 0 ? h->cfg.l2_budget_bytes : h->l2_bytes / 10 * 9;
     int32_t layout = h->cfg.layout;
     if (layout == B200J_LAYOUT_AUTO) layout = ((int64_t)direct_slots * 16 <= budget) ? B200J_LAYOUT_DIRECT : B200J_LAYOUT_RADIX;
     h->layout = layout;

@@ -135,7 +135,7 @@ typedef struct {
     int32_t   radix_bits;             /* 0 = choose; else log2(number of radix partitions)            */
     float     load_factor;            /* 0 = default 0.5                                              */
     int64_t   expected_build_rows;    /* sizing hint, 0 = unknown                                     */
-    int64_t   l2_budget_bytes;        /* 0 = 1/2 of cudaDevAttrL2CacheSize                            */
+    int64_t   l2_budget_bytes;        /* 0 = 0.9 x cudaDevAttrL2CacheSize (measured crossover) */
     void     *stream;                 /* cudaStream_t to run on; NULL = the library creates its own   */
     uint32_t  flags;                  /* B200J_FLAG_*                                                 */
 } b200j_config;
