@@ -115,6 +115,9 @@ struct b200j_handle {
     int probe_ctas_per_sm = 4;
     int dense_ctas_per_sm = 4;
     bool dense_ok = true;              // B200J_NO_DENSE=1 forces the staged probe kernel (tuning / tests)
+    uint64_t l1_table_bytes = 512 << 10; // direct tables up to this size are probed through L1 (B200J_L1_TABLE_BYTES)
+    float miss_frac = 0.f;             // share of probe rows without a match in the last pair-producing probe launch
+    float dense_miss_max = 0.3f;       // direct layout: above this miss share the staged kernel is used (B200J_DENSE_MISS_MAX)
     int64_t l2_bytes = 0;
     bool timing = false;
 
@@ -163,6 +166,7 @@ struct b200j_handle {
         tv.parts = (const PartEnt *)parts.p;
         tv.nb = (uint32_t)(n_slots / 2);
         tv.radix_bits = radix_bits;
+        tv.l1 = (radix_bits == 0 && n_slots * 16 <= l1_table_bytes) ? 1u : 0u;
         return tv;
     }
 };
@@ -777,7 +781,9 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
         // Dense path (probe.cuh): unique build keys behind the partition pass. The partitioned row-id array becomes the
         // result's probe-index column as it is; the kernel writes one build index (or NULL) per partitioned row.
         // Direct layout: same kernel over the caller's keys when they can be read as 16 B vectors and carry no bitmap.
-        const bool dense_direct = !radix && pvalid == nullptr && ((uintptr_t)pkeys & 15) == 0;
+        // Inner / Left joins pay a compaction pass when the dense result has holes: with many misses (a filtered dimension
+        // table on the build side) the staged kernel, which never writes the holes, is the cheaper one on the direct layout.
+        const bool dense_direct = !radix && pvalid == nullptr && ((uintptr_t)pkeys & 15) == 0 && (pl.mode == PM_OUTER || h->miss_frac < h->dense_miss_max);
         if ((radix || dense_direct) && !count_only && h->dense_ok && h->st.duplicate_rows == 0 && pn > 0 && (pl.mode == PM_PAIRS || pl.mode == PM_OUTER)) {
             void *tr = nullptr;
             if (radix) {
@@ -826,6 +832,7 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
                 CU(cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
                 CU(cudaStreamSynchronize(h->stream));
                 const int64_t misses = (int64_t)h->h_ctr->build_null_out;
+                h->miss_frac = (float)((double)misses / (double)pn);
                 tr_.mark("dense probe + counters");
                 if (pl.mode == PM_OUTER) {
                     if (extra > 0) {      // NULL-key probe rows: their row ids already sit at the tail of the row-id array
@@ -939,6 +946,7 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
                     CU(cudaGetLastError());
                     CU(cudaStreamSynchronize(h->stream));
                 }
+                if (pl.mode == PM_PAIRS && h->st.duplicate_rows == 0 && pn > 0) h->miss_frac = (float)(1.0 - (double)total / (double)pn);
                 ro->build_idx = ob;
                 ro->probe_idx = op;
                 free_temps(h, temps);
@@ -1578,6 +1586,8 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
             else
                 cudaGetLastError();
             if (const char *e = getenv("B200J_NO_DENSE")) h->dense_ok = atoi(e) == 0;
+            if (const char *e = getenv("B200J_DENSE_MISS_MAX")) h->dense_miss_max = (float)atof(e);
+            if (const char *e = getenv("B200J_L1_TABLE_BYTES")) h->l1_table_bytes = (uint64_t)atoll(e);
         }
         h->l2_bytes = prop.l2CacheSize;
         if (cfg->stream) {
@@ -1680,6 +1690,7 @@ int32_t b200j_reset(b200j_handle *h) {
         std::fill(h->probe_done.begin(), h->probe_done.end(), 0);
         h->n_build_done = h->n_probe_done = 0;
         h->built = false;
+        h->miss_frac = 0.f;
         h->n_slots = 0;
     });
 }
