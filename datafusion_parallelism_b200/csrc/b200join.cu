@@ -116,6 +116,8 @@ struct b200j_handle {
     int dense_ctas_per_sm = 4;
     bool dense_ok = true;              // B200J_NO_DENSE=1 forces the staged probe kernel (tuning / tests)
     uint64_t l1_table_bytes = 512 << 10; // direct tables up to this size are probed through L1 (B200J_L1_TABLE_BYTES)
+    float thin_lf_min = 0.2f;          // lowest load factor the auto-thinning of small direct tables goes to (B200J_THIN_LF_MIN; 0.5 = off)
+    uint64_t thin_table_bytes = 48ull << 20;   // ... while the table stays within this many bytes (B200J_THIN_TABLE_BYTES)
     float miss_frac = 0.f;             // share of probe rows without a match in the last pair-producing probe launch
     float dense_miss_max = 0.3f;       // direct layout: above this miss share the staged kernel is used (B200J_DENSE_MISS_MAX)
     int64_t l2_bytes = 0;
@@ -549,11 +551,18 @@ void run_build(H *h) {
     const float lf = h->cfg.load_factor > 0.f ? std::min(h->cfg.load_factor, 0.9f) : 0.5f;
 
     // ---- layout choice: direct while the table fits the L2 budget
-    const uint64_t direct_slots = table_slots_for(n, lf);
+    uint64_t direct_slots = table_slots_for(n, lf);
     // measured on B200 (profiles/r1_i_sizing_sweep.txt): the un-partitioned probe beats partition + probe up to a ~130 MB table
     const int64_t budget = h->cfg.l2_budget_bytes > 0 ? h->cfg.l2_budget_bytes : h->l2_bytes / 10 * 9;
     int32_t layout = h->cfg.layout;
     if (layout == B200J_LAYOUT_AUTO) layout = ((int64_t)direct_slots * 16 <= budget) ? B200J_LAYOUT_DIRECT : B200J_LAYOUT_RADIX;
+    // A small direct table is spread thinner when the caller left the load factor open: at 0.5 about a third of the 2-slot
+    // buckets are full, and a probe key that is NOT in the table then has to walk (measured: 95 % misses cost 13.3 ms per 1 B
+    // probe rows against 9.1 ms for 100 % hits). Down to 0.2 while the table stays within ~48 MB, well inside the L2.
+    if (layout == B200J_LAYOUT_DIRECT && h->cfg.load_factor <= 0.f && n > 0) {
+        const float thin = std::max(h->thin_lf_min, std::min(0.5f, (float)((double)n * 16.0 / (double)h->thin_table_bytes)));
+        if (thin < lf) direct_slots = table_slots_for(n, thin);
+    }
     h->layout = layout;
 
     dev_alloc(h, h->zero_slot, 2 * sizeof(Slot));       // a whole bucket: the probe loads 32 B
@@ -1588,6 +1597,8 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
             if (const char *e = getenv("B200J_NO_DENSE")) h->dense_ok = atoi(e) == 0;
             if (const char *e = getenv("B200J_DENSE_MISS_MAX")) h->dense_miss_max = (float)atof(e);
             if (const char *e = getenv("B200J_L1_TABLE_BYTES")) h->l1_table_bytes = (uint64_t)atoll(e);
+            if (const char *e = getenv("B200J_THIN_LF_MIN")) h->thin_lf_min = std::min(0.5f, std::max(0.05f, (float)atof(e)));
+            if (const char *e = getenv("B200J_THIN_TABLE_BYTES")) h->thin_table_bytes = std::max<uint64_t>(1, (uint64_t)atoll(e));
         }
         h->l2_bytes = prop.l2CacheSize;
         if (cfg->stream) {

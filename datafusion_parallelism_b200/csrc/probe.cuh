@@ -566,26 +566,42 @@ __global__ void __launch_bounds__(PD_THREADS) probe_dense_kernel(ProbeArgs a) {
 }
 
 // Compaction of a dense result: keeps the rows whose build index is not NULL. One global atomic per tile.
+// Rows are read as coalesced 16 B / 8 B vectors (lane-contiguous), the survivors are ranked with one block scan, staged in
+// shared memory in rank order and written out as contiguous runs, so both directions move whole sectors. The order of the
+// surviving pairs inside a tile is the vector order, not the row order (the result is a multiset).
 constexpr int CP_THREADS = 256;
 constexpr int CP_ITEMS   = 8;
 constexpr int CP_TILE    = CP_THREADS * CP_ITEMS;
+constexpr int CP_VECS    = CP_ITEMS / 2;
 __global__ void __launch_bounds__(CP_THREADS) compact_pairs_kernel(const uint64_t *__restrict__ in_build, const uint32_t *__restrict__ in_probe,
                                                                    uint64_t n, uint64_t *__restrict__ out_build, uint32_t *__restrict__ out_probe,
                                                                    unsigned long long *counter) {
+    __shared__ unsigned long long s_b[CP_TILE];
+    __shared__ uint32_t s_p[CP_TILE];
     __shared__ uint32_t s_w[CP_THREADS / 32];
     __shared__ unsigned long long s_base;
+    __shared__ uint32_t s_tot;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const uint64_t n_tiles = (n + CP_TILE - 1) / CP_TILE;
     for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const uint64_t i0 = tile * CP_TILE + (uint64_t)t * CP_ITEMS;      // CP_ITEMS consecutive rows per thread
-        uint64_t b[CP_ITEMS];
+        unsigned long long b[CP_ITEMS];
         uint32_t p[CP_ITEMS], c = 0;
 #pragma unroll
-        for (int q = 0; q < CP_ITEMS; q++) {
-            const bool in = i0 + q < n;
-            b[q] = in ? __ldcs(reinterpret_cast<const unsigned long long *>(in_build) + i0 + q) : ~0ULL;
-            p[q] = in ? __ldcs(in_probe + i0 + q) : 0u;
-            c += b[q] != ~0ULL ? 1u : 0u;
+        for (int v = 0; v < CP_VECS; v++) {
+            const uint64_t r0 = tile * CP_TILE + ((uint64_t)v * CP_THREADS + (uint64_t)t) * 2;
+            if (r0 + 1 < n) {
+                const ulonglong2 x = __ldcs(reinterpret_cast<const ulonglong2 *>(in_build + r0));
+                const uint2 y = __ldcs(reinterpret_cast<const uint2 *>(in_probe + r0));
+                b[2 * v] = x.x; b[2 * v + 1] = x.y;
+                p[2 * v] = y.x; p[2 * v + 1] = y.y;
+            } else {
+                const bool in = r0 < n;
+                b[2 * v] = in ? __ldcs(reinterpret_cast<const unsigned long long *>(in_build) + r0) : ~0ULL;
+                p[2 * v] = in ? __ldcs(in_probe + r0) : 0u;
+                b[2 * v + 1] = ~0ULL;
+                p[2 * v + 1] = 0u;
+            }
+            c += (b[2 * v] != ~0ULL ? 1u : 0u) + (b[2 * v + 1] != ~0ULL ? 1u : 0u);
         }
         uint32_t incl = c;
 #pragma unroll
@@ -593,19 +609,26 @@ __global__ void __launch_bounds__(CP_THREADS) compact_pairs_kernel(const uint64_
         if (lane == 31) s_w[warp] = incl;
         __syncthreads();
         if (t == 0) {
-            unsigned long long tot = 0;
+            uint32_t tot = 0;
             for (int i = 0; i < CP_THREADS / 32; i++) tot += s_w[i];
-            s_base = tot ? atomicAdd(counter, tot) : 0ULL;
+            s_tot = tot;
+            s_base = tot ? atomicAdd(counter, (unsigned long long)tot) : 0ULL;
         }
-        __syncthreads();
-        unsigned long long pos = s_base + incl - c;
+        uint32_t pos = incl - c;
         for (int i = 0; i < warp; i++) pos += s_w[i];
 #pragma unroll
         for (int q = 0; q < CP_ITEMS; q++) {
             if (b[q] == ~0ULL) continue;
-            out_build[pos] = b[q];
-            out_probe[pos] = p[q];
+            s_b[pos] = b[q];
+            s_p[pos] = p[q];
             pos++;
+        }
+        __syncthreads();
+        const uint32_t tot = s_tot;
+        const unsigned long long base = s_base;
+        for (uint32_t i = (uint32_t)t; i < tot; i += CP_THREADS) {
+            __stcs(reinterpret_cast<unsigned long long *>(out_build) + base + i, s_b[i]);
+            __stcs(out_probe + base + i, s_p[i]);
         }
         __syncthreads();
     }

@@ -12,12 +12,13 @@ ap.add_argument("--layout", default="direct")
 ap.add_argument("--radix-bits", type=int, default=0)
 ap.add_argument("--lf", type=float, default=0.5)
 ap.add_argument("--reps", type=int, default=3)
+ap.add_argument("--miss-mult", type=int, default=1, help="probe keys uniform over build x this many ids: hit rate = 1 / miss_mult")
 a = ap.parse_args()
 
 torch.cuda.set_device(0)
 g = torch.Generator(device="cuda"); g.manual_seed(3)
 bk = torch.randperm(a.build, device="cuda", generator=g, dtype=torch.int64)
-pk = torch.randint(0, a.build, (a.probe,), device="cuda", generator=g, dtype=torch.int64)
+pk = torch.randint(0, a.build * a.miss_mult, (a.probe,), device="cuda", generator=g, dtype=torch.int64)
 torch.cuda.synchronize()
 for rep in range(a.reps):
     with d.HashJoin("inner", layout=a.layout, radix_bits=a.radix_bits, load_factor=a.lf, timing=True, expected_build_rows=a.build) as j:
