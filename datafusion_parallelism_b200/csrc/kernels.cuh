@@ -744,7 +744,7 @@ __device__ __forceinline__ void probe_tile(const ProbeArgs &a, uint32_t tile, in
             idx[q] = home_bucket(h, nb);
             const Slot *p = key[q] ? bucket_ptr(a.tv, base, idx[q]) : a.tv.zero_slot;
             k0[q] = v0[q] = k1[q] = v1[q] = 0ULL;
-            if (!GUARD || ((pending >> q) & 1u)) load_bucket(p, k0[q], v0[q], k1[q], v1[q], a.tv.l1 != 0u);
+            if (!GUARD || ((pending >> q) & 1u)) load_bucket(p, k0[q], v0[q], k1[q], v1[q], (!RADIX && a.tv.l1 != 0u));
         }
 #pragma unroll
         for (int q = 0; q < PROBE_ITEMS; q++) {
@@ -769,7 +769,7 @@ __device__ __forceinline__ void probe_tile(const ProbeArgs &a, uint32_t tile, in
         for (;;) {
             i = next_bucket(i, nb);
             unsigned long long k0, v0, k1, v1;
-            load_bucket(bucket_ptr(a.tv, base, i), k0, v0, k1, v1, a.tv.l1 != 0u);
+            load_bucket(bucket_ptr(a.tv, base, i), k0, v0, k1, v1, (!RADIX && a.tv.l1 != 0u));
             const bool hit0 = k0 == k, hit1 = k1 == k;
             if (hit0 | hit1 | (k0 == 0ULL) | (k1 == 0ULL)) {
                 const unsigned long long v = hit0 ? v0 : ((hit1 && k0 != 0ULL) ? v1 : 0ULL);

@@ -155,7 +155,7 @@ __global__ void __launch_bounds__(PF_THREADS) probe_fast_kernel(ProbeArgs a) {
                 uint32_t base, nb;
                 locate<RADIX>(a.tv, (uint32_t)(h >> 32), base, nb);
                 const Slot *p = key[q] ? bucket_ptr(a.tv, base, home_bucket(h, nb)) : a.tv.zero_slot;
-                load_bucket(p, k0[q], v0[q], k1[q], v1[q], a.tv.l1 != 0u);
+                load_bucket(p, k0[q], v0[q], k1[q], v1[q], (!RADIX && a.tv.l1 != 0u));
             }
             // ---- resolve from that bucket: hit, provable miss (bucket has a free slot; slots fill in order, so a free
             //      slot shows in the odd one), or "needs the slow path" (bucket full without the key, or a run)
@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(PF_THREADS) probe_fast_kernel(ProbeArgs a) {
                 const Slot *p = key ? bucket_ptr(a.tv, base, idx) : a.tv.zero_slot;
                 for (;;) {
                     unsigned long long k0, v0, k1, v1;
-                    load_bucket(p, k0, v0, k1, v1, a.tv.l1 != 0u);
+                    load_bucket(p, k0, v0, k1, v1, (!RADIX && a.tv.l1 != 0u));
                     const bool hit0 = k0 == key, hit1 = k1 == key;
                     if (hit0 | hit1 | (k1 == 0ULL)) {
                         const unsigned long long v = hit0 ? v0 : (hit1 ? v1 : 0ULL);
@@ -398,8 +398,8 @@ __device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long lo
         for (;;) {
             const uint32_t b2 = next_bucket(b, nb);
             unsigned long long k0, v0, k1, v1, k2, v2, k3, v3;
-            load_bucket(bucket_ptr(a.tv, base, b), k0, v0, k1, v1, a.tv.l1 != 0u);
-            load_bucket(bucket_ptr(a.tv, base, b2), k2, v2, k3, v3, a.tv.l1 != 0u);
+            load_bucket(bucket_ptr(a.tv, base, b), k0, v0, k1, v1, (!RADIX && a.tv.l1 != 0u));
+            load_bucket(bucket_ptr(a.tv, base, b2), k2, v2, k3, v3, (!RADIX && a.tv.l1 != 0u));
             if (k0 == key) { res = (uint32_t)v0; break; }
             if (k1 == key) { res = (uint32_t)v1; break; }
             if (k1 == 0ULL) break;
@@ -476,7 +476,7 @@ __global__ void __launch_bounds__(PD_THREADS) probe_dense_kernel(ProbeArgs a) {
                 uint32_t base, nb;
                 locate<RADIX>(a.tv, (uint32_t)(h >> 32), base, nb);
                 const Slot *p = key[q] ? bucket_ptr(a.tv, base, home_bucket(h, nb)) : a.tv.zero_slot;
-                load_bucket(p, k0[q], v0[q], k1[q], v1[q], a.tv.l1 != 0u);
+                load_bucket(p, k0[q], v0[q], k1[q], v1[q], (!RADIX && a.tv.l1 != 0u));
             }
             // ---- resolve; unresolved lookups go to the warp's queue
             unsigned long long res[PD_ITEMS];
