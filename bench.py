@@ -57,7 +57,7 @@ def parse_args():
     ap.add_argument("--layout", default="auto")
     ap.add_argument("--radix-bits", type=int, default=0)
     ap.add_argument("--load-factor", type=float, default=0.0)
-    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-probe-sample", type=int, default=250_000_000)
@@ -402,11 +402,15 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
             r.release()
         return tot
 
-    step_host()                       # warm-up: pinned result buffers, pool growth
+    for _ in range(2):                # warm-up: pinned result buffers, pool growth, first-touch of the pinned pages
+        step_host()
     barrier()
     t0 = time.perf_counter()
+    ms_steps = []
     for _ in range(steps):
+        ts = time.perf_counter()
         tot = step_host()
+        ms_steps.append(round((time.perf_counter() - ts) * 1e3, 1))
     barrier()
     dt = time.perf_counter() - t0
     if dist is not None:
@@ -416,7 +420,7 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
     hb.free()
     hp.free()
     return {"value": (n_build + n_probe) * world / (dt / steps), "unit": UNIT, "h2d_bytes_per_step": 8 * (n_build + n_probe),
-            "d2h_bytes_per_step": 12 * tot, "steps": steps, "ms_per_step": dt / steps * 1e3,
+            "d2h_bytes_per_step": 12 * tot, "steps": steps, "ms_per_step": dt / steps * 1e3, "ms_steps_rank0": ms_steps,
             "api": ("HashJoin.build_push/probe_batch(host numpy over b200j_host_alloc pinned buffers, OUT_PAIRS|OUT_HOST) -> b200j_* C ABI" if world == 1 else
                     f"DistributedJoin.build_push_host/probe_host_chunks(pinned numpy in, pinned pairs out, {host_chunk}-row chunks) -> b200j_* C ABI")}
 
