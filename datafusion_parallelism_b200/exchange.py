@@ -267,7 +267,10 @@ class DistributedJoin:
         self.join.build_finish(partition)
 
     # ---- heavy hitters (SURVEY §8e "skew") ------------------------------------------------------------------------
-    HOT_JOIN_TYPES = ("inner", "right", "right_semi", "right_anti")   # left-side marks would have to travel back to the owners
+    # Left-family joins: the visited marks of the broadcast (hot) build rows live on every rank; probe_finish OR-reduces them
+    # and the owner alone emits / withholds those rows ("OR-reduce those few bits").
+    HOT_JOIN_TYPES = ("inner", "right", "right_semi", "right_anti", "left", "full", "left_semi", "left_anti")
+    LEFT_FAMILY = ("left", "full", "left_semi", "left_anti")
 
     def enable_hot_routing(self, sample_keys, hot_fraction: Optional[float] = None, sample_rows: int = 1 << 20, max_hot: int = 256):
         """Collective, after build_finish. Finds the heavy-hitter probe keys from a sample of this rank's probe keys, agrees
@@ -490,7 +493,40 @@ class DistributedJoin:
         yield finish(pending)
 
     def probe_finish(self, partition: int, want: int = OUT_PAIRS):
-        return self.join.probe_finish(partition, want=want)
+        """The finaliser batch of this rank's build rows (Left / Full / LeftSemi / LeftAnti; empty otherwise).
+        With heavy-hitter routing the build rows of hot keys were probed on EVERY rank (against the broadcast copy), never in
+        their owner's table: collective then. Every rank turns its hot join's finaliser into one "matched here" flag per
+        broadcast row, the flags are OR-reduced over the ranks, and each owner drops its hot rows from its own finaliser
+        batch and puts back the ones the join type wants (unmatched everywhere: Left / Full / LeftAnti; matched anywhere:
+        LeftSemi). Returns host arrays in that case (`HostPairs`)."""
+        if self.hot_join is None or self.join_type not in self.LEFT_FAMILY:
+            return self.join.probe_finish(partition, want=want)
+        torch, dist = self.torch, self.dist
+        from .join import OUT_HOST
+        main = self.join.probe_finish(partition, want=OUT_PAIRS | OUT_HOST)
+        mb, _ = main.numpy()
+        main.release()
+        hot = self.hot_join.probe_finish(0, want=OUT_PAIRS | OUT_HOST)
+        hb, _ = hot.numpy()
+        hot.release()
+        n_hot_rows = int(self.hot_bidx.shape[0])
+        if self.join_type == "left_semi":
+            flag = np.zeros(n_hot_rows, dtype=np.int32)             # finaliser = matched rows
+            flag[hb.astype(np.int64)] = 1
+        else:
+            flag = np.ones(n_hot_rows, dtype=np.int32)              # finaliser = unmatched rows
+            flag[hb.astype(np.int64)] = 0
+        t = torch.from_numpy(flag).to("cuda")
+        if n_hot_rows:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        matched = t.cpu().numpy().astype(bool)
+        mine = self.hot_owner == self.rank
+        my_bidx = self.hot_bidx[mine].astype(np.uint64)
+        keep = ~np.isin(mb, my_bidx)
+        back = my_bidx[matched[mine]] if self.join_type == "left_semi" else my_bidx[~matched[mine]]
+        b = np.concatenate([mb[keep], back]).astype(np.uint64)
+        from .join import NULL_PROBE
+        return HostPairs(b, np.full(b.shape[0], NULL_PROBE, dtype=np.uint32))
 
     def _origin(self, side: _Side, idx: np.ndarray):
         """(source rank, source row) of received rows `idx` of one side (host arrays; for tests and late materialisation)."""
@@ -537,6 +573,22 @@ class DistributedJoin:
             self.hot_join.close()
         self.xjoin.close()
         self.join.close()
+
+
+class HostPairs:
+    """A finished result held in host arrays (same reading interface as PairResult)."""
+
+    def __init__(self, build_idx: np.ndarray, probe_idx: np.ndarray):
+        self.build_idx, self.probe_idx = build_idx, probe_idx
+        self.n = int(build_idx.shape[0])
+        self.hot = None
+        self.n_hot = 0
+
+    def numpy(self):
+        return self.build_idx, self.probe_idx
+
+    def release(self):
+        pass
 
 
 class _RawCudaArray:
