@@ -304,7 +304,7 @@ def run_b200(args):
     rows_per_launch = n_probe * K / max(1, st["probe_launches"]) if world == 1 else st["probe_rows"] / max(1, st["probe_launches"])
     dense = st.get("dense_probe_launches", 0) == st["probe_launches"] and st["probe_launches"] > 0
     if dense:        # 8 B key in + 8 B build index out per row, plus ONE pass over the table per launch (it is L2-resident per partition)
-        bpt, kname, table_b = B_PROBE_DENSE, "probe_dense_kernel<8,false,true>", st["table_bytes"]
+        bpt, kname, table_b = B_PROBE_DENSE, "probe_dense_kernel<8,false,true,false>", st["table_bytes"]
     elif radix:
         bpt, kname, table_b = B_PROBE_KERNEL_RADIX, "probe_fast_kernel<8,PM_PAIRS,false,true>", st["table_bytes"]
     else:

@@ -118,6 +118,7 @@ struct b200j_handle {
     uint64_t l1_table_bytes = 512 << 10; // direct tables up to this size are probed through L1 (B200J_L1_TABLE_BYTES)
     float thin_lf_min = 0.2f;          // lowest load factor the auto-thinning of small direct tables goes to (B200J_THIN_LF_MIN; 0.5 = off)
     uint64_t thin_table_bytes = 48ull << 20;   // ... while the table stays within this many bytes (B200J_THIN_TABLE_BYTES)
+    bool skew_l1 = true;               // radix dense probe: L1-allocating bucket loads for skewed batches (B200J_SKEW_L1=0 turns it off)
     float miss_frac = 0.f;             // share of probe rows without a match in the last pair-producing probe launch
     float dense_miss_max = 0.3f;       // direct layout: above this miss share the staged kernel is used (B200J_DENSE_MISS_MAX)
     int64_t l2_bytes = 0;
@@ -821,9 +822,22 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
                 {
                     PhaseTimer tm(h, &h->st.ms_probe);
                     const int grid = grid_for(h, pn, PD_SUPER, h->dense_ctas_per_sm);
+                    // L1-allocating bucket loads: a small direct table, or a skewed batch behind the radix pass (a partition far
+                    // above the mean size = heavy-hitter keys, whose buckets every SM would otherwise fetch from the same L2 sectors)
+                    bool l1 = a.tv.l1 != 0u;
+                    if (radix) {
+                        const int P = 1 << h->radix_bits;
+                        int64_t biggest = 0;
+                        for (int p = 0; p < P; p++) biggest = std::max<int64_t>(biggest, (int64_t)h->rscratch.h_off[p + 1] - (int64_t)h->rscratch.h_off[p]);
+                        l1 = h->skew_l1 && P >= 8 && biggest * P > 3 * pn;
+                    }
                     auto launch = [&](auto KW, auto MARK) {
-                        if (radix) probe_dense_kernel<decltype(KW)::value, decltype(MARK)::value, true><<<grid, PD_THREADS, 0, h->stream>>>(a);
-                        else probe_dense_kernel<decltype(KW)::value, decltype(MARK)::value, false><<<grid, PD_THREADS, 0, h->stream>>>(a);
+                        constexpr int kw_ = decltype(KW)::value;
+                        constexpr bool mk_ = decltype(MARK)::value;
+                        if (radix && l1) probe_dense_kernel<kw_, mk_, true, true><<<grid, PD_THREADS, 0, h->stream>>>(a);
+                        else if (radix) probe_dense_kernel<kw_, mk_, true, false><<<grid, PD_THREADS, 0, h->stream>>>(a);
+                        else if (l1) probe_dense_kernel<kw_, mk_, false, true><<<grid, PD_THREADS, 0, h->stream>>>(a);
+                        else probe_dense_kernel<kw_, mk_, false, false><<<grid, PD_THREADS, 0, h->stream>>>(a);
                     };
                     if (kw == 8) {
                         if (pl.mark) launch(std::integral_constant<int, 8>{}, std::true_type{});
@@ -1590,13 +1604,14 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
                 h->probe_ctas_per_sm = occ;
             else
                 cudaGetLastError();
-            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, probe_dense_kernel<8, false, true>, PD_THREADS, 0) == cudaSuccess && occ > 0)
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, probe_dense_kernel<8, false, true, false>, PD_THREADS, 0) == cudaSuccess && occ > 0)
                 h->dense_ctas_per_sm = occ;
             else
                 cudaGetLastError();
             if (const char *e = getenv("B200J_NO_DENSE")) h->dense_ok = atoi(e) == 0;
             if (const char *e = getenv("B200J_DENSE_MISS_MAX")) h->dense_miss_max = (float)atof(e);
             if (const char *e = getenv("B200J_L1_TABLE_BYTES")) h->l1_table_bytes = (uint64_t)atoll(e);
+            if (const char *e = getenv("B200J_SKEW_L1")) h->skew_l1 = atoi(e) != 0;
             if (const char *e = getenv("B200J_THIN_LF_MIN")) h->thin_lf_min = std::min(0.5f, std::max(0.05f, (float)atof(e)));
             if (const char *e = getenv("B200J_THIN_TABLE_BYTES")) h->thin_table_bytes = std::max<uint64_t>(1, (uint64_t)atoll(e));
         }

@@ -382,7 +382,7 @@ struct PDShared {
     uint32_t           next;
 };
 
-template <bool MARK, bool RADIX>
+template <bool MARK, bool RADIX, bool L1>
 __device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long long *qkey, uint32_t *qidx, uint32_t first, uint32_t cnt,
                                             int lane, uint32_t &misses) {
     // entries [first, first + cnt) of the warp's queue, one per lane (cnt <= 32)
@@ -398,8 +398,8 @@ __device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long lo
         for (;;) {
             const uint32_t b2 = next_bucket(b, nb);
             unsigned long long k0, v0, k1, v1, k2, v2, k3, v3;
-            load_bucket(bucket_ptr(a.tv, base, b), k0, v0, k1, v1, (!RADIX && a.tv.l1 != 0u));
-            load_bucket(bucket_ptr(a.tv, base, b2), k2, v2, k3, v3, (!RADIX && a.tv.l1 != 0u));
+            load_bucket(bucket_ptr(a.tv, base, b), k0, v0, k1, v1, L1);
+            load_bucket(bucket_ptr(a.tv, base, b2), k2, v2, k3, v3, L1);
             if (k0 == key) { res = (uint32_t)v0; break; }
             if (k1 == key) { res = (uint32_t)v1; break; }
             if (k1 == 0ULL) break;
@@ -414,7 +414,9 @@ __device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long lo
     }
 }
 
-template <int KW, bool MARK, bool RADIX>
+// L1: bucket loads allocate in L1 -- a small direct table, or a probe batch with heavy-hitter keys (every SM otherwise asks
+// the L2 for the same few sectors); off for uniform keys over a big table, where an L1 line is never reused.
+template <int KW, bool MARK, bool RADIX, bool L1>
 __global__ void __launch_bounds__(PD_THREADS) probe_dense_kernel(ProbeArgs a) {
     constexpr int PER_VEC = 16 / KW;
     constexpr int NVEC = PD_ITEMS / PER_VEC;
@@ -476,7 +478,7 @@ __global__ void __launch_bounds__(PD_THREADS) probe_dense_kernel(ProbeArgs a) {
                 uint32_t base, nb;
                 locate<RADIX>(a.tv, (uint32_t)(h >> 32), base, nb);
                 const Slot *p = key[q] ? bucket_ptr(a.tv, base, home_bucket(h, nb)) : a.tv.zero_slot;
-                load_bucket(p, k0[q], v0[q], k1[q], v1[q], (!RADIX && a.tv.l1 != 0u));
+                load_bucket(p, k0[q], v0[q], k1[q], v1[q], L1);
             }
             // ---- resolve; unresolved lookups go to the warp's queue
             unsigned long long res[PD_ITEMS];
@@ -554,13 +556,13 @@ __global__ void __launch_bounds__(PD_THREADS) probe_dense_kernel(ProbeArgs a) {
                 __syncwarp();
                 while (qn >= 32u) {
                     qn -= 32u;
-                    dense_drain<MARK, RADIX>(a, qkey, qidx, qn, 32u, lane, misses);
+                    dense_drain<MARK, RADIX, L1>(a, qkey, qidx, qn, 32u, lane, misses);
                     __syncwarp();
                 }
             }
         }
     }
-    if (qn) dense_drain<MARK, RADIX>(a, qkey, qidx, 0u, qn, lane, misses);
+    if (qn) dense_drain<MARK, RADIX, L1>(a, qkey, qidx, 0u, qn, lane, misses);
     const unsigned long long z = warp_sum_u32(misses);
     if (lane == 0 && z) atomicAdd(&a.ctr->build_null_out, z);
 }
