@@ -303,10 +303,13 @@ def run_b200(args):
     probe_launch_ms = st["ms_probe"] / max(1, st["probe_launches"])
     rows_per_launch = n_probe * K / max(1, st["probe_launches"]) if world == 1 else st["probe_rows"] / max(1, st["probe_launches"])
     dense = st.get("dense_probe_launches", 0) == st["probe_launches"] and st["probe_launches"] > 0
+    # the table term of the ALGORITHMIC bytes is counted at load factor 0.5 (32 B per distinct build key) whatever the table's
+    # actual size: spreading the table thinner must not raise the roofline fraction
+    table_alg = min(st["table_bytes"], 32 * max(1, st["distinct_keys"]) + 4096)
     if dense:        # 8 B key in + 8 B build index out per row, plus ONE pass over the table per launch (it is L2-resident per partition)
-        bpt, kname, table_b = B_PROBE_DENSE, "probe_dense_kernel<8,false,true,false>", st["table_bytes"]
+        bpt, kname, table_b = B_PROBE_DENSE, "probe_dense_kernel<8,false,true,false>", table_alg
     elif radix:
-        bpt, kname, table_b = B_PROBE_KERNEL_RADIX, "probe_fast_kernel<8,PM_PAIRS,false,true>", st["table_bytes"]
+        bpt, kname, table_b = B_PROBE_KERNEL_RADIX, "probe_fast_kernel<8,PM_PAIRS,false,true>", table_alg
     else:
         bpt, kname, table_b = B_PROBE, "probe_fast_kernel<8,PM_PAIRS,false,false>", 0
     bytes_per_launch = rows_per_launch * bpt + table_b

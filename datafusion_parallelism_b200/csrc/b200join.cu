@@ -119,6 +119,7 @@ struct b200j_handle {
     float thin_lf_min = 0.2f;          // lowest load factor the auto-thinning of small direct tables goes to (B200J_THIN_LF_MIN; 0.5 = off)
     uint64_t thin_table_bytes = 48ull << 20;   // ... while the table stays within this many bytes (B200J_THIN_TABLE_BYTES)
     bool skew_l1 = true;               // radix dense probe: L1-allocating bucket loads for skewed batches (B200J_SKEW_L1=0 turns it off)
+    float radix_lf = 0.42f;            // load factor of the radix layout's tables when the caller leaves it open (B200J_RADIX_LF)
     float miss_frac = 0.f;             // share of probe rows without a match in the last pair-producing probe launch
     float dense_miss_max = 0.3f;       // direct layout: above this miss share the staged kernel is used (B200J_DENSE_MISS_MAX)
     int64_t l2_bytes = 0;
@@ -635,7 +636,11 @@ void run_build(H *h) {
         }
         tm.stop();
     } else {
-        radix_build(h, keys, validity, kw, n, lf, budget);
+        // load factor left open: 0.42 behind the radix pass (profiles/r1_j_radix_load_factor.txt). At 100 M unique keys, 2^7
+        // partitions: insert 3.66 -> 3.48 ms and probe kernel 6.97 -> 6.74 ms per 1 B rows against 0.5; 0.35 is better still for
+        // probe keys that miss (11.7 -> 10.4 ms at 95 % misses) but makes duplicate-heavy builds slower (C3 exp: insert 9.3 ->
+        // 11.5 ms), 0.42 is neutral there; at 0.25 the partition outgrows its share of the L2.
+        radix_build(h, keys, validity, kw, n, h->cfg.load_factor > 0.f ? lf : h->radix_lf, budget);
     }
     CU(cudaStreamSynchronize(h->stream));
     h->st.layout = h->layout;
@@ -1612,6 +1617,7 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
             if (const char *e = getenv("B200J_DENSE_MISS_MAX")) h->dense_miss_max = (float)atof(e);
             if (const char *e = getenv("B200J_L1_TABLE_BYTES")) h->l1_table_bytes = (uint64_t)atoll(e);
             if (const char *e = getenv("B200J_SKEW_L1")) h->skew_l1 = atoi(e) != 0;
+            if (const char *e = getenv("B200J_RADIX_LF")) h->radix_lf = std::min(0.9f, std::max(0.05f, (float)atof(e)));
             if (const char *e = getenv("B200J_THIN_LF_MIN")) h->thin_lf_min = std::min(0.5f, std::max(0.05f, (float)atof(e)));
             if (const char *e = getenv("B200J_THIN_TABLE_BYTES")) h->thin_table_bytes = std::max<uint64_t>(1, (uint64_t)atoll(e));
         }

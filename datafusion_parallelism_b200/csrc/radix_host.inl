@@ -125,7 +125,7 @@ int choose_radix_bits(H *h, int64_t n, float lf, int64_t budget) {
     // aim at per-partition tables of a quarter of the L2 (half of an explicit l2_budget_bytes): measured on B200, the probe
     // kernel runs at the same speed from 2^7 to 2^10 partitions at 100 M build rows (and 20 % slower at 2^6), while the
     // partition pass gets slower with every bit
-    double table_bytes = 16.0 * (double)n / lf;
+    double table_bytes = 16.0 * (double)n / std::max(lf, 0.5f);     // the partition count follows the key count; a lower load factor only spreads a partition
     const double target = std::max<double>(h->cfg.l2_budget_bytes > 0 ? (double)budget / 2.0 : (double)h->l2_bytes / 4.0, 1 << 20);
     int bits = 1;
     while (bits < RP_MAX_BITS && table_bytes / (double)(1 << bits) > target) bits++;
