@@ -217,6 +217,42 @@ def test_utf8_with_int_key_device_batches(pkg):
         r.release()
 
 
+@pytest.mark.parametrize("join_type", ["inner", "left", "right", "full"])
+@pytest.mark.parametrize("dtype", [np.int64, np.int32])
+@pytest.mark.parametrize("n_build", [40, 60_000])
+def test_dense_direct_paths(pkg, join_type, dtype, n_build):
+    """Unique build keys on the direct layout from DEVICE buffers: the un-compacted dense kernel (all hits), dense + compaction
+    (first batch with misses), the staged kernel once the previous batch had > 30 % misses, a misaligned key slice (staged
+    kernel again: the dense one reads 16 B vectors), and back to dense. n_build = 40 also takes the L1-allocating loads of
+    tiny tables. Every batch is compared with the oracle."""
+    import torch
+    rng = np.random.default_rng(hash((join_type, str(dtype), n_build, "dd")) & 0xFFFFFFFF)
+    bk = (rng.permutation(n_build * 3)[:n_build]).astype(dtype)              # unique, key 0 may be present
+    hits = lambda n: bk[rng.integers(0, n_build, n)]
+    mostly_misses = lambda n: np.where(rng.random(n) < 0.1, bk[rng.integers(0, n_build, n)], rng.integers(n_build * 3, n_build * 6, n)).astype(dtype)
+    batches = [hits(30_001), mostly_misses(30_000), mostly_misses(25_003), hits(20_002), hits(20_000), hits(7)]
+    oj = oracle.OracleJoin(join_type, [bk])
+    with pkg.HashJoin(join_type, key_widths=(bk.dtype.itemsize,), layout="direct") as j:
+        j.build_push(0, [torch.from_numpy(bk).cuda()])
+        j.build_finish(0)
+        launches = []
+        for i, pb in enumerate(batches):
+            t = torch.from_numpy(np.concatenate([pb[:1], pb])).cuda()
+            dev = t[1:] if i == 3 else t[1:].clone()                          # batch 3: pointer 4 / 8 B past a 16 B boundary
+            r = j.probe_batch(0, [dev], want=pkg.OUT_PAIRS | pkg.OUT_HOST)
+            assert_pairs_equal(r.numpy(), oj.probe_batch([pb], len(pb)), f"{join_type} batch {i}")
+            r.release()
+            launches.append(j.stats()["dense_probe_launches"])
+        r = j.probe_finish(0)
+        assert_pairs_equal(r.numpy(), oj.finish(), f"{join_type} finaliser")
+        r.release()
+    dense = [b - a for a, b in zip([0] + launches[:-1], launches)]
+    if join_type in ("inner", "left"):
+        assert dense == [1, 1, 0, 0, 1, 1], dense         # batch 2: staged after 90 % misses; batch 3: misaligned keys
+    else:
+        assert dense == [1, 1, 1, 0, 1, 1], dense         # Right / Full keep the NULL rows: dense at any miss rate
+
+
 @pytest.mark.parametrize("layout,radix_bits", LAYOUT_CASES)
 def test_unique_keys_one_to_one(pkg, layout, radix_bits):
     """The BASELINE C1/C2 shape in miniature: unique build keys (a permutation), uniform probe, every probe row matches once."""
