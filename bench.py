@@ -137,10 +137,15 @@ def cpu_join_sample(n_build: int, n_probe_full: int, probe_sample: int, reps: in
     oracle.build()
     bk = oracle.gen_permutation_i64(n_build, 3)
     pk = oracle.gen_uniform_i64(min(probe_sample, n_probe_full), n_build, 4)
-    cores = oracle.MtJoin.max_threads()
+    # all host threads this process may run on -- NOT omp_get_max_threads(): torchrun exports OMP_NUM_THREADS=1 to its workers,
+    # which would quietly turn the N > 1 reference arm into a single-threaded run
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        cores = os.cpu_count() or oracle.MtJoin.max_threads()
     out = []
     for it in range(warmup + reps):
-        j = oracle.MtJoin(bk)
+        j = oracle.MtJoin(bk, threads=cores)
         tb = j.build_seconds
         tp, matched, _ = j.probe(pk)
         assert matched == pk.shape[0], (matched, pk.shape[0])
