@@ -140,6 +140,13 @@ struct __align__(16) Slot {
     uint32_t           count;
 };
 
+// Top bit of the EVEN slot's count: "a key whose home bucket this is was placed further on" (set by the insert that leaves its
+// full home bucket). A lookup that does not find its key in a full home bucket whose bit is clear has proven a miss: every key
+// homed there is still there. Only home buckets are asked; count readers mask the bit.
+constexpr uint32_t SLOT_OVF   = 0x80000000u;
+constexpr uint32_t COUNT_MASK = 0x7fffffffu;
+__device__ __forceinline__ bool bucket_overflowed(unsigned long long v0) { return (v0 >> 63) != 0ULL; }
+
 struct Counters {
     // reset before every probe launch (24 contiguous bytes)
     unsigned long long out_count;     // rows produced (may exceed capacity: then nothing past capacity is written)
@@ -198,7 +205,7 @@ __device__ __forceinline__ Slot load_slot(const Slot *p) {
     Slot s;
     s.key = v.x;
     s.row = (uint32_t)v.y;
-    s.count = (uint32_t)(v.y >> 32);
+    s.count = (uint32_t)(v.y >> 32) & COUNT_MASK;
     return s;
 }
 
@@ -390,19 +397,25 @@ __device__ __forceinline__ Slot *find_or_claim(const TableView &tv, const HashKe
     uint32_t base, nb;
     locate<RADIX>(tv, (uint32_t)(h >> 32), base, nb);
     uint32_t b = home_bucket(h, nb);
-    for (;;) {
+    for (bool home = true;; home = false) {
         Slot *s = bucket_ptr(tv, base, b);      // slots of a bucket fill in order: even first
+        // look first, then claim: claiming without the pre-read was measured slower (3.98 vs 3.70 ms / 100 M rows) and lets
+        // the rows of a heavy hitter hammer its slot with compare-and-swaps (Zipf build 12.8 -> 33 ms). The look is ONE 32 B
+        // load of the whole bucket (one L2 request, where two 8 B key loads were two), and it brings the overflow bit along.
+        unsigned long long k[2], v0, v1;
+        asm volatile("ld.global.cg.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(k[0]), "=l"(v0), "=l"(k[1]), "=l"(v1) : "l"(s) : "memory");
 #pragma unroll
         for (int j = 0; j < 2; j++, s++) {
-            // look first, then claim: claiming without the pre-read was measured slower (3.98 vs 3.70 ms / 100 M rows) and lets
-            // the rows of a heavy hitter hammer its slot with compare-and-swaps (Zipf build 12.8 -> 33 ms)
-            unsigned long long cur = __ldcg(&s->key);
+            unsigned long long cur = k[j];
             if (cur == 0ULL) {
                 cur = CLAIM128 ? claim_slot128(s, key, row) : atomicCAS(&s->key, 0ULL, (unsigned long long)key);
                 if (cur == 0ULL) { distinct++; return s; }
             }
             if (cur == key) return s;
         }
+        // leaving the full home bucket: tell the probes that it overflowed (v0 is from before our claims: a stale clear bit
+        // only costs a redundant atomicOr)
+        if (home && !bucket_overflowed(v0)) atomicOr(&bucket_ptr(tv, base, b)->count, SLOT_OVF);
         b = next_bucket(b, nb);
     }
 }
@@ -441,11 +454,11 @@ __global__ void __launch_bounds__(TILE_THREADS) build_insert_kernel(BuildArgs a)
                 const unsigned peers = __match_any_sync(am, (unsigned long long)s);
                 const int leader = __ffs(peers) - 1;
                 uint32_t base = 0;
-                if ((t & 31) == leader) base = atomicAdd(&s->count, (uint32_t)__popc(peers));
+                if ((t & 31) == leader) base = atomicAdd(&s->count, (uint32_t)__popc(peers)) & COUNT_MASK;
                 base = __shfl_sync(peers, base, leader);
                 pos = base + __popc(peers & ((1u << (t & 31)) - 1u));
             } else {
-                pos = atomicAdd(&s->count, 1u);
+                pos = atomicAdd(&s->count, 1u) & COUNT_MASK;
             }
             if (pos == 0) {
                 s->row = r;
@@ -749,10 +762,10 @@ __device__ __forceinline__ void probe_tile(const ProbeArgs &a, uint32_t tile, in
 #pragma unroll
         for (int q = 0; q < PROBE_ITEMS; q++) {
             const bool hit0 = k0[q] == key[q], hit1 = k1[q] == key[q];
-            const bool done = hit0 | hit1 | (k0[q] == 0ULL) | (k1[q] == 0ULL);
+            const bool done = hit0 | hit1 | (k0[q] == 0ULL) | (k1[q] == 0ULL) | !bucket_overflowed(v0[q]);   // home bucket: see SLOT_OVF
             const unsigned long long v = hit0 ? v0[q] : ((hit1 && k0[q] != 0ULL) ? v1[q] : 0ULL);
             srow[q] = (uint32_t)v;
-            scnt[q] = (uint32_t)(v >> 32);
+            scnt[q] = (uint32_t)(v >> 32) & COUNT_MASK;
             if (done) pending &= ~(1u << q);
         }
     }
@@ -775,7 +788,7 @@ __device__ __forceinline__ void probe_tile(const ProbeArgs &a, uint32_t tile, in
                 const unsigned long long v = hit0 ? v0 : ((hit1 && k0 != 0ULL) ? v1 : 0ULL);
 #pragma unroll
                 for (int j = 0; j < PROBE_ITEMS; j++)
-                    if (q == j) { srow[j] = (uint32_t)v; scnt[j] = (uint32_t)(v >> 32); }
+                    if (q == j) { srow[j] = (uint32_t)v; scnt[j] = (uint32_t)(v >> 32) & COUNT_MASK; }
                 break;
             }
         }

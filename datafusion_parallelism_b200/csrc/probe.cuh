@@ -165,8 +165,8 @@ __global__ void __launch_bounds__(PF_THREADS) probe_fast_kernel(ProbeArgs a) {
             for (int q = 0; q < PF_ITEMS; q++) {
                 const bool hit0 = k0[q] == key[q], hit1 = k1[q] == key[q];
                 const unsigned long long v = hit0 ? v0[q] : (hit1 ? v1[q] : 0ULL);
-                const uint32_t cnt = (uint32_t)(v >> 32);
-                const bool resolved = hit0 | hit1 | (k1[q] == 0ULL);
+                const uint32_t cnt = (uint32_t)(v >> 32) & COUNT_MASK;
+                const bool resolved = hit0 | hit1 | (k1[q] == 0ULL) | !bucket_overflowed(v0[q]);      // home bucket: see SLOT_OVF
                 srow[q] = (uint32_t)v;
                 bool o, s;
                 if (MODE == PM_PAIRS) { o = cnt == 1u; s = !resolved || cnt > 1u; }
@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(PF_THREADS) probe_fast_kernel(ProbeArgs a) {
                     if (hit0 | hit1 | (k1 == 0ULL)) {
                         const unsigned long long v = hit0 ? v0 : (hit1 ? v1 : 0ULL);
                         srow = (uint32_t)v;
-                        scnt = (uint32_t)(v >> 32);
+                        scnt = (uint32_t)(v >> 32) & COUNT_MASK;
                         break;
                     }
                     idx = next_bucket(idx, nb);
@@ -488,8 +488,8 @@ __global__ void __launch_bounds__(PD_THREADS) probe_dense_kernel(ProbeArgs a) {
             for (int q = 0; q < PD_ITEMS; q++) {
                 const bool hit0 = k0[q] == key[q], hit1 = k1[q] == key[q];
                 const unsigned long long v = hit0 ? v0[q] : v1[q];
-                const bool hit = (hit0 | hit1) && (uint32_t)(v >> 32) != 0u;      // count 0: the zero-key side bucket when key 0 is absent
-                pend[q] = inb[q] && !(hit0 | hit1) && k1[q] != 0ULL;
+                const bool hit = (hit0 | hit1) && ((uint32_t)(v >> 32) & COUNT_MASK) != 0u;      // count 0: the zero-key side bucket when key 0 is absent
+                pend[q] = inb[q] && !(hit0 | hit1) && k1[q] != 0ULL && bucket_overflowed(v0[q]);   // full home bucket that never overflowed: a miss
                 res[q] = hit ? (unsigned long long)(uint32_t)v : ~0ULL;
                 n_pend += pend[q] ? 1u : 0u;
                 if (inb[q] && !pend[q]) {
