@@ -374,6 +374,10 @@ constexpr int PD_WTILE   = 32 * PD_ITEMS;             // rows per warp iteration
 #define B200J_PD_SUPER 16384
 #endif
 constexpr int PD_SUPER   = B200J_PD_SUPER;             // rows per CTA claim (one global atomic)
+#ifndef B200J_PD_MIN_CTAS
+#define B200J_PD_MIN_CTAS 1
+#endif
+constexpr int PD_MIN_CTAS = B200J_PD_MIN_CTAS;        // measured with 5 (48 registers, no spills, 8-byte keys behind the radix pass): C2 probe kernel 7.04 -> 6.95 ms at load factor 0.5; 6 spills: 9.8 ms. Default stays 1 until the GPU suite has run with 5 (r1_l ended without a box)
 constexpr int PD_QCAP    = 32 + PD_WTILE;             // a queue holds < 32 entries between iterations
 
 struct PDShared {
@@ -417,7 +421,7 @@ __device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long lo
 // L1: bucket loads allocate in L1 -- a small direct table, or a probe batch with heavy-hitter keys (every SM otherwise asks
 // the L2 for the same few sectors); off for uniform keys over a big table, where an L1 line is never reused.
 template <int KW, bool MARK, bool RADIX, bool L1>
-__global__ void __launch_bounds__(PD_THREADS) probe_dense_kernel(ProbeArgs a) {
+__global__ void __launch_bounds__(PD_THREADS, (KW == 8 && RADIX) ? PD_MIN_CTAS : 1) probe_dense_kernel(ProbeArgs a) {
     constexpr int PER_VEC = 16 / KW;
     constexpr int NVEC = PD_ITEMS / PER_VEC;
     constexpr uint32_t FULL = 0xffffffffu;
