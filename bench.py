@@ -61,6 +61,9 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-probe-sample", type=int, default=250_000_000)
+    ap.add_argument("--stock-scale", type=int, default=10, help="the Acero (stock HashJoinExec stand-in) baseline joins 1/this of the workload")
+    ap.add_argument("--no-verify", action="store_true")
+    ap.add_argument("--no-gather", action="store_true")
     ap.add_argument("--host-chunk-rows", type=int, default=1 << 27, help="N>1 e2e: probe rows per pipelined host chunk (DistributedJoin.probe_host_chunks)")
     ap.add_argument("--exchange-chunk-rows", type=int, default=0, help="N>1: > 0 = probe rows per exchange / local-join pipeline stage (DistributedJoin.probe_chunks)")
     ap.add_argument("--shuffle", default="p2p", choices=["p2p", "nccl"], help="N>1: fused peer-store scatter or NCCL all-to-all")
@@ -158,10 +161,34 @@ def cpu_join_sample(n_build: int, n_probe_full: int, probe_sample: int, reps: in
     probe_tps = pk.shape[0] / tp
     whole = (n_build + n_probe_full) / (n_build / build_tps + n_probe_full / probe_tps)
     return {"value": whole, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"full {n_build}-row build + {pk.shape[0]}-row probe sample of the {n_probe_full}-row probe side "
-                      f"(probe time scaled to the full side); oracle/cpu_join_mt.c, OpenMP x {cores} threads",
+            "sample": (f"full {n_build}-row build + the full {n_probe_full}-row probe side" if pk.shape[0] == n_probe_full else
+                       f"PROJECTED from a {100.0 * pk.shape[0] / n_probe_full:.0f} % probe sample: full {n_build}-row build timed, "
+                       f"{pk.shape[0]} of the {n_probe_full} probe rows timed and the probe time scaled to the full side")
+                      + f"; oracle/cpu_join_mt.c, OpenMP x {cores} threads",
             "build_tuples_per_s": build_tps, "probe_tuples_per_s": probe_tps,
             "build_s": tb, "probe_sample_s": tp}, tb + tp
+
+
+def acero_join_sample(n_build: int, n_probe_full: int, scale: int = 10):
+    """Stand-in for DataFusion's stock HashJoinExec (the `None` join replacement, src/parse_sql.rs:37-54), which cannot be built
+    here: pyarrow Acero's multi-threaded hash join on the same key distributions at 1/scale of the workload (inner join, one
+    int64 payload per side, output table materialised)."""
+    import numpy as np
+    import pyarrow as pa
+    import oracle
+    nb, npr = max(1, n_build // scale), max(1, n_probe_full // scale)
+    bk = oracle.gen_permutation_i64(nb, 3)
+    pk = oracle.gen_uniform_i64(npr, nb, 4)
+    bt = pa.table({"k": bk, "b_row": np.arange(nb, dtype=np.int64)})
+    pt = pa.table({"k": pk, "p_row": np.arange(npr, dtype=np.int64)})
+    t0 = time.perf_counter()
+    out = pt.join(bt, keys="k", join_type="inner", use_threads=True)
+    dt = time.perf_counter() - t0
+    assert out.num_rows == npr, (out.num_rows, npr)
+    return {"value": (nb + npr) / dt, "unit": UNIT, "cores": pa.cpu_count(), "kind": "stand-in",
+            "engine": f"pyarrow {pa.__version__} Acero Table.join (stock HashJoinExec stand-in: DataFusion is not buildable here, no cargo)",
+            "sample": f"1/{scale} scale of the workload: {nb}-row unique int64 build x {npr}-row uniform probe, inner join, output materialised",
+            "seconds": dt}
 
 
 def run_reference(args):
@@ -274,6 +301,12 @@ def run_b200(args):
         expect = tot
     if world == 1 and expect is not None:
         assert expect == n_probe, f"1:1 workload produced {expect} rows for {n_probe} probe rows"
+    verified = None
+    if not args.no_verify:
+        verified = (verify_single(args, d, torch, dev, join, bk, pk) if world == 1 else
+                    verify_distributed(args, d, torch, dist, dev, join, bk, pk, rank, world))
+        torch.cuda.empty_cache()
+        step_device()                   # back to the steady state the warm-up left (block cache, L2)
 
     join.reset_stats()
     sampler = ClockSampler(local_rank)
@@ -351,6 +384,10 @@ def run_b200(args):
         del bk, pk
         torch.cuda.empty_cache()
         cpu, _ = cpu_join_sample(n_build, n_probe, args.cpu_probe_sample, reps=1, warmup=0)
+        try:
+            cpu["stock"] = acero_join_sample(n_build, n_probe, args.stock_scale)
+        except Exception as exc:          # a host without the RAM for the 1/10-scale tables: say so, keep the line
+            cpu["stock"] = {"unavailable": repr(exc)[:200]}
 
     if rank == 0:
         line = {
@@ -358,11 +395,83 @@ def run_b200(args):
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64",
             "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e, "gpu_launches": gpu_launches,
             "roofline": roofline, "cpu_baseline": cpu, "phases": phases,
+            "verified": bool(verified and verified.get("ok")), "verification": verified,
         }
         print(json.dumps(line))
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def verify_single(args, d, torch, dev, join, bk, pk):
+    """Full-size check of one whole join, outside the timed region: every (build_idx, probe_idx) pair joins equal keys, every
+    probe row appears exactly once (1:1 workload), the pair count is the probe row count."""
+    n_build, n_probe, chunk = args.build_rows, args.probe_rows, args.chunk_rows
+    join.reset()
+    join.build_push(0, [bk])
+    join.build_finish(0)
+    total, S = 0, 1 << 27
+    for lo in range(0, n_probe, chunk):
+        m = min(chunk, n_probe - lo)
+        r = join.probe_batch(0, [pk[lo:lo + m]], want=d.OUT_PAIRS)
+        assert r.n == m, f"1:1 workload: {r.n} pairs for {m} probe rows"
+        b_, p_ = r.device_arrays()
+        tb, tp = torch.as_tensor(b_, device=dev), torch.as_tensor(p_, device=dev)
+        psum = 0
+        for s0 in range(0, r.n, S):
+            bb = tb[s0:s0 + S]
+            pp = tp[s0:s0 + S].long() & 0xFFFFFFFF
+            assert int(bb.min()) >= 0 and int(bb.max()) < n_build and int(pp.max()) < m, "index out of range"
+            assert torch.equal(bk[bb], pk[lo:lo + m][pp]), "a pair joins two different keys"
+            psum += int(pp.sum())
+            del bb, pp
+        assert psum == m * (m - 1) // 2, "probe rows are not covered exactly once"
+        total += r.n
+        r.release()
+    assert total == n_probe
+    return {"ok": True, "pairs_checked": total, "checks": ["count == probe rows", "build_key[build_idx] == probe_key[probe_idx] on every pair",
+                                                           "sum(probe_idx) == n(n-1)/2"]}
+
+
+def verify_distributed(args, d, torch, dist, dev, join, bk, pk, rank, world):
+    """N > 1, outside the timed region: (1) the pair counts of all ranks add up to world x probe rows; (2) the exchange lost and
+    invented nothing: count and wrapping sum of the keys sent == of the keys received, over all ranks; (3) every received key
+    hashes to this rank (b200j_hash_keys on a sample); (4) on a 2^24-row sample of this rank's result, the received build key
+    at build_idx equals the received probe key at probe_idx."""
+    from datafusion_parallelism_b200.exchange import _RawCudaArray
+    n_build, n_probe = args.build_rows, args.probe_rows
+    join.reset()
+    join.build_push(0, [bk])
+    join.build_finish(0)
+    r = join.probe_batch(0, [pk], want=d.OUT_PAIRS)
+    n_recv_b = int(join.build.plan.recv_rows[rank])
+    n_recv_p = int(join.probe.plan.recv_rows[rank])
+    kdt = "<i8"
+    rb = torch.as_tensor(_RawCudaArray(join.build.recv_keys_ptr, n_recv_b, kdt), device=dev)
+    rp = torch.as_tensor(_RawCudaArray(join.probe.recv_keys_ptr, n_recv_p, kdt), device=dev)
+    t = torch.tensor([r.n, n_recv_b, n_recv_p, int(bk.sum()), int(rb.sum()), int(pk.sum()), int(rp.sum())], device=dev, dtype=torch.int64)
+    dist.all_reduce(t)          # int64 sums wrap: a checksum of checksums
+    tot, nb_, np_, sb, srb, sp, srp = [int(x) for x in t.tolist()]
+    assert tot == n_probe * world, f"{tot} pairs over all ranks for {n_probe * world} probe rows"
+    assert nb_ == n_build * world and np_ == n_probe * world, "rows lost or duplicated by the exchange"
+    assert sb == srb and sp == srp, "key checksum differs between what was sent and what was received"
+    S = min(1 << 22, n_recv_p)
+    if S:
+        h = torch.empty(S, dtype=torch.int64, device=dev)
+        join.join.hash_keys_device([rp[:S]], h.data_ptr())
+        torch.cuda.synchronize()
+        dest = (((h >> 32) & 0xFFFFF) * world) >> 20
+        assert bool((dest == rank).all()), "a received key does not hash to this rank"
+    S = min(1 << 24, r.n)
+    if S:
+        b_, p_ = r.device_arrays()
+        tb = torch.as_tensor(b_, device=dev)[:S]
+        tp = torch.as_tensor(p_, device=dev)[:S].long() & 0xFFFFFFFF
+        assert torch.equal(rb[tb], rp[tp]), "a pair joins two different keys"
+    r.release()
+    return {"ok": True, "pairs_all_ranks": tot, "checks": ["sum of pair counts == world x probe rows", "exchange conserves row count and key checksum",
+                                                          "received keys hash to the receiving rank (2^22 sample)",
+                                                          "build_key[build_idx] == probe_key[probe_idx] (2^24 sample per rank)"]}
 
 
 def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):

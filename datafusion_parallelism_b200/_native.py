@@ -100,6 +100,7 @@ SIGNATURES = {
     "b200j_reset_stats": (C.c_int32, [C.c_void_p]),
     "b200j_synchronize": (C.c_int32, [C.c_void_p]),
     "b200j_reset": (C.c_int32, [C.c_void_p]),
+    "b200j_trim": (C.c_int32, [C.c_void_p]),
     "b200j_build_push": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(Batch)]),
     "b200j_build_finish": (C.c_int32, [C.c_void_p, C.c_int32]),
     "b200j_probe_batch": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(Batch), C.c_uint32, C.POINTER(Result)]),

@@ -159,6 +159,7 @@ struct b200j_handle {
     std::vector<PinnedBuf> pinned_cache;
     std::vector<CachedBlock> blocks;   // device buffers >= 1 MiB, reused across calls (see big_alloc)
     size_t blocks_free_bytes = 0;
+    size_t cache_limit = (size_t)64 << 30;   // free cached bytes kept at most (set in b200j_create)
     b200j_stats st{};
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 
@@ -192,7 +193,8 @@ void do_gathered_release(H *h, b200j_gathered *g);
 // release threshold at its maximum, more than the probe kernel itself. All work of a handle is ordered on one stream, so
 // a block freed here may be handed out again at once.
 constexpr size_t BIG_BLOCK = (size_t)1 << 20;
-constexpr size_t BIG_CACHE_LIMIT = (size_t)96 << 30;
+// Free cached blocks are kept up to h->cache_limit bytes (40 % of the device's memory unless B200J_CACHE_LIMIT_BYTES says
+// otherwise); b200j_trim gives all of them back at once (another allocator in the process may need the room).
 
 template <typename T>
 cudaError_t big_alloc(H *h, T **out, size_t bytes) {
@@ -237,7 +239,7 @@ cudaError_t big_free(H *h, void *p) {
             h->blocks[i].in_use = false;
             h->blocks_free_bytes += h->blocks[i].cap;
             // bounded cache: give the largest free blocks back to the pool beyond the limit
-            while (h->blocks_free_bytes > BIG_CACHE_LIMIT) {
+            while (h->blocks_free_bytes > h->cache_limit) {
                 int big = -1;
                 for (size_t j = 0; j < h->blocks.size(); j++)
                     if (!h->blocks[j].in_use && (big < 0 || h->blocks[j].cap > h->blocks[big].cap)) big = (int)j;
@@ -249,6 +251,21 @@ cudaError_t big_free(H *h, void *p) {
             return cudaSuccess;
         }
     return cudaFreeAsync(p, h->stream);
+}
+
+// Gives every cached free block back to the stream-ordered pool and trims the pool itself (b200j_trim).
+void cache_trim(H *h) {
+    for (size_t i = 0; i < h->blocks.size();) {
+        if (!h->blocks[i].in_use) {
+            cudaFreeAsync(h->blocks[i].p, h->stream);
+            h->blocks_free_bytes -= h->blocks[i].cap;
+            h->blocks.erase(h->blocks.begin() + i);
+        } else i++;
+    }
+    CU(cudaStreamSynchronize(h->stream));
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, h->cfg.device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
+    cudaGetLastError();
 }
 
 void dev_alloc(H *h, DevBuf &b, size_t bytes) {
@@ -515,8 +532,9 @@ void do_build_push(H *h, int32_t partition, const b200j_batch *b) {
     for (int i = 0; i < h->cfg.n_build_payload; i++) store_append(h, h->bpayload[i], b->payload[i], h->n_build, b->n_rows, b->mem, temps);
     free_temps(h, temps);
     h->n_build += b->n_rows;
-    // host buffers are borrowed for the call only
-    if (b->mem == B200J_MEM_HOST) CU(cudaStreamSynchronize(h->stream));
+    // input buffers are borrowed for the call only (include/b200join.h): the copies out of them -- host OR device -- have to be
+    // complete when the call returns, or a caller that frees / reuses a device batch right away corrupts the build side
+    CU(cudaStreamSynchronize(h->stream));
     tm.stop();
 }
 
@@ -657,6 +675,7 @@ void run_build(H *h) {
 void do_build_finish(H *h, int32_t partition) {
     REQUIRE(partition >= 0 && partition < h->cfg.n_partitions, B200J_ERR_INVALID, "partition out of range");
     REQUIRE(!h->build_done[partition], B200J_ERR_STATE, "State already consumed: build_finish called twice for this partition");
+    REQUIRE(!h->shuffle_armed, B200J_ERR_STATE, "build_finish between b200j_shuffle_count and b200j_shuffle_scatter");
     h->build_done[partition] = 1;
     h->n_build_done++;
     if (h->n_build_done == h->cfg.n_partitions) run_build(h);   // the last owner does the work (LimitedRc / InitializeLast)
@@ -1272,6 +1291,8 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
     REQUIRE(partition >= 0 && partition < h->cfg.n_partitions, B200J_ERR_INVALID, "partition out of range");
     REQUIRE(h->built, B200J_ERR_INVALID, "probe before every partition finished the build side");
     REQUIRE(!h->probe_done[partition], B200J_ERR_STATE, "probe_batch after probe_finish");
+    // the pending scatter's offsets live in the handle's partition scratch, which a radix probe would overwrite
+    REQUIRE(!h->shuffle_armed, B200J_ERR_STATE, "probe_batch between b200j_shuffle_count and b200j_shuffle_scatter");
     REQUIRE(out != nullptr && out->struct_size >= sizeof(b200j_result), B200J_ERR_INVALID, "result struct missing or too small");
     check_batch(h, b, h->cfg.n_probe_payload);
     REQUIRE(b->n_rows < 0xffff0000LL, B200J_ERR_UNSUPPORTED, "probe batch of more than 2^32 - 2^16 rows (probe indices are UInt32)");
@@ -1328,15 +1349,21 @@ int64_t select_bits(H *h, const uint32_t *bm, int64_t n, bool want_set, void **o
     if (out32) *out32 = nullptr;
     if (n == 0) return 0;
     void *o64 = nullptr, *o32 = nullptr;
-    if (out64) CU(big_alloc(h, &o64, (size_t)n * 8));
-    if (out32) CU(big_alloc(h, &o32, (size_t)n * 4));
-    CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
-    bitmap_select_kernel<<<grid_for(h, (n + 31) / 32, 256, 8), 256, 0, h->stream>>>(bm, n, want_set ? 1 : 0, (uint64_t *)o64, (uint32_t *)o32,
-                                                                                     (uint64_t)n, &h->d_ctr->out_count);
-    h->st.kernel_launches++;
-    CU(cudaGetLastError());
-    CU(cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
-    CU(cudaStreamSynchronize(h->stream));
+    try {
+        if (out64) CU(big_alloc(h, &o64, (size_t)n * 8));
+        if (out32) CU(big_alloc(h, &o32, (size_t)n * 4));
+        CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
+        bitmap_select_kernel<<<grid_for(h, (n + 31) / 32, 256, 8), 256, 0, h->stream>>>(bm, n, want_set ? 1 : 0, (uint64_t *)o64, (uint32_t *)o32,
+                                                                                         (uint64_t)n, &h->d_ctr->out_count);
+        h->st.kernel_launches++;
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+    } catch (...) {
+        if (o64) big_free(h, o64);
+        if (o32) big_free(h, o32);
+        throw;
+    }
     if (out64) *out64 = o64;
     if (out32) *out32 = o32;
     return (int64_t)h->h_ctr->out_count;
@@ -1427,9 +1454,17 @@ void do_apply_pairs(H *h, int32_t partition, int64_t n_probe_rows, int32_t mem, 
             CU(cudaMemsetAsync(s, 0, sb, h->stream));
             seen = (uint32_t *)s;
         }
-        if (n_pairs > 0 && (mark || seen)) {
-            mark_pairs_kernel<<<grid_for(h, n_pairs, 256, 8), 256, 0, h->stream>>>(db, dp, n_pairs, seen, mark ? (uint32_t *)h->visited.p : nullptr);
+        if (n_pairs > 0) {
+            // the pairs come from the caller (the JoinFilter round trip): an index outside the probe batch / the build side is
+            // B200J_ERR_INVALID, never a write outside the bitmaps
+            CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
+            mark_pairs_kernel<<<grid_for(h, n_pairs, 256, 8), 256, 0, h->stream>>>(db, dp, n_pairs, seen, mark ? (uint32_t *)h->visited.p : nullptr,
+                                                                                   (uint64_t)n_probe_rows, (uint64_t)h->n_build, &h->d_ctr->build_null_out);
             h->st.kernel_launches++;
+            CU(cudaGetLastError());
+            CU(cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
+            CU(cudaStreamSynchronize(h->stream));
+            REQUIRE(h->h_ctr->build_null_out == 0, B200J_ERR_INVALID, "apply_pairs: pair index outside the probe batch / the build side");
         }
         int64_t n_extra = 0;
         void *extra32 = nullptr;
@@ -1622,6 +1657,9 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
             if (const char *e = getenv("B200J_THIN_TABLE_BYTES")) h->thin_table_bytes = std::max<uint64_t>(1, (uint64_t)atoll(e));
         }
         h->l2_bytes = prop.l2CacheSize;
+        h->cache_limit = (size_t)((double)prop.totalGlobalMem * 0.4);
+        if (const char *e = getenv("B200J_CACHE_LIMIT_BYTES")) h->cache_limit = (size_t)std::max<long long>(0, atoll(e));
+        set_kernel_attributes();       // per device: opt-in shared-memory sizes of the partition kernels
         if (cfg->stream) {
             h->stream = (cudaStream_t)cfg->stream;
         } else {
@@ -1729,6 +1767,10 @@ int32_t b200j_reset(b200j_handle *h) {
 
 int32_t b200j_synchronize(b200j_handle *h) {
     return guarded(h, [&] { CU(cudaStreamSynchronize(h->stream)); });
+}
+
+int32_t b200j_trim(b200j_handle *h) {
+    return guarded(h, [&] { cache_trim(h); });
 }
 
 int32_t b200j_build_push(b200j_handle *h, int32_t partition, const b200j_batch *batch) {

@@ -995,12 +995,21 @@ __global__ void __launch_bounds__(256) bitmap_select_kernel(const uint32_t *__re
 }
 
 // apply_pairs: mark `seen` probe rows and `visited` build rows of caller-filtered pairs.
+// Indices come from the caller: a probe index >= n_probe_rows or a build index >= n_build (other than the NULL marker) is
+// counted in *n_bad and marks nothing.
 __global__ void __launch_bounds__(256) mark_pairs_kernel(const uint64_t *__restrict__ build_idx, const uint32_t *__restrict__ probe_idx,
-                                                         int64_t n, uint32_t *seen, uint32_t *visited) {
+                                                         int64_t n, uint32_t *seen, uint32_t *visited, uint64_t n_probe_rows, uint64_t n_build,
+                                                         unsigned long long *n_bad) {
+    uint32_t bad = 0;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        if (seen) mark_visited(seen, probe_idx[i]);
-        if (visited && build_idx[i] != ~0ULL) mark_visited(visited, (uint32_t)build_idx[i]);
+        const uint64_t b = build_idx[i];
+        const uint32_t p = probe_idx[i];
+        if ((uint64_t)p >= n_probe_rows || (b != ~0ULL && b >= n_build)) { bad++; continue; }
+        if (seen) mark_visited(seen, p);
+        if (visited && b != ~0ULL) mark_visited(visited, (uint32_t)b);
     }
+    const unsigned long long z = warp_sum_u32(bad);
+    if ((threadIdx.x & 31) == 0 && z) atomicAdd(n_bad, z);
 }
 
 // Fills (NULL, probe) / (build, NULL) sides of index-only results.

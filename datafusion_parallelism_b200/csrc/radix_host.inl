@@ -84,13 +84,17 @@ void part_hist(H *h, PartPlan &pl, bool sync) {
     if (sync) CU(cudaStreamSynchronize(h->stream));
 }
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE attribute: set for the current device by every b200j_create
+// (a process may hold handles on several devices).
+void set_kernel_attributes() {
+    CU(cudaFuncSetAttribute(part_scatter_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(part_scatter_kernel<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(part_scatter_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(part_scatter_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+}
+
 template <int KW, bool DEST>
 void part_scatter_launch(H *h, PartPlan &pl) {
-    static bool attr = false;
-    if (!attr) {
-        CU(cudaFuncSetAttribute(part_scatter_kernel<KW, DEST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr = true;
-    }
     part_scatter_kernel<KW, DEST><<<pl.grid, SC_THREADS, part_scatter_smem(KW, pl.a.n_bins), h->stream>>>(pl.a);
 }
 

@@ -344,6 +344,10 @@ class HashJoin:
         """Re-arm for another execution of the same join (keeps streams and device allocations)."""
         self._check(N.lib().b200j_reset(self._h))
 
+    def trim(self):
+        """Give the handle's cached free device blocks back to the driver (b200j_trim)."""
+        self._check(N.lib().b200j_trim(self._h))
+
 
 class PinnedArray:
     """Page-locked host memory from b200j_host_alloc, viewed as a numpy array (full-speed PCIe copies)."""

@@ -218,6 +218,10 @@ int32_t     b200j_synchronize(b200j_handle *h);             /* wait for the hand
  * ParallelHashJoin::execute on a fresh OnceLock, parallel_hash_join.rs:144-151): drops the build
  * side and the table, keeps streams and device allocations. Outstanding results stay valid. */
 int32_t     b200j_reset(b200j_handle *h);
+/* The handle keeps freed device blocks of 1 MiB and more for reuse (a cudaMallocAsync of an 8 GB block costs as much
+ * as the probe kernel), up to 40 % of the device's memory (B200J_CACHE_LIMIT_BYTES overrides). b200j_trim gives every
+ * cached free block back to the driver: call it when another allocator in the process needs the room. */
+int32_t     b200j_trim(b200j_handle *h);
 
 /* ---- build side ------------------------------------------------------------------------------ */
 /* Append one build batch (rows are numbered in arrival order, like offset_counter.fetch_add,

@@ -1,0 +1,283 @@
+"""GPU tests of the drop-in claim itself: the reference's own golden scenarios (src/lib.rs) through the CUDA path
+(HashJoin + gather + the JoinFilter round trip, compared as ROWS with the literal expected batches), the call pattern of
+N DataFusion partitions on N host threads (parallel_hash_join.rs:144-167), and the borrowed-buffer / bad-index rules of
+include/b200join.h."""
+import threading
+
+import numpy as np
+import pyarrow as pa
+import pyarrow.compute as pc
+import pytest
+
+import oracle
+from helpers import load_golden, rows_multiset, table_from_dict
+
+pytestmark = pytest.mark.gpu
+
+G = load_golden()
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    import datafusion_parallelism_b200 as d
+    assert d.device_count() >= 1, "no CUDA device: -m gpu tests must run on the B200 box"
+    return d
+
+
+def _width_or_utf8(pkg, typ):
+    return pkg.T_UTF8 if (pa.types.is_string(typ) or pa.types.is_binary(typ)) else typ.bit_width // 8
+
+
+def gpu_join_tables(pkg, build: pa.Table, probe_batches, on, join_type, filter_expr=None, layout="auto", radix_bits=0,
+                    build_batch_rows=None):
+    """The whole join through the C ABI the way the Rust operator would drive it: build batches pushed, every probe batch
+    probed (pairs stay on the device unless a JoinFilter has to see them) and gathered, then the finaliser batch.
+    Returns a table with the oracle's column naming (l.<build columns in schema order>, r.<probe columns>)."""
+    bkey, pkey = [b for b, _ in on], [p for _, p in on]
+    bpay = [n for n in build.column_names if n not in bkey]
+    probe_schema = probe_batches[0].schema
+    ppay = [n for n in probe_schema.names if n not in pkey]
+    left_only, right_only = join_type in ("left_semi", "left_anti"), join_type in ("right_semi", "right_anti")
+    out_names, out_types = [], []
+    if not right_only:
+        out_names += [f"l.{n}" for n in bkey + bpay]
+        out_types += [build.schema.field(n).type for n in bkey + bpay]
+    if not left_only:
+        out_names += [f"r.{n}" for n in pkey + ppay]
+        out_types += [probe_schema.field(n).type for n in pkey + ppay]
+    want_order = ([f"l.{n}" for n in build.column_names] if not right_only else []) + \
+                 ([f"r.{n}" for n in probe_schema.names] if not left_only else [])
+    pieces = []
+    with pkg.HashJoin(join_type, key_widths=tuple(_width_or_utf8(pkg, build.schema.field(n).type) for n in bkey),
+                      build_payload_types=tuple(_width_or_utf8(pkg, build.schema.field(n).type) for n in bpay),
+                      probe_payload_types=tuple(_width_or_utf8(pkg, probe_schema.field(n).type) for n in ppay),
+                      layout=layout, radix_bits=radix_bits) as j:
+        step = build_batch_rows or max(build.num_rows, 1)
+        for lo in range(0, max(build.num_rows, 1), step):
+            bb = build.slice(lo, step).combine_chunks()
+            j.build_push(0, [bb.column(n) for n in bkey], [bb.column(n) for n in bpay])
+        j.build_finish(0)
+        for pb in probe_batches:
+            pb = pb.combine_chunks()
+            keys, pay = [pb.column(n) for n in pkey], [pb.column(n) for n in ppay]
+            if filter_expr is None:
+                res = j.probe_batch(0, keys, want=pkg.OUT_PAIRS)
+            else:
+                # JoinFilter stays with the caller (apply_join_filter_to_indices, datafusion_private.rs:295-328)
+                assert filter_expr == "l.value != r.value"
+                m = j.probe_batch(0, keys, want=pkg.OUT_PAIRS | pkg.OUT_HOST | pkg.OUT_MATCHES_ONLY)
+                b, p = m.numpy()
+                m.release()
+                lv = build.column("value").take(pa.array(b.astype(np.int64)))
+                rv = pb.column("value").take(pa.array(p.astype(np.int64)))
+                keep = np.asarray(pc.fill_null(pc.not_equal(lv, rv), False)) if len(b) else np.zeros(0, dtype=bool)
+                res = j.apply_pairs(0, pb.num_rows, b[keep], p[keep], want=pkg.OUT_PAIRS | pkg.OUT_HOST)
+            if not left_only:
+                g = j.gather(res, keys, pay)
+                pieces.append(pa.Table.from_arrays(g.to_arrow(out_types), names=out_names))
+                g.release()
+            res.release()
+        fin = j.probe_finish(0, want=pkg.OUT_PAIRS | pkg.OUT_HOST)
+        if fin.n or not pieces:
+            g = j.gather(fin, None)
+            pieces.append(pa.Table.from_arrays(g.to_arrow(out_types), names=out_names))
+            g.release()
+        fin.release()
+    return pa.concat_tables(pieces).select(want_order)
+
+
+@pytest.mark.parametrize("sc", G["scenarios"], ids=[s["name"] for s in G["scenarios"]])
+@pytest.mark.parametrize("probe_split", [None, 1, 2])
+@pytest.mark.parametrize("layout,radix_bits", [("direct", 0), ("radix", 2)])
+def test_lib_rs_scenarios_through_cuda(pkg, sc, probe_split, layout, radix_bits):
+    """The ten src/lib.rs scenarios (Int32 key with NULLs, Utf8 payload, all join types, the post-join JoinFilter): output
+    ROWS of the CUDA path against the reference's literal expected batches."""
+    left, right = table_from_dict(sc["left"]), table_from_dict(sc["right"])
+    batches = [right] if probe_split is None else [right.slice(i, probe_split) for i in range(0, right.num_rows, probe_split)]
+    out = gpu_join_tables(pkg, left, batches, sc["on"], sc["join_type"], sc["filter"], layout, radix_bits)
+    if sc.get("post_filter"):
+        assert sc["post_filter"] == "r.id is not null"
+        out = out.filter(pc.is_valid(out.column("r.id")))
+    assert rows_multiset(out) == rows_multiset(sc["expected"])
+    # and the same rows as the oracle's whole-join output, column by column
+    want = oracle.join_tables(left, batches, sc["on"], sc["join_type"], None if sc["filter"] is None else
+                              (lambda b, p, bi, pi: np.asarray(pc.fill_null(pc.not_equal(
+                                  b.column("value").take(pa.array(bi.astype(np.int64))),
+                                  p.column("value").take(pa.array(pi.astype(np.int64)))), False))))
+    if sc.get("post_filter"):
+        want = want.filter(pc.is_valid(want.column("r.id")))
+    assert rows_multiset(out) == rows_multiset(want)
+
+
+def test_inner_join_no_filter_chain_through_cuda(pkg):
+    """inner_join_no_filter (src/lib.rs:67-132): a 1024-row table joined four times with a small table, 64-row batches on
+    both sides; every join's output is the next join's build side."""
+    sc = G["chain_scenario"]
+    n = sc["batch_size"] * sc["batches"]
+    ids = pa.array(np.arange(n, dtype=np.int32))
+    acc = pa.Table.from_arrays([ids, ids, ids, ids, pa.array(["hello"] * n)], names=["id1", "id2", "id3", "id4", "value"])
+    small = pa.Table.from_arrays([ids, pa.array(["world"] * n)], names=["id", "value"])
+    for k, (lk, rk) in enumerate(sc["joins"]):
+        probe_batches = [small.slice(i, sc["batch_size"]) for i in range(0, n, sc["batch_size"])]
+        acc = gpu_join_tables(pkg, acc, probe_batches, [(lk, rk)], "inner", build_batch_rows=sc["batch_size"])
+        acc = acc.rename_columns([c[2:] if c.startswith("l.") else f"s{k}.{c[2:]}" for c in acc.column_names])
+    assert acc.num_rows == 1024 and acc.num_columns == 13
+    order = np.argsort(np.asarray(acc.column(0)))
+    for ci in (0, 1, 2, 3, 5, 7, 9, 11):
+        assert np.array_equal(np.asarray(acc.column(ci))[order], np.arange(1024))
+    assert set(acc.column(4).to_pylist()) == {"hello"}
+    for ci in (6, 8, 10, 12):
+        assert set(acc.column(ci).to_pylist()) == {"world"}
+
+
+@pytest.mark.parametrize("join_type", ["inner", "left", "full", "right_anti", "left_semi"])
+@pytest.mark.parametrize("layout,radix_bits", [("direct", 0), ("radix", 4)])
+def test_partitions_on_concurrent_host_threads(pkg, join_type, layout, radix_bits):
+    """What ParallelHashJoin::execute does from N tokio workers (parallel_hash_join.rs:144-167): every partition pushes its
+    build batches, finishes its build stream, probes its own probe batches and finishes its probe stream -- all N
+    partitions at once, on N host threads, against ONE shared handle. Results are compared per probe batch with the
+    oracle; exactly one partition (the last to finish) gets the finaliser rows."""
+    n_part, per_part_build, per_part_probe = 6, 5, 7
+    rng = np.random.default_rng(hash((join_type, layout, "mt")) & 0xFFFFFFFF)
+    build_batches = [[rng.integers(0, 4000, int(rng.integers(1, 900))).astype(np.int64) for _ in range(per_part_build)] for _ in range(n_part)]
+    probe_batches = [[rng.integers(-200, 4400, int(rng.integers(1, 3000))).astype(np.int64) for _ in range(per_part_probe)] for _ in range(n_part)]
+    results = [[None] * per_part_probe for _ in range(n_part)]
+    fins = [None] * n_part
+    errors = []
+    build_barrier = threading.Barrier(n_part)
+    with pkg.HashJoin(join_type, key_widths=(8,), n_partitions=n_part, layout=layout, radix_bits=radix_bits) as j:
+        def worker(part):
+            try:
+                for bb in build_batches[part]:
+                    j.build_push(part, [bb])
+                j.build_finish(part)
+                build_barrier.wait()                  # the reference's probe side waits for the shared build as well
+                for i, pb in enumerate(probe_batches[part]):
+                    r = j.probe_batch(part, [pb])
+                    results[part][i] = r.numpy()
+                    r.release()
+                r = j.probe_finish(part)
+                fins[part] = r.numpy()
+                r.release()
+            except BaseException as e:           # noqa: BLE001 - reported below
+                errors.append((part, repr(e)))
+                try:
+                    build_barrier.abort()
+                except Exception:
+                    pass
+        threads = [threading.Thread(target=worker, args=(p,)) for p in range(n_part)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join(timeout=120)
+        assert not errors, errors
+        assert all(not t.is_alive() for t in threads)
+        stats = j.stats()
+    # Row numbering = arrival order, which is a race between the threads: compare KEYS, not row ids. For every probe batch
+    # the multiset of (build key, probe row) must equal the oracle's, whatever order the build batches arrived in.
+    all_build = np.concatenate([b for part in build_batches for b in part])
+    assert stats["build_rows"] == len(all_build)
+    oj = oracle.OracleJoin(join_type, [all_build])
+    NULLB = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+    n_fin = 0
+    for part in range(n_part):
+        for i, pb in enumerate(probe_batches[part]):
+            wb, wp = oj.probe_batch([pb], len(pb))
+            gb, gp = results[part][i]
+            assert len(gb) == len(wb), (part, i)
+            matched = gb != NULLB
+            if join_type not in ("right_anti", "left_semi"):
+                # counts per probe row are arrival-order independent
+                assert np.array_equal(np.sort(gp[matched]), np.sort(wp[wb != NULLB]))
+                assert np.array_equal(np.sort(gp[~matched]), np.sort(wp[wb == NULLB]))
+            else:
+                assert np.array_equal(np.sort(gp), np.sort(wp))
+        n_fin += 1 if len(fins[part][0]) or len(fins[part][1]) else 0
+    wfb, wfp = oj.finish()
+    total_fin = sum(len(f[0]) for f in fins)
+    assert total_fin == len(wfb)
+    assert n_fin <= 1                                  # only the last partition emits the finaliser
+
+
+def test_pair_build_keys_with_concurrent_partitions(pkg):
+    """Same concurrent call pattern, but with the pairs checked through the gather: (build key, probe key) of every output
+    row must be equal -- this holds for any arrival order of the build batches."""
+    n_part = 4
+    rng = np.random.default_rng(99)
+    build_batches = [[rng.permutation(np.arange(p * 10_000 + q * 2_000, p * 10_000 + (q + 1) * 2_000)).astype(np.int64) for q in range(5)] for p in range(n_part)]
+    probe_batches = [[rng.integers(0, n_part * 10_000, 20_000).astype(np.int64) for _ in range(3)] for _ in range(n_part)]
+    errors, out = [], []
+    lock = threading.Lock()
+    barrier = threading.Barrier(n_part)
+    with pkg.HashJoin("inner", key_widths=(8,), n_partitions=n_part) as j:
+        def worker(part):
+            try:
+                for bb in build_batches[part]:
+                    j.build_push(part, [bb])
+                j.build_finish(part)
+                barrier.wait()
+                for pb in probe_batches[part]:
+                    r = j.probe_batch(part, [pb], want=pkg.OUT_PAIRS)
+                    g = j.gather(r, [pb])
+                    cols = g.to_arrow([pa.int64(), pa.int64()])
+                    with lock:
+                        out.append((len(pb), cols[0].to_numpy(), cols[1].to_numpy()))
+                    g.release()
+                    r.release()
+                j.probe_finish(part).release()
+            except BaseException as e:           # noqa: BLE001
+                errors.append(repr(e))
+                try:
+                    barrier.abort()
+                except Exception:
+                    pass
+        ts = [threading.Thread(target=worker, args=(p,)) for p in range(n_part)]
+        [t.start() for t in ts]
+        [t.join(timeout=120) for t in ts]
+    assert not errors, errors
+    assert len(out) == n_part * 3
+    for n_rows, bkeys, pkeys in out:
+        assert len(bkeys) == n_rows                    # unique build keys covering the probe range: 1:1
+        assert np.array_equal(bkeys, pkeys)
+
+
+def test_device_build_batch_is_borrowed_for_the_call_only(pkg):
+    """include/b200join.h: input buffers are borrowed for the duration of the call. A device batch overwritten right after
+    build_push returns (timing off, so nothing else synchronises) must not change the build side."""
+    import torch
+    n = 4_000_000
+    keys = np.arange(1, n + 1, dtype=np.int64)
+    side = torch.cuda.Stream()
+    with pkg.HashJoin("inner", key_widths=(8,), layout="direct") as j:
+        for lo in range(0, n, n // 4):
+            t = torch.from_numpy(keys[lo:lo + n // 4]).cuda()
+            torch.cuda.synchronize()
+            j.build_push(0, [t])
+            with torch.cuda.stream(side):            # a different stream than the handle's: no implicit ordering
+                t.fill_(-7)
+        j.build_finish(0)
+        torch.cuda.synchronize()
+        probe = torch.from_numpy(np.array([1, n // 2, n, -7, n + 1], dtype=np.int64)).cuda()
+        r = j.probe_batch(0, [probe], want=pkg.OUT_PAIRS | pkg.OUT_HOST)
+        b, p = r.numpy()
+        r.release()
+    o = np.argsort(p)
+    assert p[o].tolist() == [0, 1, 2] and b[o].tolist() == [0, n // 2 - 1, n - 1]
+
+
+def test_apply_pairs_rejects_out_of_range_indices(pkg):
+    bk = np.arange(100, dtype=np.int64)
+    for jt in ("left", "right", "full"):
+        with pkg.HashJoin(jt, key_widths=(8,)) as j:
+            j.build_push(0, [bk])
+            j.build_finish(0)
+            for b, p in (([100], [0]), ([0], [50]), ([2**40], [1])):
+                with pytest.raises(pkg.B200JoinError) as e:
+                    j.apply_pairs(0, 50, np.array(b, dtype=np.uint64), np.array(p, dtype=np.uint32))
+                assert e.value.code == -1
+            # NULL build marker and in-range pairs are fine afterwards
+            r = j.apply_pairs(0, 50, np.array([3, 99], dtype=np.uint64), np.array([0, 49], dtype=np.uint32))
+            assert r.n >= 2
+            r.release()
+            j.trim()
