@@ -7,6 +7,7 @@
 #include "../../include/b200join.h"
 #include "kernels.cuh"
 #include "radix.cuh"
+#include "radix_block.cuh"
 #include "probe.cuh"
 #include "gather.cuh"
 
@@ -114,6 +115,10 @@ struct b200j_handle {
     int sm_count = 148;
     int probe_ctas_per_sm = 4;
     int dense_ctas_per_sm = 4;
+    int seg_ctas_per_sm = 4;
+    bool block_part_ok = true;         // B200J_NO_BLOCK_PART=1: the dense radix probe keeps the two-pass global partition of round 1
+    int pb_clusters[2][PB_MAX_BITS + 1] = {};   // resident clusters of part_block_kernel per key width / radix bits (0 = not asked yet)
+    unsigned long long *d_part_rows = nullptr, *h_part_rows = nullptr;   // rows per partition of the last block-partitioned batch
     bool dense_ok = true;              // B200J_NO_DENSE=1 forces the staged probe kernel (tuning / tests)
     uint64_t l1_table_bytes = 512 << 10; // direct tables up to this size are probed through L1 (B200J_L1_TABLE_BYTES)
     float thin_lf_min = 0.2f;          // lowest load factor the auto-thinning of small direct tables goes to (B200J_THIN_LF_MIN; 0.5 = off)
@@ -185,6 +190,9 @@ void radix_build(H *h, const void *keys, const uint8_t *validity, int kw, int64_
 void radix_partition(H *h, const void *keys, const uint8_t *validity, int64_t bit_offset, int kw, int64_t n, int bits,
                      void *out_keys, uint32_t *out_rid, double *ms_acc);
 void radix_release(H *h);
+struct ProbePlan;
+int64_t probe_dense_blocked(H *h, const void *d_keys, const uint8_t *d_validity, int64_t bit_offset, int64_t n, const ProbePlan &pl,
+                            ResultOwner *ro, int64_t *n_build_null);
 void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, uint32_t want, b200j_gathered *out);
 void do_gathered_release(H *h, b200j_gathered *g);
 
@@ -787,6 +795,9 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
     int64_t cap = count_only ? 0 : estimate_out_cap(h, n, pl);
     *n_build_null = 0;
     if (n == 0) return 0;
+    if (radix && !count_only && h->dense_ok && h->block_part_ok && h->radix_bits <= PB_MAX_BITS && h->st.duplicate_rows == 0 &&
+        (pl.mode == PM_PAIRS || pl.mode == PM_OUTER))
+        return probe_dense_blocked(h, d_keys, d_validity, bit_offset, n, pl, ro, n_build_null);
     std::vector<void *> temps;
     Trace tr_;
     try {
@@ -845,7 +856,7 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
                 a.ctr = h->d_ctr;
                 {
                     PhaseTimer tm(h, &h->st.ms_probe);
-                    const int grid = grid_for(h, pn, PD_SUPER, h->dense_ctas_per_sm);
+                    const int grid = grid_for(h, pn, PD_CHUNK * PD_WARPS, h->dense_ctas_per_sm);
                     // L1-allocating bucket loads: a small direct table, or a skewed batch behind the radix pass (a partition far
                     // above the mean size = heavy-hitter keys, whose buckets every SM would otherwise fetch from the same L2 sectors)
                     bool l1 = a.tv.l1 != 0u;
@@ -1648,6 +1659,12 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
                 h->dense_ctas_per_sm = occ;
             else
                 cudaGetLastError();
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, probe_dense_seg_kernel<8, false, false>, PD_THREADS, 0) == cudaSuccess && occ > 0)
+                h->seg_ctas_per_sm = occ;
+            else
+                cudaGetLastError();
+            if (const char *e = getenv("B200J_SEG_CTAS")) h->seg_ctas_per_sm = std::max(1, atoi(e));
+            if (const char *e = getenv("B200J_NO_BLOCK_PART")) h->block_part_ok = atoi(e) == 0;
             if (const char *e = getenv("B200J_NO_DENSE")) h->dense_ok = atoi(e) == 0;
             if (const char *e = getenv("B200J_DENSE_MISS_MAX")) h->dense_miss_max = (float)atof(e);
             if (const char *e = getenv("B200J_L1_TABLE_BYTES")) h->l1_table_bytes = (uint64_t)atoll(e);
@@ -1678,6 +1695,8 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
         CU(cudaMalloc((void **)&h->d_ctr, sizeof(Counters)));
         CU(cudaHostAlloc((void **)&h->h_ctr, sizeof(Counters), cudaHostAllocDefault));
         memset(h->h_ctr, 0, sizeof(Counters));
+        CU(cudaMalloc((void **)&h->d_part_rows, ((size_t)(1 << PB_MAX_BITS) + 2) * 8));
+        CU(cudaHostAlloc((void **)&h->h_part_rows, ((size_t)(1 << PB_MAX_BITS) + 2) * 8, cudaHostAllocDefault));
         h->bkeys.resize(cfg->n_keys);
         for (int i = 0; i < cfg->n_keys; i++) h->bkeys[i].type = cfg->key_widths[i];
         h->bpayload.resize(cfg->n_build_payload);
@@ -1717,6 +1736,8 @@ int32_t b200j_destroy(b200j_handle *h) {
     for (auto &p : h->pinned_cache) { pinned_size(p.p, true); cudaFreeHost(p.p); }
     if (h->d_ctr) cudaFree(h->d_ctr);
     if (h->h_ctr) cudaFreeHost(h->h_ctr);
+    if (h->d_part_rows) cudaFree(h->d_part_rows);
+    if (h->h_part_rows) cudaFreeHost(h->h_part_rows);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->copy_in) cudaStreamDestroy(h->copy_in);

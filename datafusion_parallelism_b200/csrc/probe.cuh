@@ -370,10 +370,10 @@ constexpr int PD_THREADS = 256;
 constexpr int PD_WARPS   = PD_THREADS / 32;
 constexpr int PD_ITEMS   = 4;
 constexpr int PD_WTILE   = 32 * PD_ITEMS;             // rows per warp iteration
-#ifndef B200J_PD_SUPER
-#define B200J_PD_SUPER 16384
+#ifndef B200J_PD_CHUNK
+#define B200J_PD_CHUNK 1024
 #endif
-constexpr int PD_SUPER   = B200J_PD_SUPER;             // rows per CTA claim (one global atomic)
+constexpr int PD_CHUNK   = B200J_PD_CHUNK;             // rows per WARP claim (one global atomic); a multiple of PD_WTILE
 #ifndef B200J_PD_MIN_CTAS
 #define B200J_PD_MIN_CTAS 1
 #endif
@@ -383,9 +383,12 @@ constexpr int PD_QCAP    = 32 + PD_WTILE;             // a queue holds < 32 entr
 struct PDShared {
     unsigned long long qkey[PD_WARPS][PD_QCAP];
     uint32_t           qidx[PD_WARPS][PD_QCAP];
-    uint32_t           next;
 };
+static_assert(PD_CHUNK % PD_WTILE == 0, "a warp's claim is a whole number of its 128-row iterations");
 
+#ifndef B200J_DRAIN_PAIR
+#define B200J_DRAIN_PAIR 1      // a drained lookup fetches two consecutive buckets per round (0: one)
+#endif
 template <bool MARK, bool RADIX, bool L1>
 __device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long long *qkey, uint32_t *qidx, uint32_t first, uint32_t cnt,
                                             int lane, uint32_t &misses) {
@@ -399,6 +402,7 @@ __device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long lo
         locate<RADIX>(a.tv, (uint32_t)(h >> 32), base, nb);
         uint32_t b = next_bucket(home_bucket(h, nb), nb);          // the home bucket was full without the key
         unsigned long long res = ~0ULL;
+#if B200J_DRAIN_PAIR
         for (;;) {
             const uint32_t b2 = next_bucket(b, nb);
             unsigned long long k0, v0, k1, v1, k2, v2, k3, v3;
@@ -412,6 +416,16 @@ __device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long lo
             if (k3 == 0ULL) break;
             b = next_bucket(b2, nb);
         }
+#else
+        for (;;) {
+            unsigned long long k0, v0, k1, v1;
+            load_bucket(bucket_ptr(a.tv, base, b), k0, v0, k1, v1, L1);
+            if (k0 == key) { res = (uint32_t)v0; break; }
+            if (k1 == key) { res = (uint32_t)v1; break; }
+            if (k1 == 0ULL) break;
+            b = next_bucket(b, nb);
+        }
+#endif
         a.out_build[oi] = res;
         if (res == ~0ULL) misses++;
         else if (MARK) mark_visited(a.visited, (uint32_t)res);
@@ -428,20 +442,24 @@ __global__ void __launch_bounds__(PD_THREADS, (KW == 8 && RADIX) ? PD_MIN_CTAS :
     __shared__ PDShared sh;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const uint32_t n = (uint32_t)a.n;
-    const uint32_t n_super = (uint32_t)(((uint64_t)n + PD_SUPER - 1) / PD_SUPER);
     unsigned long long *qkey = sh.qkey[warp];
     uint32_t *qidx = sh.qidx[warp];
     uint32_t qn = 0;                                      // warp-uniform
     uint32_t misses = 0;
+    // Work is claimed per WARP in chunks of PD_CHUNK rows from one global counter (no block barrier anywhere in this kernel).
+    // The rows in flight over the whole GPU are then a window of (resident warps x PD_CHUNK) consecutive rows of the
+    // partitioned stream: measured with scripts/ubench/probe_bounds.cu, the probe runs at 203 G rows/s when every lookup hits
+    // L2 and at 147 G rows/s when the window spans 2.3 partitions' tables (the CTA-wide 16 K-row claims of round 1: 9.7 M rows
+    // in flight against 7.8 M rows per partition at C2). The next claim is issued before the current chunk is processed.
+    uint32_t claim = 0;
+    if (lane == 0) claim = atomicAdd(&a.ctr->next_tile, 1u);
     for (;;) {
-        __syncthreads();
-        if (t == 0) sh.next = atomicAdd(&a.ctr->next_tile, 1u);
-        __syncthreads();
-        const uint32_t sup = sh.next;
-        if (sup >= n_super) break;
-        const uint32_t s0 = sup * (uint32_t)PD_SUPER;
-        const uint32_t s1 = (uint32_t)min((uint64_t)s0 + PD_SUPER, (uint64_t)n);
-        for (uint32_t wb = s0 + (uint32_t)warp * PD_WTILE; wb < s1; wb += PD_WARPS * PD_WTILE) {
+        const uint32_t cur = __shfl_sync(FULL, claim, 0);
+        if ((uint64_t)cur * PD_CHUNK >= (uint64_t)n) break;
+        if (lane == 0) claim = atomicAdd(&a.ctr->next_tile, 1u);
+        const uint32_t s0 = cur * (uint32_t)PD_CHUNK;
+        const uint32_t s1 = (uint32_t)min((uint64_t)s0 + PD_CHUNK, (uint64_t)n);
+        for (uint32_t wb = s0; wb < s1; wb += PD_WTILE) {
             // ---- keys: lane takes NVEC vectors, 32 vectors apart
             uint64_t key[PD_ITEMS];
             uint32_t idx0[NVEC];
@@ -567,6 +585,230 @@ __global__ void __launch_bounds__(PD_THREADS, (KW == 8 && RADIX) ? PD_MIN_CTAS :
         }
     }
     if (qn) dense_drain<MARK, RADIX, L1>(a, qkey, qidx, 0u, qn, lane, misses);
+    const unsigned long long z = warp_sum_u32(misses);
+    if (lane == 0 && z) atomicAdd(&a.ctr->build_null_out, z);
+}
+
+// =====================================================================================================================
+// Dense probe over the BLOCK-LOCALLY partitioned stream of radix_block.cuh (round 2). Unit u = (partition p, block b), p major:
+// the rows of partition p inside block b are the segment [seg[b][p], seg[b][p + 1]) of the block's PB_BLOCK rows. Warps claim
+// SEG_UNITS consecutive units from one global counter, so the whole GPU sweeps partition 0's segments, then partition 1's ...
+// and the table of the partition being probed stays in L2 (the window of rows in flight is resident warps x ~1 K rows). Lane j
+// of the warp fetches the bounds of unit j of the claim; the warp then walks the segments 128 rows at a time: 8 B key loads
+// and 8 B result stores, 32 lanes contiguous, whatever the segment's alignment. The partition is known from the unit, not
+// from the hash: no per-row descriptor load. p == P are the NULL-key rows: they never match (src/lib.rs:149-193) and get the
+// NULL build index without a lookup. Pending lookups (home bucket full without the key) go through the same warp-private
+// queue as in probe_dense_kernel.
+// =====================================================================================================================
+#ifndef B200J_SEG_FLAT
+#define B200J_SEG_FLAT 0       // 1: the claim's segments walked as one virtual stream with key prefetch (measured slower: 7.6 vs 7.2 ms at C2)
+#endif
+#ifndef B200J_SEG_UNITS
+#define B200J_SEG_UNITS 4
+#endif
+constexpr int SEG_UNITS = B200J_SEG_UNITS;             // units per warp claim (a power of two <= 32)
+static_assert(SEG_UNITS >= 2 && SEG_UNITS <= 32 && (SEG_UNITS & (SEG_UNITS - 1)) == 0, "SEG_UNITS");
+#ifndef B200J_SEG_MIN_CTAS
+#define B200J_SEG_MIN_CTAS 4
+#endif
+
+struct SegArgs {
+    const uint32_t *seg;          // [n_blocks][P + 2]
+    uint32_t        n_blocks;
+    uint32_t        n_units;      // n_blocks * P, or n_blocks * (P + 1) when the batch has NULL keys
+    uint32_t        block_rows;   // PB_BLOCK
+    uint32_t        mis;          // see pb_block_base
+};
+
+template <int KW, bool MARK, bool L1>
+__global__ void __launch_bounds__(PD_THREADS, B200J_SEG_MIN_CTAS) probe_dense_seg_kernel(ProbeArgs a, SegArgs sg) {
+    using KeyT = typename std::conditional<KW == 8, unsigned long long, uint32_t>::type;
+    constexpr uint32_t FULL = 0xffffffffu;
+    __shared__ PDShared sh;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const KeyT *keys = reinterpret_cast<const KeyT *>(a.keys);
+    unsigned long long *out = reinterpret_cast<unsigned long long *>(a.out_build);
+    unsigned long long *qkey = sh.qkey[warp];
+    uint32_t *qidx = sh.qidx[warp];
+    uint32_t qn = 0, misses = 0;
+    const uint32_t P = 1u << a.tv.radix_bits;
+    const uint32_t n_claims = (sg.n_units + SEG_UNITS - 1) / SEG_UNITS;
+    uint32_t claim = 0;
+    if (lane == 0) claim = atomicAdd(&a.ctr->next_tile, 1u);
+    for (;;) {
+        const uint32_t cur = __shfl_sync(FULL, claim, 0);
+        if (cur >= n_claims) break;
+        if (lane == 0) claim = atomicAdd(&a.ctr->next_tile, 1u);
+        // ---- lane j: bounds and table of unit j of the claim. The claim's segments are then walked as ONE stream of `total`
+        //      virtual rows: virtual row v lies in the segment s with cum[s - 1] <= v < cum[s].
+        uint32_t my_start = 0, my_len = 0, my_base = 0, my_nb = 0;
+        {
+            const uint32_t u = cur * SEG_UNITS + (uint32_t)lane;
+            if (lane < SEG_UNITS && u < sg.n_units) {
+                const uint32_t p = u / sg.n_blocks, b = u - p * sg.n_blocks;
+                const uint2 e = make_uint2(__ldg(sg.seg + (size_t)b * (P + 2) + p), __ldg(sg.seg + (size_t)b * (P + 2) + p + 1));
+                my_start = (b == 0 ? 0u : b * sg.block_rows - sg.mis) + e.x;
+                my_len = e.y - e.x;
+                if (p < P) {
+                    const uint2 pe = __ldg(reinterpret_cast<const uint2 *>(a.tv.parts + p));
+                    my_base = pe.x;
+                    my_nb = pe.y;
+                }                                               // p == P: NULL keys, nb stays 0
+            }
+        }
+#if B200J_SEG_FLAT
+        uint32_t my_cum = my_len;                               // inclusive prefix of the lengths over the lanes
+#pragma unroll
+        for (int o = 1; o < SEG_UNITS; o <<= 1) { const uint32_t y = __shfl_up_sync(FULL, my_cum, o); if (lane >= o) my_cum += y; }
+        const uint32_t total = __shfl_sync(FULL, my_cum, SEG_UNITS - 1);
+        uint32_t cum[SEG_UNITS];                                // warp-uniform copies: the segment search is SEG_UNITS compares
+#pragma unroll
+        for (int j = 0; j < SEG_UNITS; j++) cum[j] = __shfl_sync(FULL, my_cum, j);
+        const uint32_t my_delta = my_start - (my_cum - my_len);     // position of virtual row v of my segment = v + my_delta
+
+        // keys of one 128-row iteration: position of every row (0xffffffff past the end) and its key, loads in flight
+        auto load_iter = [&](uint32_t v0, uint32_t (&pos)[PD_ITEMS], KeyT (&k)[PD_ITEMS]) {
+#pragma unroll
+            for (int q = 0; q < PD_ITEMS; q++) {
+                const uint32_t v = v0 + q * 32 + lane;
+                uint32_t s = 0;
+#pragma unroll
+                for (int j = 0; j < SEG_UNITS - 1; j++) s += (v >= cum[j]) ? 1u : 0u;
+                const uint32_t d = __shfl_sync(FULL, my_delta, s);
+                pos[q] = v < total ? v + d : 0xffffffffu;
+                k[q] = v < total ? __ldcs(keys + pos[q]) : (KeyT)0;
+            }
+        };
+        uint32_t pos[PD_ITEMS], npos[PD_ITEMS];
+        KeyT kraw[PD_ITEMS], nk[PD_ITEMS];
+        load_iter(0, npos, nk);
+        for (uint32_t v0 = 0; v0 < total; v0 += PD_WTILE) {
+            uint64_t key[PD_ITEMS];
+#pragma unroll
+            for (int q = 0; q < PD_ITEMS; q++) { pos[q] = npos[q]; kraw[q] = nk[q]; }
+            // the next iteration's keys are requested before this iteration's lookups are consumed (ncu, first version: 42 % of
+            // all stall samples sat on the first use of a key)
+            if (v0 + PD_WTILE < total) load_iter(v0 + PD_WTILE, npos, nk);
+            unsigned long long k0[PD_ITEMS], v0_[PD_ITEMS], k1[PD_ITEMS], v1[PD_ITEMS];
+            bool inb[PD_ITEMS], nullrow[PD_ITEMS];
+#pragma unroll
+            for (int q = 0; q < PD_ITEMS; q++) {
+                const uint32_t v = v0 + q * 32 + lane;
+                uint32_t s = 0;
+#pragma unroll
+                for (int j = 0; j < SEG_UNITS - 1; j++) s += (v >= cum[j]) ? 1u : 0u;
+                const uint32_t base = __shfl_sync(FULL, my_base, s), nb = __shfl_sync(FULL, my_nb, s);
+                inb[q] = pos[q] != 0xffffffffu;
+                nullrow[q] = inb[q] && nb == 0u;
+                key[q] = (uint64_t)kraw[q];
+                const uint64_t h = hash_one(a.hk, key[q]);
+                const Slot *p = (key[q] && nb) ? bucket_ptr(a.tv, base, home_bucket(h, nb)) : a.tv.zero_slot;
+                load_bucket(p, k0[q], v0_[q], k1[q], v1[q], L1);
+            }
+            bool pend[PD_ITEMS];
+            uint32_t n_pend = 0;
+#pragma unroll
+            for (int q = 0; q < PD_ITEMS; q++) {
+                const bool hit0 = k0[q] == key[q], hit1 = k1[q] == key[q];
+                const unsigned long long v = hit0 ? v0_[q] : v1[q];
+                const bool hit = !nullrow[q] && (hit0 | hit1) && ((uint32_t)(v >> 32) & COUNT_MASK) != 0u;
+                pend[q] = inb[q] && !nullrow[q] && !(hit0 | hit1) && k1[q] != 0ULL && bucket_overflowed(v0_[q]);
+                n_pend += pend[q] ? 1u : 0u;
+                if (inb[q] && !pend[q]) {
+                    __stcs(out + pos[q], hit ? (unsigned long long)(uint32_t)v : ~0ULL);
+                    if (!hit) misses++;
+                    else if (MARK) mark_visited(a.visited, (uint32_t)v);
+                }
+            }
+            const uint32_t b0 = __ballot_sync(FULL, n_pend & 1u), b1 = __ballot_sync(FULL, n_pend & 2u), b2 = __ballot_sync(FULL, n_pend & 4u);
+            const uint32_t wtot = __popc(b0) + 2u * __popc(b1) + 4u * __popc(b2);
+            if (wtot) {
+                const uint32_t lt = (1u << lane) - 1u;
+                uint32_t qp = qn + __popc(b0 & lt) + 2u * __popc(b1 & lt) + 4u * __popc(b2 & lt);
+#pragma unroll
+                for (int q = 0; q < PD_ITEMS; q++) {
+                    if (!pend[q]) continue;
+                    qkey[qp] = key[q];
+                    qidx[qp] = pos[q];
+                    qp++;
+                }
+                qn += wtot;
+                __syncwarp();
+                while (qn >= 32u) {
+                    qn -= 32u;
+                    dense_drain<MARK, true, L1>(a, qkey, qidx, qn, 32u, lane, misses);
+                    __syncwarp();
+                }
+            }
+        }
+    }
+#else
+#pragma unroll 1
+        for (int s = 0; s < SEG_UNITS; s++) {
+            const uint32_t len = __shfl_sync(FULL, my_len, s);
+            if (len == 0) continue;
+            const uint32_t start = __shfl_sync(FULL, my_start, s);
+            const uint32_t base = __shfl_sync(FULL, my_base, s), nb = __shfl_sync(FULL, my_nb, s);
+            if (nb == 0) {                                      // NULL-key rows
+                for (uint32_t i = lane; i < len; i += 32) __stcs(out + start + i, ~0ULL);
+                misses += (len + 31u - (uint32_t)lane) / 32u;
+                continue;
+            }
+            for (uint32_t i0 = 0; i0 < len; i0 += PD_WTILE) {
+                uint64_t key[PD_ITEMS];
+                bool inb[PD_ITEMS];
+#pragma unroll
+                for (int q = 0; q < PD_ITEMS; q++) {
+                    inb[q] = i0 + q * 32 + lane < len;
+                    key[q] = inb[q] ? (uint64_t)__ldcs(keys + start + i0 + q * 32 + lane) : 0ULL;
+                }
+                unsigned long long k0[PD_ITEMS], v0[PD_ITEMS], k1[PD_ITEMS], v1[PD_ITEMS];
+#pragma unroll
+                for (int q = 0; q < PD_ITEMS; q++) {
+                    const uint64_t h = hash_one(a.hk, key[q]);
+                    const Slot *p = key[q] ? bucket_ptr(a.tv, base, home_bucket(h, nb)) : a.tv.zero_slot;
+                    load_bucket(p, k0[q], v0[q], k1[q], v1[q], L1);
+                }
+                bool pend[PD_ITEMS];
+                uint32_t n_pend = 0;
+#pragma unroll
+                for (int q = 0; q < PD_ITEMS; q++) {
+                    const bool hit0 = k0[q] == key[q], hit1 = k1[q] == key[q];
+                    const unsigned long long v = hit0 ? v0[q] : v1[q];
+                    const bool hit = (hit0 | hit1) && ((uint32_t)(v >> 32) & COUNT_MASK) != 0u;
+                    pend[q] = inb[q] && !(hit0 | hit1) && k1[q] != 0ULL && bucket_overflowed(v0[q]);
+                    n_pend += pend[q] ? 1u : 0u;
+                    if (inb[q] && !pend[q]) {
+                        __stcs(out + start + i0 + q * 32 + lane, hit ? (unsigned long long)(uint32_t)v : ~0ULL);
+                        if (!hit) misses++;
+                        else if (MARK) mark_visited(a.visited, (uint32_t)v);
+                    }
+                }
+                const uint32_t b0 = __ballot_sync(FULL, n_pend & 1u), b1 = __ballot_sync(FULL, n_pend & 2u), b2 = __ballot_sync(FULL, n_pend & 4u);
+                const uint32_t wtot = __popc(b0) + 2u * __popc(b1) + 4u * __popc(b2);
+                if (wtot) {
+                    const uint32_t lt = (1u << lane) - 1u;
+                    uint32_t pos = qn + __popc(b0 & lt) + 2u * __popc(b1 & lt) + 4u * __popc(b2 & lt);
+#pragma unroll
+                    for (int q = 0; q < PD_ITEMS; q++) {
+                        if (!pend[q]) continue;
+                        qkey[pos] = key[q];
+                        qidx[pos] = start + i0 + q * 32 + lane;
+                        pos++;
+                    }
+                    qn += wtot;
+                    __syncwarp();
+                    while (qn >= 32u) {
+                        qn -= 32u;
+                        dense_drain<MARK, true, L1>(a, qkey, qidx, qn, 32u, lane, misses);
+                        __syncwarp();
+                    }
+                }
+            }
+        }
+    }
+#endif
+    if (qn) dense_drain<MARK, true, L1>(a, qkey, qidx, 0u, qn, lane, misses);
     const unsigned long long z = warp_sum_u32(misses);
     if (lane == 0 && z) atomicAdd(&a.ctr->build_null_out, z);
 }

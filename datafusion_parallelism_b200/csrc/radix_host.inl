@@ -91,6 +91,12 @@ void set_kernel_attributes() {
     CU(cudaFuncSetAttribute(part_scatter_kernel<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(part_scatter_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(part_scatter_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(part_block_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(part_block_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    if (PB_CLUSTER > 8) {       // clusters of more than 8 CTAs are a non-portable size: opt in
+        CU(cudaFuncSetAttribute(part_block_kernel<8>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        CU(cudaFuncSetAttribute(part_block_kernel<4>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    }
 }
 
 template <int KW, bool DEST>
@@ -300,4 +306,162 @@ void do_shuffle_set_hot(H *h, const uint64_t *keys, int32_t n) {
     CU(cudaStreamSynchronize(h->stream));              // `tab` is a stack-owned vector
     h->hot_mask = size - 1;
     h->hot_n = kept;
+}
+
+
+// ---- block-local partition + segment-walking dense probe (radix_block.cuh, probe_dense_seg_kernel) -----------------------
+template <int KW>
+void part_block_launch(H *h, const BlockPartArgs &a, uint32_t n_bins) {
+    cudaLaunchConfig_t cfg{};
+    cfg.blockDim = dim3(PB_THREADS);
+    cfg.dynamicSmemBytes = part_block_smem(KW, n_bins);
+    cfg.stream = h->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = PB_CLUSTER;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    // clusters that can be resident at once (2 CTAs per SM, a cluster inside one GPC): a persistent grid of that many
+    int &cached = h->pb_clusters[KW == 8 ? 1 : 0][a.radix_bits];
+    if (cached == 0) {
+        cfg.gridDim = dim3((unsigned)(h->sm_count * PB_CTAS / PB_CLUSTER * PB_CLUSTER));
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, part_block_kernel<KW>, &cfg) != cudaSuccess || n <= 0) {
+            cudaGetLastError();
+            n = std::max(1, h->sm_count * PB_CTAS / PB_CLUSTER);
+        }
+        cached = n;
+    }
+    const int n_clusters = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)a.n_blocks, (int64_t)cached));
+    cfg.gridDim = dim3((unsigned)(n_clusters * PB_CLUSTER));
+    CU(cudaLaunchKernelEx(&cfg, part_block_kernel<KW>, a));
+    h->st.kernel_launches++;
+}
+
+// Dense probe of `n` device-resident keys against unique build keys behind the radix layout. On return ro owns the
+// result arrays; returns the number of result rows. PM_OUTER keeps the rows without a match (NULL build index), PM_PAIRS
+// pays one compaction pass when there were any (NULL-key rows count as rows without a match).
+int64_t probe_dense_blocked(H *h, const void *d_keys, const uint8_t *d_validity, int64_t bit_offset, int64_t n, const ProbePlan &pl,
+                            ResultOwner *ro, int64_t *n_build_null) {
+    const int kw = h->table_kw;
+    const uint32_t P = 1u << h->radix_bits;
+    const uint32_t mis = (uint32_t)(((uintptr_t)d_keys & 15) / (uintptr_t)kw);
+    const uint32_t n_tiles = (uint32_t)(((uint64_t)n + mis + PB_TILE - 1) / PB_TILE);
+    const uint32_t n_blocks = (n_tiles + PB_CLUSTER - 1) / PB_CLUSTER;
+    void *tk = nullptr, *tr = nullptr, *seg = nullptr, *ob = nullptr, *ob2 = nullptr, *op2 = nullptr;
+    Trace tr_;
+    try {
+        CU(big_alloc(h, &tk, (size_t)n * kw + 16));
+        CU(big_alloc(h, &tr, (size_t)n * 4 + 16));
+        CU(big_alloc(h, &seg, (size_t)n_blocks * (P + 2) * 4 + 16));
+        CU(big_alloc(h, &ob, (size_t)n * 8 + 16));
+        CU(cudaMemsetAsync(h->d_part_rows, 0, (size_t)(P + 1) * 8, h->stream));
+        BlockPartArgs ba{};
+        ba.keys = d_keys;
+        ba.validity = d_validity;
+        ba.bit_offset = bit_offset;
+        ba.n = (uint32_t)n;
+        ba.mis = mis;
+        ba.radix_bits = h->radix_bits;
+        ba.n_blocks = n_blocks;
+        ba.hk = h->hk;
+        ba.out_keys = tk;
+        ba.out_rid = (uint32_t *)tr;
+        ba.seg = (uint32_t *)seg;
+        ba.part_rows = h->d_part_rows;
+        ba.rid_base = h->probe_rid_base;
+        {
+            PhaseTimer tm(h, &h->st.ms_probe_partition);
+            if (kw == 8) part_block_launch<8>(h, ba, P); else part_block_launch<4>(h, ba, P);
+            CU(cudaGetLastError());
+            tm.stop();
+        }
+        CU(cudaMemcpyAsync(h->h_part_rows, h->d_part_rows, (size_t)(P + 1) * 8, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        tr_.mark("block partition");
+        const int64_t n_null = (int64_t)h->h_part_rows[P];
+        int64_t biggest = 0;
+        for (uint32_t p = 0; p < P; p++) biggest = std::max<int64_t>(biggest, (int64_t)h->h_part_rows[p]);
+        const bool l1 = h->skew_l1 && P >= 8 && biggest * (int64_t)P > 3 * (n - n_null);
+
+        ProbeArgs a{};
+        a.keys = tk;
+        a.n = n;
+        a.tv = h->view();
+        a.hk = h->hk;
+        a.out_build = (uint64_t *)ob;
+        a.out_probe = (uint32_t *)tr;
+        a.out_cap = (uint64_t)n;
+        a.visited = (uint32_t *)h->visited.p;
+        a.ctr = h->d_ctr;
+        SegArgs sg{};
+        sg.seg = (const uint32_t *)seg;
+        sg.n_blocks = n_blocks;
+        sg.n_units = n_blocks * (n_null > 0 ? P + 1 : P);
+        sg.block_rows = PB_BLOCK;
+        sg.mis = mis;
+        {
+            PhaseTimer tm(h, &h->st.ms_probe);
+            const int64_t n_claims = ((int64_t)sg.n_units + SEG_UNITS - 1) / SEG_UNITS;
+            const int grid = grid_for(h, n_claims, PD_WARPS, h->seg_ctas_per_sm);
+            auto launch = [&](auto KW, auto MARK) {
+                constexpr int kw_ = decltype(KW)::value;
+                constexpr bool mk_ = decltype(MARK)::value;
+                if (l1) probe_dense_seg_kernel<kw_, mk_, true><<<grid, PD_THREADS, 0, h->stream>>>(a, sg);
+                else probe_dense_seg_kernel<kw_, mk_, false><<<grid, PD_THREADS, 0, h->stream>>>(a, sg);
+            };
+            if (kw == 8) {
+                if (pl.mark) launch(std::integral_constant<int, 8>{}, std::true_type{});
+                else launch(std::integral_constant<int, 8>{}, std::false_type{});
+            } else {
+                if (pl.mark) launch(std::integral_constant<int, 4>{}, std::true_type{});
+                else launch(std::integral_constant<int, 4>{}, std::false_type{});
+            }
+            h->st.kernel_launches++;
+            h->st.probe_launches++;
+            h->st.dense_probe_launches++;
+            CU(cudaGetLastError());
+            tm.stop();
+        }
+        CU(cudaMemcpyAsync(h->h_ctr, h->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        tr_.mark("segment probe + counters");
+        const int64_t misses = (int64_t)h->h_ctr->build_null_out;       // rows without a match, NULL-key rows included
+        h->miss_frac = n > n_null ? (float)((double)(misses - n_null) / (double)(n - n_null)) : 0.f;
+        big_free(h, tk); tk = nullptr;
+        big_free(h, seg); seg = nullptr;
+        if (pl.mode == PM_OUTER || misses == 0) {
+            *n_build_null = misses;
+            ro->build_idx = ob;
+            ro->probe_idx = tr;
+            return n;
+        }
+        const int64_t keep = n - misses;
+        CU(big_alloc(h, &ob2, (size_t)std::max<int64_t>(keep, 1) * 8));
+        CU(big_alloc(h, &op2, (size_t)std::max<int64_t>(keep, 1) * 4));
+        CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
+        {
+            PhaseTimer tm(h, &h->st.ms_probe);
+            compact_pairs_kernel<<<grid_for(h, n, CP_TILE, 8), CP_THREADS, 0, h->stream>>>((const uint64_t *)ob, (const uint32_t *)tr, (uint64_t)n,
+                                                                                           (uint64_t *)ob2, (uint32_t *)op2, &h->d_ctr->out_count);
+            h->st.kernel_launches++;
+            h->st.compact_launches++;
+            CU(cudaGetLastError());
+            tm.stop();
+        }
+        CU(cudaStreamSynchronize(h->stream));
+        big_free(h, ob);
+        big_free(h, tr);
+        *n_build_null = 0;
+        ro->build_idx = ob2;
+        ro->probe_idx = op2;
+        return keep;
+    } catch (...) {
+        for (void *p : {tk, tr, seg, ob, ob2, op2})
+            if (p) big_free(h, p);
+        throw;
+    }
 }

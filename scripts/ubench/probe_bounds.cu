@@ -130,6 +130,92 @@ __global__ void __launch_bounds__(256, MINB) seg_kernel(Args a) {
     }
 }
 
+
+// T: the streams go through shared memory with bulk-async copies (cp.async.bulk + mbarrier in, cp.async.bulk + bulk groups
+// out) in a per-WARP ring of NST stages of CH rows; L1TEX then only sees the table lookups (LDS / STS for keys and results).
+__device__ __forceinline__ uint32_t s32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+template <int CH, int NST, int WARPS, int MINB>
+__global__ void __launch_bounds__(WARPS * 32, MINB) tma_kernel(Args a) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned long long *buf = reinterpret_cast<unsigned long long *>(smem) + (size_t)warp * NST * CH;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (size_t)WARPS * NST * CH * 8) + warp * NST;
+    const uint64_t rows_per_part = a.n / a.n_part;
+    const uint32_t n_chunks = (uint32_t)(a.n / CH);
+    if (lane == 0) {
+        for (int s = 0; s < NST; s++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(s32(bars + s)) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    uint32_t chunk_of[NST];
+    uint32_t uses = 0;                                   // chunks consumed so far (stage = uses % NST, parity = (uses / NST) & 1)
+    auto issue = [&](int s) -> uint32_t {                // lane 0: claim a chunk and start its load into stage s
+        uint32_t c = 0xffffffffu;
+        if (lane == 0) {
+            c = atomicAdd(a.ctr, 1u);
+            if (c < n_chunks) {
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(bars + s)), "r"(CH * 8) : "memory");
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(s32(buf + s * CH)),
+                             "l"(a.keys + (uint64_t)c * CH), "r"(CH * 8), "r"(s32(bars + s)) : "memory");
+            }
+        }
+        return __shfl_sync(0xffffffffu, c, 0);
+    };
+#pragma unroll
+    for (int s = 0; s < NST - 1; s++) chunk_of[s] = issue(s);
+    chunk_of[NST - 1] = 0xffffffffu;
+    for (;;) {
+        const int s = uses % NST;
+        uint32_t c = chunk_of[0];
+#pragma unroll
+        for (int j = 1; j < NST; j++) if (s == j) c = chunk_of[j];
+        if (c >= n_chunks) break;
+        {   // wait for the stage's keys
+            const uint32_t par = (uses / NST) & 1u;
+            uint32_t ok;
+            do {
+                asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(s32(bars + s)), "r"(par) : "memory");
+            } while (!ok);
+        }
+        unsigned long long *st = buf + s * CH;
+        const uint64_t row0 = (uint64_t)c * CH;
+        const uint32_t p = (uint32_t)(row0 / rows_per_part) < a.n_part ? (uint32_t)(row0 / rows_per_part) : a.n_part - 1;
+#pragma unroll 1
+        for (int i0 = 0; i0 < CH; i0 += 128) {
+            unsigned long long key[4];
+#pragma unroll
+            for (int q = 0; q < 2; q++) {
+                const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(st + i0 + (q * 32 + lane) * 2);
+                key[2 * q] = v.x ^ (row0 + i0 + (q * 32 + lane) * 2);
+                key[2 * q + 1] = v.y ^ (row0 + i0 + (q * 32 + lane) * 2 + 1);
+            }
+            unsigned long long k0[4], v0[4], k1[4], v1[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) ldb(bucket(a, p, key[q]), k0[q], v0[q], k1[q], v1[q]);
+            unsigned long long r[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) r[q] = (k0[q] == key[q]) ? v0[q] : ((k1[q] == key[q]) ? v1[q] : ~0ULL);
+#pragma unroll
+            for (int q = 0; q < 2; q++) *reinterpret_cast<ulonglong2 *>(st + i0 + (q * 32 + lane) * 2) = make_ulonglong2(r[2 * q], r[2 * q + 1]);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) {
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.out + row0), "r"(s32(st)), "r"(CH * 8) : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            // the stage consumed BEFORE this one may be refilled once its store has read it: all groups but the newest
+            asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        }
+        __syncwarp();
+        uses++;
+        const int rs = (uses + NST - 2) % NST;          // the stage consumed before this one ( = the one NOT loaded ahead )
+        const uint32_t nc = issue(rs);
+#pragma unroll
+        for (int j = 0; j < NST; j++) if (rs == j) chunk_of[j] = nc;
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
 template <typename F>
 static float timeit(F &&f, unsigned int *ctr) {
     cudaEvent_t e0, e1;
@@ -173,24 +259,30 @@ int main() {
 #define RUN_STREAM(ITEMS, MODE, MINB, label)                                                                        \
         { snprintf(nm, sizeof nm, "%s%s items=%d ctas/sm=%d", rg, label, ITEMS, MINB);                              \
           report(nm, timeit([&] { stream_kernel<ITEMS, MODE, MINB><<<sms * MINB, 256>>>(a); }, ctr)); }
-        RUN_STREAM(4, 0, 8, "G gather only      ")
         RUN_STREAM(8, 0, 4, "G gather only      ")
         RUN_STREAM(4, 1, 4, "S stream           ")
-        RUN_STREAM(4, 1, 6, "S stream           ")
-        RUN_STREAM(4, 1, 8, "S stream           ")
         RUN_STREAM(8, 1, 4, "S stream           ")
         RUN_STREAM(4, 2, 4, "P stream+prefetch  ")
-        RUN_STREAM(4, 2, 6, "P stream+prefetch  ")
         RUN_STREAM(8, 2, 3, "P stream+prefetch  ")
-        RUN_STREAM(8, 2, 4, "P stream+prefetch  ")
-        for (uint32_t seg : {128u, 256u, 512u, 2048u}) {
+
+#define RUN_TMA(CH, NST, WARPS, MINB)                                                                                 \
+        { const size_t sm = (size_t)WARPS * NST * CH * 8 + WARPS * NST * 8;                                                \
+          CK(cudaFuncSetAttribute(tma_kernel<CH, NST, WARPS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
+          snprintf(nm, sizeof nm, "%sT bulk-async ch=%d st=%d warps=%d ctas/sm=%d", rg, CH, NST, WARPS, MINB);          \
+          report(nm, timeit([&] { tma_kernel<CH, NST, WARPS, MINB><<<sms * MINB, WARPS * 32, sm>>>(a); }, ctr)); }
+        RUN_TMA(512, 3, 8, 2)
+        RUN_TMA(512, 3, 4, 4)
+        RUN_TMA(256, 3, 8, 4)
+        RUN_TMA(256, 3, 4, 8)
+        RUN_TMA(256, 4, 4, 6)
+        RUN_TMA(128, 4, 8, 6)
+        RUN_TMA(1024, 2, 4, 3)
+        for (uint32_t seg : {128u, 512u}) {
             a.seg = seg;
             a.n_blk = (uint32_t)(n / ((uint64_t)seg * a.n_part));
             if (regime == 0) { a.n_part = P; a.n_blk = (uint32_t)(n / ((uint64_t)seg * P)); }   // same walk, one shared 32 MB table
             Args w = a;
             if (regime == 0) w.nb = (1u << 20) / P;      // P tables of 256 KB: the whole set is L2-resident
-            snprintf(nm, sizeof nm, "%sW segments of %u rows items=4 ctas/sm=6", rg, seg);
-            report(nm, timeit([&] { seg_kernel<4, 6><<<sms * 6, 256>>>(w); }, ctr));
             snprintf(nm, sizeof nm, "%sW segments of %u rows items=4 ctas/sm=4", rg, seg);
             report(nm, timeit([&] { seg_kernel<4, 4><<<sms * 4, 256>>>(w); }, ctr));
             if (regime == 0) a.n_part = 1;
