@@ -63,6 +63,7 @@ def parse_args():
     ap.add_argument("--cpu-probe-sample", type=int, default=250_000_000)
     ap.add_argument("--stock-scale", type=int, default=10, help="the Acero (stock HashJoinExec stand-in) baseline joins 1/this of the workload")
     ap.add_argument("--no-verify", action="store_true")
+    ap.add_argument("--e2e-wide", action="store_true", help="e2e returns (u64, u32) pairs instead of B200J_OUT_BUILD_U32's (u32, u32)")
     ap.add_argument("--no-gather", action="store_true")
     ap.add_argument("--host-chunk-rows", type=int, default=1 << 27, help="N>1 e2e: probe rows per pipelined host chunk (DistributedJoin.probe_host_chunks)")
     ap.add_argument("--exchange-chunk-rows", type=int, default=0, help="N>1: > 0 = probe rows per exchange / local-join pipeline stage (DistributedJoin.probe_chunks)")
@@ -345,7 +346,8 @@ def run_b200(args):
     # actual size: spreading the table thinner must not raise the roofline fraction
     table_alg = min(st["table_bytes"], 32 * max(1, st["distinct_keys"]) + 4096)
     if dense:        # 8 B key in + 8 B build index out per row, plus ONE pass over the table per launch (it is L2-resident per partition)
-        bpt, kname, table_b = B_PROBE_DENSE, "probe_dense_kernel<8,false,true,false>", table_alg
+        seg = st.get("seg_probe_launches", 0) == st["probe_launches"]
+        bpt, kname, table_b = B_PROBE_DENSE, ("probe_dense_seg_kernel<8,false,false>" if seg else "probe_dense_kernel<8,false,true,false>"), table_alg
     elif radix:
         bpt, kname, table_b = B_PROBE_KERNEL_RADIX, "probe_fast_kernel<8,PM_PAIRS,false,true>", table_alg
     else:
@@ -493,6 +495,9 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
     checksum = 0
 
     host_chunk = min(chunk, args.host_chunk_rows)
+    # (build_idx u32, probe_idx u32) pairs come back unless --e2e-wide: 8 instead of 12 bytes per pair over PCIe
+    out_flags = 0 if (args.e2e_wide or world > 1) else d.OUT_BUILD_U32
+    pair_bytes = 12 if (args.e2e_wide or world > 1) else 8
 
     def step_host():
         if world > 1:
@@ -514,7 +519,7 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
         join.build_push(0, [hb.array])
         join.build_finish(0)
         for lo in range(0, n_probe, chunk):
-            r = join.probe_batch(0, [hp.array[lo:lo + chunk]], want=d.OUT_PAIRS | d.OUT_HOST)
+            r = join.probe_batch(0, [hp.array[lo:lo + chunk]], want=d.OUT_PAIRS | d.OUT_HOST | out_flags)
             tot += r.n
             r.release()
         return tot
@@ -537,8 +542,8 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
     hb.free()
     hp.free()
     return {"value": (n_build + n_probe) * world / (dt / steps), "unit": UNIT, "h2d_bytes_per_step": 8 * (n_build + n_probe),
-            "d2h_bytes_per_step": 12 * tot, "steps": steps, "ms_per_step": dt / steps * 1e3, "ms_steps_rank0": ms_steps,
-            "api": ("HashJoin.build_push/probe_batch(host numpy over b200j_host_alloc pinned buffers, OUT_PAIRS|OUT_HOST) -> b200j_* C ABI" if world == 1 else
+            "d2h_bytes_per_step": pair_bytes * tot, "pair_format": "(u64 build_idx, u32 probe_idx)" if pair_bytes == 12 else "(u32 build_idx, u32 probe_idx) [B200J_OUT_BUILD_U32]", "steps": steps, "ms_per_step": dt / steps * 1e3, "ms_steps_rank0": ms_steps,
+            "api": ("HashJoin.build_push/probe_batch(host numpy over b200j_host_alloc pinned buffers, OUT_PAIRS|OUT_HOST" + ("|OUT_BUILD_U32" if pair_bytes == 8 else "") + ") -> b200j_* C ABI" if world == 1 else
                     f"DistributedJoin.build_push_host/probe_host_chunks(pinned numpy in, pinned pairs out, {host_chunk}-row chunks) -> b200j_* C ABI")}
 
 

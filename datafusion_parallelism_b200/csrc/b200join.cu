@@ -81,6 +81,7 @@ struct ResultOwner {
     void *build_idx = nullptr;
     void *probe_idx = nullptr;
     int32_t mem = B200J_MEM_DEVICE;
+    int32_t bwidth = 8;               // bytes per build index: 4 after B200J_OUT_BUILD_U32 narrowing
 };
 
 struct CachedBlock {
@@ -772,6 +773,7 @@ void fill_result(b200j_result *out, ResultOwner *ro, int64_t n, int mem) {
     out->build_idx = (uint64_t *)ro->build_idx;
     out->probe_idx = (uint32_t *)ro->probe_idx;
     out->_owner = ro;
+    if (out->struct_size >= offsetof(b200j_result, build_idx_width) + sizeof(int32_t)) out->build_idx_width = ro->bwidth;
 }
 
 void release_owner(H *h, ResultOwner *ro) {
@@ -1024,11 +1026,27 @@ int64_t probe_device(H *h, const void *d_keys, const uint8_t *d_validity, int64_
     }
 }
 
+// B200J_OUT_BUILD_U32: the device result's build indices narrowed to 32 bits (in a new buffer; the wide one is recycled)
+void narrow_result(H *h, ResultOwner *ro, int64_t n) {
+    if (ro->bwidth == 4 || !ro->build_idx || ro->mem != B200J_MEM_DEVICE) return;
+    void *nb = nullptr;
+    CU(big_alloc(h, &nb, (size_t)std::max<int64_t>(n, 1) * 4 + 16));
+    if (n > 0) {
+        narrow_u64_u32_kernel<<<grid_for(h, n / 2 + 1, 256, 8), 256, 0, h->stream>>>((const uint64_t *)ro->build_idx, (uint32_t *)nb, n);
+        h->st.kernel_launches++;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { big_free(h, nb); CU(e); }
+    big_free(h, ro->build_idx);          // stream-ordered: the kernel above has been enqueued before any reuse
+    ro->build_idx = nb;
+    ro->bwidth = 4;
+}
+
 void move_result_to_host(H *h, ResultOwner *ro, int64_t n) {
     void *hb = nullptr, *hp = nullptr;
     if (ro->build_idx) {
-        hb = pinned_take(h, (size_t)std::max<int64_t>(n, 1) * 8);
-        CU(cudaMemcpyAsync(hb, ro->build_idx, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
+        hb = pinned_take(h, (size_t)std::max<int64_t>(n, 1) * ro->bwidth);
+        CU(cudaMemcpyAsync(hb, ro->build_idx, (size_t)n * ro->bwidth, cudaMemcpyDeviceToHost, h->stream));
     }
     if (ro->probe_idx) {
         hp = pinned_take(h, (size_t)std::max<int64_t>(n, 1) * 4);
@@ -1089,8 +1107,9 @@ struct HostPipe {               // everything the pipelined probe must give back
     }
 };
 
-int64_t probe_host_pipelined(H *h, const b200j_column &kc, int64_t n, const ProbePlan &pl, bool count_only, ResultOwner *ro,
+int64_t probe_host_pipelined(H *h, const b200j_column &kc, int64_t n, const ProbePlan &pl, bool count_only, bool narrow, ResultOwner *ro,
                              int64_t *n_build_null) {
+    const size_t bw = narrow ? 4 : 8;        // bytes per build index in the pinned result
     const int kw = h->table_kw;
     const int64_t chunk = host_chunk_rows();
     const int64_t n_chunks = (n + chunk - 1) / chunk;
@@ -1112,7 +1131,7 @@ int64_t probe_host_pipelined(H *h, const b200j_column &kc, int64_t n, const Prob
     int64_t host_cap = 0;
     if (!count_only && want_probe) {
         host_cap = std::max<int64_t>(estimate_out_cap(h, n, pl), 1);
-        if (want_build) hp.hb = pinned_take(h, (size_t)host_cap * 8);
+        if (want_build) hp.hb = pinned_take(h, (size_t)host_cap * bw);
         hp.hp = pinned_take(h, (size_t)host_cap * 4);
     }
     auto issue_h2d = [&](int64_t k) {
@@ -1157,8 +1176,8 @@ int64_t probe_host_pipelined(H *h, const b200j_column &kc, int64_t n, const Prob
                 CU(cudaStreamSynchronize(h->copy_out));
                 const int64_t ncap = std::max<int64_t>((int64_t)((double)(total + cnt) * ((double)n / (double)(lo + m)) * 1.1) + 4096, total + cnt);
                 if (want_build) {
-                    void *nb = pinned_take(h, (size_t)ncap * 8);
-                    memcpy(nb, hp.hb, (size_t)total * 8);
+                    void *nb = pinned_take(h, (size_t)ncap * bw);
+                    memcpy(nb, hp.hb, (size_t)total * bw);
                     pinned_give(h, hp.hb);
                     hp.hb = nb;
                 }
@@ -1168,13 +1187,14 @@ int64_t probe_host_pipelined(H *h, const b200j_column &kc, int64_t n, const Prob
                 hp.hp = np;
                 host_cap = ncap;
             }
-            // results of probe_device are complete (it synchronises the stream); a kernel may still be rebasing row ids
+            if (narrow && want_build && cnt > 0) narrow_result(h, &pd.ro, cnt);
+            // results of probe_device are complete (it synchronises the stream); a kernel may still be rebasing row ids / narrowing
             CU(cudaEventCreateWithFlags(&pd.done, cudaEventDisableTiming));
             CU(cudaEventRecord(pd.done, h->stream));
             CU(cudaStreamWaitEvent(h->copy_out, pd.done, 0));
             if (cnt > 0) {
                 if (want_build)
-                    CU(cudaMemcpyAsync((char *)hp.hb + (size_t)total * 8, pd.ro.build_idx, (size_t)cnt * 8, cudaMemcpyDeviceToHost, h->copy_out));
+                    CU(cudaMemcpyAsync((char *)hp.hb + (size_t)total * bw, pd.ro.build_idx, (size_t)cnt * bw, cudaMemcpyDeviceToHost, h->copy_out));
                 CU(cudaMemcpyAsync((char *)hp.hp + (size_t)total * 4, pd.ro.probe_idx, (size_t)cnt * 4, cudaMemcpyDeviceToHost, h->copy_out));
             }
             CU(cudaEventRecord(pd.done, h->copy_out));
@@ -1195,6 +1215,7 @@ int64_t probe_host_pipelined(H *h, const b200j_column &kc, int64_t n, const Prob
         ro->build_idx = hp.hb;
         ro->probe_idx = hp.hp;
         ro->mem = B200J_MEM_HOST;
+        ro->bwidth = (int32_t)bw;
         hp.hb = hp.hp = nullptr;
     }
     return total;
@@ -1272,8 +1293,10 @@ void do_probe_composite(H *h, int32_t partition, const b200j_batch *b, uint32_t 
                     if (ro->build_idx) big_free(h, ro->build_idx);
                     if (ro->probe_idx) big_free(h, ro->probe_idx);
                     ro->build_idx = ro->probe_idx = nullptr;
-                } else if (want & B200J_OUT_HOST) {
-                    move_result_to_host(h, ro, cnt);
+                } else {
+                    if (want & B200J_OUT_BUILD_U32) narrow_result(h, ro, cnt);
+                    if (want & B200J_OUT_HOST) move_result_to_host(h, ro, cnt);
+                    else if (want & B200J_OUT_BUILD_U32) CU(cudaStreamSynchronize(h->stream));
                 }
             } catch (...) {
                 release_owner(h, ro);
@@ -1323,7 +1346,7 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
             const b200j_column &kc = b->keys[0];
             total = probe_device(h, n ? kc.values : nullptr, n ? kc.validity : nullptr, n ? kc.bit_offset : 0, n, pl, count_only, ro, &n_bnull);
         } else if (((want & B200J_OUT_HOST) || count_only) && n > host_chunk_rows() + host_chunk_rows() / 2) {
-            total = probe_host_pipelined(h, b->keys[0], n, pl, count_only, ro, &n_bnull);
+            total = probe_host_pipelined(h, b->keys[0], n, pl, count_only, (want & B200J_OUT_BUILD_U32) != 0, ro, &n_bnull);
         } else {
             const b200j_column &kc = b->keys[0];
             void *dk = nullptr;
@@ -1338,8 +1361,10 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
             if (ro->build_idx) big_free(h, ro->build_idx);
             if (ro->probe_idx) big_free(h, ro->probe_idx);
             ro->build_idx = ro->probe_idx = nullptr;
-        } else if ((want & B200J_OUT_HOST) && ro->mem != B200J_MEM_HOST) {
-            move_result_to_host(h, ro, total);
+        } else {
+            if (want & B200J_OUT_BUILD_U32) narrow_result(h, ro, total);
+            if ((want & B200J_OUT_HOST) && ro->mem != B200J_MEM_HOST) move_result_to_host(h, ro, total);
+            else if (want & B200J_OUT_BUILD_U32) CU(cudaStreamSynchronize(h->stream));
         }
         free_temps(h, temps);
         fill_result(out, ro, total, ro->mem);
@@ -1416,8 +1441,10 @@ void do_probe_finish(H *h, int32_t partition, uint32_t want, b200j_result *out) 
         if (want & B200J_OUT_COUNT_ONLY) {
             if (ro->build_idx) big_free(h, ro->build_idx);
             ro->build_idx = nullptr;
-        } else if (want & B200J_OUT_HOST) {
-            move_result_to_host(h, ro, n);
+        } else {
+            if (want & B200J_OUT_BUILD_U32) narrow_result(h, ro, n);
+            if (want & B200J_OUT_HOST) move_result_to_host(h, ro, n);
+            else CU(cudaStreamSynchronize(h->stream));
         }
         fill_result(out, ro, n, ro->mem);
         out->n_build_null = 0;
@@ -1500,6 +1527,7 @@ void do_apply_pairs(H *h, int32_t partition, int64_t n_probe_rows, int32_t mem, 
             }
         }
         CU(cudaGetLastError());
+        if (!(want & B200J_OUT_COUNT_ONLY) && (want & B200J_OUT_BUILD_U32)) narrow_result(h, ro, n);
         if (!(want & B200J_OUT_COUNT_ONLY) && (want & B200J_OUT_HOST)) move_result_to_host(h, ro, n);
         else CU(cudaStreamSynchronize(h->stream));
         free_temps(h, temps);
@@ -1766,7 +1794,7 @@ int32_t b200j_reset_stats(b200j_handle *h) {
     h->st.ms_build_copy = h->st.ms_build_partition = h->st.ms_build_insert = 0;
     h->st.ms_probe_partition = h->st.ms_probe = h->st.ms_gather = 0;
     h->st.probe_launches = h->st.kernel_launches = h->st.probe_retries = 0;
-    h->st.dense_probe_launches = h->st.compact_launches = 0;
+    h->st.dense_probe_launches = h->st.compact_launches = h->st.seg_probe_launches = 0;
     h->st.ms_exchange_partition = 0;
     return B200J_OK;
 }

@@ -153,7 +153,8 @@ void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, 
             CU(cudaMemcpyAsync(d, p, (size_t)n * w, cudaMemcpyHostToDevice, h->stream));
             return d;
         };
-        g.bidx = (const uint64_t *)stage_idx(pairs->build_idx, 8);
+        const int bwidth = (pairs->struct_size >= offsetof(b200j_result, build_idx_width) + sizeof(int32_t) && pairs->build_idx_width == 4) ? 4 : 8;
+        g.bidx = (const uint64_t *)stage_idx(pairs->build_idx, (size_t)bwidth);
         g.pidx = (const uint32_t *)stage_idx(pairs->probe_idx, 4);
         void *dn = nullptr;
         CU(big_alloc(h, &dn, (size_t)(n_cols + 1) * 8)); g.temps.push_back(dn);
@@ -170,7 +171,8 @@ void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, 
                 s.offsets64 = 1;
                 s.validity = cs.has_nulls ? (const uint8_t *)cs.validity.p : nullptr;
                 if (h->n_build == 0) s.values = s.offsets = nullptr;
-                gather_one_column<uint64_t>(g, col, cs.type, s, g.bidx);
+                if (bwidth == 4) gather_one_column<uint32_t>(g, col, cs.type, s, reinterpret_cast<const uint32_t *>(g.bidx));     // B200J_OUT_BUILD_U32 pairs
+                else gather_one_column<uint64_t>(g, col, cs.type, s, g.bidx);
             }
         }
         if (want_probe) {

@@ -1020,6 +1020,16 @@ __global__ void __launch_bounds__(256) fill_u32_kernel(uint32_t *p, int64_t n, u
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
 }
 
+// B200J_OUT_BUILD_U32: build indices narrowed to 32 bits (the NULL marker ~0 stays all ones)
+__global__ void __launch_bounds__(256) narrow_u64_u32_kernel(const uint64_t *__restrict__ in, uint32_t *__restrict__ out, int64_t n) {
+    const int64_t n2 = n >> 1;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (int64_t)gridDim.x * blockDim.x) {
+        const ulonglong2 v = __ldcs(reinterpret_cast<const ulonglong2 *>(in) + i);
+        __stcs(reinterpret_cast<uint2 *>(out) + i, make_uint2((uint32_t)v.x, (uint32_t)v.y));
+    }
+    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) out[n - 1] = (uint32_t)in[n - 1];
+}
+
 // Probe row ids of one chunk of a host batch -> row ids of the batch (direct layout; the radix layout's partition pass
 // adds the base while it writes the row-id array). NULL markers stay.
 __global__ void __launch_bounds__(256) add_base_u32_kernel(uint32_t *p, int64_t n, uint32_t base) {

@@ -423,6 +423,7 @@ int64_t probe_dense_blocked(H *h, const void *d_keys, const uint8_t *d_validity,
             h->st.kernel_launches++;
             h->st.probe_launches++;
             h->st.dense_probe_launches++;
+            h->st.seg_probe_launches++;
             CU(cudaGetLastError());
             tm.stop();
         }

@@ -15,7 +15,7 @@ from . import _native as N
 JOIN_TYPES = {"inner": 0, "left": 1, "right": 2, "full": 3, "left_semi": 4, "right_semi": 5, "left_anti": 6, "right_anti": 7}
 LAYOUTS = {"auto": 0, "direct": 1, "radix": 2}
 MEM_HOST, MEM_DEVICE = 0, 1
-OUT_PAIRS, OUT_HOST, OUT_MATCHES_ONLY, OUT_COUNT_ONLY = 1, 2, 4, 8
+OUT_PAIRS, OUT_HOST, OUT_MATCHES_ONLY, OUT_COUNT_ONLY, OUT_BUILD_U32 = 1, 2, 4, 8, 16
 FLAG_TIMING = 1
 NULL_BUILD = np.uint64(0xFFFFFFFFFFFFFFFF)
 NULL_PROBE = np.uint32(0xFFFFFFFF)
@@ -124,6 +124,7 @@ class PairResult:
         self.mem = int(res.mem)
         self.n_build_null = int(res.n_build_null)
         self.n_probe_null = int(res.n_probe_null)
+        self.build_idx_width = int(res.build_idx_width) or 8
 
     @property
     def build_ptr(self) -> int:
@@ -140,7 +141,11 @@ class PairResult:
         n = self.n
         b = np.full(n, NULL_BUILD, dtype=np.uint64)
         p = np.full(n, NULL_PROBE, dtype=np.uint32)
-        if n and self._res.build_idx:
+        if n and self._res.build_idx and self.build_idx_width == 4:
+            # B200J_OUT_BUILD_U32: widened here for the callers' convenience (NULL side: UINT32_MAX -> UINT64_MAX)
+            b32 = np.ctypeslib.as_array(C.cast(self._res.build_idx, C.POINTER(C.c_uint32)), shape=(n,))
+            b = np.where(b32 == NULL_PROBE, NULL_BUILD, b32.astype(np.uint64))
+        elif n and self._res.build_idx:
             b = np.ctypeslib.as_array(C.cast(self._res.build_idx, C.POINTER(C.c_uint64)), shape=(n,)).copy()
         if n and self._res.probe_idx:
             p = np.ctypeslib.as_array(C.cast(self._res.probe_idx, C.POINTER(C.c_uint32)), shape=(n,)).copy()
@@ -149,7 +154,7 @@ class PairResult:
     def device_arrays(self):
         if self.mem != MEM_DEVICE:
             raise ValueError("host result")
-        b = DeviceArray(self._res.build_idx, self.n, "<i8", self) if self._res.build_idx else None
+        b = DeviceArray(self._res.build_idx, self.n, "<i8" if self.build_idx_width == 8 else "<i4", self) if self._res.build_idx else None
         p = DeviceArray(self._res.probe_idx, self.n, "<i4", self) if self._res.probe_idx else None
         return b, p
 

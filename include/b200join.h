@@ -90,6 +90,9 @@ extern "C" {
                                         no visited marking — the caller applies a JoinFilter and comes back
                                         through b200j_apply_pairs                                          */
 #define B200J_OUT_COUNT_ONLY    8u   /* count the result rows, write nothing                              */
+#define B200J_OUT_BUILD_U32     16u  /* build indices as uint32_t (a device holds < 2^31 build rows): b200j_result.build_idx then
+                                        points at uint32_t values, NULL side = UINT32_MAX, build_idx_width = 4. A host result
+                                        crosses PCIe with 8 instead of 12 bytes per pair; arrow's take accepts UInt32 indices */
 
 typedef struct b200j_handle b200j_handle;
 
@@ -154,6 +157,8 @@ typedef struct {
     int64_t   n_build_null;           /* rows whose build side is NULL                                */
     int64_t   n_probe_null;
     void     *_owner;                 /* private                                                      */
+    int32_t   build_idx_width;        /* 8 (uint64_t, the default) or 4 (B200J_OUT_BUILD_U32)          */
+    int32_t   _pad;
 } b200j_result;
 
 /* Gathered output column (Arrow layout), produced by b200j_gather. */
@@ -203,6 +208,7 @@ typedef struct {
                                          row-id array is the result's probe-index column)               */
     int64_t  compact_launches;        /* dense results with misses compacted afterwards (Inner / Left)  */
     double   ms_exchange_partition;   /* b200j_shuffle_count + b200j_shuffle_scatter kernels             */
+    int64_t  seg_probe_launches;      /* dense probe launches over the block-locally partitioned stream (probe_dense_seg_kernel) */
 } b200j_stats;
 
 /* ---- lifecycle ------------------------------------------------------------------------------- */

@@ -281,3 +281,60 @@ def test_apply_pairs_rejects_out_of_range_indices(pkg):
             assert r.n >= 2
             r.release()
             j.trim()
+
+
+@pytest.mark.parametrize("join_type", ["inner", "left", "right", "full", "left_anti", "right_semi"])
+@pytest.mark.parametrize("layout,radix_bits", [("direct", 0), ("radix", 4)])
+def test_build_indices_as_u32(pkg, monkeypatch, join_type, layout, radix_bits):
+    """B200J_OUT_BUILD_U32: same pairs with 32-bit build indices (NULL side = UINT32_MAX), from the device-result path, the
+    host-result path, the pipelined host path (many ragged chunks) and the finaliser; the gather accepts them as they are."""
+    import torch
+    monkeypatch.setenv("B200J_HOST_CHUNK_ROWS", "4099")
+    rng = np.random.default_rng(hash((join_type, layout, "u32")) & 0xFFFFFFFF)
+    for unique in (True, False):
+        nb = 30_000
+        bk = (rng.permutation(nb * 2)[:nb] if unique else rng.integers(0, nb // 3, nb)).astype(np.int64)
+        pk = rng.integers(-100, nb * 2 + 100, 50_001).astype(np.int64)
+        bpay = rng.integers(0, 1 << 40, nb).astype(np.int64)
+        oj = oracle.OracleJoin(join_type, [bk])
+        want = oj.probe_batch([pk], len(pk))
+        want_fin = oj.finish()
+        wb, wp = want
+        with pkg.HashJoin(join_type, key_widths=(8,), build_payload_types=(8,), layout=layout, radix_bits=radix_bits) as j:
+            j.build_push(0, [bk], [bpay])
+            j.build_finish(0)
+            flags = pkg.OUT_PAIRS | pkg.OUT_BUILD_U32
+            # host keys -> pinned host pairs through the pipelined path
+            r = j.probe_batch(0, [pk], want=flags | pkg.OUT_HOST | pkg.OUT_MATCHES_ONLY)
+            assert r.build_idx_width == 4 or r.n == 0
+            hb, hp_ = r.numpy()                                           # widened by the veneer
+            r.release()
+            mb, mp = oracle.OracleJoin("inner", [bk]).probe_batch([pk], len(pk))      # matches only = the inner join's pairs
+            o1, o2 = np.lexsort((hb, hp_)), np.lexsort((mb, mp))
+            assert np.array_equal(hb[o1], mb[o2]) and np.array_equal(hp_[o1], mp[o2])
+            dpk = torch.from_numpy(pk).cuda()
+            r = j.probe_batch(0, [dpk], want=flags)                      # device keys -> device pairs
+            assert r.mem == pkg.MEM_DEVICE
+            b_, p_ = r.device_arrays()
+            if r.n and b_ is not None:
+                assert r.build_idx_width == 4
+                gb = torch.as_tensor(b_, device="cuda").cpu().numpy().view(np.uint32)
+                gp = torch.as_tensor(p_, device="cuda").cpu().numpy().view(np.uint32)
+                gb64 = np.where(gb == np.uint32(0xFFFFFFFF), np.uint64(0xFFFFFFFFFFFFFFFF), gb.astype(np.uint64))
+                o1, o2 = np.lexsort((gb64, gp)), np.lexsort((wb, wp))
+                assert np.array_equal(gb64[o1], wb[o2]) and np.array_equal(gp[o1], wp[o2])
+                if join_type in ("inner", "left", "right", "full"):
+                    g = j.gather(r, [dpk], want=pkg.OUT_HOST)            # u32 build indices straight into the gather
+                    cols = g.to_arrow([pa.int64(), pa.int64(), pa.int64()])
+                    gk, gpay, gpk = (c.to_numpy(zero_copy_only=False) for c in cols)
+                    g.release()
+                    m = gb != np.uint32(0xFFFFFFFF)
+                    assert np.array_equal(gk[m].astype(np.int64), bk[gb[m].astype(np.int64)])
+                    assert np.array_equal(gpay[m].astype(np.int64), bpay[gb[m].astype(np.int64)])
+                    assert np.array_equal(gpk.astype(np.int64), pk[gp.astype(np.int64)])
+            r.release()
+            r = j.probe_finish(0, want=flags | pkg.OUT_HOST)
+            fb, fp = r.numpy()
+            r.release()
+        o1, o2 = np.lexsort((fb, fp)), np.lexsort(want_fin)
+        assert np.array_equal(fb[o1], want_fin[0][o2])
