@@ -215,7 +215,7 @@ def run_reference(args):
 
 def workload_config(args, n_gpus):
     return {"workload": f"C2: {args.build_rows}-row int64 unique-key build x {args.probe_rows}-row uniform probe, 1:1 matches, "
-                        f"inner join, (build_idx u64, probe_idx u32) pairs out" + (f"; per GPU, {n_gpus} GPUs, key space x{n_gpus}, "
+                        f"{'one int64 build payload column, ' if n_gpus == 1 else ''}inner join, (build_idx u64, probe_idx u32) pairs out" + (f"; per GPU, {n_gpus} GPUs, key space x{n_gpus}, "
                         "hash-partition + NVLink exchange of both sides" if n_gpus > 1 else ""),
             "build_rows_per_gpu": args.build_rows, "probe_rows_per_gpu": args.probe_rows,
             "probe_chunk_rows": args.chunk_rows if (n_gpus == 1 or args.exchange_chunk_rows <= 0) else min(args.chunk_rows, args.exchange_chunk_rows),
@@ -267,13 +267,18 @@ def run_b200(args):
         join = DistributedJoin("inner", key_width=8, stream=stream, layout=args.layout, radix_bits=args.radix_bits,
                                load_factor=args.load_factor, expected_build_rows=int(n_build * 1.1), mode=args.shuffle, timing=True)
     else:
-        join = d.HashJoin("inner", key_widths=(8,), layout=args.layout, radix_bits=args.radix_bits, load_factor=args.load_factor,
-                          expected_build_rows=n_build, stream=stream.cuda_stream, timing=True)
+        # the build side carries one int64 payload column (here: the row number, so the gather can be checked)
+        join = d.HashJoin("inner", key_widths=(8,), build_payload_types=(8,), layout=args.layout, radix_bits=args.radix_bits,
+                          load_factor=args.load_factor, expected_build_rows=n_build, stream=stream.cuda_stream, timing=True)
+    bpay = torch.arange(n_build, device=dev, dtype=torch.int64) if world == 1 else None
 
     def step_device():
         """one whole join, inputs resident in HBM; returns matched rows"""
         join.reset()
-        join.build_push(0, [bk])
+        if world == 1:
+            join.build_push(0, [bk], [bpay])
+        else:
+            join.build_push(0, [bk])
         join.build_finish(0)
         tot = 0
         if world > 1 and args.exchange_chunk_rows > 0:
@@ -376,6 +381,11 @@ def run_b200(args):
     }
     gpu_launches = int(st["kernel_launches"])
 
+    # ---- output gather (a6, take_multiple_record_batch) as its own phase: build key + build payload at build_idx, probe key at
+    #      probe_idx, device to device, for the whole C2 result ("reported as its own phase")
+    if world == 1 and not args.no_gather:
+        phases["gather"] = run_gather_phase(args, d, torch, dev, join, bk, bpay, pk, hbm_gbs)
+
     # ---- e2e: host buffers through the public API
     e2e = None
     if not args.no_e2e:
@@ -410,7 +420,7 @@ def verify_single(args, d, torch, dev, join, bk, pk):
     probe row appears exactly once (1:1 workload), the pair count is the probe row count."""
     n_build, n_probe, chunk = args.build_rows, args.probe_rows, args.chunk_rows
     join.reset()
-    join.build_push(0, [bk])
+    join.build_push(0, [bk], [torch.arange(n_build, device=dev, dtype=torch.int64)])
     join.build_finish(0)
     total, S = 0, 1 << 27
     for lo in range(0, n_probe, chunk):
@@ -476,6 +486,40 @@ def verify_distributed(args, d, torch, dist, dev, join, bk, pk, rank, world):
                                                           "build_key[build_idx] == probe_key[probe_idx] (2^24 sample per rank)"]}
 
 
+def run_gather_phase(args, d, torch, dev, join, bk, bpay, pk, hbm_gbs):
+    import ctypes as C
+    n_build, n_probe = args.build_rows, args.probe_rows
+    m = min(n_probe, args.chunk_rows)
+    join.reset()
+    join.build_push(0, [bk], [bpay])
+    join.build_finish(0)
+    r = join.probe_batch(0, [pk[:m]], want=d.OUT_PAIRS)
+    times = []
+    ok = None
+    for rep in range(3):
+        st0 = join.stats()["ms_gather"]
+        g = join.gather(r, [pk[:m]], want=0)                     # device in, device out
+        times.append(join.stats()["ms_gather"] - st0)
+        if rep == 0:
+            cols = [g.column_buffers(i) for i in range(g.n_cols)]
+            S = min(g.n_rows, 1 << 26)
+            from datafusion_parallelism_b200.exchange import _RawCudaArray
+            gbk, gbp, gpk = (torch.as_tensor(_RawCudaArray(c["values"], S, "<i8"), device=dev) for c in cols[:3])
+            b_, p_ = r.device_arrays()
+            tb = torch.as_tensor(b_, device=dev)[:S]
+            tp = torch.as_tensor(p_, device=dev)[:S].long() & 0xFFFFFFFF
+            ok = bool(torch.equal(gbk, gpk)) and bool(torch.equal(gbp, tb)) and bool(torch.equal(gpk, pk[:m][tp])) and g.n_rows == r.n
+            del gbk, gbp, gpk, tb, tp
+        g.release()
+    n_out = r.n
+    r.release()
+    ms = min(times)
+    bytes_per_row = 12 + 3 * 8 + 3 * 8          # index pair read + three 8-byte columns read + written
+    return {"ms": ms, "ms_all": times, "rows": n_out, "columns": "build key i64 + build payload i64 (random reads at build_idx) + probe key i64 (at probe_idx)",
+            "bytes_per_row": bytes_per_row, "rows_per_s": n_out / (ms * 1e-3), "gather_roofline_frac": n_out * bytes_per_row / (ms * 1e-3) / 1e9 / hbm_gbs,
+            "verified": ok}
+
+
 def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
     """Same join through host buffers: pinned Arrow key buffers in, pinned index pairs out, every step."""
     import numpy as np
@@ -488,6 +532,10 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
         avail = 64 << 30
     hb = d.PinnedArray(n_build, np.int64)
     hp = d.PinnedArray(n_probe, np.int64)
+    hpay = None
+    if world == 1:
+        hpay = d.PinnedArray(n_build, np.int64)              # the build side's payload column crosses PCIe as well
+        hpay.array[:] = np.arange(n_build, dtype=np.int64)
     torch.from_numpy(hb.array).copy_(bk)
     torch.from_numpy(hp.array).copy_(pk)
     torch.cuda.synchronize()
@@ -516,7 +564,7 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
             for r in join.probe_host_chunks(0, hp.array, chunk_rows=host_chunk, want=d.OUT_PAIRS):
                 tot += r.n
             return tot
-        join.build_push(0, [hb.array])
+        join.build_push(0, [hb.array], [hpay.array])
         join.build_finish(0)
         for lo in range(0, n_probe, chunk):
             r = join.probe_batch(0, [hp.array[lo:lo + chunk]], want=d.OUT_PAIRS | d.OUT_HOST | out_flags)
@@ -541,7 +589,9 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
         dt = float(t.item())
     hb.free()
     hp.free()
-    return {"value": (n_build + n_probe) * world / (dt / steps), "unit": UNIT, "h2d_bytes_per_step": 8 * (n_build + n_probe),
+    if hpay is not None:
+        hpay.free()
+    return {"value": (n_build + n_probe) * world / (dt / steps), "unit": UNIT, "h2d_bytes_per_step": 8 * (n_build + n_probe) + (8 * n_build if world == 1 else 0),
             "d2h_bytes_per_step": pair_bytes * tot, "pair_format": "(u64 build_idx, u32 probe_idx)" if pair_bytes == 12 else "(u32 build_idx, u32 probe_idx) [B200J_OUT_BUILD_U32]", "steps": steps, "ms_per_step": dt / steps * 1e3, "ms_steps_rank0": ms_steps,
             "api": ("HashJoin.build_push/probe_batch(host numpy over b200j_host_alloc pinned buffers, OUT_PAIRS|OUT_HOST" + ("|OUT_BUILD_U32" if pair_bytes == 8 else "") + ") -> b200j_* C ABI" if world == 1 else
                     f"DistributedJoin.build_push_host/probe_host_chunks(pinned numpy in, pinned pairs out, {host_chunk}-row chunks) -> b200j_* C ABI")}

@@ -57,6 +57,89 @@ __global__ void __launch_bounds__(256) gather_fixed_kernel(GatherSrc src, const 
     if (lane == 0 && z) atomicAdd(null_count, z);
 }
 
+// All fixed-width columns of one side in ONE launch (round 2). A warp takes 128 consecutive output rows, lane l the rows
+// l, l + 32, l + 64, l + 96 of them: the index loads and every column's stores are lane-contiguous, a ballot per item IS the
+// output validity word, and each thread has 4 independent random reads per column in flight (the gather is bound by the
+// latency and sector traffic of those reads: 32 B moved per value). The index array is read once for all columns.
+constexpr int GF_MAX_COLS = 8;
+constexpr int GF_ITEMS = 4;
+struct GatherCol {
+    const void    *values;       // null: the side has no rows / the finaliser's NULL probe side
+    const uint8_t *validity;
+    int64_t        bit_offset;
+    void          *dst;
+    uint32_t      *dst_valid;
+    int32_t        width;        // 1, 2, 4, 8, 16
+    int32_t        _pad;
+};
+struct GatherCols {
+    GatherCol c[GF_MAX_COLS];
+    int32_t   n;
+    int32_t   _pad;
+};
+
+template <typename T>
+__device__ __forceinline__ void gather_items(const GatherCol &gc, const int64_t (&j)[GF_ITEMS], const bool (&have)[GF_ITEMS], int64_t row0, int lane,
+                                             int64_t n, uint32_t &nulls) {
+    T v[GF_ITEMS];
+    bool valid[GF_ITEMS];
+#pragma unroll
+    for (int q = 0; q < GF_ITEMS; q++) {
+        valid[q] = have[q] && gc.values != nullptr && bit_valid(gc.validity, gc.bit_offset + j[q]);
+        v[q] = T{};
+        if (valid[q]) v[q] = reinterpret_cast<const T *>(gc.values)[j[q]];
+    }
+#pragma unroll
+    for (int q = 0; q < GF_ITEMS; q++) {
+        const int64_t i = row0 + q * 32 + lane;
+        if (i < n) {
+            reinterpret_cast<T *>(gc.dst)[i] = v[q];
+            if (!valid[q]) nulls++;
+        }
+        const uint32_t word = __ballot_sync(0xffffffffu, valid[q]);
+        if (lane == 0 && row0 + q * 32 < n) gc.dst_valid[(row0 + q * 32) >> 5] = word;
+    }
+}
+
+template <typename IdxT>
+__global__ void __launch_bounds__(256) gather_fixed_multi_kernel(GatherCols cols, const IdxT *__restrict__ idx, int64_t n,
+                                                                 unsigned long long *null_counts /* [cols.n] */) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    uint32_t nulls[GF_MAX_COLS];
+#pragma unroll
+    for (int c = 0; c < GF_MAX_COLS; c++) nulls[c] = 0;
+    for (int64_t row0 = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (32 * GF_ITEMS); row0 < n; row0 += warps * (32 * GF_ITEMS)) {
+        int64_t j[GF_ITEMS];
+        bool have[GF_ITEMS];
+#pragma unroll
+        for (int q = 0; q < GF_ITEMS; q++) {
+            const int64_t i = row0 + q * 32 + lane;
+            const IdxT x = (idx != nullptr && i < n) ? __ldcs(idx + i) : (IdxT)~(IdxT)0;
+            have[q] = !idx_is_null(x);
+            j[q] = have[q] ? (int64_t)x : 0;
+        }
+#pragma unroll
+        for (int c = 0; c < GF_MAX_COLS; c++) {
+            if (c >= cols.n) break;
+            const GatherCol &gc = cols.c[c];
+            switch (gc.width) {
+                case 1: gather_items<uint8_t>(gc, j, have, row0, lane, n, nulls[c]); break;
+                case 2: gather_items<uint16_t>(gc, j, have, row0, lane, n, nulls[c]); break;
+                case 4: gather_items<uint32_t>(gc, j, have, row0, lane, n, nulls[c]); break;
+                case 8: gather_items<unsigned long long>(gc, j, have, row0, lane, n, nulls[c]); break;
+                default: gather_items<ulonglong2>(gc, j, have, row0, lane, n, nulls[c]); break;
+            }
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < GF_MAX_COLS; c++) {
+        if (c >= cols.n) break;
+        const unsigned long long z = warp_sum_u32(nulls[c]);
+        if (lane == 0 && z) atomicAdd(null_counts + c, z);
+    }
+}
+
 __device__ __forceinline__ int64_t utf8_off(const GatherSrc &s, int64_t j) {
     return s.offsets64 ? reinterpret_cast<const int64_t *>(s.offsets)[j] : (int64_t)reinterpret_cast<const int32_t *>(s.offsets)[j];
 }

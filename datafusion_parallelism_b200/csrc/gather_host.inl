@@ -17,6 +17,7 @@ struct GatherCtx {
     std::vector<void *> temps;
     GatheredOwner *own;
     unsigned long long *d_nulls;       // device counter per column (array)
+    unsigned long long *d_nulls_scratch;   // GF_MAX_COLS counters of the multi-column launch in flight
 };
 
 void *gather_dev_alloc(GatherCtx &g, size_t bytes) {
@@ -93,6 +94,59 @@ void gather_one_column(GatherCtx &g, int col, int type, const GatherSrc &src, co
     }
 }
 
+// All columns of one side: the fixed-width ones go through gather_fixed_multi_kernel, up to GF_MAX_COLS per launch (the
+// index array is read once per launch, not once per column); Utf8 columns take the three-pass path above.
+struct SideCol {
+    int type;
+    GatherSrc src;
+};
+template <typename IdxT>
+void gather_side(GatherCtx &g, int first_col, const std::vector<SideCol> &sc, const IdxT *idx) {
+    H *h = g.h;
+    const int64_t n = g.n;
+    GatherCols batch{};
+    int batch_cols[GF_MAX_COLS];
+    auto flush = [&]() {
+        if (batch.n == 0) return;
+        if (n > 0) {
+            // the kernel's null counters are indexed by position in the batch: count into a scratch row, add up afterwards
+            const int grid = grid_for(h, (n + 127) / 128, 8, 8);
+            gather_fixed_multi_kernel<IdxT><<<grid, 256, 0, h->stream>>>(batch, idx, n, g.d_nulls_scratch);
+            h->st.kernel_launches++;
+            CU(cudaGetLastError());
+            for (int k = 0; k < batch.n; k++)
+                CU(cudaMemcpyAsync(g.d_nulls + batch_cols[k], g.d_nulls_scratch + k, 8, cudaMemcpyDeviceToDevice, h->stream));
+            CU(cudaMemsetAsync(g.d_nulls_scratch, 0, GF_MAX_COLS * 8, h->stream));
+        }
+        batch = GatherCols{};
+    };
+    for (size_t k = 0; k < sc.size(); k++) {
+        const int col = first_col + (int)k;
+        if (sc[k].type == B200J_T_UTF8) {
+            gather_one_column<IdxT>(g, col, sc[k].type, sc[k].src, idx);
+            continue;
+        }
+        b200j_out_column &oc = g.own->cols[col];
+        oc = b200j_out_column{};
+        const size_t vwords = (size_t)((n + 31) / 32 + 4);
+        uint32_t *dvalid = (uint32_t *)gather_dev_alloc(g, vwords * 4);
+        oc.validity = (uint8_t *)dvalid;
+        void *dst = gather_dev_alloc(g, (size_t)n * sc[k].type + 16);
+        oc.values = dst;
+        oc.values_bytes = n * sc[k].type;
+        GatherCol &gc = batch.c[batch.n];
+        gc.values = sc[k].src.values;
+        gc.validity = sc[k].src.validity;
+        gc.bit_offset = sc[k].src.bit_offset;
+        gc.dst = dst;
+        gc.dst_valid = dvalid;
+        gc.width = sc[k].type;
+        batch_cols[batch.n] = col;
+        if (++batch.n == GF_MAX_COLS) flush();
+    }
+    flush();
+}
+
 // stages one column of a (host or device) batch; returns the device-side source descriptor
 GatherSrc gather_stage_column(GatherCtx &g, const b200j_column &c, int type, int64_t n_rows, int mem) {
     H *h = g.h;
@@ -140,7 +194,7 @@ void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, 
     }
     const int64_t n = pairs->n;
     GatheredOwner *own = new GatheredOwner();
-    GatherCtx g{h, n, nullptr, nullptr, {}, own, nullptr};
+    GatherCtx g{h, n, nullptr, nullptr, {}, own, nullptr, nullptr};
     try {
         const int n_cols = (want_build ? nk + nbp : 0) + (want_probe ? nk + npp : 0);
         own->cols.resize(std::max(n_cols, 1));
@@ -157,13 +211,15 @@ void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, 
         g.bidx = (const uint64_t *)stage_idx(pairs->build_idx, (size_t)bwidth);
         g.pidx = (const uint32_t *)stage_idx(pairs->probe_idx, 4);
         void *dn = nullptr;
-        CU(big_alloc(h, &dn, (size_t)(n_cols + 1) * 8)); g.temps.push_back(dn);
-        CU(cudaMemsetAsync(dn, 0, (size_t)(n_cols + 1) * 8, h->stream));
+        CU(big_alloc(h, &dn, (size_t)(n_cols + 1 + GF_MAX_COLS) * 8)); g.temps.push_back(dn);
+        CU(cudaMemsetAsync(dn, 0, (size_t)(n_cols + 1 + GF_MAX_COLS) * 8, h->stream));
         g.d_nulls = (unsigned long long *)dn;
+        g.d_nulls_scratch = g.d_nulls + n_cols + 1;
         PhaseTimer tm(h, &h->st.ms_gather);
         int col = 0;
         if (want_build) {
-            for (int i = 0; i < nk + nbp; i++, col++) {
+            std::vector<SideCol> sc;
+            for (int i = 0; i < nk + nbp; i++) {
                 const ColStore &cs = i < nk ? h->bkeys[i] : h->bpayload[i - nk];
                 GatherSrc s{};
                 s.values = cs.values.p;
@@ -171,18 +227,24 @@ void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, 
                 s.offsets64 = 1;
                 s.validity = cs.has_nulls ? (const uint8_t *)cs.validity.p : nullptr;
                 if (h->n_build == 0) s.values = s.offsets = nullptr;
-                if (bwidth == 4) gather_one_column<uint32_t>(g, col, cs.type, s, reinterpret_cast<const uint32_t *>(g.bidx));     // B200J_OUT_BUILD_U32 pairs
-                else gather_one_column<uint64_t>(g, col, cs.type, s, g.bidx);
+                sc.push_back(SideCol{cs.type, s});
             }
+            if (bwidth == 4) gather_side<uint32_t>(g, col, sc, reinterpret_cast<const uint32_t *>(g.bidx));     // B200J_OUT_BUILD_U32 pairs
+            else gather_side<uint64_t>(g, col, sc, g.bidx);
+            col += nk + nbp;
         }
         if (want_probe) {
-            for (int i = 0; i < nk + npp; i++, col++) {
+            std::vector<SideCol> sc;
+            const bool have_probe = probe_batch && probe_batch->n_rows > 0;
+            for (int i = 0; i < nk + npp; i++) {
                 const int type = i < nk ? h->key_widths[i] : h->probe_payload_types[i - nk];
                 GatherSrc s{};
-                if (probe_batch && probe_batch->n_rows > 0)
+                if (have_probe)
                     s = gather_stage_column(g, i < nk ? probe_batch->keys[i] : probe_batch->payload[i - nk], type, probe_batch->n_rows, probe_batch->mem);
-                gather_one_column<uint32_t>(g, col, type, s, (probe_batch && probe_batch->n_rows > 0) ? g.pidx : nullptr);
+                sc.push_back(SideCol{type, s});
             }
+            gather_side<uint32_t>(g, col, sc, have_probe ? g.pidx : nullptr);
+            col += nk + npp;
         }
         tm.stop();
         // null counts; a column without nulls drops its validity buffer pointer (Arrow: NULL bitmap = no nulls)
