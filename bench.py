@@ -63,11 +63,12 @@ def parse_args():
     ap.add_argument("--cpu-probe-sample", type=int, default=250_000_000)
     ap.add_argument("--stock-scale", type=int, default=10, help="the Acero (stock HashJoinExec stand-in) baseline joins 1/this of the workload")
     ap.add_argument("--no-verify", action="store_true")
+    ap.add_argument("--overlap-build", type=int, default=0, help="N>1: 1 = exchange the probe side while the local table is built")
     ap.add_argument("--e2e-wide", action="store_true", help="e2e returns (u64, u32) pairs instead of B200J_OUT_BUILD_U32's (u32, u32)")
     ap.add_argument("--no-gather", action="store_true")
     ap.add_argument("--host-chunk-rows", type=int, default=1 << 27, help="N>1 e2e: probe rows per pipelined host chunk (DistributedJoin.probe_host_chunks)")
     ap.add_argument("--exchange-chunk-rows", type=int, default=0, help="N>1: > 0 = probe rows per exchange / local-join pipeline stage (DistributedJoin.probe_chunks)")
-    ap.add_argument("--shuffle", default="p2p", choices=["p2p", "nccl"], help="N>1: fused peer-store scatter or NCCL all-to-all")
+    ap.add_argument("--shuffle", default="p2p", choices=["p2p", "nccl", "ce", "pull"], help="N>1: fused peer-store scatter, NCCL all-to-all, or single-pass local scatter + copy-engine transfers")
     return ap.parse_args()
 
 
@@ -279,6 +280,14 @@ def run_b200(args):
             join.build_push(0, [bk], [bpay])
         else:
             join.build_push(0, [bk])
+        if world > 1 and args.overlap_build and args.exchange_chunk_rows <= 0 and chunk >= n_probe:
+            # the probe side crosses NVLink while the local table is being built
+            token = join.probe_exchange_begin([pk])
+            join.build_finish(0)
+            r = join.probe_batch_received(0, token, want=d.OUT_PAIRS)
+            tot = r.n
+            r.release()
+            return tot
         join.build_finish(0)
         tot = 0
         if world > 1 and args.exchange_chunk_rows > 0:
@@ -341,6 +350,8 @@ def run_b200(args):
     for k in ("ms_exchange_build", "ms_exchange_probe"):
         if k in st:
             ph[k] = st[k] / K
+    if world > 1:
+        ph["ms_exchange_kernels"] = st["ms_exchange_partition"] / K       # the partition / scatter kernels inside the two exchange phases
     build_ms = ph["ms_build_copy"] + ph["ms_build_partition"] + ph["ms_build_insert"]
     probe_ms = ph["ms_probe_partition"] + ph["ms_probe"]
     radix = st["layout"] == 2
@@ -458,9 +469,9 @@ def verify_distributed(args, d, torch, dist, dev, join, bk, pk, rank, world):
     r = join.probe_batch(0, [pk], want=d.OUT_PAIRS)
     n_recv_b = int(join.build.plan.recv_rows[rank])
     n_recv_p = int(join.probe.plan.recv_rows[rank])
-    kdt = "<i8"
-    rb = torch.as_tensor(_RawCudaArray(join.build.recv_keys_ptr, n_recv_b, kdt), device=dev)
-    rp = torch.as_tensor(_RawCudaArray(join.probe.recv_keys_ptr, n_recv_p, kdt), device=dev)
+    rb = join.received(join.build, "keys")          # local copies of what this rank received (one piece per source in mode "pull")
+    rp = join.received(join.probe, "keys")
+    assert rb.shape[0] == n_recv_b and rp.shape[0] == n_recv_p
     t = torch.tensor([r.n, n_recv_b, n_recv_p, int(bk.sum()), int(rb.sum()), int(pk.sum()), int(rp.sum())], device=dev, dtype=torch.int64)
     dist.all_reduce(t)          # int64 sums wrap: a checksum of checksums
     tot, nb_, np_, sb, srb, sp, srp = [int(x) for x in t.tolist()]

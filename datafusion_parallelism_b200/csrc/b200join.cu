@@ -77,6 +77,9 @@ struct ColStore {          // one column of the concatenated build side (JoinSta
     int64_t data_bytes = 0;
 };
 
+// b200j_result grew at its end (build_idx_width): callers built against the first layout stay valid
+constexpr size_t RESULT_V1_SIZE = offsetof(b200j_result, build_idx_width);
+
 struct ResultOwner {
     void *build_idx = nullptr;
     void *probe_idx = nullptr;
@@ -120,6 +123,8 @@ struct b200j_handle {
     bool block_part_ok = true;         // B200J_NO_BLOCK_PART=1: the dense radix probe keeps the two-pass global partition of round 1
     int pb_clusters[2][PB_MAX_BITS + 1] = {};   // resident clusters of part_block_kernel per key width / radix bits (0 = not asked yet)
     unsigned long long *d_part_rows = nullptr, *h_part_rows = nullptr;   // rows per partition of the last block-partitioned batch
+    uint32_t *d_reserve = nullptr;     // region cursors of b200j_shuffle_local_scatter
+    cudaStream_t lanes[4] = {nullptr, nullptr, nullptr, nullptr};        // copy lanes of b200j_copy_async
     bool dense_ok = true;              // B200J_NO_DENSE=1 forces the staged probe kernel (tuning / tests)
     uint64_t l1_table_bytes = 512 << 10; // direct tables up to this size are probed through L1 (B200J_L1_TABLE_BYTES)
     float thin_lf_min = 0.2f;          // lowest load factor the auto-thinning of small direct tables goes to (B200J_THIN_LF_MIN; 0.5 = off)
@@ -192,6 +197,8 @@ void radix_partition(H *h, const void *keys, const uint8_t *validity, int64_t bi
                      void *out_keys, uint32_t *out_rid, double *ms_acc);
 void radix_release(H *h);
 struct ProbePlan;
+struct ProbePiece;
+int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces, const ProbePlan &pl, ResultOwner *ro, int64_t *n_build_null);
 int64_t probe_dense_blocked(H *h, const void *d_keys, const uint8_t *d_validity, int64_t bit_offset, int64_t n, const ProbePlan &pl,
                             ResultOwner *ro, int64_t *n_build_null);
 void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, uint32_t want, b200j_gathered *out);
@@ -1327,7 +1334,7 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
     REQUIRE(!h->probe_done[partition], B200J_ERR_STATE, "probe_batch after probe_finish");
     // the pending scatter's offsets live in the handle's partition scratch, which a radix probe would overwrite
     REQUIRE(!h->shuffle_armed, B200J_ERR_STATE, "probe_batch between b200j_shuffle_count and b200j_shuffle_scatter");
-    REQUIRE(out != nullptr && out->struct_size >= sizeof(b200j_result), B200J_ERR_INVALID, "result struct missing or too small");
+    REQUIRE(out != nullptr && out->struct_size >= RESULT_V1_SIZE, B200J_ERR_INVALID, "result struct missing or too small");
     check_batch(h, b, h->cfg.n_probe_payload);
     REQUIRE(b->n_rows < 0xffff0000LL, B200J_ERR_UNSUPPORTED, "probe batch of more than 2^32 - 2^16 rows (probe indices are UInt32)");
     if (h->composite) {
@@ -1379,6 +1386,9 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
     }
 }
 
+void do_probe_pieces(H *h, int32_t partition, int32_t n_pieces, const void *const *piece_keys, const int64_t *piece_rows, uint32_t want,
+                     b200j_result *out);
+
 // bitmap -> indices on the device; returns count. out64/out32: which side receives the indices.
 int64_t select_bits(H *h, const uint32_t *bm, int64_t n, bool want_set, void **out64, void **out32) {
     if (out64) *out64 = nullptr;
@@ -1423,7 +1433,7 @@ void do_probe_finish(H *h, int32_t partition, uint32_t want, b200j_result *out) 
     REQUIRE(partition >= 0 && partition < h->cfg.n_partitions, B200J_ERR_INVALID, "partition out of range");
     REQUIRE(h->built, B200J_ERR_INVALID, "probe_finish before the build side finished");
     REQUIRE(!h->probe_done[partition], B200J_ERR_STATE, "State already consumed: probe_finish called twice for this partition");
-    REQUIRE(out != nullptr && out->struct_size >= sizeof(b200j_result), B200J_ERR_INVALID, "result struct missing or too small");
+    REQUIRE(out != nullptr && out->struct_size >= RESULT_V1_SIZE, B200J_ERR_INVALID, "result struct missing or too small");
     h->probe_done[partition] = 1;
     h->n_probe_done++;
     ResultOwner *ro = new ResultOwner();
@@ -1460,7 +1470,7 @@ void do_apply_pairs(H *h, int32_t partition, int64_t n_probe_rows, int32_t mem, 
                     const uint32_t *probe_idx, uint32_t want, b200j_result *out) {
     REQUIRE(partition >= 0 && partition < h->cfg.n_partitions, B200J_ERR_INVALID, "partition out of range");
     REQUIRE(h->built, B200J_ERR_INVALID, "apply_pairs before the build side finished");
-    REQUIRE(out != nullptr && out->struct_size >= sizeof(b200j_result), B200J_ERR_INVALID, "result struct missing or too small");
+    REQUIRE(out != nullptr && out->struct_size >= RESULT_V1_SIZE, B200J_ERR_INVALID, "result struct missing or too small");
     REQUIRE(n_pairs >= 0 && n_probe_rows >= 0 && n_probe_rows < 0xffffffffLL, B200J_ERR_INVALID, "bad pair / row counts");
     REQUIRE(n_pairs == 0 || (build_idx && probe_idx), B200J_ERR_INVALID, "pair arrays missing");
     const int jt = h->cfg.join_type;
@@ -1573,6 +1583,8 @@ void do_hash_keys(H *h, const b200j_batch *b, uint64_t *out) {
 void do_shuffle_count(H *h, const b200j_batch *b, int32_t n_dest, int64_t *counts);
 void do_shuffle_set_hot(H *h, const uint64_t *keys, int32_t n);
 void do_shuffle_scatter(H *h, int32_t n_dest, void *const *dest_keys, uint32_t *const *dest_rowid, const int64_t *dest_offset, uint32_t rowid_base);
+void do_shuffle_local_scatter(H *h, const b200j_batch *b, int32_t n_dest, void *send_keys, uint32_t *send_rowid, int64_t region_rows,
+                              uint32_t rowid_base, int64_t *counts);
 
 template <typename F>
 int32_t guarded(b200j_handle *h, F &&f) {
@@ -1765,6 +1777,9 @@ int32_t b200j_destroy(b200j_handle *h) {
     if (h->d_ctr) cudaFree(h->d_ctr);
     if (h->h_ctr) cudaFreeHost(h->h_ctr);
     if (h->d_part_rows) cudaFree(h->d_part_rows);
+    if (h->d_reserve) cudaFree(h->d_reserve);
+    for (int i = 0; i < 4; i++)
+        if (h->lanes[i]) cudaStreamDestroy(h->lanes[i]);
     if (h->h_part_rows) cudaFreeHost(h->h_part_rows);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -1831,6 +1846,10 @@ int32_t b200j_build_finish(b200j_handle *h, int32_t partition) {
 int32_t b200j_probe_batch(b200j_handle *h, int32_t partition, const b200j_batch *batch, uint32_t want, b200j_result *out) {
     return guarded(h, [&] { do_probe_batch(h, partition, batch, want, out); });
 }
+int32_t b200j_probe_pieces(b200j_handle *h, int32_t partition, int32_t n_pieces, const void *const *piece_keys, const int64_t *piece_rows,
+                           uint32_t want, b200j_result *out) {
+    return guarded(h, [&] { do_probe_pieces(h, partition, n_pieces, piece_keys, piece_rows, want, out); });
+}
 int32_t b200j_apply_pairs(b200j_handle *h, int32_t partition, int64_t n_probe_rows, int32_t mem, int64_t n_pairs,
                           const uint64_t *build_idx, const uint32_t *probe_idx, uint32_t want, b200j_result *out) {
     return guarded(h, [&] { do_apply_pairs(h, partition, n_probe_rows, mem, n_pairs, build_idx, probe_idx, want, out); });
@@ -1867,6 +1886,30 @@ int32_t b200j_shuffle_set_hot(b200j_handle *h, const uint64_t *keys, int32_t n) 
 int32_t b200j_shuffle_scatter(b200j_handle *h, int32_t n_dest, void *const *dest_keys, uint32_t *const *dest_rowid, const int64_t *dest_offset,
                               uint32_t rowid_base) {
     return guarded(h, [&] { do_shuffle_scatter(h, n_dest, dest_keys, dest_rowid, dest_offset, rowid_base); });
+}
+int32_t b200j_shuffle_local_scatter(b200j_handle *h, const b200j_batch *batch, int32_t n_dest, void *send_keys, uint32_t *send_rowid,
+                                    int64_t region_rows, uint32_t rowid_base, int64_t *counts) {
+    return guarded(h, [&] { do_shuffle_local_scatter(h, batch, n_dest, send_keys, send_rowid, region_rows, rowid_base, counts); });
+}
+int32_t b200j_copy_async(b200j_handle *h, void *dst, const void *src, size_t bytes, int32_t lane) {
+    return guarded(h, [&] {
+        REQUIRE(lane >= 0 && lane < 4, B200J_ERR_INVALID, "copy lane must be in 0..3");
+        if (bytes == 0) return;
+        REQUIRE(dst && src, B200J_ERR_INVALID, "b200j_copy_async: NULL pointer");
+        if (!h->lanes[lane]) CU(cudaStreamCreateWithFlags(&h->lanes[lane], cudaStreamNonBlocking));
+        cudaEvent_t ev = nullptr;                       // the copy starts after what the handle's stream holds now
+        CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        cudaEventRecord(ev, h->stream);
+        cudaStreamWaitEvent(h->lanes[lane], ev, 0);
+        cudaEventDestroy(ev);
+        CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, h->lanes[lane]));
+    });
+}
+int32_t b200j_copy_wait(b200j_handle *h) {
+    return guarded(h, [&] {
+        for (int i = 0; i < 4; i++)
+            if (h->lanes[i]) CU(cudaStreamSynchronize(h->lanes[i]));
+    });
 }
 int32_t b200j_ipc_alloc(b200j_handle *h, size_t bytes, void **ptr, uint8_t *handle_out) {
     return guarded(h, [&] {

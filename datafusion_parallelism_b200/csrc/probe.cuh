@@ -614,10 +614,9 @@ static_assert(SEG_UNITS >= 2 && SEG_UNITS <= 32 && (SEG_UNITS & (SEG_UNITS - 1))
 
 struct SegArgs {
     const uint32_t *seg;          // [n_blocks][P + 2]
+    const uint32_t *block_base;   // [n_blocks] first row of every block in the partitioned arrays
     uint32_t        n_blocks;
     uint32_t        n_units;      // n_blocks * P, or n_blocks * (P + 1) when the batch has NULL keys
-    uint32_t        block_rows;   // PB_BLOCK
-    uint32_t        mis;          // see pb_block_base
 };
 
 template <int KW, bool MARK, bool L1>
@@ -647,7 +646,7 @@ __global__ void __launch_bounds__(PD_THREADS, B200J_SEG_MIN_CTAS) probe_dense_se
             if (lane < SEG_UNITS && u < sg.n_units) {
                 const uint32_t p = u / sg.n_blocks, b = u - p * sg.n_blocks;
                 const uint2 e = make_uint2(__ldg(sg.seg + (size_t)b * (P + 2) + p), __ldg(sg.seg + (size_t)b * (P + 2) + p + 1));
-                my_start = (b == 0 ? 0u : b * sg.block_rows - sg.mis) + e.x;
+                my_start = __ldg(sg.block_base + b) + e.x;
                 my_len = e.y - e.x;
                 if (p < P) {
                     const uint2 pe = __ldg(reinterpret_cast<const uint2 *>(a.tv.parts + p));

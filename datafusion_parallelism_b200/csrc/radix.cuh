@@ -95,6 +95,12 @@ struct PartArgs {
     const unsigned long long *hot_keys;   // DEST mode: open-addressing set of heavy-hitter key values (0 = empty slot) or null
     uint32_t            hot_mask;         // its size - 1
     uint32_t            rid_base;         // added to the local row index (row ids of a chunked side)
+    // Single-pass mode (b200j_shuffle_local_scatter): no histogram pass. Every bin owns a region of reserve_cap rows; a tile
+    // reserves its run of a bin with ONE atomicAdd on reserve[bin] (a handful of global atomics per 8192 rows). A run that
+    // would cross the region's end is dropped and *reserve_ovf set: the caller retries with larger regions.
+    uint32_t           *reserve;          // [n_bins + 1] rows reserved so far per bin, or null (two-pass mode: cursors from cta_hist)
+    uint32_t            reserve_cap;
+    uint32_t           *reserve_ovf;
 };
 
 
@@ -324,6 +330,7 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
     __shared__ __align__(8) uint64_t s_bar[2];
     __shared__ uint32_t s_wsum[SC_THREADS / 32];
     __shared__ uint32_t s_total;
+    __shared__ uint32_t s_drop;          // bit p: this tile's run of bin p did not fit its region (single-pass mode)
     __shared__ KeyT *s_dkeys[RP_MAX_DEST + 2];
     __shared__ uint32_t *s_drid[RP_MAX_DEST + 2];
 
@@ -332,10 +339,12 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
     const uint32_t vend = a.n + mis;                                   // end of the aligned "virtual" row space
     const uint32_t n_tiles = (uint32_t)(((uint64_t)vend + SC_TILE - 1) / SC_TILE);
     const uint32_t t0 = blockIdx.x * a.tiles_per_cta, t1 = min(t0 + a.tiles_per_cta, n_tiles);
+    const bool reserve = a.reserve != nullptr;
     for (uint32_t p = t; p < P1; p += SC_THREADS) {
         s_cnt[p] = 0;
-        s_cur[p] = a.bin_base[p] + a.cta_hist[(size_t)p * gridDim.x + blockIdx.x];
+        s_cur[p] = reserve ? 0u : a.bin_base[p] + a.cta_hist[(size_t)p * gridDim.x + blockIdx.x];
     }
+    if (t == 0) s_drop = 0;
     if (DEST && t <= RP_MAX_DEST + 1) { s_dkeys[t] = reinterpret_cast<KeyT *>(a.dest_keys[t]); s_drid[t] = a.dest_rid[t]; }
     if (t == 0) { mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -399,7 +408,25 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
                     in = vrow >= mis && vrow < vend;
                     if (in && a.validity != nullptr && !bit_valid(a.validity, a.bit_offset + (int64_t)(vrow - mis))) bin = a.n_bins;
                 }
-                packed[v * PER_VEC + j] = in ? ((bin << 16) | atomicAdd(&s_cnt[bin], 1u)) : 0xffffffffu;
+                if (DEST) {
+                    // few bins (ranks + NULL + hot <= 18): a per-lane shared-memory atomic would serialise 32 lanes on a handful of
+                    // addresses (2 GPUs: 16-way). The lanes of a bin are matched with 5 ballots and ONE lane adds their number.
+                    const uint32_t mb = in ? bin : 31u;
+                    uint32_t peers = 0xffffffffu;
+#pragma unroll
+                    for (int bit = 0; bit < 5; bit++) {
+                        const bool one = (mb >> bit) & 1u;
+                        const uint32_t bl = __ballot_sync(0xffffffffu, one);
+                        peers &= one ? bl : ~bl;
+                    }
+                    const int leader = __ffs(peers) - 1;
+                    uint32_t base = 0;
+                    if (lane == leader && in) base = atomicAdd(&s_cnt[bin], (uint32_t)__popc(peers));
+                    base = __shfl_sync(0xffffffffu, base, leader);
+                    packed[v * PER_VEC + j] = in ? ((bin << 16) | (base + __popc(peers & ((1u << lane) - 1u)))) : 0xffffffffu;
+                } else {
+                    packed[v * PER_VEC + j] = in ? ((bin << 16) | atomicAdd(&s_cnt[bin], 1u)) : 0xffffffffu;
+                }
             }
         }
         __syncthreads();
@@ -426,7 +453,12 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
             __syncthreads();
             uint32_t run = s_wsum[warp] + incl - sum;
             for (uint32_t i = lo; i < hi; i++) {
-                const uint32_t c = s_cnt[i], cur = s_cur[i];
+                const uint32_t c = s_cnt[i];
+                uint32_t cur = s_cur[i];
+                if (reserve) {
+                    cur = c ? atomicAdd(a.reserve + i, c) : 0u;
+                    if (c && (cur > a.reserve_cap || c > a.reserve_cap - cur)) { atomicOr(&s_drop, 1u << (i & 31u)); atomicExch(a.reserve_ovf, 1u); }
+                }
                 s_off[i] = run;
                 s_delta[i] = cur - run;
                 s_cur[i] = cur + c;
@@ -449,6 +481,7 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
         // ---- write-out
         const uint32_t total = inner ? (uint32_t)SC_TILE : s_total;
         const uint32_t rid0 = vbase - mis + a.rid_base;
+        const uint32_t drop = s_drop;
         // unrolled by the whole tile (16 rows per thread): the shared-memory reads of all iterations are in flight before the
         // first global store. 1 B rows, 2^7 bins, histogram + scatter: unroll 2 6.78, 4 6.82, 8 6.40, 16 6.35 ms (63 -> 64
         // registers, no spills); an L2 prefetch of the next tile on top of it bought nothing (profiles/r1_l_scatter_unroll.txt)
@@ -458,6 +491,7 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
             const uint32_t p = pm >> 16, src = pm & 0xffffu;
             const uint32_t dst = s_delta[p] + i;
             if (DEST) {
+                if (drop && ((drop >> (p & 31u)) & 1u)) continue;
                 s_dkeys[p][dst] = stage[src];
                 s_drid[p][dst] = rid0 + src;
             } else {
@@ -466,6 +500,7 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
             }
         }
         __syncthreads();
+        if (reserve && t == 0) s_drop = 0;
         if (SC_NBUF == 1 && tile + 1 < t1) fetch(tile + 1, 0);
     }
 }

@@ -67,8 +67,11 @@ struct BlockPartArgs {
     void               *out_keys;
     uint32_t           *out_rid;
     uint32_t           *seg;              // [n_blocks][P + 2]: starts of bins 0 .. P (P = NULL keys) inside the block, then the block's row count
+    uint32_t           *block_base;       // [n_blocks] first output row of every block (written here, read by the probe)
     unsigned long long *part_rows;        // [P + 1] rows per partition over the whole batch (atomics, one per bin per block) or null
     uint32_t            rid_base;
+    uint32_t            out_base;         // rows of the pieces in front of this one (a batch may arrive as several pieces, e.g. one per source
+                                          // rank of the multi-GPU exchange): this piece's blocks start there in out_keys / out_rid
 };
 
 // first output row of block b: blocks are cut in the 16 B-aligned virtual row space, so block 0 is short by `mis` rows
@@ -294,8 +297,9 @@ __global__ void __launch_bounds__(PB_THREADS, PB_CTAS) part_block_kernel(BlockPa
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += y; }
             uint32_t run = incl - sum;
-            const uint32_t base = pb_block_base(blk, mis);
+            const uint32_t base = a.out_base + pb_block_base(blk, mis);
             uint32_t *seg = a.seg + (size_t)blk * (P + 2);
+            if (crank == 0 && lane == 0) a.block_base[blk] = base;
             for (uint32_t i = lo; i < hi; i++) {
                 const uint32_t c = s_tot[i];
                 s_delta[i] = base + run + s_delta[i] - s_off[i];
@@ -328,7 +332,7 @@ __global__ void __launch_bounds__(PB_THREADS, PB_CTAS) part_block_kernel(BlockPa
         // ---- write-out: consecutive threads -> consecutive elements of a bin's run -> consecutive addresses
         if (have) {
             const uint32_t total = inner ? (uint32_t)PB_TILE : s_scan[0];
-            const uint32_t rid0 = vbase - mis + a.rid_base;
+            const uint32_t rid0 = vbase - mis + a.rid_base + a.out_base;
 #pragma unroll 16
             for (uint32_t i = t; i < total; i += PB_THREADS) {
                 const uint32_t pm = s_perm[i];

@@ -282,6 +282,52 @@ void do_shuffle_scatter(H *h, int32_t n_dest, void *const *dest_keys, uint32_t *
     tm.stop();
 }
 
+// Single-pass local scatter by destination (b200j_shuffle_local_scatter): regions of `region_rows` rows per bin, reserved tile
+// by tile with atomics; counts come back in the API order [ranks][NULL][hot].
+void do_shuffle_local_scatter(H *h, const b200j_batch *b, int32_t n_dest, void *send_keys, uint32_t *send_rowid, int64_t region_rows,
+                              uint32_t rowid_base, int64_t *counts) {
+    check_batch(h, b, 0);
+    REQUIRE(h->cfg.n_keys == 1 && h->key_widths[0] != B200J_T_UTF8, B200J_ERR_UNSUPPORTED, "the exchange partitions one fixed-width key column");
+    REQUIRE(n_dest >= 1 && n_dest <= B200J_MAX_DEST, B200J_ERR_INVALID, "n_dest must be in 1..16");
+    REQUIRE(counts != nullptr, B200J_ERR_INVALID, "counts is NULL");
+    REQUIRE(b->mem == B200J_MEM_DEVICE || b->n_rows == 0, B200J_ERR_UNSUPPORTED, "the exchange takes device-resident batches");
+    REQUIRE(region_rows > 0 && region_rows < 0xffff0000LL, B200J_ERR_INVALID, "region_rows out of range");
+    REQUIRE(!h->shuffle_armed, B200J_ERR_STATE, "b200j_shuffle_local_scatter between b200j_shuffle_count and b200j_shuffle_scatter");
+    const bool hot = h->hot_n > 0;
+    const int n_api = n_dest + 1 + (hot ? 1 : 0);
+    for (int d = 0; d < n_api; d++) counts[d] = 0;
+    if (b->n_rows == 0) return;
+    REQUIRE(send_keys && send_rowid, B200J_ERR_INVALID, "send buffers missing");
+    const int kw = h->key_widths[0];
+    const b200j_column &kc = b->keys[0];
+    PartPlan pl = part_plan(h, kc.values, kc.validity, kc.bit_offset, kw, b->n_rows, 0, n_dest);
+    if (!h->d_reserve) CU(cudaMalloc((void **)&h->d_reserve, (B200J_MAX_DEST + 4) * 4));
+    CU(cudaMemsetAsync(h->d_reserve, 0, (B200J_MAX_DEST + 4) * 4, h->stream));
+    pl.a.reserve = h->d_reserve;
+    pl.a.reserve_cap = (uint32_t)region_rows;
+    pl.a.reserve_ovf = h->d_reserve + B200J_MAX_DEST + 3;
+    for (int d = 0; d < n_api; d++) {
+        // API order [ranks][NULL][hot] -> internal bin order [ranks][hot][NULL]
+        const int bin = d < n_dest ? d : (hot ? (d == n_dest ? n_dest + 1 : n_dest) : n_dest);
+        pl.a.dest_keys[bin] = (char *)send_keys + (size_t)d * (size_t)region_rows * kw;
+        pl.a.dest_rid[bin] = send_rowid + (size_t)d * (size_t)region_rows;
+    }
+    pl.a.rid_base = rowid_base;
+    {
+        PhaseTimer tm(h, &h->st.ms_exchange_partition);
+        part_scatter(h, pl);
+        tm.stop();
+    }
+    uint32_t got[B200J_MAX_DEST + 4];
+    CU(cudaMemcpyAsync(got, h->d_reserve, sizeof(got), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    REQUIRE(got[B200J_MAX_DEST + 3] == 0, B200J_ERR_INVALID, "region too small: a destination received more rows than region_rows");
+    for (int d = 0; d < n_api; d++) {
+        const int bin = d < n_dest ? d : (hot ? (d == n_dest ? n_dest + 1 : n_dest) : n_dest);
+        counts[d] = (int64_t)got[bin];
+    }
+}
+
 // Heavy-hitter key set of the exchange: rows with these keys stay on the rank that holds them (see part_is_hot).
 void do_shuffle_set_hot(H *h, const uint64_t *keys, int32_t n) {
     REQUIRE(n >= 0 && n <= 65536, B200J_ERR_INVALID, "hot key count must be in 0..65536");
@@ -340,42 +386,69 @@ void part_block_launch(H *h, const BlockPartArgs &a, uint32_t n_bins) {
     h->st.kernel_launches++;
 }
 
-// Dense probe of `n` device-resident keys against unique build keys behind the radix layout. On return ro owns the
-// result arrays; returns the number of result rows. PM_OUTER keeps the rows without a match (NULL build index), PM_PAIRS
-// pays one compaction pass when there were any (NULL-key rows count as rows without a match).
-int64_t probe_dense_blocked(H *h, const void *d_keys, const uint8_t *d_validity, int64_t bit_offset, int64_t n, const ProbePlan &pl,
-                            ResultOwner *ro, int64_t *n_build_null) {
+// One piece of a probe batch: `n` device-resident keys (possibly in a peer GPU's memory mapped with b200j_ipc_open: the
+// partition pass then PULLS them over NVLink while it partitions -- the multi-GPU exchange fused into the local join).
+struct ProbePiece {
+    const void    *keys;
+    const uint8_t *validity;
+    int64_t        bit_offset;
+    int64_t        n;
+};
+
+// Dense probe of device-resident keys against unique build keys behind the radix layout; the batch is the concatenation
+// of `pieces` (probe indices count across the pieces). On return ro owns the result arrays; returns the number of result
+// rows. PM_OUTER keeps the rows without a match (NULL build index), PM_PAIRS pays one compaction pass when there were any
+// (NULL-key rows count as rows without a match).
+int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces, const ProbePlan &pl, ResultOwner *ro, int64_t *n_build_null) {
     const int kw = h->table_kw;
     const uint32_t P = 1u << h->radix_bits;
-    const uint32_t mis = (uint32_t)(((uintptr_t)d_keys & 15) / (uintptr_t)kw);
-    const uint32_t n_tiles = (uint32_t)(((uint64_t)n + mis + PB_TILE - 1) / PB_TILE);
-    const uint32_t n_blocks = (n_tiles + PB_CLUSTER - 1) / PB_CLUSTER;
+    int64_t n = 0;
+    uint32_t n_blocks = 0;
+    std::vector<uint32_t> piece_blocks(n_pieces), piece_mis(n_pieces);
+    for (int i = 0; i < n_pieces; i++) {
+        piece_mis[i] = (uint32_t)(((uintptr_t)pieces[i].keys & 15) / (uintptr_t)kw);
+        const uint32_t n_tiles = (uint32_t)(((uint64_t)pieces[i].n + piece_mis[i] + PB_TILE - 1) / PB_TILE);
+        piece_blocks[i] = pieces[i].n > 0 ? (n_tiles + PB_CLUSTER - 1) / PB_CLUSTER : 0u;
+        n_blocks += piece_blocks[i];
+        n += pieces[i].n;
+    }
+    REQUIRE(n < 0xffff0000LL, B200J_ERR_UNSUPPORTED, "probe batch of more than 2^32 - 2^16 rows (probe indices are UInt32)");
     void *tk = nullptr, *tr = nullptr, *seg = nullptr, *ob = nullptr, *ob2 = nullptr, *op2 = nullptr;
     Trace tr_;
     try {
         CU(big_alloc(h, &tk, (size_t)n * kw + 16));
         CU(big_alloc(h, &tr, (size_t)n * 4 + 16));
-        CU(big_alloc(h, &seg, (size_t)n_blocks * (P + 2) * 4 + 16));
+        CU(big_alloc(h, &seg, (size_t)n_blocks * (P + 3) * 4 + 16));       // [n_blocks][P + 2] segment bounds, then [n_blocks] block bases
         CU(big_alloc(h, &ob, (size_t)n * 8 + 16));
+        uint32_t *block_base = (uint32_t *)seg + (size_t)n_blocks * (P + 2);
         CU(cudaMemsetAsync(h->d_part_rows, 0, (size_t)(P + 1) * 8, h->stream));
-        BlockPartArgs ba{};
-        ba.keys = d_keys;
-        ba.validity = d_validity;
-        ba.bit_offset = bit_offset;
-        ba.n = (uint32_t)n;
-        ba.mis = mis;
-        ba.radix_bits = h->radix_bits;
-        ba.n_blocks = n_blocks;
-        ba.hk = h->hk;
-        ba.out_keys = tk;
-        ba.out_rid = (uint32_t *)tr;
-        ba.seg = (uint32_t *)seg;
-        ba.part_rows = h->d_part_rows;
-        ba.rid_base = h->probe_rid_base;
         {
             PhaseTimer tm(h, &h->st.ms_probe_partition);
-            if (kw == 8) part_block_launch<8>(h, ba, P); else part_block_launch<4>(h, ba, P);
-            CU(cudaGetLastError());
+            uint32_t blk0 = 0;
+            int64_t row0 = 0;
+            for (int i = 0; i < n_pieces; i++) {
+                if (pieces[i].n == 0) continue;
+                BlockPartArgs ba{};
+                ba.keys = pieces[i].keys;
+                ba.validity = pieces[i].validity;
+                ba.bit_offset = pieces[i].bit_offset;
+                ba.n = (uint32_t)pieces[i].n;
+                ba.mis = piece_mis[i];
+                ba.radix_bits = h->radix_bits;
+                ba.n_blocks = piece_blocks[i];
+                ba.hk = h->hk;
+                ba.out_keys = tk;
+                ba.out_rid = (uint32_t *)tr;
+                ba.seg = (uint32_t *)seg + (size_t)blk0 * (P + 2);
+                ba.block_base = block_base + blk0;
+                ba.part_rows = h->d_part_rows;
+                ba.rid_base = h->probe_rid_base;
+                ba.out_base = (uint32_t)row0;
+                if (kw == 8) part_block_launch<8>(h, ba, P); else part_block_launch<4>(h, ba, P);
+                CU(cudaGetLastError());
+                blk0 += piece_blocks[i];
+                row0 += pieces[i].n;
+            }
             tm.stop();
         }
         CU(cudaMemcpyAsync(h->h_part_rows, h->d_part_rows, (size_t)(P + 1) * 8, cudaMemcpyDeviceToHost, h->stream));
@@ -399,10 +472,9 @@ int64_t probe_dense_blocked(H *h, const void *d_keys, const uint8_t *d_validity,
         a.ctr = h->d_ctr;
         SegArgs sg{};
         sg.seg = (const uint32_t *)seg;
+        sg.block_base = block_base;
         sg.n_blocks = n_blocks;
         sg.n_units = n_blocks * (n_null > 0 ? P + 1 : P);
-        sg.block_rows = PB_BLOCK;
-        sg.mis = mis;
         {
             PhaseTimer tm(h, &h->st.ms_probe);
             const int64_t n_claims = ((int64_t)sg.n_units + SEG_UNITS - 1) / SEG_UNITS;
@@ -463,6 +535,78 @@ int64_t probe_dense_blocked(H *h, const void *d_keys, const uint8_t *d_validity,
     } catch (...) {
         for (void *p : {tk, tr, seg, ob, ob2, op2})
             if (p) big_free(h, p);
+        throw;
+    }
+}
+
+int64_t probe_dense_blocked(H *h, const void *d_keys, const uint8_t *d_validity, int64_t bit_offset, int64_t n, const ProbePlan &pl,
+                            ResultOwner *ro, int64_t *n_build_null) {
+    const ProbePiece one{d_keys, d_validity, bit_offset, n};
+    return probe_dense_blocked_pieces(h, &one, 1, pl, ro, n_build_null);
+}
+
+// b200j_probe_pieces: see include/b200join.h. The dense path behind the radix layout takes the pieces as they are; every
+// other path gets them concatenated into one device buffer first.
+void do_probe_pieces(H *h, int32_t partition, int32_t n_pieces, const void *const *piece_keys, const int64_t *piece_rows, uint32_t want,
+                     b200j_result *out) {
+    REQUIRE(partition >= 0 && partition < h->cfg.n_partitions, B200J_ERR_INVALID, "partition out of range");
+    REQUIRE(h->built, B200J_ERR_INVALID, "probe before every partition finished the build side");
+    REQUIRE(!h->probe_done[partition], B200J_ERR_STATE, "probe_pieces after probe_finish");
+    REQUIRE(!h->shuffle_armed, B200J_ERR_STATE, "probe_pieces between b200j_shuffle_count and b200j_shuffle_scatter");
+    REQUIRE(out != nullptr && out->struct_size >= RESULT_V1_SIZE, B200J_ERR_INVALID, "result struct missing or too small");
+    REQUIRE(!h->composite, B200J_ERR_UNSUPPORTED, "probe_pieces takes a single fixed-width key column");
+    REQUIRE(n_pieces >= 0 && n_pieces <= 64, B200J_ERR_INVALID, "n_pieces must be in 0..64");
+    REQUIRE(n_pieces == 0 || (piece_keys && piece_rows), B200J_ERR_INVALID, "piece arrays missing");
+    const ProbePlan pl = plan_for(h->cfg.join_type, (want & B200J_OUT_MATCHES_ONLY) != 0);
+    const bool count_only = (want & B200J_OUT_COUNT_ONLY) != 0;
+    const int kw = h->key_widths[0];
+    std::vector<ProbePiece> pieces;
+    int64_t n = 0;
+    for (int i = 0; i < n_pieces; i++) {
+        REQUIRE(piece_rows[i] >= 0, B200J_ERR_INVALID, "negative piece length");
+        REQUIRE(piece_rows[i] == 0 || piece_keys[i] != nullptr, B200J_ERR_INVALID, "piece without keys");
+        pieces.push_back(ProbePiece{piece_keys[i], nullptr, 0, piece_rows[i]});
+        n += piece_rows[i];
+    }
+    REQUIRE(n < 0xffff0000LL, B200J_ERR_UNSUPPORTED, "probe batch of more than 2^32 - 2^16 rows (probe indices are UInt32)");
+    ResultOwner *ro = new ResultOwner();
+    void *cat = nullptr;
+    try {
+        int64_t total = 0, n_bnull = 0;
+        const bool blocked = h->layout == B200J_LAYOUT_RADIX && !count_only && h->dense_ok && h->block_part_ok && h->radix_bits <= PB_MAX_BITS &&
+                             h->st.duplicate_rows == 0 && (pl.mode == PM_PAIRS || pl.mode == PM_OUTER);
+        if (n == 0) {
+            total = 0;
+        } else if (blocked) {
+            total = probe_dense_blocked_pieces(h, pieces.data(), (int)pieces.size(), pl, ro, &n_bnull);
+        } else {
+            CU(big_alloc(h, &cat, (size_t)n * kw + 16));
+            int64_t at = 0;
+            for (const ProbePiece &pc : pieces) {
+                if (pc.n) CU(cudaMemcpyAsync((char *)cat + (size_t)at * kw, pc.keys, (size_t)pc.n * kw, cudaMemcpyDefault, h->stream));
+                at += pc.n;
+            }
+            total = probe_device(h, cat, nullptr, 0, n, pl, count_only, ro, &n_bnull);
+        }
+        if (count_only) {
+            if (ro->build_idx) big_free(h, ro->build_idx);
+            if (ro->probe_idx) big_free(h, ro->probe_idx);
+            ro->build_idx = ro->probe_idx = nullptr;
+        } else {
+            if (want & B200J_OUT_BUILD_U32) narrow_result(h, ro, total);
+            if ((want & B200J_OUT_HOST) && ro->mem != B200J_MEM_HOST) move_result_to_host(h, ro, total);
+            else if (want & B200J_OUT_BUILD_U32) CU(cudaStreamSynchronize(h->stream));
+        }
+        if (cat) big_free(h, cat);
+        cat = nullptr;
+        fill_result(out, ro, total, ro->mem);
+        out->n_build_null = n_bnull;
+        out->n_probe_null = 0;
+        h->st.probe_rows += n;
+        h->st.result_rows += total;
+    } catch (...) {
+        if (cat) big_free(h, cat);
+        release_owner(h, ro);
         throw;
     }
 }

@@ -25,25 +25,28 @@ IPC_BYTES = 64
 class ExchangePlan:
     """What every rank derives from the all-gathered count matrix counts[src][dst] (rows of src that hash to dst)."""
 
-    def __init__(self, counts: np.ndarray, rank: int):
+    def __init__(self, counts: np.ndarray, rank: int, src_order: Optional[Sequence[int]] = None):
         counts = np.asarray(counts, dtype=np.int64)
         world = counts.shape[0]
         assert counts.shape == (world, world)
         self.world, self.rank, self.counts = world, rank, counts
+        # the order in which the sources' rows sit in MY received batch: rank order for the push modes; rotated to start behind
+        # me in mode "pull" (all ranks reading source 0 first would queue up on one GPU's NVLink egress)
+        self.src_order = np.arange(world) if src_order is None else np.asarray(src_order, dtype=np.int64)
         self.recv_rows = counts.sum(axis=0)                      # rows every rank receives
         self.max_recv = int(self.recv_rows.max())
         # where MY rows start inside destination d's receive buffer: after the rows of lower ranks
         self.dest_offset = np.array([int(counts[:rank, d].sum()) for d in range(world)], dtype=np.int64)
-        # where rank s's rows start inside MY receive buffer
-        self.src_offset = np.concatenate([[0], np.cumsum(counts[:, rank])]).astype(np.int64)
+        # where the rows of the k-th source (src_order[k]) start inside MY received batch
+        self.src_offset = np.concatenate([[0], np.cumsum(counts[self.src_order, rank])]).astype(np.int64)
         self.send_split = [int(x) for x in counts[rank, :]]
         self.recv_split = [int(x) for x in counts[:, rank]]
         self.send_offset = np.concatenate([[0], np.cumsum(counts[rank, :])]).astype(np.int64)
 
     def origin_of(self, recv_index: np.ndarray):
         """(source rank, position inside that source's segment) of rows of my receive buffer."""
-        src = np.searchsorted(self.src_offset[1:], recv_index, side="right")
-        return src, recv_index - self.src_offset[src]
+        k = np.searchsorted(self.src_offset[1:], recv_index, side="right")
+        return self.src_order[k], recv_index - self.src_offset[k]
 
 
 class _PeerBuffer:
@@ -113,6 +116,23 @@ def shuffle_scatter(join: HashJoin, n_dest: int, dest_keys: Sequence[int], dest_
     join._check(N.lib().b200j_shuffle_scatter(join._h, n_dest, dk, dr, do, rowid_base))
 
 
+def shuffle_local_scatter(join: HashJoin, keys, n_dest: int, send_keys_ptr: int, send_rid_ptr: int, region_rows: int, rowid_base: int = 0) -> np.ndarray:
+    """b200j_shuffle_local_scatter: one pass over `keys` (device column); every (key, row id) lands in the region of its
+    destination inside the local send buffers. Returns the rows per region: [ranks][NULL keys]([hot keys])."""
+    b, keep = make_batch([keys])
+    counts = (C.c_int64 * (n_dest + 2))()
+    join._check(N.lib().b200j_shuffle_local_scatter(join._h, C.byref(b), n_dest, send_keys_ptr, send_rid_ptr, region_rows, rowid_base, counts))
+    return np.array(list(counts), dtype=np.int64)
+
+
+def copy_async(join: HashJoin, dst: int, src: int, nbytes: int, lane: int = 0):
+    join._check(N.lib().b200j_copy_async(join._h, dst, src, nbytes, lane))
+
+
+def copy_wait(join: HashJoin):
+    join._check(N.lib().b200j_copy_wait(join._h))
+
+
 class _Side:
     """Receive (and, for NCCL, send) buffers of one join side on this rank."""
 
@@ -166,7 +186,7 @@ class DistributedJoin:
             return
         torch = self.torch
         cap = int(rows * 1.1) + 4096
-        if self.mode == "p2p":
+        if self.mode in ("p2p", "ce"):
             for b in (side.keys, side.rid):
                 if b is not None:
                     b.close(self.dist)
@@ -190,6 +210,13 @@ class DistributedJoin:
         hot = self.hot is not None and side is not self.build        # the build side is never routed: its rows go to their owners
         if self.hot is not None:
             shuffle_set_hot(xj, self.hot if hot else None)
+        if self.mode == "ce":
+            n_recv = self._exchange_ce(side, keys, rowid_base, xj, xs, hot)
+            side.pieces = [(side.recv_keys_ptr, n_recv)]
+            side.rid_pieces = [(side.recv_rid_ptr, n_recv)]
+            return n_recv
+        if self.mode == "pull":
+            return self._exchange_pull(side, keys, rowid_base, xj, xs, hot)
         counts = shuffle_count(xj, keys, W, hot)
         with torch.cuda.stream(xs):
             mine = torch.from_numpy(counts[:W].copy()).to(keys.device)
@@ -233,7 +260,156 @@ class DistributedJoin:
             xs.synchronize()
             recv_keys_ptr, recv_rid_ptr = side.keys.data_ptr(), side.rid.data_ptr()
         side.recv_keys_ptr, side.recv_rid_ptr = recv_keys_ptr, recv_rid_ptr
+        n_recv = int(plan.recv_rows[self.rank])
+        side.pieces = [(recv_keys_ptr, n_recv)]
+        side.rid_pieces = [(recv_rid_ptr, n_recv)]
+        return n_recv
+
+    def _exchange_ce(self, side: _Side, keys, rowid_base: int, xj: HashJoin, xs, hot: bool) -> int:
+        """Mode "ce": the exchange is carried by the copy engines. ONE kernel scatters the batch by destination into local send
+        regions (single read of the keys, no histogram pass: b200j_shuffle_local_scatter), the ranks all-gather the counts,
+        and every region then crosses NVLink as one cudaMemcpyAsync into the peer's receive buffer at its exact (dense)
+        offset -- no SM is busy with the transfer, so it overlaps the local join of the previous chunk for real (the fused
+        peer-store scatter of mode "p2p" competes with the join for SMs and L2: 33 -> 40 ms/step at 2 GPUs when overlapped)."""
+        torch, dist = self.torch, self.dist
+        W = self.world
+        n = int(keys.shape[0])
+        n_regions = W + 2
+        grow = 1.0
+        while True:
+            need = int(n / W * 1.15 * grow) + 65536
+            if side.send_keys is None or getattr(side, "send_cap", 0) < need:
+                side.send_keys = torch.empty(n_regions * need, dtype=self._key_dtype, device=keys.device)
+                side.send_rid = torch.empty(n_regions * need, dtype=torch.int32, device=keys.device)
+                side.send_cap = need
+            cap = side.send_cap
+            try:
+                counts, ovf = shuffle_local_scatter(xj, keys, W, side.send_keys.data_ptr(), side.send_rid.data_ptr(), cap, rowid_base), 0
+            except B200JoinError as e:
+                if "region too small" not in str(e):
+                    raise
+                counts, ovf = np.zeros(W + 2, dtype=np.int64), 1
+            # every rank has to take the same branch: the overflow flag travels with the counts
+            with torch.cuda.stream(xs):
+                mine = torch.from_numpy(np.concatenate([counts[:W], [ovf]]).astype(np.int64)).to(keys.device)
+                allc = torch.empty(W * (W + 1), dtype=torch.int64, device=keys.device)
+                dist.all_gather_into_tensor(allc, mine, group=self.group)
+                full = allc.cpu().numpy().reshape(W, W + 1)
+            if int(full[:, W].sum()) == 0:
+                break
+            if ovf:                                 # a skewed destination: twice the region size on my retry
+                grow *= 2.0
+        matrix = full[:, :W]
+        plan = ExchangePlan(matrix, self.rank)
+        side.plan = plan
+        self._ensure(side, plan.max_recv)
+        kw = self.kw
+        sk, sr = side.send_keys.data_ptr(), side.send_rid.data_ptr()
+        for i in range(W):
+            d = (self.rank + i) % W             # start with my own region: the ranks do not all hit rank 0 first
+            m = int(counts[d])
+            if m == 0:
+                continue
+            off = int(plan.dest_offset[d])
+            copy_async(xj, side.keys.ptrs[d] + off * kw, sk + d * cap * kw, m * kw, lane=(2 * i) % 4)
+            copy_async(xj, side.rid.ptrs[d] + off * 4, sr + d * cap * 4, m * 4, lane=(2 * i + 1) % 4)
+        n_null = int(counts[W])
+        side.null_keys = side.send_keys[W * cap: W * cap + n_null] if n_null else None
+        side.null_rid = side.send_rid[W * cap: W * cap + n_null] if n_null else None
+        side.n_hot = 0
+        if hot:
+            side.n_hot = int(counts[W + 1])
+            side.hot_keys = side.send_keys[(W + 1) * cap: (W + 1) * cap + max(side.n_hot, 1)]
+            side.hot_rid = side.send_rid[(W + 1) * cap: (W + 1) * cap + max(side.n_hot, 1)]
+        copy_wait(xj)
+        dist.barrier(group=self.group)          # every peer's copies have landed in my receive buffer
+        side.recv_keys_ptr, side.recv_rid_ptr = side.keys.local, side.rid.local
         return int(plan.recv_rows[self.rank])
+
+    def _exchange_pull(self, side: _Side, keys, rowid_base: int, xj: HashJoin, xs, hot: bool) -> int:
+        """Mode "pull": nothing is pushed. ONE kernel scatters the batch by destination into LOCAL send regions that every peer
+        has mapped (cudaIpc); the ranks all-gather the counts; the destination's local join then takes the W regions meant for
+        it as the PIECES of one batch (b200j_probe_pieces / build_push per piece) and its partition pass pulls the keys over
+        NVLink while it partitions them: the transfer is fused into a pass the join makes anyway, only the 8-byte keys cross
+        the link (the source row ids stay where they are until somebody asks for an origin), and no receive buffer is written
+        and read back. Loads can be kept in flight by the thousands per SM, peer STORES cannot (the push scatter of mode "p2p"
+        reaches 480-550 GB/s of the 770 GB/s a peer copy gets)."""
+        torch, dist = self.torch, self.dist
+        W, kw = self.world, self.kw
+        n = int(keys.shape[0])
+        n_regions = W + 2
+        grow = 1.0
+        first = True
+        while True:
+            need = (int(n / W * 1.15 * grow) + 65536 + 63) // 64 * 64
+            if first or grow > 1.0:
+                # ONE collective: region size = the largest any rank needs, and nobody is still pulling from the regions about to be
+                # overwritten (every rank gets here only after its previous local join has returned)
+                with torch.cuda.stream(xs):
+                    t = torch.tensor([need], dtype=torch.int64, device=keys.device)
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+                    need = int(t.item())
+                first = False
+            if getattr(side, "send_cap", 0) < need:       # collective: every rank sees the same `need`
+                for b in (getattr(side, "send_pk", None), getattr(side, "send_pr", None)):
+                    if b is not None:
+                        b.close(dist)
+                side.send_pk = _PeerBuffer(xj, dist, n_regions * need * kw + 64)
+                side.send_pr = _PeerBuffer(xj, dist, n_regions * need * 4 + 64)
+                side.send_cap = need
+            cap = side.send_cap
+            try:
+                counts, ovf = shuffle_local_scatter(xj, keys, W, side.send_pk.local, side.send_pr.local, cap, rowid_base), 0
+            except B200JoinError as e:
+                if "region too small" not in str(e):
+                    raise
+                counts, ovf = np.zeros(W + 2, dtype=np.int64), 1
+            with torch.cuda.stream(xs):
+                mine = torch.from_numpy(np.concatenate([counts[:W], [ovf]]).astype(np.int64)).to(keys.device)
+                allc = torch.empty(W * (W + 1), dtype=torch.int64, device=keys.device)
+                dist.all_gather_into_tensor(allc, mine, group=self.group)     # ... and every peer's scatter has finished
+                full = allc.cpu().numpy().reshape(W, W + 1)
+            if int(full[:, W].sum()) == 0:
+                break
+            grow *= 2.0                                  # somebody's region overflowed: everybody retries with larger ones
+        matrix = full[:, :W]
+        plan = ExchangePlan(matrix, self.rank)
+        side.plan = plan
+        me = self.rank
+        order = [(me + i) % W for i in range(W)]         # my own region first, then the peers behind me: no two ranks start on the same source
+        plan = ExchangePlan(matrix, me, src_order=order)
+        side.plan = plan
+        side.pieces = [(side.send_pk.ptrs[s] + me * cap * kw, int(matrix[s, me])) for s in order]
+        side.rid_pieces = [(side.send_pr.ptrs[s] + me * cap * 4, int(matrix[s, me])) for s in order]
+        n_null = int(counts[W])
+        side.null_keys = torch.as_tensor(_RawCudaArray(side.send_pk.local + W * cap * kw, n_null, "<i8" if kw == 8 else "<i4"), device=keys.device) if n_null else None
+        side.null_rid = torch.as_tensor(_RawCudaArray(side.send_pr.local + W * cap * 4, n_null, "<i4"), device=keys.device) if n_null else None
+        side.n_hot = 0
+        if hot:
+            side.n_hot = int(counts[W + 1])
+            m = max(side.n_hot, 1)
+            side.hot_keys = torch.as_tensor(_RawCudaArray(side.send_pk.local + (W + 1) * cap * kw, m, "<i8" if kw == 8 else "<i4"), device=keys.device)
+            side.hot_rid = torch.as_tensor(_RawCudaArray(side.send_pr.local + (W + 1) * cap * 4, m, "<i4"), device=keys.device)
+        side.recv_keys_ptr = side.recv_rid_ptr = None
+        return int(plan.recv_rows[me])
+
+    def received(self, side: _Side, what: str = "keys"):
+        """The rows this rank received for one side as ONE local tensor (copies: tests, verification, late materialisation)."""
+        torch = self.torch
+        pieces = side.pieces if what == "keys" else side.rid_pieces
+        ts = "<i4" if (what != "keys" or self.kw == 4) else "<i8"
+        dev = torch.device("cuda", torch.cuda.current_device())
+        parts = [torch.as_tensor(_RawCudaArray(p, m, ts)).to(dev) for p, m in pieces if m]
+        if not parts:
+            return torch.empty(0, dtype=torch.int32 if ts == "<i4" else torch.int64, device=dev)
+        return torch.cat(parts)
+
+    def _local_probe(self, partition: int, side: _Side, want: int):
+        pieces = [(p, m) for p, m in side.pieces]
+        if len(pieces) == 1:
+            p, m = pieces[0]
+            return self.join.probe_batch(partition, [_dev_column(p, m, self.kw, keep=(side.keys,))], want=want)
+        return self.join.probe_pieces(partition, pieces, want=want)
 
     # ---- the HashJoin call shape --------------------------------------------------------------------------------
     def _timed(self, which: str, fn):
@@ -261,7 +437,9 @@ class DistributedJoin:
         k = keys[0]
         n_recv = self._timed("build", lambda: self._exchange(self.build, k, rowid_base=0))
         self.build_rows_local += n_recv
-        self.join.build_push(partition, [_dev_column(self.build.recv_keys_ptr, n_recv, self.kw, keep=(self.build.keys,))])
+        for ptr, m in self.build.pieces:          # mode "pull": one piece per source rank, copied out of the peers' send regions
+            if m:
+                self.join.build_push(partition, [_dev_column(ptr, m, self.kw, keep=(self.build.keys,))])
 
     def build_finish(self, partition: int):
         self.join.build_finish(partition)
@@ -352,9 +530,45 @@ class DistributedJoin:
         (source rank, source row) with `origin_build` / `origin_probe`."""
         k = keys[0]
         n_recv = self._timed("probe", lambda: self._exchange(self.probe, k, rowid_base=0))
-        res = self.join.probe_batch(partition, [_dev_column(self.probe.recv_keys_ptr, n_recv, self.kw, keep=(self.probe.keys,))], want=want)
+        res = self._local_probe(partition, self.probe, want)
         res.exchange_plan = self.probe.plan
         return self._probe_hot(self.probe, res, want)
+
+    def probe_exchange_begin(self, keys: Sequence, side_index: int = 0):
+        """Starts the exchange of one probe batch on the exchange handle / stream from a helper thread and returns a token for
+        probe_batch_received. Meant to run beside build_finish: the NVLink exchange of the probe side then overlaps the local
+        table build (which touches neither the probe keys nor the receive buffers). Collective: every rank calls it."""
+        import threading
+        torch = self.torch
+        dev = torch.cuda.current_device()
+        side = self.probe_sides[side_index]
+        box = {}
+
+        def run():
+            try:
+                torch.cuda.set_device(dev)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(self.xstream)
+                box["n"] = self._exchange(side, keys[0], rowid_base=0, overlapped=True)
+                e1.record(self.xstream)
+                e1.synchronize()
+                self.ms_exchange["probe"] += e0.elapsed_time(e1)
+            except BaseException as exc:
+                box["n"] = exc
+        th = threading.Thread(target=run, daemon=True)
+        th.start()
+        return (th, box, side)
+
+    def probe_batch_received(self, partition: int, token, want: int = OUT_PAIRS):
+        """Joins the rows a probe_exchange_begin delivered (local probe on the join's own stream)."""
+        th, box, side = token
+        th.join()
+        if isinstance(box["n"], BaseException):
+            raise box["n"]
+        self.probe = side
+        res = self._local_probe(partition, side, want)
+        res.exchange_plan = side.plan
+        return self._probe_hot(side, res, want)
 
     def probe_chunks(self, partition: int, key_chunks: Sequence, want: int = OUT_PAIRS):
         """Generator over the results of a sequence of probe chunks (device key tensors), with the partition + exchange
@@ -398,7 +612,7 @@ class DistributedJoin:
             th = start(k + 1) if k + 1 < len(chunks) else None
             side = self.probe_sides[k & 1]
             self.probe = side
-            res = self.join.probe_batch(partition, [_dev_column(side.recv_keys_ptr, got, self.kw, keep=(side.keys,))], want=want)
+            res = self._local_probe(partition, side, want)
             res.exchange_plan = side.plan
             yield self._probe_hot(side, res, want)
 
@@ -530,19 +744,7 @@ class DistributedJoin:
 
     def _origin(self, side: _Side, idx: np.ndarray):
         """(source rank, source row) of received rows `idx` of one side (host arrays; for tests and late materialisation)."""
-        torch = self.torch
-        n_recv = int(side.plan.recv_rows[self.rank])
-        if self.mode == "p2p":
-            rid = np.empty(n_recv, dtype=np.uint32)
-            if n_recv:
-                t = torch.empty(n_recv, dtype=torch.int32, device="cuda")
-                import ctypes
-                # device-to-device view through cudaMemcpy via torch: wrap the raw pointer
-                src = _RawCudaArray(side.recv_rid_ptr, n_recv, "<i4")
-                t.copy_(torch.as_tensor(src, device="cuda"))
-                rid = t.cpu().numpy().view(np.uint32)
-        else:
-            rid = side.rid[:n_recv].cpu().numpy().view(np.uint32)
+        rid = self.received(side, "rid").cpu().numpy().view(np.uint32)
         src_rank, _ = side.plan.origin_of(np.asarray(idx, dtype=np.int64))
         return src_rank, rid[np.asarray(idx, dtype=np.int64)]
 
@@ -563,12 +765,16 @@ class DistributedJoin:
         self.ms_exchange = {"build": 0.0, "probe": 0.0}
 
     def close(self):
-        if self.mode == "p2p":
+        if self.mode in ("p2p", "ce", "pull"):
             for side in [self.build] + self.probe_sides:
                 for b in (side.keys, side.rid):
                     if b is not None:
                         b.close(self.dist)
                 side.keys = side.rid = None
+                for b in (getattr(side, "send_pk", None), getattr(side, "send_pr", None)):
+                    if b is not None:
+                        b.close(self.dist)
+                side.send_pk = side.send_pr = None
         if self.hot_join is not None:
             self.hot_join.close()
         self.xjoin.close()

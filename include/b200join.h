@@ -241,6 +241,13 @@ int32_t b200j_build_finish(b200j_handle *h, int32_t partition);
 /* ---- probe side ------------------------------------------------------------------------------ */
 int32_t b200j_probe_batch(b200j_handle *h, int32_t partition, const b200j_batch *batch, uint32_t want,
                           b200j_result *out);
+/* One probe batch handed over as several device-resident pieces of its (single, fixed-width, non-NULL) key column: the
+ * batch is their concatenation, probe_idx counts across the pieces. A piece may live in a PEER GPU's memory mapped with
+ * b200j_ipc_open: the radix-partition pass of the local join then pulls it over NVLink while it partitions, which is how
+ * the multi-GPU exchange is fused into the join (DistributedJoin mode "pull": the pieces are the regions the source ranks
+ * scattered for this rank with b200j_shuffle_local_scatter). */
+int32_t b200j_probe_pieces(b200j_handle *h, int32_t partition, int32_t n_pieces, const void *const *piece_keys, const int64_t *piece_rows,
+                           uint32_t want, b200j_result *out);
 /* Join-type post-processing (a7) of caller-filtered pairs of one probe batch of `n_probe_rows` rows. */
 int32_t b200j_apply_pairs(b200j_handle *h, int32_t partition, int64_t n_probe_rows, int32_t mem, int64_t n_pairs,
                           const uint64_t *build_idx, const uint32_t *probe_idx, uint32_t want, b200j_result *out);
@@ -269,6 +276,19 @@ int32_t b200j_shuffle_count(b200j_handle *h, const b200j_batch *batch, int32_t n
 int32_t b200j_shuffle_scatter(b200j_handle *h, int32_t n_dest, void *const *dest_keys /* [n_dest + 1] */,
                               uint32_t *const *dest_rowid /* [n_dest + 1] */, const int64_t *dest_offset /* [n_dest + 1] first row to
                               write in each destination buffer */, uint32_t rowid_base /* added to the batch-local row index */);
+/* Single-pass variant for exchanges carried by the copy engines (round 2): ONE kernel reads the batch once and writes every
+ * (key, row id) into the region of its destination inside LOCAL send buffers -- send_keys / send_rowid hold n_dest + 1 (+ 1
+ * with a hot set) regions of `region_rows` rows each, in the order [ranks][NULL keys][hot keys]. No histogram pass: a tile
+ * reserves its run in a region with one atomic. counts[] receives the rows written per region. The regions are then handed
+ * to the peers with b200j_copy_async (cudaMemcpyAsync over NVLink: no SM is busy while the local join of the previous
+ * chunk runs). Returns B200J_ERR_INVALID with "region too small" when a region overflowed (nothing past a region's end is
+ * written): call again with larger regions. */
+int32_t b200j_shuffle_local_scatter(b200j_handle *h, const b200j_batch *batch, int32_t n_dest, void *send_keys, uint32_t *send_rowid,
+                                    int64_t region_rows, uint32_t rowid_base, int64_t *counts /* [n_dest + 1], [n_dest + 2] with a hot set */);
+/* Enqueue a device-to-device copy (same device, or a peer mapped with b200j_ipc_open) on one of the handle's copy lanes
+ * (0..3); it starts after the work enqueued on the handle's stream so far. b200j_copy_wait blocks until every lane is idle. */
+int32_t b200j_copy_async(b200j_handle *h, void *dst, const void *src, size_t bytes, int32_t lane);
+int32_t b200j_copy_wait(b200j_handle *h);
 /* Heavy-hitter routing (SURVEY §8e "skew"). Rows whose key is in the hot set are NOT sent to the key's owner: they go
  * to one extra, rank-local destination, to be joined there against the build rows of the hot keys, which the caller
  * broadcasts (a hot key would otherwise deliver its whole probe volume to one GPU). With a non-empty hot set the count /

@@ -176,3 +176,48 @@ def test_hot_keys_stay_local(dtype):
         shuffle_set_hot(j, None)
         assert np.array_equal(shuffle_count(j, dev, world)[: world + 1], plain[: world + 1])
         shuffle_scatter(j, world, [t.data_ptr() for t in sk[: world + 1]], [t.data_ptr() for t in sr[: world + 1]], [0] * (world + 1))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype,world,null_frac", [(np.int64, 2, 0.0), (np.int64, 8, 0.05), (np.int32, 3, 0.0)])
+def test_single_pass_local_scatter_matches_two_pass(dtype, world, null_frac):
+    """b200j_shuffle_local_scatter (one read of the keys, regions reserved tile by tile) delivers exactly the rows that the
+    two-pass count + scatter delivers to every destination; a region that is too small is an error, not a silent overrun."""
+    import torch
+    import datafusion_parallelism_b200 as d
+    from datafusion_parallelism_b200.exchange import shuffle_count, shuffle_scatter, shuffle_local_scatter
+    rng = np.random.default_rng(13)
+    kw, n = np.dtype(dtype).itemsize, 300_001
+    tdt = torch.int64 if kw == 8 else torch.int32
+    keys = rng.integers(-5000, 1 << 30, n).astype(dtype)
+    with d.HashJoin("inner", key_widths=(kw,)) as j:
+        dev = torch.from_numpy(np.concatenate([keys[:1], keys])).cuda()[1:]          # misaligned start as well
+        col = dev
+        if null_frac > 0:
+            valid = rng.random(n) >= null_frac
+            vbits = torch.from_numpy(np.packbits(valid.astype(np.uint8), bitorder="little")).cuda()
+            col = d.column(dev, validity=vbits)
+        counts = shuffle_count(j, col, world)
+        sk = [torch.empty(n, dtype=tdt, device="cuda") for _ in range(world + 1)]
+        sr = [torch.empty(n, dtype=torch.int32, device="cuda") for _ in range(world + 1)]
+        shuffle_scatter(j, world, [t.data_ptr() for t in sk], [t.data_ptr() for t in sr], [0] * (world + 1))
+        j.synchronize()
+        cap = int(counts[: world + 1].max()) + 17
+        send_k = torch.full(((world + 2) * cap,), -1, dtype=tdt, device="cuda")
+        send_r = torch.full(((world + 2) * cap,), -1, dtype=torch.int32, device="cuda")
+        got = shuffle_local_scatter(j, col, world, send_k.data_ptr(), send_r.data_ptr(), cap, rowid_base=1000)
+        assert np.array_equal(got[: world + 1], counts[: world + 1])
+        for dst in range(world + 1):
+            m = int(counts[dst])
+            want_rows = np.sort(sr[dst][:m].cpu().numpy().view(np.uint32))
+            rows = send_r[dst * cap: dst * cap + m].cpu().numpy().view(np.uint32)
+            ks = send_k[dst * cap: dst * cap + m].cpu().numpy()
+            assert np.array_equal(np.sort(rows) - 1000, want_rows)
+            if dst < world:
+                assert np.array_equal(ks, keys[(rows - 1000).astype(np.int64)])
+            assert (send_r[dst * cap + m: (dst + 1) * cap].cpu().numpy() == -1).all()       # nothing past the reserved rows
+        small = max(1, int(counts[:world].min()) // 2)
+        with pytest.raises(d.B200JoinError) as e:
+            shuffle_local_scatter(j, col, world, send_k.data_ptr(), send_r.data_ptr(), small)
+        assert "region too small" in str(e.value)
+        assert (send_r[(world + 1) * cap:].cpu().numpy() == -1).all()                       # and no write beyond the regions handed in

@@ -338,3 +338,39 @@ def test_build_indices_as_u32(pkg, monkeypatch, join_type, layout, radix_bits):
             r.release()
         o1, o2 = np.lexsort((fb, fp)), np.lexsort(want_fin)
         assert np.array_equal(fb[o1], want_fin[0][o2])
+
+
+@pytest.mark.parametrize("join_type", ["inner", "right", "full", "right_anti"])
+@pytest.mark.parametrize("unique,layout,radix_bits", [(True, "radix", 5), (False, "radix", 3), (True, "direct", 0)])
+def test_probe_pieces_equals_one_batch(pkg, join_type, unique, layout, radix_bits):
+    """b200j_probe_pieces: a probe batch handed over as ragged device-resident pieces (what the multi-GPU "pull" exchange
+    hands to the local join: one region per source rank) gives the pairs of the concatenated batch -- through the
+    block-local partition (unique build keys behind the radix layout) and through the concatenating fall-back."""
+    import torch
+    rng = np.random.default_rng(hash((join_type, unique, layout)) & 0xFFFFFFFF)
+    nb = 40_000
+    bk = (rng.permutation(nb * 2)[:nb] if unique else rng.integers(0, nb // 4, nb)).astype(np.int64)
+    lens = [70_001, 0, 33, 4096 * 8 * 3 + 5, 1, 50_000]
+    pk = rng.integers(-50, nb * 2 + 50, sum(lens)).astype(np.int64)
+    oj = oracle.OracleJoin(join_type, [bk])
+    want = oj.probe_batch([pk], len(pk))
+    dev = torch.from_numpy(np.concatenate([pk[:1], pk])).cuda()        # pieces start at odd offsets of one allocation: misaligned as well
+    pieces, at = [], 1
+    for m in lens:
+        pieces.append((dev[at:at + m].data_ptr() if m else 0, m))
+        at += m
+    with pkg.HashJoin(join_type, key_widths=(8,), layout=layout, radix_bits=radix_bits) as j:
+        j.build_push(0, [bk])
+        j.build_finish(0)
+        r = j.probe_pieces(0, pieces, want=pkg.OUT_PAIRS | pkg.OUT_HOST)
+        got = r.numpy()
+        r.release()
+        r = j.probe_pieces(0, pieces, want=pkg.OUT_PAIRS | pkg.OUT_COUNT_ONLY)
+        assert r.n == len(want[0])
+        r.release()
+        st = j.stats()
+    o1, o2 = np.lexsort(got), np.lexsort(want)
+    assert got[0].shape == want[0].shape
+    assert np.array_equal(got[0][o1], want[0][o2]) and np.array_equal(got[1][o1], want[1][o2])
+    if unique and layout == "radix" and join_type in ("inner", "right", "full"):
+        assert st["seg_probe_launches"] >= 1
