@@ -106,7 +106,7 @@ SIGNATURES = {
     "b200j_build_push": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(Batch)]),
     "b200j_build_finish": (C.c_int32, [C.c_void_p, C.c_int32]),
     "b200j_probe_batch": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(Batch), C.c_uint32, C.POINTER(Result)]),
-    "b200j_probe_pieces": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.c_uint32, C.POINTER(Result)]),
+    "b200j_probe_pieces": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.c_int32, C.c_uint32, C.POINTER(Result)]),
     "b200j_apply_pairs": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
                                       C.c_uint32, C.POINTER(Result)]),
     "b200j_probe_finish": (C.c_int32, [C.c_void_p, C.c_int32, C.c_uint32, C.POINTER(Result)]),
@@ -117,7 +117,7 @@ SIGNATURES = {
     "b200j_shuffle_count": (C.c_int32, [C.c_void_p, C.POINTER(Batch), C.c_int32, C.POINTER(C.c_int64)]),
     "b200j_shuffle_set_hot": (C.c_int32, [C.c_void_p, C.POINTER(C.c_uint64), C.c_int32]),
     "b200j_shuffle_scatter": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.c_uint32]),
-    "b200j_shuffle_local_scatter": (C.c_int32, [C.c_void_p, C.POINTER(Batch), C.c_int32, C.c_void_p, C.c_void_p, C.c_int64, C.c_uint32, C.POINTER(C.c_int64)]),
+    "b200j_shuffle_local_scatter": (C.c_int32, [C.c_void_p, C.POINTER(Batch), C.c_int32, C.c_void_p, C.c_void_p, C.c_int64, C.c_uint32, C.c_int32, C.POINTER(C.c_int64)]),
     "b200j_copy_async": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int32]),
     "b200j_copy_wait": (C.c_int32, [C.c_void_p]),
     "b200j_ipc_alloc": (C.c_int32, [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]),

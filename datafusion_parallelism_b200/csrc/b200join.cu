@@ -120,6 +120,7 @@ struct b200j_handle {
     int probe_ctas_per_sm = 4;
     int dense_ctas_per_sm = 4;
     int seg_ctas_per_sm = 4;
+    bool narrow_ok = true;             // 8-byte probe keys go through the partitioned stream as 32-bit values until one does not fit (B200J_NO_NARROW=1: never)
     bool block_part_ok = true;         // B200J_NO_BLOCK_PART=1: the dense radix probe keeps the two-pass global partition of round 1
     int pb_clusters[2][PB_MAX_BITS + 1] = {};   // resident clusters of part_block_kernel per key width / radix bits (0 = not asked yet)
     unsigned long long *d_part_rows = nullptr, *h_part_rows = nullptr;   // rows per partition of the last block-partitioned batch
@@ -198,7 +199,8 @@ void radix_partition(H *h, const void *keys, const uint8_t *validity, int64_t bi
 void radix_release(H *h);
 struct ProbePlan;
 struct ProbePiece;
-int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces, const ProbePlan &pl, ResultOwner *ro, int64_t *n_build_null);
+int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces, const ProbePlan &pl, ResultOwner *ro, int64_t *n_build_null,
+                                   int piece_kw = 0);
 int64_t probe_dense_blocked(H *h, const void *d_keys, const uint8_t *d_validity, int64_t bit_offset, int64_t n, const ProbePlan &pl,
                             ResultOwner *ro, int64_t *n_build_null);
 void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, uint32_t want, b200j_gathered *out);
@@ -1386,8 +1388,8 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
     }
 }
 
-void do_probe_pieces(H *h, int32_t partition, int32_t n_pieces, const void *const *piece_keys, const int64_t *piece_rows, uint32_t want,
-                     b200j_result *out);
+void do_probe_pieces(H *h, int32_t partition, int32_t n_pieces, const void *const *piece_keys, const int64_t *piece_rows, int32_t piece_key_width,
+                     uint32_t want, b200j_result *out);
 
 // bitmap -> indices on the device; returns count. out64/out32: which side receives the indices.
 int64_t select_bits(H *h, const uint32_t *bm, int64_t n, bool want_set, void **out64, void **out32) {
@@ -1584,7 +1586,7 @@ void do_shuffle_count(H *h, const b200j_batch *b, int32_t n_dest, int64_t *count
 void do_shuffle_set_hot(H *h, const uint64_t *keys, int32_t n);
 void do_shuffle_scatter(H *h, int32_t n_dest, void *const *dest_keys, uint32_t *const *dest_rowid, const int64_t *dest_offset, uint32_t rowid_base);
 void do_shuffle_local_scatter(H *h, const b200j_batch *b, int32_t n_dest, void *send_keys, uint32_t *send_rowid, int64_t region_rows,
-                              uint32_t rowid_base, int64_t *counts);
+                              uint32_t rowid_base, int32_t key_out_width, int64_t *counts);
 
 template <typename F>
 int32_t guarded(b200j_handle *h, F &&f) {
@@ -1705,6 +1707,7 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
                 cudaGetLastError();
             if (const char *e = getenv("B200J_SEG_CTAS")) h->seg_ctas_per_sm = std::max(1, atoi(e));
             if (const char *e = getenv("B200J_NO_BLOCK_PART")) h->block_part_ok = atoi(e) == 0;
+            if (const char *e = getenv("B200J_NO_NARROW")) h->narrow_ok = atoi(e) == 0;
             if (const char *e = getenv("B200J_NO_DENSE")) h->dense_ok = atoi(e) == 0;
             if (const char *e = getenv("B200J_DENSE_MISS_MAX")) h->dense_miss_max = (float)atof(e);
             if (const char *e = getenv("B200J_L1_TABLE_BYTES")) h->l1_table_bytes = (uint64_t)atoll(e);
@@ -1825,6 +1828,7 @@ int32_t b200j_reset(b200j_handle *h) {
         h->n_build_done = h->n_probe_done = 0;
         h->built = false;
         h->miss_frac = 0.f;
+        if (!getenv("B200J_NO_NARROW") || atoi(getenv("B200J_NO_NARROW")) == 0) h->narrow_ok = true;
         h->n_slots = 0;
     });
 }
@@ -1847,8 +1851,8 @@ int32_t b200j_probe_batch(b200j_handle *h, int32_t partition, const b200j_batch 
     return guarded(h, [&] { do_probe_batch(h, partition, batch, want, out); });
 }
 int32_t b200j_probe_pieces(b200j_handle *h, int32_t partition, int32_t n_pieces, const void *const *piece_keys, const int64_t *piece_rows,
-                           uint32_t want, b200j_result *out) {
-    return guarded(h, [&] { do_probe_pieces(h, partition, n_pieces, piece_keys, piece_rows, want, out); });
+                           int32_t piece_key_width, uint32_t want, b200j_result *out) {
+    return guarded(h, [&] { do_probe_pieces(h, partition, n_pieces, piece_keys, piece_rows, piece_key_width, want, out); });
 }
 int32_t b200j_apply_pairs(b200j_handle *h, int32_t partition, int64_t n_probe_rows, int32_t mem, int64_t n_pairs,
                           const uint64_t *build_idx, const uint32_t *probe_idx, uint32_t want, b200j_result *out) {
@@ -1888,8 +1892,8 @@ int32_t b200j_shuffle_scatter(b200j_handle *h, int32_t n_dest, void *const *dest
     return guarded(h, [&] { do_shuffle_scatter(h, n_dest, dest_keys, dest_rowid, dest_offset, rowid_base); });
 }
 int32_t b200j_shuffle_local_scatter(b200j_handle *h, const b200j_batch *batch, int32_t n_dest, void *send_keys, uint32_t *send_rowid,
-                                    int64_t region_rows, uint32_t rowid_base, int64_t *counts) {
-    return guarded(h, [&] { do_shuffle_local_scatter(h, batch, n_dest, send_keys, send_rowid, region_rows, rowid_base, counts); });
+                                    int64_t region_rows, uint32_t rowid_base, int32_t key_out_width, int64_t *counts) {
+    return guarded(h, [&] { do_shuffle_local_scatter(h, batch, n_dest, send_keys, send_rowid, region_rows, rowid_base, key_out_width, counts); });
 }
 int32_t b200j_copy_async(b200j_handle *h, void *dst, const void *src, size_t bytes, int32_t lane) {
     return guarded(h, [&] {

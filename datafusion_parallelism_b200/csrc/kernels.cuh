@@ -1030,6 +1030,11 @@ __global__ void __launch_bounds__(256) narrow_u64_u32_kernel(const uint64_t *__r
     if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) out[n - 1] = (uint32_t)in[n - 1];
 }
 
+// 32-bit key pieces of the multi-GPU exchange -> 8-byte keys (the concatenating fall-back of b200j_probe_pieces)
+__global__ void __launch_bounds__(256) widen_u32_u64_kernel(const uint32_t *__restrict__ in, unsigned long long *__restrict__ out, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = (unsigned long long)in[i];
+}
+
 // Probe row ids of one chunk of a host batch -> row ids of the batch (direct layout; the radix layout's partition pass
 // adds the base while it writes the row-id array). NULL markers stay.
 __global__ void __launch_bounds__(256) add_base_u32_kernel(uint32_t *p, int64_t n, uint32_t base) {

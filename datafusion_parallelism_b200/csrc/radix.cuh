@@ -101,6 +101,10 @@ struct PartArgs {
     uint32_t           *reserve;          // [n_bins + 1] rows reserved so far per bin, or null (two-pass mode: cursors from cta_hist)
     uint32_t            reserve_cap;
     uint32_t           *reserve_ovf;
+    // DEST mode, 8-byte keys: the destination buffers take the keys as 32-bit values (half the bytes over NVLink); a key outside
+    // [0, 2^32) sets *narrow_ovf and the caller repeats the pass wide
+    uint32_t            narrow_out;
+    uint32_t           *narrow_ovf;
 };
 
 
@@ -373,6 +377,8 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
             }
         }
     };
+    bool wide_seen = false;
+    const bool narrow_out = DEST && KW == 8 && a.narrow_out != 0u;
     uint32_t n_bulk[2] = {0, 0};         // bulk copies issued so far per buffer (mbarrier phase parity)
     fetch(t0, 0);
     for (uint32_t tile = t0; tile < t1; tile++) {
@@ -402,6 +408,7 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
 #pragma unroll
             for (int j = 0; j < PER_VEC; j++) {
                 uint32_t bin = part_bin<DEST>(a, hash_one(a.hk, (uint64_t)k[j]), (uint64_t)k[j]);
+                if (DEST && KW == 8) wide_seen |= ((unsigned long long)k[j] >> 32) != 0ULL;
                 bool in = true;
                 if (!inner) {
                     const uint32_t vrow = vbase + src0 + j;
@@ -492,7 +499,8 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
             const uint32_t dst = s_delta[p] + i;
             if (DEST) {
                 if (drop && ((drop >> (p & 31u)) & 1u)) continue;
-                s_dkeys[p][dst] = stage[src];
+                if (narrow_out) reinterpret_cast<uint32_t *>(s_dkeys[p])[dst] = (uint32_t)stage[src];
+                else s_dkeys[p][dst] = stage[src];
                 s_drid[p][dst] = rid0 + src;
             } else {
                 out_keys[dst] = stage[src];
@@ -503,6 +511,7 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
         if (reserve && t == 0) s_drop = 0;
         if (SC_NBUF == 1 && tile + 1 < t1) fetch(tile + 1, 0);
     }
+    if (narrow_out && __any_sync(0xffffffffu, wide_seen) && lane == 0) atomicExch(a.narrow_ovf, 1u);
 }
 
 // (NULL, probe) rows for the NULL-key probe rows of Right / Full / RightAnti.

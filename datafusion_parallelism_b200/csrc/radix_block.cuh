@@ -70,6 +70,7 @@ struct BlockPartArgs {
     uint32_t           *block_base;       // [n_blocks] first output row of every block (written here, read by the probe)
     unsigned long long *part_rows;        // [P + 1] rows per partition over the whole batch (atomics, one per bin per block) or null
     uint32_t            rid_base;
+    uint32_t           *narrow_ovf;       // NARROW: set to 1 when a key does not fit 32 bits (the caller then repeats the pass wide)
     uint32_t            out_base;         // rows of the pieces in front of this one (a batch may arrive as several pieces, e.g. one per source
                                           // rank of the multi-GPU exchange): this piece's blocks start there in out_keys / out_rid
 };
@@ -135,9 +136,15 @@ __host__ __device__ inline size_t part_block_smem(int kw, uint32_t n_bins) {
     return (size_t)PB_TILE * kw + (size_t)PB_TILE * 4 + (size_t)PB_WARPS * Q * 2 + Q * 4 * 5 + 256;
 }
 
-template <int KW>
+// NARROW (KW == 8 only): the partitioned stream carries the keys as 32-bit values. Join keys are mostly small non-negative
+// integers (ids, surrogate keys): 4 B instead of 8 B per row written here and read again by the probe, which zero-extends
+// them before hashing and comparing, so nothing changes for the table or the result. A key outside [0, 2^32) raises
+// *narrow_ovf; the host then repeats the pass wide and stops trying for this join (b200join.cu: narrow_ok).
+template <int KW, bool NARROW = false>
 __global__ void __launch_bounds__(PB_THREADS, PB_CTAS) part_block_kernel(BlockPartArgs a) {
+    static_assert(!NARROW || KW == 8, "only 8-byte keys are narrowed");
     using KeyT = typename std::conditional<KW == 8, unsigned long long, uint32_t>::type;
+    using OutT = typename std::conditional<(KW == 8 && !NARROW), unsigned long long, uint32_t>::type;
     constexpr int PER_VEC = 16 / KW;
     constexpr int NVEC = PB_ITEMS / PER_VEC;
     constexpr uint32_t TILE_BYTES = (uint32_t)PB_TILE * KW;
@@ -162,7 +169,8 @@ __global__ void __launch_bounds__(PB_THREADS, PB_CTAS) part_block_kernel(BlockPa
     const uint32_t n_tiles = (uint32_t)(((uint64_t)vend + PB_TILE - 1) / PB_TILE);
     const uint32_t crank = cluster_ctarank();
     const KeyT *gkeys = reinterpret_cast<const KeyT *>(a.keys) - mis;
-    KeyT *out_keys = reinterpret_cast<KeyT *>(a.out_keys);
+    OutT *out_keys = reinterpret_cast<OutT *>(a.out_keys);
+    bool wide_seen = false;
     unsigned short *my_wcnt = s_wcnt + (size_t)warp * Q;
 
     if (t == 0) mbar_init(&s_bar, 1);
@@ -221,6 +229,7 @@ __global__ void __launch_bounds__(PB_THREADS, PB_CTAS) part_block_kernel(BlockPa
                 }
 #pragma unroll
                 for (int j = 0; j < PER_VEC; j++) {
+                    if (NARROW) wide_seen |= ((unsigned long long)k[j] >> 32) != 0ULL;
                     uint32_t bin = (uint32_t)(hash_one(a.hk, (uint64_t)k[j]) >> (64 - a.radix_bits));
                     if (!inner) {
                         const uint32_t vrow = vbase + src0 + j;
@@ -338,13 +347,14 @@ __global__ void __launch_bounds__(PB_THREADS, PB_CTAS) part_block_kernel(BlockPa
                 const uint32_t pm = s_perm[i];
                 const uint32_t p = pm >> 16, src = pm & 0xffffu;
                 const uint32_t dst = s_delta[p] + i;
-                out_keys[dst] = s_stage[src];
+                out_keys[dst] = (OutT)s_stage[src];
                 a.out_rid[dst] = rid0 + src;
             }
         }
         __syncthreads();
         fetch((blk + blk_step) * PB_CLUSTER + crank);
     }
+    if (NARROW && __any_sync(0xffffffffu, wide_seen) && lane == 0) atomicExch(a.narrow_ovf, 1u);     // keys of rows outside the batch are zeros
     // a CTA's shared memory must outlive the peers' reads of it
     cluster_arrive();
     cluster_wait();

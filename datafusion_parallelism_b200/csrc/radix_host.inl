@@ -93,7 +93,9 @@ void set_kernel_attributes() {
     CU(cudaFuncSetAttribute(part_scatter_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(part_block_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(part_block_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    if (PB_CLUSTER > 8) {       // clusters of more than 8 CTAs are a non-portable size: opt in
+    CU(cudaFuncSetAttribute((part_block_kernel<8, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    if (PB_CLUSTER > 8) {
+        CU(cudaFuncSetAttribute((part_block_kernel<8, true>), cudaFuncAttributeNonPortableClusterSizeAllowed, 1));       // clusters of more than 8 CTAs are a non-portable size: opt in
         CU(cudaFuncSetAttribute(part_block_kernel<8>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         CU(cudaFuncSetAttribute(part_block_kernel<4>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     }
@@ -285,7 +287,7 @@ void do_shuffle_scatter(H *h, int32_t n_dest, void *const *dest_keys, uint32_t *
 // Single-pass local scatter by destination (b200j_shuffle_local_scatter): regions of `region_rows` rows per bin, reserved tile
 // by tile with atomics; counts come back in the API order [ranks][NULL][hot].
 void do_shuffle_local_scatter(H *h, const b200j_batch *b, int32_t n_dest, void *send_keys, uint32_t *send_rowid, int64_t region_rows,
-                              uint32_t rowid_base, int64_t *counts) {
+                              uint32_t rowid_base, int32_t key_out_width, int64_t *counts) {
     check_batch(h, b, 0);
     REQUIRE(h->cfg.n_keys == 1 && h->key_widths[0] != B200J_T_UTF8, B200J_ERR_UNSUPPORTED, "the exchange partitions one fixed-width key column");
     REQUIRE(n_dest >= 1 && n_dest <= B200J_MAX_DEST, B200J_ERR_INVALID, "n_dest must be in 1..16");
@@ -299,6 +301,8 @@ void do_shuffle_local_scatter(H *h, const b200j_batch *b, int32_t n_dest, void *
     if (b->n_rows == 0) return;
     REQUIRE(send_keys && send_rowid, B200J_ERR_INVALID, "send buffers missing");
     const int kw = h->key_widths[0];
+    const int okw = key_out_width > 0 ? key_out_width : kw;
+    REQUIRE(okw == kw || (okw == 4 && kw == 8), B200J_ERR_INVALID, "key_out_width must be the key width, or 4 for 8-byte keys");
     const b200j_column &kc = b->keys[0];
     PartPlan pl = part_plan(h, kc.values, kc.validity, kc.bit_offset, kw, b->n_rows, 0, n_dest);
     if (!h->d_reserve) CU(cudaMalloc((void **)&h->d_reserve, (B200J_MAX_DEST + 4) * 4));
@@ -306,10 +310,12 @@ void do_shuffle_local_scatter(H *h, const b200j_batch *b, int32_t n_dest, void *
     pl.a.reserve = h->d_reserve;
     pl.a.reserve_cap = (uint32_t)region_rows;
     pl.a.reserve_ovf = h->d_reserve + B200J_MAX_DEST + 3;
+    pl.a.narrow_out = okw != kw ? 1u : 0u;
+    pl.a.narrow_ovf = h->d_reserve + B200J_MAX_DEST + 2;
     for (int d = 0; d < n_api; d++) {
         // API order [ranks][NULL][hot] -> internal bin order [ranks][hot][NULL]
         const int bin = d < n_dest ? d : (hot ? (d == n_dest ? n_dest + 1 : n_dest) : n_dest);
-        pl.a.dest_keys[bin] = (char *)send_keys + (size_t)d * (size_t)region_rows * kw;
+        pl.a.dest_keys[bin] = (char *)send_keys + (size_t)d * (size_t)region_rows * okw;
         pl.a.dest_rid[bin] = send_rowid + (size_t)d * (size_t)region_rows;
     }
     pl.a.rid_base = rowid_base;
@@ -322,6 +328,7 @@ void do_shuffle_local_scatter(H *h, const b200j_batch *b, int32_t n_dest, void *
     CU(cudaMemcpyAsync(got, h->d_reserve, sizeof(got), cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     REQUIRE(got[B200J_MAX_DEST + 3] == 0, B200J_ERR_INVALID, "region too small: a destination received more rows than region_rows");
+    REQUIRE(okw == kw || got[B200J_MAX_DEST + 2] == 0, B200J_ERR_INVALID, "keys do not fit 32 bits: repeat with key_out_width = 8");
     for (int d = 0; d < n_api; d++) {
         const int bin = d < n_dest ? d : (hot ? (d == n_dest ? n_dest + 1 : n_dest) : n_dest);
         counts[d] = (int64_t)got[bin];
@@ -356,7 +363,7 @@ void do_shuffle_set_hot(H *h, const uint64_t *keys, int32_t n) {
 
 
 // ---- block-local partition + segment-walking dense probe (radix_block.cuh, probe_dense_seg_kernel) -----------------------
-template <int KW>
+template <int KW, bool NARROW = false>
 void part_block_launch(H *h, const BlockPartArgs &a, uint32_t n_bins) {
     cudaLaunchConfig_t cfg{};
     cfg.blockDim = dim3(PB_THREADS);
@@ -374,7 +381,7 @@ void part_block_launch(H *h, const BlockPartArgs &a, uint32_t n_bins) {
     if (cached == 0) {
         cfg.gridDim = dim3((unsigned)(h->sm_count * PB_CTAS / PB_CLUSTER * PB_CLUSTER));
         int n = 0;
-        if (cudaOccupancyMaxActiveClusters(&n, part_block_kernel<KW>, &cfg) != cudaSuccess || n <= 0) {
+        if (cudaOccupancyMaxActiveClusters(&n, part_block_kernel<KW, NARROW>, &cfg) != cudaSuccess || n <= 0) {
             cudaGetLastError();
             n = std::max(1, h->sm_count * PB_CTAS / PB_CLUSTER);
         }
@@ -382,7 +389,7 @@ void part_block_launch(H *h, const BlockPartArgs &a, uint32_t n_bins) {
     }
     const int n_clusters = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)a.n_blocks, (int64_t)cached));
     cfg.gridDim = dim3((unsigned)(n_clusters * PB_CLUSTER));
-    CU(cudaLaunchKernelEx(&cfg, part_block_kernel<KW>, a));
+    CU(cudaLaunchKernelEx(&cfg, part_block_kernel<KW, NARROW>, a));
     h->st.kernel_launches++;
 }
 
@@ -399,8 +406,9 @@ struct ProbePiece {
 // of `pieces` (probe indices count across the pieces). On return ro owns the result arrays; returns the number of result
 // rows. PM_OUTER keeps the rows without a match (NULL build index), PM_PAIRS pays one compaction pass when there were any
 // (NULL-key rows count as rows without a match).
-int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces, const ProbePlan &pl, ResultOwner *ro, int64_t *n_build_null) {
-    const int kw = h->table_kw;
+int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces, const ProbePlan &pl, ResultOwner *ro, int64_t *n_build_null,
+                                   int piece_kw) {
+    const int kw = piece_kw > 0 ? piece_kw : h->table_kw;      // key width of the pieces: the table's, or 4 = zero-extended values of 8-byte keys
     const uint32_t P = 1u << h->radix_bits;
     int64_t n = 0;
     uint32_t n_blocks = 0;
@@ -416,12 +424,18 @@ int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces,
     void *tk = nullptr, *tr = nullptr, *seg = nullptr, *ob = nullptr, *ob2 = nullptr, *op2 = nullptr;
     Trace tr_;
     try {
-        CU(big_alloc(h, &tk, (size_t)n * kw + 16));
-        CU(big_alloc(h, &tr, (size_t)n * 4 + 16));
-        CU(big_alloc(h, &seg, (size_t)n_blocks * (P + 3) * 4 + 16));       // [n_blocks][P + 2] segment bounds, then [n_blocks] block bases
-        CU(big_alloc(h, &ob, (size_t)n * 8 + 16));
+        // 8-byte keys travel through the partitioned stream as 32-bit values while they fit (see part_block_kernel NARROW)
+        bool narrow = kw == 8 && h->narrow_ok;
+        uint32_t *d_ovf = (uint32_t *)(h->d_part_rows + (1 << PB_MAX_BITS) + 1);
+    again:
+        const int skw = narrow ? 4 : kw;                 // key width in the partitioned stream
+        if (tk) { big_free(h, tk); tk = nullptr; }
+        CU(big_alloc(h, &tk, (size_t)n * skw + 16));
+        if (!tr) CU(big_alloc(h, &tr, (size_t)n * 4 + 16));
+        if (!seg) CU(big_alloc(h, &seg, (size_t)n_blocks * (P + 3) * 4 + 16));       // [n_blocks][P + 2] segment bounds, then [n_blocks] block bases
+        if (!ob) CU(big_alloc(h, &ob, (size_t)n * 8 + 16));
         uint32_t *block_base = (uint32_t *)seg + (size_t)n_blocks * (P + 2);
-        CU(cudaMemsetAsync(h->d_part_rows, 0, (size_t)(P + 1) * 8, h->stream));
+        CU(cudaMemsetAsync(h->d_part_rows, 0, ((size_t)(1 << PB_MAX_BITS) + 2) * 8, h->stream));
         {
             PhaseTimer tm(h, &h->st.ms_probe_partition);
             uint32_t blk0 = 0;
@@ -444,17 +458,26 @@ int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces,
                 ba.part_rows = h->d_part_rows;
                 ba.rid_base = h->probe_rid_base;
                 ba.out_base = (uint32_t)row0;
-                if (kw == 8) part_block_launch<8>(h, ba, P); else part_block_launch<4>(h, ba, P);
+                ba.narrow_ovf = d_ovf;
+                if (narrow) part_block_launch<8, true>(h, ba, P);
+                else if (kw == 8) part_block_launch<8>(h, ba, P);
+                else part_block_launch<4>(h, ba, P);
                 CU(cudaGetLastError());
                 blk0 += piece_blocks[i];
                 row0 += pieces[i].n;
             }
             tm.stop();
         }
-        CU(cudaMemcpyAsync(h->h_part_rows, h->d_part_rows, (size_t)(P + 1) * 8, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaMemcpyAsync(h->h_part_rows, h->d_part_rows, ((size_t)(1 << PB_MAX_BITS) + 2) * 8, cudaMemcpyDeviceToHost, h->stream));
         CU(cudaMemsetAsync(h->d_ctr, 0, COUNTERS_LAUNCH_BYTES, h->stream));
         CU(cudaStreamSynchronize(h->stream));
         tr_.mark("block partition");
+        if (narrow && (uint32_t)h->h_part_rows[(1 << PB_MAX_BITS) + 1] != 0u) {
+            // a key outside [0, 2^32): once more with 8-byte keys, and no further attempts for this join
+            narrow = false;
+            h->narrow_ok = false;
+            goto again;
+        }
         const int64_t n_null = (int64_t)h->h_part_rows[P];
         int64_t biggest = 0;
         for (uint32_t p = 0; p < P; p++) biggest = std::max<int64_t>(biggest, (int64_t)h->h_part_rows[p]);
@@ -485,7 +508,7 @@ int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces,
                 if (l1) probe_dense_seg_kernel<kw_, mk_, true><<<grid, PD_THREADS, 0, h->stream>>>(a, sg);
                 else probe_dense_seg_kernel<kw_, mk_, false><<<grid, PD_THREADS, 0, h->stream>>>(a, sg);
             };
-            if (kw == 8) {
+            if (skw == 8) {
                 if (pl.mark) launch(std::integral_constant<int, 8>{}, std::true_type{});
                 else launch(std::integral_constant<int, 8>{}, std::false_type{});
             } else {
@@ -547,8 +570,8 @@ int64_t probe_dense_blocked(H *h, const void *d_keys, const uint8_t *d_validity,
 
 // b200j_probe_pieces: see include/b200join.h. The dense path behind the radix layout takes the pieces as they are; every
 // other path gets them concatenated into one device buffer first.
-void do_probe_pieces(H *h, int32_t partition, int32_t n_pieces, const void *const *piece_keys, const int64_t *piece_rows, uint32_t want,
-                     b200j_result *out) {
+void do_probe_pieces(H *h, int32_t partition, int32_t n_pieces, const void *const *piece_keys, const int64_t *piece_rows, int32_t piece_key_width,
+                     uint32_t want, b200j_result *out) {
     REQUIRE(partition >= 0 && partition < h->cfg.n_partitions, B200J_ERR_INVALID, "partition out of range");
     REQUIRE(h->built, B200J_ERR_INVALID, "probe before every partition finished the build side");
     REQUIRE(!h->probe_done[partition], B200J_ERR_STATE, "probe_pieces after probe_finish");
@@ -560,6 +583,8 @@ void do_probe_pieces(H *h, int32_t partition, int32_t n_pieces, const void *cons
     const ProbePlan pl = plan_for(h->cfg.join_type, (want & B200J_OUT_MATCHES_ONLY) != 0);
     const bool count_only = (want & B200J_OUT_COUNT_ONLY) != 0;
     const int kw = h->key_widths[0];
+    const int pkw = piece_key_width > 0 ? piece_key_width : kw;
+    REQUIRE(pkw == kw || (pkw == 4 && kw == 8), B200J_ERR_INVALID, "piece_key_width must be the key width, or 4 for 8-byte keys");
     std::vector<ProbePiece> pieces;
     int64_t n = 0;
     for (int i = 0; i < n_pieces; i++) {
@@ -578,12 +603,17 @@ void do_probe_pieces(H *h, int32_t partition, int32_t n_pieces, const void *cons
         if (n == 0) {
             total = 0;
         } else if (blocked) {
-            total = probe_dense_blocked_pieces(h, pieces.data(), (int)pieces.size(), pl, ro, &n_bnull);
+            total = probe_dense_blocked_pieces(h, pieces.data(), (int)pieces.size(), pl, ro, &n_bnull, pkw);
         } else {
             CU(big_alloc(h, &cat, (size_t)n * kw + 16));
             int64_t at = 0;
             for (const ProbePiece &pc : pieces) {
-                if (pc.n) CU(cudaMemcpyAsync((char *)cat + (size_t)at * kw, pc.keys, (size_t)pc.n * kw, cudaMemcpyDefault, h->stream));
+                if (pc.n && pkw == kw) CU(cudaMemcpyAsync((char *)cat + (size_t)at * kw, pc.keys, (size_t)pc.n * kw, cudaMemcpyDefault, h->stream));
+                else if (pc.n) {
+                    widen_u32_u64_kernel<<<grid_for(h, pc.n, 256, 8), 256, 0, h->stream>>>((const uint32_t *)pc.keys, (unsigned long long *)cat + at, pc.n);
+                    h->st.kernel_launches++;
+                    CU(cudaGetLastError());
+                }
                 at += pc.n;
             }
             total = probe_device(h, cat, nullptr, 0, n, pl, count_only, ro, &n_bnull);

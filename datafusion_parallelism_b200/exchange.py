@@ -116,12 +116,14 @@ def shuffle_scatter(join: HashJoin, n_dest: int, dest_keys: Sequence[int], dest_
     join._check(N.lib().b200j_shuffle_scatter(join._h, n_dest, dk, dr, do, rowid_base))
 
 
-def shuffle_local_scatter(join: HashJoin, keys, n_dest: int, send_keys_ptr: int, send_rid_ptr: int, region_rows: int, rowid_base: int = 0) -> np.ndarray:
+def shuffle_local_scatter(join: HashJoin, keys, n_dest: int, send_keys_ptr: int, send_rid_ptr: int, region_rows: int, rowid_base: int = 0,
+                          key_out_width: int = 0) -> np.ndarray:
     """b200j_shuffle_local_scatter: one pass over `keys` (device column); every (key, row id) lands in the region of its
     destination inside the local send buffers. Returns the rows per region: [ranks][NULL keys]([hot keys])."""
     b, keep = make_batch([keys])
     counts = (C.c_int64 * (n_dest + 2))()
-    join._check(N.lib().b200j_shuffle_local_scatter(join._h, C.byref(b), n_dest, send_keys_ptr, send_rid_ptr, region_rows, rowid_base, counts))
+    join._check(N.lib().b200j_shuffle_local_scatter(join._h, C.byref(b), n_dest, send_keys_ptr, send_rid_ptr, region_rows, rowid_base,
+                                                    key_out_width, counts))
     return np.array(list(counts), dtype=np.int64)
 
 
@@ -160,6 +162,7 @@ class DistributedJoin:
         self.group = group
         self.world, self.rank = dist.get_world_size(), dist.get_rank()
         self.mode, self.kw = mode, key_width
+        self.narrow_keys = join_kwargs.pop("narrow_keys", True)      # mode "pull": 8-byte probe keys cross NVLink as 32-bit values while they fit
         self.stream = stream if stream is not None else torch.cuda.current_stream()
         join_kwargs.setdefault("device", torch.cuda.current_device())     # one process per GPU: the handle lives on this rank's device
         self.join = HashJoin(join_type, key_widths=(key_width,), stream=self.stream.cuda_stream, **join_kwargs)
@@ -358,17 +361,28 @@ class DistributedJoin:
                 side.send_pr = _PeerBuffer(xj, dist, n_regions * need * 4 + 64)
                 side.send_cap = need
             cap = side.send_cap
+            # probe-side keys cross NVLink as 32-bit values while every rank's keys fit (8-byte keys only; the build side is
+            # appended to the store as it is, so it stays wide)
+            okw = 4 if (kw == 8 and side is not self.build and self.narrow_keys and getattr(side, "narrow", True)) else kw
+            ovf = wide = 0
             try:
-                counts, ovf = shuffle_local_scatter(xj, keys, W, side.send_pk.local, side.send_pr.local, cap, rowid_base), 0
+                counts = shuffle_local_scatter(xj, keys, W, side.send_pk.local, side.send_pr.local, cap, rowid_base, key_out_width=okw)
             except B200JoinError as e:
-                if "region too small" not in str(e):
+                counts = np.zeros(W + 2, dtype=np.int64)
+                if "region too small" in str(e):
+                    ovf = 1
+                elif "do not fit 32 bits" in str(e):
+                    wide = 1
+                else:
                     raise
-                counts, ovf = np.zeros(W + 2, dtype=np.int64), 1
             with torch.cuda.stream(xs):
-                mine = torch.from_numpy(np.concatenate([counts[:W], [ovf]]).astype(np.int64)).to(keys.device)
-                allc = torch.empty(W * (W + 1), dtype=torch.int64, device=keys.device)
+                mine = torch.from_numpy(np.concatenate([counts[:W], [ovf, wide]]).astype(np.int64)).to(keys.device)
+                allc = torch.empty(W * (W + 2), dtype=torch.int64, device=keys.device)
                 dist.all_gather_into_tensor(allc, mine, group=self.group)     # ... and every peer's scatter has finished
-                full = allc.cpu().numpy().reshape(W, W + 1)
+                full = allc.cpu().numpy().reshape(W, W + 2)
+            if int(full[:, W + 1].sum()):
+                side.narrow = False                      # somebody's keys need 64 bits: every rank scatters again, wide, from now on
+                continue
             if int(full[:, W].sum()) == 0:
                 break
             grow *= 2.0                                  # somebody's region overflowed: everybody retries with larger ones
@@ -379,16 +393,18 @@ class DistributedJoin:
         order = [(me + i) % W for i in range(W)]         # my own region first, then the peers behind me: no two ranks start on the same source
         plan = ExchangePlan(matrix, me, src_order=order)
         side.plan = plan
-        side.pieces = [(side.send_pk.ptrs[s] + me * cap * kw, int(matrix[s, me])) for s in order]
+        side.piece_kw = okw
+        side.pieces = [(side.send_pk.ptrs[s] + me * cap * okw, int(matrix[s, me])) for s in order]
         side.rid_pieces = [(side.send_pr.ptrs[s] + me * cap * 4, int(matrix[s, me])) for s in order]
         n_null = int(counts[W])
-        side.null_keys = torch.as_tensor(_RawCudaArray(side.send_pk.local + W * cap * kw, n_null, "<i8" if kw == 8 else "<i4"), device=keys.device) if n_null else None
+        side.null_keys = torch.as_tensor(_RawCudaArray(side.send_pk.local + W * cap * okw, n_null, "<i8" if okw == 8 else "<i4"), device=keys.device) if n_null else None
         side.null_rid = torch.as_tensor(_RawCudaArray(side.send_pr.local + W * cap * 4, n_null, "<i4"), device=keys.device) if n_null else None
         side.n_hot = 0
         if hot:
             side.n_hot = int(counts[W + 1])
             m = max(side.n_hot, 1)
-            side.hot_keys = torch.as_tensor(_RawCudaArray(side.send_pk.local + (W + 1) * cap * kw, m, "<i8" if kw == 8 else "<i4"), device=keys.device)
+            hk_ = torch.as_tensor(_RawCudaArray(side.send_pk.local + (W + 1) * cap * okw, m, "<i8" if okw == 8 else "<i4"), device=keys.device)
+            side.hot_keys = hk_ if okw == kw else (hk_.to(torch.int64) & 0xFFFFFFFF)
             side.hot_rid = torch.as_tensor(_RawCudaArray(side.send_pr.local + (W + 1) * cap * 4, m, "<i4"), device=keys.device)
         side.recv_keys_ptr = side.recv_rid_ptr = None
         return int(plan.recv_rows[me])
@@ -397,19 +413,24 @@ class DistributedJoin:
         """The rows this rank received for one side as ONE local tensor (copies: tests, verification, late materialisation)."""
         torch = self.torch
         pieces = side.pieces if what == "keys" else side.rid_pieces
-        ts = "<i4" if (what != "keys" or self.kw == 4) else "<i8"
+        pkw = getattr(side, "piece_kw", self.kw)
+        ts = "<i4" if (what != "keys" or pkw == 4) else "<i8"
         dev = torch.device("cuda", torch.cuda.current_device())
         parts = [torch.as_tensor(_RawCudaArray(p, m, ts)).to(dev) for p, m in pieces if m]
         if not parts:
             return torch.empty(0, dtype=torch.int32 if ts == "<i4" else torch.int64, device=dev)
-        return torch.cat(parts)
+        out = torch.cat(parts)
+        if what == "keys" and pkw != self.kw:           # 32-bit pieces of 8-byte keys: zero-extended
+            out = out.to(torch.int64) & 0xFFFFFFFF
+        return out
 
     def _local_probe(self, partition: int, side: _Side, want: int):
         pieces = [(p, m) for p, m in side.pieces]
-        if len(pieces) == 1:
+        pkw = getattr(side, "piece_kw", self.kw)
+        if len(pieces) == 1 and pkw == self.kw:
             p, m = pieces[0]
             return self.join.probe_batch(partition, [_dev_column(p, m, self.kw, keep=(side.keys,))], want=want)
-        return self.join.probe_pieces(partition, pieces, want=want)
+        return self.join.probe_pieces(partition, pieces, want=want, key_width=pkw if pkw != self.kw else 0)
 
     # ---- the HashJoin call shape --------------------------------------------------------------------------------
     def _timed(self, which: str, fn):

@@ -289,7 +289,7 @@ class HashJoin:
         self._check(N.lib().b200j_probe_batch(self._h, partition, C.byref(b), want, C.byref(r)))
         return PairResult(self, r)
 
-    def probe_pieces(self, partition: int, pieces: Sequence, want: int = OUT_PAIRS) -> PairResult:
+    def probe_pieces(self, partition: int, pieces: Sequence, want: int = OUT_PAIRS, key_width: int = 0) -> PairResult:
         """One probe batch handed over as several device-resident pieces of its key column: `pieces` = [(device pointer, rows)].
         The batch is their concatenation (b200j_probe_pieces); a pointer may be peer memory mapped with b200j_ipc_open."""
         n = len(pieces)
@@ -297,7 +297,7 @@ class HashJoin:
         rows = (C.c_int64 * max(1, n))(*[int(m) for _, m in pieces])
         r = N.Result()
         r.struct_size = C.sizeof(N.Result)
-        self._check(N.lib().b200j_probe_pieces(self._h, partition, n, ptrs, rows, want, C.byref(r)))
+        self._check(N.lib().b200j_probe_pieces(self._h, partition, n, ptrs, rows, key_width, want, C.byref(r)))
         return PairResult(self, r)
 
     def apply_pairs(self, partition: int, n_probe_rows: int, build_idx, probe_idx, want: int = OUT_PAIRS | OUT_HOST) -> PairResult:

@@ -247,6 +247,7 @@ int32_t b200j_probe_batch(b200j_handle *h, int32_t partition, const b200j_batch 
  * the multi-GPU exchange is fused into the join (DistributedJoin mode "pull": the pieces are the regions the source ranks
  * scattered for this rank with b200j_shuffle_local_scatter). */
 int32_t b200j_probe_pieces(b200j_handle *h, int32_t partition, int32_t n_pieces, const void *const *piece_keys, const int64_t *piece_rows,
+                           int32_t piece_key_width /* 0 = the join's key width; 4 with 8-byte join keys = zero-extended 32-bit values */,
                            uint32_t want, b200j_result *out);
 /* Join-type post-processing (a7) of caller-filtered pairs of one probe batch of `n_probe_rows` rows. */
 int32_t b200j_apply_pairs(b200j_handle *h, int32_t partition, int64_t n_probe_rows, int32_t mem, int64_t n_pairs,
@@ -284,7 +285,11 @@ int32_t b200j_shuffle_scatter(b200j_handle *h, int32_t n_dest, void *const *dest
  * chunk runs). Returns B200J_ERR_INVALID with "region too small" when a region overflowed (nothing past a region's end is
  * written): call again with larger regions. */
 int32_t b200j_shuffle_local_scatter(b200j_handle *h, const b200j_batch *batch, int32_t n_dest, void *send_keys, uint32_t *send_rowid,
-                                    int64_t region_rows, uint32_t rowid_base, int64_t *counts /* [n_dest + 1], [n_dest + 2] with a hot set */);
+                                    int64_t region_rows, uint32_t rowid_base, int32_t key_out_width,
+                                    int64_t *counts /* [n_dest + 1], [n_dest + 2] with a hot set */);
+/* key_out_width: 0 / the key width = keys as they are; 4 with 8-byte keys = the regions take the keys as 32-bit values (half
+ * the bytes the peers pull over NVLink; b200j_probe_pieces takes such pieces with piece_key_width = 4). A key outside
+ * [0, 2^32) then fails the call with B200J_ERR_INVALID "keys do not fit 32 bits": repeat it with key_out_width = 8. */
 /* Enqueue a device-to-device copy (same device, or a peer mapped with b200j_ipc_open) on one of the handle's copy lanes
  * (0..3); it starts after the work enqueued on the handle's stream so far. b200j_copy_wait blocks until every lane is idle. */
 int32_t b200j_copy_async(b200j_handle *h, void *dst, const void *src, size_t bytes, int32_t lane);

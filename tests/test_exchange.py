@@ -221,3 +221,36 @@ def test_single_pass_local_scatter_matches_two_pass(dtype, world, null_frac):
             shuffle_local_scatter(j, col, world, send_k.data_ptr(), send_r.data_ptr(), small)
         assert "region too small" in str(e.value)
         assert (send_r[(world + 1) * cap:].cpu().numpy() == -1).all()                       # and no write beyond the regions handed in
+
+
+@pytest.mark.gpu
+def test_local_scatter_narrow_keys():
+    """key_out_width = 4: the regions receive 8-byte keys as 32-bit values; a key that does not fit fails the call."""
+    import torch
+    import datafusion_parallelism_b200 as d
+    from datafusion_parallelism_b200.exchange import shuffle_local_scatter
+    rng = np.random.default_rng(2)
+    n, world = 150_003, 4
+    keys = rng.integers(0, 2**32, n).astype(np.int64)
+    with d.HashJoin("inner", key_widths=(8,)) as j:
+        dev = torch.from_numpy(keys).cuda()
+        cap = n
+        wide_k = torch.empty((world + 2) * cap, dtype=torch.int64, device="cuda")
+        wide_r = torch.empty((world + 2) * cap, dtype=torch.int32, device="cuda")
+        c8 = shuffle_local_scatter(j, dev, world, wide_k.data_ptr(), wide_r.data_ptr(), cap)
+        nar_k = torch.empty((world + 2) * cap, dtype=torch.int32, device="cuda")
+        nar_r = torch.empty((world + 2) * cap, dtype=torch.int32, device="cuda")
+        c4 = shuffle_local_scatter(j, dev, world, nar_k.data_ptr(), nar_r.data_ptr(), cap, key_out_width=4)
+        assert np.array_equal(c4, c8)
+        for dst in range(world):
+            m = int(c8[dst])
+            rows = nar_r[dst * cap: dst * cap + m].cpu().numpy().view(np.uint32).astype(np.int64)
+            got = nar_k[dst * cap: dst * cap + m].cpu().numpy().view(np.uint32).astype(np.int64)
+            assert np.array_equal(got, keys[rows])
+            assert np.array_equal(np.sort(rows), np.sort(wide_r[dst * cap: dst * cap + m].cpu().numpy().view(np.uint32).astype(np.int64)))
+        for bad in (-1, 2**32):
+            keys2 = keys.copy()
+            keys2[n // 2] = bad
+            with pytest.raises(d.B200JoinError) as e:
+                shuffle_local_scatter(j, torch.from_numpy(keys2).cuda(), world, nar_k.data_ptr(), nar_r.data_ptr(), cap, key_out_width=4)
+            assert "do not fit 32 bits" in str(e.value)

@@ -374,3 +374,57 @@ def test_probe_pieces_equals_one_batch(pkg, join_type, unique, layout, radix_bit
     assert np.array_equal(got[0][o1], want[0][o2]) and np.array_equal(got[1][o1], want[1][o2])
     if unique and layout == "radix" and join_type in ("inner", "right", "full"):
         assert st["seg_probe_launches"] >= 1
+
+
+@pytest.mark.parametrize("join_type", ["inner", "full"])
+def test_narrow_key_stream_falls_back_on_wide_keys(pkg, join_type):
+    """Behind the radix layout 8-byte probe keys travel through the partitioned stream as 32-bit values while they fit; a batch
+    with a key outside [0, 2^32) (negative, or large) must be repeated wide -- results are those of the oracle either way."""
+    rng = np.random.default_rng(31)
+    small = rng.permutation(200_000)[:60_000].astype(np.int64)
+    wide = np.array([-1, -2**62, 2**32, 2**32 + 5, 2**63 - 1, 2**40 + 123], dtype=np.int64)
+    bk = np.concatenate([small, wide])
+    batches = [rng.integers(0, 220_000, 100_000).astype(np.int64),                                  # fits 32 bits
+               np.concatenate([rng.integers(0, 220_000, 50_000), wide, [-5, 2**33]]).astype(np.int64),     # does not
+               rng.integers(0, 220_000, 70_001).astype(np.int64)]
+    oj = oracle.OracleJoin(join_type, [bk])
+    with pkg.HashJoin(join_type, key_widths=(8,), layout="radix", radix_bits=4) as j:
+        j.build_push(0, [bk])
+        j.build_finish(0)
+        for i, pb in enumerate(batches):
+            r = j.probe_batch(0, [pb])
+            got, want = r.numpy(), oj.probe_batch([pb], len(pb))
+            r.release()
+            o1, o2 = np.lexsort(got), np.lexsort(want)
+            assert got[0].shape == want[0].shape, i
+            assert np.array_equal(got[0][o1], want[0][o2]) and np.array_equal(got[1][o1], want[1][o2]), i
+        assert j.stats()["seg_probe_launches"] == 3
+
+
+@pytest.mark.parametrize("unique,layout,radix_bits", [(True, "radix", 5), (False, "radix", 3), (True, "direct", 0)])
+def test_probe_pieces_with_32_bit_keys_of_a_64_bit_join(pkg, unique, layout, radix_bits):
+    """piece_key_width = 4: the pieces hold the zero-extended 32-bit values of 8-byte keys (what the "pull" exchange sends
+    over NVLink while every key fits 32 bits)."""
+    import torch
+    rng = np.random.default_rng(hash((unique, layout, "n32")) & 0xFFFFFFFF)
+    nb = 50_000
+    bk = (rng.permutation(nb * 2)[:nb] if unique else rng.integers(0, nb // 4, nb)).astype(np.int64)
+    bk[:3] = [2**32 + 7, -9, 2**40]                                   # build keys no 32-bit probe value can reach
+    lens = [40_001, 7, 4096 * 8 * 2 + 11]
+    pk32 = rng.integers(0, nb * 2 + 50, sum(lens)).astype(np.uint32)
+    pk32[::5000] = 0xFFFFFFF0                                          # large unsigned values stay positive when widened
+    want = oracle.OracleJoin("inner", [bk]).probe_batch([pk32.astype(np.int64)], len(pk32))
+    dev = torch.from_numpy(pk32.view(np.int32)).cuda()
+    pieces, at = [], 0
+    for m in lens:
+        pieces.append((dev[at:at + m].data_ptr(), m))
+        at += m
+    with pkg.HashJoin("inner", key_widths=(8,), layout=layout, radix_bits=radix_bits) as j:
+        j.build_push(0, [bk])
+        j.build_finish(0)
+        r = j.probe_pieces(0, pieces, want=pkg.OUT_PAIRS | pkg.OUT_HOST, key_width=4)
+        got = r.numpy()
+        r.release()
+    o1, o2 = np.lexsort(got), np.lexsort(want)
+    assert got[0].shape == want[0].shape
+    assert np.array_equal(got[0][o1], want[0][o2]) and np.array_equal(got[1][o1], want[1][o2])
