@@ -68,7 +68,7 @@ def parse_args():
     ap.add_argument("--no-gather", action="store_true")
     ap.add_argument("--host-chunk-rows", type=int, default=1 << 27, help="N>1 e2e: probe rows per pipelined host chunk (DistributedJoin.probe_host_chunks)")
     ap.add_argument("--exchange-chunk-rows", type=int, default=0, help="N>1: > 0 = probe rows per exchange / local-join pipeline stage (DistributedJoin.probe_chunks)")
-    ap.add_argument("--shuffle", default="p2p", choices=["p2p", "nccl", "ce", "pull"], help="N>1: fused peer-store scatter, NCCL all-to-all, or single-pass local scatter + copy-engine transfers")
+    ap.add_argument("--shuffle", default="pull", choices=["p2p", "nccl", "ce", "pull"], help="N>1: pull = single-pass local scatter, the receivers' partition pass pulls the regions over NVLink (default); p2p = fused peer-store scatter; nccl = NCCL all-to-all; ce = copy-engine transfers")
     return ap.parse_args()
 
 
@@ -217,7 +217,7 @@ def run_reference(args):
 def workload_config(args, n_gpus):
     return {"workload": f"C2: {args.build_rows}-row int64 unique-key build x {args.probe_rows}-row uniform probe, 1:1 matches, "
                         f"{'one int64 build payload column, ' if n_gpus == 1 else ''}inner join, (build_idx u64, probe_idx u32) pairs out" + (f"; per GPU, {n_gpus} GPUs, key space x{n_gpus}, "
-                        "hash-partition + NVLink exchange of both sides" if n_gpus > 1 else ""),
+                        f"hash-partition + NVLink exchange of both sides (mode {args.shuffle})" if n_gpus > 1 else ""),
             "build_rows_per_gpu": args.build_rows, "probe_rows_per_gpu": args.probe_rows,
             "probe_chunk_rows": args.chunk_rows if (n_gpus == 1 or args.exchange_chunk_rows <= 0) else min(args.chunk_rows, args.exchange_chunk_rows),
             "l2": "inputs (8 GB probe keys per step) are far larger than the 126 MB L2; no flush needed"}
