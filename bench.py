@@ -363,7 +363,11 @@ def run_b200(args):
     table_alg = min(st["table_bytes"], 32 * max(1, st["distinct_keys"]) + 4096)
     if dense:        # 8 B key in + 8 B build index out per row, plus ONE pass over the table per launch (it is L2-resident per partition)
         seg = st.get("seg_probe_launches", 0) == st["probe_launches"]
-        bpt, kname, table_b = B_PROBE_DENSE, ("probe_dense_seg_kernel<8,false,false>" if seg else "probe_dense_kernel<8,false,true,false>"), table_alg
+        narrow = seg and st.get("narrow_probe_launches", 0) == st["probe_launches"]
+        # the partitioned stream carries the 8-byte keys as 32-bit values when they all fit: the kernel then READS 4 B per row
+        bpt = 12 if narrow else B_PROBE_DENSE
+        kname = ("probe_dense_seg_kernel<4,false,false>" if narrow else "probe_dense_seg_kernel<8,false,false>") if seg else "probe_dense_kernel<8,false,true,false>"
+        table_b = table_alg
     elif radix:
         bpt, kname, table_b = B_PROBE_KERNEL_RADIX, "probe_fast_kernel<8,PM_PAIRS,false,true>", table_alg
     else:
@@ -374,11 +378,16 @@ def run_b200(args):
                 "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s", "frac": achieved / hbm_gbs, "traffic": None,
                 "peak_source": peak_src, "bytes_per_tuple": bpt, "table_bytes_per_launch": table_b,
                 "tuples_per_launch": rows_per_launch, "ms_per_launch": probe_launch_ms}
+    # DRAM bytes of that kernel per launch from the committed ncu --set full capture of THIS build (scripts/make_traffic_json.py);
+    # only quoted when the capture is of the kernel that ran and of the same number of rows
     tr = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr):
         try:
             with open(tr) as f:
-                roofline["traffic"] = json.load(f).get("probe_kernel_dram_bytes_per_launch")
+                tj = json.load(f)
+            if tj.get("kernel") == kname and abs(tj.get("rows_per_launch", 0) - rows_per_launch) <= 0.01 * rows_per_launch:
+                roofline["traffic"] = tj.get("probe_kernel_dram_bytes_per_launch")
+                roofline["traffic_source"] = tj.get("source")
         except Exception:
             pass
     local_build = st["build_rows"]

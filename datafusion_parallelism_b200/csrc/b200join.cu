@@ -120,6 +120,10 @@ struct b200j_handle {
     int probe_ctas_per_sm = 4;
     int dense_ctas_per_sm = 4;
     int seg_ctas_per_sm = 4;
+    bool fused_build = false;          // radix layout: table clear + insert in one persistent kernel (build_insert_fused_kernel). Measured NEUTRAL at C2
+                                       // (insert phase 3.35 vs 3.41 ms: the insert is not waiting on DRAM), so the memset + build_insert_kernel
+                                       // path without a spin-wait stays the default; B200J_FUSED_BUILD=1 selects it
+    int fused_ctas_per_sm = 5;
     bool narrow_ok = true;             // 8-byte probe keys go through the partitioned stream as 32-bit values until one does not fit (B200J_NO_NARROW=1: never)
     bool block_part_ok = true;         // B200J_NO_BLOCK_PART=1: the dense radix probe keeps the two-pass global partition of round 1
     int pb_clusters[2][PB_MAX_BITS + 1] = {};   // resident clusters of part_block_kernel per key width / radix bits (0 = not asked yet)
@@ -172,6 +176,9 @@ struct b200j_handle {
     std::vector<CachedBlock> blocks;   // device buffers >= 1 MiB, reused across calls (see big_alloc)
     size_t blocks_free_bytes = 0;
     size_t cache_limit = (size_t)64 << 30;   // free cached bytes kept at most (set in b200j_create)
+    bool guard = false;                // B200J_GUARD=1: every block of >= 1 MiB sits between two 256-byte canaries that are checked when it is
+                                       // freed (compute-sanitizer is closed on this GPU pool: this is the library's own out-of-bounds check)
+    long guard_violations = 0;
     b200j_stats st{};
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 
@@ -214,8 +221,50 @@ constexpr size_t BIG_BLOCK = (size_t)1 << 20;
 // Free cached blocks are kept up to h->cache_limit bytes (40 % of the device's memory unless B200J_CACHE_LIMIT_BYTES says
 // otherwise); b200j_trim gives all of them back at once (another allocator in the process may need the room).
 
+constexpr size_t GUARD_BYTES = 256;
+constexpr int GUARD_PATTERN = 0xA5;
+void guard_check(H *h, void *user_ptr, size_t user_bytes);
+
+template <typename T>
+cudaError_t big_alloc_raw(H *h, T **out, size_t bytes);
+cudaError_t big_free_raw(H *h, void *p);
+
+struct GuardRec { void *user; size_t bytes; };
+std::mutex g_guard_mu;
+std::vector<GuardRec> g_guard_recs;
+
 template <typename T>
 cudaError_t big_alloc(H *h, T **out, size_t bytes) {
+    if (!h->guard) return big_alloc_raw(h, out, bytes);
+    *out = nullptr;
+    const size_t ub = (bytes + 15) & ~(size_t)15;
+    char *raw = nullptr;
+    cudaError_t e = big_alloc_raw(h, &raw, ub + 2 * GUARD_BYTES);
+    if (e != cudaSuccess) return e;
+    cudaMemsetAsync(raw, GUARD_PATTERN, GUARD_BYTES, h->stream);
+    cudaMemsetAsync(raw + GUARD_BYTES + ub, GUARD_PATTERN, GUARD_BYTES, h->stream);
+    *out = (T *)(raw + GUARD_BYTES);
+    std::lock_guard<std::mutex> g(g_guard_mu);
+    g_guard_recs.push_back(GuardRec{raw + GUARD_BYTES, ub});
+    return cudaSuccess;
+}
+
+cudaError_t big_free(H *h, void *p) {
+    if (!p || !h->guard) return big_free_raw(h, p);
+    size_t ub = 0;
+    bool found = false;
+    {
+        std::lock_guard<std::mutex> g(g_guard_mu);
+        for (size_t i = 0; i < g_guard_recs.size(); i++)
+            if (g_guard_recs[i].user == p) { ub = g_guard_recs[i].bytes; g_guard_recs.erase(g_guard_recs.begin() + i); found = true; break; }
+    }
+    if (!found) return big_free_raw(h, p);          // allocated before the guard was switched on
+    guard_check(h, p, ub);
+    return big_free_raw(h, (char *)p - GUARD_BYTES);
+}
+
+template <typename T>
+cudaError_t big_alloc_raw(H *h, T **out, size_t bytes) {
     *out = nullptr;
     if (bytes < BIG_BLOCK) return cudaMallocAsync((void **)out, bytes, h->stream);
     int best = -1;
@@ -250,7 +299,7 @@ cudaError_t big_alloc(H *h, T **out, size_t bytes) {
     return cudaSuccess;
 }
 
-cudaError_t big_free(H *h, void *p) {
+cudaError_t big_free_raw(H *h, void *p) {
     if (!p) return cudaSuccess;
     for (size_t i = 0; i < h->blocks.size(); i++)
         if (h->blocks[i].p == p) {
@@ -269,6 +318,23 @@ cudaError_t big_free(H *h, void *p) {
             return cudaSuccess;
         }
     return cudaFreeAsync(p, h->stream);
+}
+
+void guard_check(H *h, void *user_ptr, size_t user_bytes) {
+    unsigned char host[2 * GUARD_BYTES];
+    cudaStreamSynchronize(h->stream);
+    if (cudaMemcpy(host, (char *)user_ptr - GUARD_BYTES, GUARD_BYTES, cudaMemcpyDeviceToHost) != cudaSuccess ||
+        cudaMemcpy(host + GUARD_BYTES, (char *)user_ptr + user_bytes, GUARD_BYTES, cudaMemcpyDeviceToHost) != cudaSuccess) {
+        cudaGetLastError();
+        return;
+    }
+    for (size_t i = 0; i < 2 * GUARD_BYTES; i++)
+        if (host[i] != GUARD_PATTERN) {
+            h->guard_violations++;
+            fprintf(stderr, "[b200j] GUARD VIOLATION: %s canary of a %zu-byte block overwritten at byte %zu\n", i < GUARD_BYTES ? "front" : "back",
+                    user_bytes, i % GUARD_BYTES);
+            break;
+        }
 }
 
 // Gives every cached free block back to the stream-ordered pool and trims the pool itself (b200j_trim).
@@ -1708,6 +1774,12 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
             if (const char *e = getenv("B200J_SEG_CTAS")) h->seg_ctas_per_sm = std::max(1, atoi(e));
             if (const char *e = getenv("B200J_NO_BLOCK_PART")) h->block_part_ok = atoi(e) == 0;
             if (const char *e = getenv("B200J_NO_NARROW")) h->narrow_ok = atoi(e) == 0;
+            if (const char *e = getenv("B200J_FUSED_BUILD")) h->fused_build = atoi(e) != 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, build_insert_fused_kernel<8>, TILE_THREADS, 0) == cudaSuccess && occ > 0)
+                h->fused_ctas_per_sm = occ;
+            else
+                cudaGetLastError();
+            if (const char *e = getenv("B200J_FUSED_CTAS")) h->fused_ctas_per_sm = std::max(1, atoi(e));
             if (const char *e = getenv("B200J_NO_DENSE")) h->dense_ok = atoi(e) == 0;
             if (const char *e = getenv("B200J_DENSE_MISS_MAX")) h->dense_miss_max = (float)atof(e);
             if (const char *e = getenv("B200J_L1_TABLE_BYTES")) h->l1_table_bytes = (uint64_t)atoll(e);
@@ -1719,6 +1791,7 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
         h->l2_bytes = prop.l2CacheSize;
         h->cache_limit = (size_t)((double)prop.totalGlobalMem * 0.4);
         if (const char *e = getenv("B200J_CACHE_LIMIT_BYTES")) h->cache_limit = (size_t)std::max<long long>(0, atoll(e));
+        if (const char *e = getenv("B200J_GUARD")) h->guard = atoi(e) != 0;
         set_kernel_attributes();       // per device: opt-in shared-memory sizes of the partition kernels
         if (cfg->stream) {
             h->stream = (cudaStream_t)cfg->stream;
@@ -1812,7 +1885,7 @@ int32_t b200j_reset_stats(b200j_handle *h) {
     h->st.ms_build_copy = h->st.ms_build_partition = h->st.ms_build_insert = 0;
     h->st.ms_probe_partition = h->st.ms_probe = h->st.ms_gather = 0;
     h->st.probe_launches = h->st.kernel_launches = h->st.probe_retries = 0;
-    h->st.dense_probe_launches = h->st.compact_launches = h->st.seg_probe_launches = 0;
+    h->st.dense_probe_launches = h->st.compact_launches = h->st.seg_probe_launches = h->st.narrow_probe_launches = 0;
     h->st.ms_exchange_partition = 0;
     return B200J_OK;
 }
@@ -1834,7 +1907,10 @@ int32_t b200j_reset(b200j_handle *h) {
 }
 
 int32_t b200j_synchronize(b200j_handle *h) {
-    return guarded(h, [&] { CU(cudaStreamSynchronize(h->stream)); });
+    return guarded(h, [&] {
+        CU(cudaStreamSynchronize(h->stream));
+        REQUIRE(h->guard_violations == 0, B200J_ERR_CUDA, "B200J_GUARD: a kernel wrote outside one of the handle's buffers (see stderr)");
+    });
 }
 
 int32_t b200j_trim(b200j_handle *h) {

@@ -17,6 +17,7 @@
 //   bitmap_select_kernel             get_unset_indices_array / get_set_indices_array (concurrent_bit_set.rs:93-131)
 #pragma once
 #include <cstdint>
+#include <type_traits>
 #include <cuda_runtime.h>
 
 namespace b200j {
@@ -408,7 +409,16 @@ __device__ __forceinline__ Slot *find_or_claim(const TableView &tv, const HashKe
         for (int j = 0; j < 2; j++, s++) {
             unsigned long long cur = k[j];
             if (cur == 0ULL) {
+#if defined(B200J_INS_TEST) && B200J_INS_TEST == 1
+                // TIMING EXPERIMENT ONLY (racy): plain 16-byte store instead of the compare-and-swap
+                *reinterpret_cast<ulonglong2 *>(s) = make_ulonglong2((unsigned long long)key, (unsigned long long)row | (1ULL << 32));
+                cur = 0ULL;
+#elif defined(B200J_INS_TEST) && B200J_INS_TEST == 2
+                cur = atomicCAS(&s->key, 0ULL, (unsigned long long)key);          // 64-bit claim, row / count stored separately
+                if (cur == 0ULL) { s->row = row; s->count = 1u; }
+#else
                 cur = CLAIM128 ? claim_slot128(s, key, row) : atomicCAS(&s->key, 0ULL, (unsigned long long)key);
+#endif
                 if (cur == 0ULL) { distinct++; return s; }
             }
             if (cur == key) return s;
@@ -475,6 +485,119 @@ __global__ void __launch_bounds__(TILE_THREADS) build_insert_kernel(BuildArgs a)
         if (u) atomicAdd(&a.ctr->dup_rows, u);
         if (m) atomicAdd(&a.ctr->multi_slots, m);
         if (z) atomicAdd(&a.ctr->null_keys, z);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Radix layout, round 2: table clear and insert in ONE persistent kernel. The separate cudaMemset of the whole slot array
+// (3.8 GB at C2) wrote zeros to HBM that the insert kernel then pulled back into L2 line by line before it could claim a
+// slot (ncu r1_k: 7.6 GB of DRAM traffic for 2.8 GB of algorithmic bytes, the look + claim chain of every row waiting on
+// DRAM). Here the work items of ONE ordered sequence are handed out by a global counter:
+//     C(0), C(1) I(0), C(2) I(1), ... C(P-1) I(P-2), I(P-1)        C(p) = clear partition p's table (256 KB per item)
+//                                                                   I(p) = insert 1024 rows of partition p
+// so a partition's table is zeroed (full-line writes: no DRAM read) just before its rows arrive and is still in L2 when they
+// do. An I(p) item waits until every C(p) item has FINISHED (done[p] == its item count): all of them were claimed earlier in
+// the sequence by CTAs that are running, so the wait is bounded; a watchdog gives up (error flag) instead of hanging.
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t FB_CLEAR_BYTES = 256u << 10;
+constexpr uint32_t FB_TILE_ROWS = 1024;
+struct FusedBuildArgs {
+    BuildArgs           b;            // keys / rowid = the partitioned build stream, n = its rows
+    const uint32_t     *part_off;     // [P + 1] first row of every partition in the stream
+    const uint32_t     *seq_off;      // [2P + 1] first item of every group of the sequence: group 2p = C(p), group 2p + 1 = I(p) (see fused_group)
+    uint32_t            n_parts;
+    uint32_t            n_items;
+    unsigned int       *done;         // [P] finished clear items per partition
+    unsigned int       *error;        // watchdog
+};
+// group g of the sequence: g = 0 -> C(0); then pairs (C(p + 1), I(p)) for p = 0 .. P-2; last group I(P-1)
+__device__ __forceinline__ void fused_group(uint32_t g, uint32_t P, bool &is_clear, uint32_t &p) {
+    if (g == 0) { is_clear = true; p = 0; return; }
+    const uint32_t k = g - 1;                         // k even: C(k/2 + 1), k odd: I(k/2)   -- except past the last clear
+    if (k < 2 * (P - 1)) { is_clear = (k & 1u) == 0u; p = is_clear ? k / 2 + 1 : k / 2; return; }
+    is_clear = false; p = P - 1;
+}
+
+template <int KW>
+__global__ void __launch_bounds__(TILE_THREADS) build_insert_fused_kernel(FusedBuildArgs f) {
+    using KeyT = typename std::conditional<KW == 8, unsigned long long, uint32_t>::type;
+    const BuildArgs &a = f.b;
+    const int t = threadIdx.x;
+    const uint32_t P = f.n_parts, n_groups = 2 * P;
+    uint32_t distinct = 0, dups = 0, multi = 0;
+    __shared__ unsigned int s_item;
+    for (;;) {
+        __syncthreads();
+        if (t == 0) s_item = atomicAdd(&a.ctr->next_tile, 1u);
+        __syncthreads();
+        const uint32_t item = s_item;
+        if (item >= f.n_items) break;
+        // group of this item: the last g with seq_off[g] <= item (2P groups: binary search)
+        uint32_t lo = 0, hi = n_groups;
+        while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (__ldg(f.seq_off + mid) <= item) lo = mid; else hi = mid; }
+        bool is_clear; uint32_t p;
+        fused_group(lo, P, is_clear, p);
+        const uint32_t local = item - __ldg(f.seq_off + lo);
+        const uint2 pe = __ldg(reinterpret_cast<const uint2 *>(a.tv.parts + p));          // {base bucket, buckets}
+        if (is_clear) {
+            const unsigned long long bytes = (unsigned long long)pe.y * 32ull;
+            const unsigned long long b0 = (unsigned long long)local * FB_CLEAR_BYTES, b1 = min(b0 + FB_CLEAR_BYTES, bytes);
+            char *tbl = reinterpret_cast<char *>(a.tv.slots) + (unsigned long long)pe.x * 32ull;
+            for (unsigned long long o = b0 + (unsigned long long)t * 16ull; o < b1; o += (unsigned long long)TILE_THREADS * 16ull)
+                *reinterpret_cast<uint4 *>(tbl + o) = make_uint4(0u, 0u, 0u, 0u);
+            __syncthreads();
+            if (t == 0) { __threadfence(); atomicAdd(f.done + p, 1u); }
+            continue;
+        }
+        // ---- I(p): wait for the partition's table to be zeroed
+        if (t == 0) {
+            const uint32_t need = (uint32_t)(((unsigned long long)pe.y * 32ull + FB_CLEAR_BYTES - 1) / FB_CLEAR_BYTES);
+            unsigned int spins = 0;
+            while (*reinterpret_cast<volatile unsigned int *>(f.done + p) < need) {
+                __nanosleep(200);
+                if (++spins > (1u << 23)) { atomicExch(f.error, 1u); break; }           // ~2 s: never in a correct run
+            }
+            __threadfence();
+        }
+        __syncthreads();
+        const uint32_t r0 = __ldg(f.part_off + p) + local * FB_TILE_ROWS, r1 = min(r0 + FB_TILE_ROWS, __ldg(f.part_off + p + 1));
+        const KeyT *keys = reinterpret_cast<const KeyT *>(a.keys);
+#pragma unroll
+        for (int q = 0; q < (int)(FB_TILE_ROWS / TILE_THREADS); q++) {
+            const uint32_t row = r0 + (uint32_t)q * TILE_THREADS + t;
+            if (row >= r1) continue;
+            const uint64_t key = (uint64_t)__ldcs(keys + row);
+            const uint32_t r = __ldcs(a.rowid + row);
+            const uint32_t d0 = distinct;
+            Slot *s = find_or_claim<true, true>(a.tv, a.hk, key, distinct, r);
+            if (a.slot_of) a.slot_of[row] = key ? (uint32_t)(s - a.tv.slots) : 0xffffffffu;
+            if (distinct != d0) continue;
+            uint32_t pos;
+            const unsigned am = __activemask();
+            if (__any_sync(am, distinct == d0)) {
+                const unsigned peers = __match_any_sync(am, (unsigned long long)s);
+                const int leader = __ffs(peers) - 1;
+                uint32_t base = 0;
+                if ((t & 31) == leader) base = atomicAdd(&s->count, (uint32_t)__popc(peers)) & COUNT_MASK;
+                base = __shfl_sync(peers, base, leader);
+                pos = base + __popc(peers & ((1u << (t & 31)) - 1u));
+            } else {
+                pos = atomicAdd(&s->count, 1u) & COUNT_MASK;
+            }
+            if (pos == 0) {
+                s->row = r;
+                if (key == 0) distinct++;
+            } else {
+                dups++;
+                if (pos == 1) multi++;
+            }
+        }
+    }
+    const unsigned long long d = warp_sum_u32(distinct), u = warp_sum_u32(dups), m = warp_sum_u32(multi);
+    if ((t & 31) == 0) {
+        if (d) atomicAdd(&a.ctr->distinct, d);
+        if (u) atomicAdd(&a.ctr->dup_rows, u);
+        if (m) atomicAdd(&a.ctr->multi_slots, m);
     }
 }
 

@@ -173,10 +173,34 @@ void radix_build(H *h, const void *keys, const uint8_t *validity, int kw, int64_
         const uint64_t total = total_buckets * 2;
         h->n_slots = total;
         dev_alloc(h, h->slots, (size_t)total * sizeof(Slot));
-        CU(cudaMemsetAsync(h->slots.p, 0, (size_t)total * sizeof(Slot), h->stream));
+        const bool fused = h->fused_build && n_valid > 0;
+        if (!fused) CU(cudaMemsetAsync(h->slots.p, 0, (size_t)total * sizeof(Slot), h->stream));
         dev_alloc(h, h->parts, (size_t)P * sizeof(PartEnt));
         CU(cudaMemcpyAsync(h->parts.p, parts.data(), (size_t)P * sizeof(PartEnt), cudaMemcpyHostToDevice, h->stream));
-        CU(cudaStreamSynchronize(h->stream));      // parts is a stack vector
+        // fused clear + insert (build_insert_fused_kernel): the ordered item sequence C(0), C(1) I(0), ... as prefix sums
+        std::vector<uint32_t> meta;
+        uint32_t n_items = 0;
+        void *d_meta = nullptr;
+        if (fused) {
+            meta.resize((size_t)(P + 1) + (2 * P + 1) + P + 1, 0u);
+            uint32_t *part_off = meta.data(), *seq_off = part_off + P + 1;
+            for (int p = 0; p <= P; p++) part_off[p] = (uint32_t)off[p];
+            auto clear_items = [&](int p) { return (uint32_t)(((uint64_t)parts[p].nb * 32ull + FB_CLEAR_BYTES - 1) / FB_CLEAR_BYTES); };
+            auto insert_items = [&](int p) { return (uint32_t)((off[p + 1] - off[p] + FB_TILE_ROWS - 1) / FB_TILE_ROWS); };
+            uint32_t g = 0;
+            seq_off[g++] = 0;
+            n_items = clear_items(0);
+            for (int p = 0; p + 1 < P; p++) {
+                seq_off[g++] = n_items; n_items += clear_items(p + 1);
+                seq_off[g++] = n_items; n_items += insert_items(p);
+            }
+            seq_off[g++] = n_items; n_items += insert_items(P - 1);
+            seq_off[g] = n_items;                         // g == 2P
+            CU(big_alloc(h, &d_meta, meta.size() * 4 + 16));
+            temps.push_back(d_meta);
+            CU(cudaMemcpyAsync(d_meta, meta.data(), meta.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        }
+        CU(cudaStreamSynchronize(h->stream));      // parts / meta are stack vectors
 
         BuildArgs a{};
         a.hk = h->hk;
@@ -193,7 +217,24 @@ void radix_build(H *h, const void *keys, const uint8_t *validity, int kw, int64_
             temps.push_back(so);
             a.slot_of = (uint32_t *)so;
         }
-        if (n_valid > 0) {
+        if (fused) {
+            FusedBuildArgs f{};
+            f.b = a;
+            f.part_off = (const uint32_t *)d_meta;
+            f.seq_off = f.part_off + P + 1;
+            f.n_parts = (uint32_t)P;
+            f.n_items = n_items;
+            f.done = (unsigned int *)d_meta + (P + 1) + (2 * P + 1);
+            f.error = f.done + P;
+            const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)n_items, (int64_t)h->sm_count * h->fused_ctas_per_sm));
+            launch_by_kw(kw, [&](auto KW) { build_insert_fused_kernel<decltype(KW)::value><<<grid, TILE_THREADS, 0, h->stream>>>(f); });
+            h->st.kernel_launches++;
+            CU(cudaGetLastError());
+            uint32_t err = 0;
+            CU(cudaMemcpyAsync(&err, f.error, 4, cudaMemcpyDeviceToHost, h->stream));
+            CU(cudaStreamSynchronize(h->stream));
+            REQUIRE(err == 0, B200J_ERR_CUDA, "fused build: a clear item did not finish in time (watchdog)");
+        } else if (n_valid > 0) {
             const int grid = grid_for(h, n_valid, TILE_ROWS, 8);
             launch_by_kw(kw, [&](auto KW) { build_insert_kernel<decltype(KW)::value, true><<<grid, TILE_THREADS, 0, h->stream>>>(a); });
             h->st.kernel_launches++;
@@ -519,6 +560,7 @@ int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces,
             h->st.probe_launches++;
             h->st.dense_probe_launches++;
             h->st.seg_probe_launches++;
+            if (narrow) h->st.narrow_probe_launches++;
             CU(cudaGetLastError());
             tm.stop();
         }

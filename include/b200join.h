@@ -209,6 +209,7 @@ typedef struct {
     int64_t  compact_launches;        /* dense results with misses compacted afterwards (Inner / Left)  */
     double   ms_exchange_partition;   /* b200j_shuffle_count + b200j_shuffle_scatter kernels             */
     int64_t  seg_probe_launches;      /* dense probe launches over the block-locally partitioned stream (probe_dense_seg_kernel) */
+    int64_t  narrow_probe_launches;   /* ... of which the stream carried 8-byte keys as 32-bit values                    */
 } b200j_stats;
 
 /* ---- lifecycle ------------------------------------------------------------------------------- */

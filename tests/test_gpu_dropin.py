@@ -428,3 +428,60 @@ def test_probe_pieces_with_32_bit_keys_of_a_64_bit_join(pkg, unique, layout, rad
     o1, o2 = np.lexsort(got), np.lexsort(want)
     assert got[0].shape == want[0].shape
     assert np.array_equal(got[0][o1], want[0][o2]) and np.array_equal(got[1][o1], want[1][o2])
+
+
+def test_guarded_buffers_stay_intact(pkg, monkeypatch):
+    """compute-sanitizer is closed on this GPU pool, so the library brings its own out-of-bounds check: with B200J_GUARD=1
+    every device block it allocates sits between two canaries that are verified when the block is freed; b200j_synchronize
+    fails if any was overwritten. Run over every kernel family: block-local partition + segment probe (NULL keys, misaligned
+    batches, 32-bit and 64-bit streams), two-pass partition + staged probe (duplicates), direct layout, composite and Utf8
+    keys, the gather, the pieces entry point, the pipelined host path, the single-pass exchange scatter."""
+    import torch
+    from datafusion_parallelism_b200.exchange import shuffle_local_scatter, shuffle_count, shuffle_scatter
+    monkeypatch.setenv("B200J_GUARD", "1")
+    monkeypatch.setenv("B200J_HOST_CHUNK_ROWS", "50021")
+    rng = np.random.default_rng(77)
+    nb = 120_000
+    uniq = rng.permutation(nb * 2)[:nb].astype(np.int64)
+    dup = rng.integers(0, nb // 5, nb).astype(np.int64)
+    pk = rng.integers(-10, nb * 2 + 10, 400_003).astype(np.int64)
+    pk_wide = pk.copy(); pk_wide[5] = 2**41
+    valid = rng.random(len(pk)) > 0.03
+    for jt in ("inner", "full", "left_anti"):
+        for bk, layout, bits in ((uniq, "radix", 5), (dup, "radix", 3), (uniq, "direct", 0), (dup, "direct", 0)):
+            with pkg.HashJoin(jt, key_widths=(8,), build_payload_types=(8,), layout=layout, radix_bits=bits) as j:
+                j.build_push(0, [bk], [bk * 3])
+                j.build_finish(0)
+                oj = oracle.OracleJoin(jt, [bk])
+                for probe in (pa.array(pk, mask=~valid), pa.array(pk_wide).slice(3), pa.array(pk[:1])):
+                    r = j.probe_batch(0, [probe], want=pkg.OUT_PAIRS | pkg.OUT_HOST)
+                    got, want = r.numpy(), oj.probe_batch([probe], len(probe))
+                    r.release()
+                    assert got[0].shape == want[0].shape
+                dpk = torch.from_numpy(np.concatenate([pk[:1], pk])).cuda()[1:]
+                r = j.probe_batch(0, [dpk], want=pkg.OUT_PAIRS | pkg.OUT_BUILD_U32)
+                if jt != "left_anti":
+                    g = j.gather(r, [dpk], want=0)
+                    g.release()
+                r.release()
+                half = len(pk) // 2
+                r = j.probe_pieces(0, [(dpk[:half].data_ptr(), half), (dpk[half:].data_ptr(), len(pk) - half)], want=pkg.OUT_PAIRS)
+                r.release()
+                j.probe_finish(0).release()
+                j.synchronize()                                  # raises if a canary was overwritten
+    with pkg.HashJoin("inner", key_widths=(8, 4)) as j:         # composite keys: row-hash table + equal_rows
+        a8, a4 = rng.integers(0, 300, 50_000).astype(np.int64), rng.integers(0, 50, 50_000).astype(np.int32)
+        j.build_push(0, [a8, a4])
+        j.build_finish(0)
+        j.probe_batch(0, [a8[::-1].copy(), a4[::-1].copy()]).release()
+        j.synchronize()
+    with pkg.HashJoin("inner", key_widths=(8,)) as j:           # exchange kernels
+        dev = torch.from_numpy(pk).cuda()
+        c = shuffle_count(j, dev, 3)
+        bufs = [torch.empty(len(pk), dtype=torch.int64, device="cuda") for _ in range(4)]
+        rids = [torch.empty(len(pk), dtype=torch.int32, device="cuda") for _ in range(4)]
+        shuffle_scatter(j, 3, [t.data_ptr() for t in bufs], [t.data_ptr() for t in rids], [0] * 4)
+        cap = int(c[:3].max()) + 64
+        sk, sr = torch.empty(5 * cap, dtype=torch.int64, device="cuda"), torch.empty(5 * cap, dtype=torch.int32, device="cuda")
+        assert np.array_equal(shuffle_local_scatter(j, dev, 3, sk.data_ptr(), sr.data_ptr(), cap)[:3], c[:3])
+        j.synchronize()
