@@ -151,6 +151,13 @@ struct b200j_handle {
     bool composite = false;            // n_keys > 1: the table is keyed on the 64-bit row hash, equality checked on candidate pairs
     int table_kw = 8;                  // width of what the table stores: the key column's, or 8 (row hash)
 
+    // coalescing feeder: one stage per partition (b200j_probe_push)
+    struct ProbeStage {
+        std::vector<ColStore> keys, payload;
+        int64_t n = 0, cap_rows = 0;
+    };
+    std::vector<ProbeStage> stages;
+
     // table
     int32_t layout = B200J_LAYOUT_DIRECT;
     int32_t radix_bits = 0;
@@ -1454,6 +1461,9 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
     }
 }
 
+void do_probe_push(H *h, int32_t partition, const b200j_batch *b);
+void do_probe_flush(H *h, int32_t partition, uint32_t want, b200j_result *out);
+void do_gather_staged(H *h, int32_t partition, const b200j_result *pairs, uint32_t want, b200j_gathered *out);
 void do_probe_pieces(H *h, int32_t partition, int32_t n_pieces, const void *const *piece_keys, const int64_t *piece_rows, int32_t piece_key_width,
                      uint32_t want, b200j_result *out);
 
@@ -1843,6 +1853,9 @@ int32_t b200j_destroy(b200j_handle *h) {
     auto fr = [&](DevBuf &b) { if (b.p) big_free(h, b.p); b.p = nullptr; };
     for (auto *v : {&h->bkeys, &h->bpayload})
         for (auto &c : *v) { fr(c.values); fr(c.offsets); fr(c.validity); }
+    for (auto &stg : h->stages)
+        for (auto *v : {&stg.keys, &stg.payload})
+            for (auto &c : *v) { fr(c.values); fr(c.offsets); fr(c.validity); }
     radix_release(h);
     fr(h->slots); fr(h->zero_slot); fr(h->rowids); fr(h->bigruns); fr(h->hot_table); fr(h->visited); fr(h->parts);
     cudaStreamSynchronize(h->stream);
@@ -1901,6 +1914,11 @@ int32_t b200j_reset(b200j_handle *h) {
         h->n_build_done = h->n_probe_done = 0;
         h->built = false;
         h->miss_frac = 0.f;
+        for (auto &stg : h->stages) {
+            stg.n = 0;
+            for (auto *v : {&stg.keys, &stg.payload})
+                for (auto &c : *v) { c.has_nulls = false; c.data_bytes = 0; }
+        }
         if (!getenv("B200J_NO_NARROW") || atoi(getenv("B200J_NO_NARROW")) == 0) h->narrow_ok = true;
         h->n_slots = 0;
     });
@@ -1952,6 +1970,20 @@ int32_t b200j_gather(b200j_handle *h, const b200j_result *pairs, const b200j_bat
 }
 int32_t b200j_gathered_release(b200j_handle *h, b200j_gathered *g) {
     return guarded(h, [&] { do_gathered_release(h, g); });
+}
+int32_t b200j_probe_push(b200j_handle *h, int32_t partition, const b200j_batch *batch) {
+    return guarded(h, [&] { do_probe_push(h, partition, batch); });
+}
+int64_t b200j_staged_rows(b200j_handle *h, int32_t partition) {
+    if (!h) return -1;
+    std::lock_guard<std::mutex> g(h->mu);
+    return (partition >= 0 && partition < (int32_t)h->stages.size()) ? h->stages[partition].n : 0;
+}
+int32_t b200j_probe_flush(b200j_handle *h, int32_t partition, uint32_t want, b200j_result *out) {
+    return guarded(h, [&] { do_probe_flush(h, partition, want, out); });
+}
+int32_t b200j_gather_staged(b200j_handle *h, int32_t partition, const b200j_result *pairs, uint32_t want, b200j_gathered *out) {
+    return guarded(h, [&] { do_gather_staged(h, partition, pairs, want, out); });
 }
 int32_t b200j_hash_keys(b200j_handle *h, const b200j_batch *batch, uint64_t *out) {
     return guarded(h, [&] { do_hash_keys(h, batch, out); });

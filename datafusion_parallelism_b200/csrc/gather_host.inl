@@ -181,7 +181,9 @@ GatherSrc gather_stage_column(GatherCtx &g, const b200j_column &c, int type, int
     return s;
 }
 
-void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, uint32_t want, b200j_gathered *out) {
+// staged_probe: the probe side comes from a partition's coalescing stage (b200j_probe_push) instead of a caller's batch
+void do_gather_impl(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, uint32_t want, b200j_gathered *out,
+                    const std::vector<SideCol> *staged_probe) {
     REQUIRE(h->built, B200J_ERR_INVALID, "gather before the build side finished");
     REQUIRE(pairs != nullptr && out != nullptr && out->struct_size >= sizeof(b200j_gathered), B200J_ERR_INVALID, "gather: missing argument");
     const int jt = h->cfg.join_type;
@@ -235,14 +237,15 @@ void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, 
         }
         if (want_probe) {
             std::vector<SideCol> sc;
-            const bool have_probe = probe_batch && probe_batch->n_rows > 0;
-            for (int i = 0; i < nk + npp; i++) {
+            const bool have_probe = staged_probe != nullptr || (probe_batch && probe_batch->n_rows > 0);
+            for (int i = 0; i < nk + npp && staged_probe == nullptr; i++) {
                 const int type = i < nk ? h->key_widths[i] : h->probe_payload_types[i - nk];
                 GatherSrc s{};
                 if (have_probe)
                     s = gather_stage_column(g, i < nk ? probe_batch->keys[i] : probe_batch->payload[i - nk], type, probe_batch->n_rows, probe_batch->mem);
                 sc.push_back(SideCol{type, s});
             }
+            if (staged_probe) sc = *staged_probe;
             gather_side<uint32_t>(g, col, sc, have_probe ? g.pidx : nullptr);
             col += nk + npp;
         }
@@ -290,6 +293,10 @@ void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, 
     }
 }
 
+void do_gather(H *h, const b200j_result *pairs, const b200j_batch *probe_batch, uint32_t want, b200j_gathered *out) {
+    do_gather_impl(h, pairs, probe_batch, want, out, nullptr);
+}
+
 void do_gathered_release(H *h, b200j_gathered *gth) {
     if (!gth || !gth->_owner) return;
     GatheredOwner *own = (GatheredOwner *)gth->_owner;
@@ -302,4 +309,87 @@ void do_gathered_release(H *h, b200j_gathered *gth) {
     gth->cols = nullptr;
     gth->n_cols = 0;
     gth->n_rows = 0;
+}
+
+
+// ---- coalescing feeder ------------------------------------------------------------------------------------------------
+H::ProbeStage &stage_of(H *h, int32_t partition) {
+    REQUIRE(partition >= 0 && partition < h->cfg.n_partitions, B200J_ERR_INVALID, "partition out of range");
+    if (h->stages.empty()) {
+        h->stages.resize(h->cfg.n_partitions);
+        for (auto &s : h->stages) {
+            s.keys.resize(h->cfg.n_keys);
+            for (int i = 0; i < h->cfg.n_keys; i++) s.keys[i].type = h->key_widths[i];
+            s.payload.resize(h->cfg.n_probe_payload);
+            for (int i = 0; i < h->cfg.n_probe_payload; i++) s.payload[i].type = h->probe_payload_types[i];
+        }
+    }
+    return h->stages[partition];
+}
+
+void do_probe_push(H *h, int32_t partition, const b200j_batch *b) {
+    H::ProbeStage &s = stage_of(h, partition);
+    REQUIRE(!h->probe_done[partition], B200J_ERR_STATE, "probe_push after probe_finish");
+    check_batch(h, b, h->cfg.n_probe_payload);
+    for (int i = 0; i < h->cfg.n_keys; i++)
+        REQUIRE(h->key_widths[i] != B200J_T_UTF8, B200J_ERR_UNSUPPORTED, "the coalescing feeder takes fixed-width key columns");
+    if (b->n_rows == 0) return;
+    REQUIRE(b->n_payload == h->cfg.n_probe_payload, B200J_ERR_INVALID, "probe_push needs every configured probe payload column");
+    REQUIRE(s.n + b->n_rows < 0xffff0000LL, B200J_ERR_UNSUPPORTED, "more than 2^32 - 2^16 staged rows: flush first");
+    std::vector<void *> temps;
+    try {
+        // store_append sizes validity bitmaps by build_cap_rows: give it this stage's capacity for the duration of the call
+        const int64_t saved = h->build_cap_rows;
+        s.cap_rows = std::max<int64_t>(s.cap_rows, std::max<int64_t>(s.n + b->n_rows, (int64_t)1 << 20));
+        h->build_cap_rows = s.cap_rows;
+        for (int i = 0; i < h->cfg.n_keys; i++) store_append(h, s.keys[i], b->keys[i], s.n, b->n_rows, b->mem, temps);
+        for (int i = 0; i < h->cfg.n_probe_payload; i++) store_append(h, s.payload[i], b->payload[i], s.n, b->n_rows, b->mem, temps);
+        h->build_cap_rows = saved;
+        s.n += b->n_rows;
+        CU(cudaStreamSynchronize(h->stream));          // the batch's buffers are borrowed for the call only
+        free_temps(h, temps);
+    } catch (...) {
+        free_temps(h, temps);
+        throw;
+    }
+}
+
+void do_probe_flush(H *h, int32_t partition, uint32_t want, b200j_result *out) {
+    H::ProbeStage &s = stage_of(h, partition);
+    std::vector<b200j_column> kc(h->cfg.n_keys);
+    for (int i = 0; i < h->cfg.n_keys; i++) {
+        kc[i].values = s.keys[i].values.p;
+        kc[i].offsets = nullptr;
+        kc[i].validity = s.keys[i].has_nulls ? (const uint8_t *)s.keys[i].validity.p : nullptr;
+        kc[i].bit_offset = 0;
+    }
+    b200j_batch b{};
+    b.struct_size = sizeof(b200j_batch);
+    b.mem = B200J_MEM_DEVICE;
+    b.n_rows = s.n;
+    b.n_keys = h->cfg.n_keys;
+    b.n_payload = 0;
+    b.keys = kc.data();
+    do_probe_batch(h, partition, &b, want, out);
+}
+
+void do_gather_staged(H *h, int32_t partition, const b200j_result *pairs, uint32_t want, b200j_gathered *out) {
+    H::ProbeStage &s = stage_of(h, partition);
+    std::vector<SideCol> sc;
+    for (auto *v : {&s.keys, &s.payload})
+        for (auto &cs : *v) {
+            GatherSrc g{};
+            if (s.n > 0) {
+                g.values = cs.values.p;
+                g.offsets = cs.offsets.p;
+                g.offsets64 = 1;
+                g.validity = cs.has_nulls ? (const uint8_t *)cs.validity.p : nullptr;
+            }
+            sc.push_back(SideCol{cs.type, g});
+        }
+    do_gather_impl(h, pairs, nullptr, want, out, &sc);
+    // the stage is consumed: the next push starts a new run of row numbers
+    s.n = 0;
+    for (auto *v : {&s.keys, &s.payload})
+        for (auto &cs : *v) { cs.has_nulls = false; cs.data_bytes = 0; }
 }

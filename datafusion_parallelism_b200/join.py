@@ -300,6 +300,26 @@ class HashJoin:
         self._check(N.lib().b200j_probe_pieces(self._h, partition, n, ptrs, rows, key_width, want, C.byref(r)))
         return PairResult(self, r)
 
+    # -- coalescing feeder (b200j_probe_push / flush / gather_staged) ----------------------------------
+    def probe_push(self, partition: int, keys: Sequence, payload: Sequence = ()):
+        b, keep = make_batch(keys, payload)
+        self._check(N.lib().b200j_probe_push(self._h, partition, C.byref(b)))
+
+    def staged_rows(self, partition: int) -> int:
+        return int(N.lib().b200j_staged_rows(self._h, partition))
+
+    def probe_flush(self, partition: int, want: int = OUT_PAIRS) -> PairResult:
+        r = N.Result()
+        r.struct_size = C.sizeof(N.Result)
+        self._check(N.lib().b200j_probe_flush(self._h, partition, want, C.byref(r)))
+        return PairResult(self, r)
+
+    def gather_staged(self, partition: int, pairs: PairResult, want: int = OUT_HOST) -> "GatheredResult":
+        g = N.Gathered()
+        g.struct_size = C.sizeof(N.Gathered)
+        self._check(N.lib().b200j_gather_staged(self._h, partition, C.byref(pairs._res), want, C.byref(g)))
+        return GatheredResult(self, g)
+
     def apply_pairs(self, partition: int, n_probe_rows: int, build_idx, probe_idx, want: int = OUT_PAIRS | OUT_HOST) -> PairResult:
         bi = np.ascontiguousarray(build_idx, dtype=np.uint64)
         pi = np.ascontiguousarray(probe_idx, dtype=np.uint32)

@@ -264,6 +264,19 @@ int32_t b200j_gather(b200j_handle *h, const b200j_result *pairs, const b200j_bat
                      b200j_gathered *out);
 int32_t b200j_gathered_release(b200j_handle *h, b200j_gathered *g);
 
+/* ---- coalescing feeder for small probe batches (replaces what WorkStealingRepartitionExec,
+ * work_stealing_repartition_exec.rs:204-295, does in front of the reference's operator) ------------------------------
+ * DataFusion hands over 8192-row batches; a GPU probe wants millions of rows per launch. b200j_probe_push COPIES one
+ * batch (key and probe payload columns, host or device) to the end of the partition's stage on the device; rows are
+ * numbered consecutively since the partition's last flush. b200j_probe_flush probes everything staged in one go
+ * (probe_idx = staged row number); b200j_gather_staged gathers with the staged probe columns -- the caller slices the
+ * gathered columns into output RecordBatches of whatever size it likes -- and empties the stage. Key columns must be
+ * fixed-width (Utf8 payload is fine). b200j_staged_rows tells the caller when it is worth flushing. */
+int32_t b200j_probe_push(b200j_handle *h, int32_t partition, const b200j_batch *batch);
+int64_t b200j_staged_rows(b200j_handle *h, int32_t partition);
+int32_t b200j_probe_flush(b200j_handle *h, int32_t partition, uint32_t want, b200j_result *out);
+int32_t b200j_gather_staged(b200j_handle *h, int32_t partition, const b200j_result *pairs, uint32_t want, b200j_gathered *out);
+
 /* ---- multi-GPU exchange (no counterpart in the reference, which is single-process) ----------
  * One process per GPU; every rank hash-partitions BOTH join sides by destination rank
  *     dest = (((hash >> 32) & 0xfffff) * n_dest) >> 20        (independent of the radix and slot bits)

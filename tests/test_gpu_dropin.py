@@ -485,3 +485,48 @@ def test_guarded_buffers_stay_intact(pkg, monkeypatch):
         sk, sr = torch.empty(5 * cap, dtype=torch.int64, device="cuda"), torch.empty(5 * cap, dtype=torch.int32, device="cuda")
         assert np.array_equal(shuffle_local_scatter(j, dev, 3, sk.data_ptr(), sr.data_ptr(), cap)[:3], c[:3])
         j.synchronize()
+
+
+@pytest.mark.parametrize("join_type", ["inner", "full", "right_anti", "left_semi"])
+@pytest.mark.parametrize("layout,radix_bits", [("direct", 0), ("radix", 3)])
+def test_coalescing_feeder_matches_per_batch_probing(pkg, join_type, layout, radix_bits):
+    """b200j_probe_push / flush / gather_staged: DataFusion-sized probe batches (8192 rows, NULL keys, an
+    Int64 and a Utf8 payload column, host memory) are staged on the device and probed in one go; the gathered rows of two
+    flush rounds + the finaliser are the oracle's whole-join rows."""
+    rng = np.random.default_rng(hash((join_type, layout, "feed")) & 0xFFFFFFFF)
+    nb, npr = 9_000, 60_000
+    build = pa.table({"id": pa.array(rng.integers(0, 6_000, nb).astype(np.int32), mask=rng.random(nb) < 0.03),
+                      "value": pa.array([f"b{i % 97}" for i in range(nb)])})
+    probe = pa.table({"id": pa.array(rng.integers(-100, 7_000, npr).astype(np.int32), mask=rng.random(npr) < 0.05),
+                      "v": pa.array(rng.integers(0, 1 << 50, npr).astype(np.int64), mask=rng.random(npr) < 0.1),
+                      "s": pa.array([None if i % 13 == 0 else "p" * (i % 9) + str(i) for i in range(npr)])})
+    batches = [probe.slice(lo, 8192) for lo in range(0, npr, 8192)]
+    want = oracle.join_tables(build, batches, [("id", "id")], join_type)
+    left_only, right_only = join_type in ("left_semi", "left_anti"), join_type in ("right_semi", "right_anti")
+    types = ([] if right_only else [pa.int32(), pa.string()]) + ([] if left_only else [pa.int32(), pa.int64(), pa.string()])
+    pieces = []
+    with pkg.HashJoin(join_type, key_widths=(4,), build_payload_types=(pkg.T_UTF8,), probe_payload_types=(8, pkg.T_UTF8),
+                      layout=layout, radix_bits=radix_bits) as j:
+        j.build_push(0, [build.column("id")], [build.column("value")])
+        j.build_finish(0)
+        for rnd in (batches[:5], batches[5:]):
+            for pb in rnd:
+                pb = pb.combine_chunks()
+                j.probe_push(0, [pb.column("id")], [pb.column("v"), pb.column("s")])
+            assert j.staged_rows(0) == sum(b.num_rows for b in rnd)
+            res = j.probe_flush(0, want=pkg.OUT_PAIRS)
+            g = j.gather_staged(0, res)
+            assert j.staged_rows(0) == 0
+            if not left_only:
+                pieces.append(pa.Table.from_arrays(g.to_arrow(types), names=want.column_names))
+            g.release()
+            res.release()
+        fin = j.probe_finish(0, want=pkg.OUT_PAIRS | pkg.OUT_HOST)
+        if fin.n or not pieces:
+            g = j.gather(fin, None)
+            pieces.append(pa.Table.from_arrays(g.to_arrow(types), names=want.column_names))
+            g.release()
+        fin.release()
+    got = pa.concat_tables(pieces)
+    assert got.num_rows == want.num_rows
+    assert rows_multiset(got) == rows_multiset(want)
