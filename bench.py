@@ -364,8 +364,9 @@ def run_b200(args):
     if dense:        # 8 B key in + 8 B build index out per row, plus ONE pass over the table per launch (it is L2-resident per partition)
         seg = st.get("seg_probe_launches", 0) == st["probe_launches"]
         narrow = seg and st.get("narrow_probe_launches", 0) == st["probe_launches"]
-        # the partitioned stream carries the 8-byte keys as 32-bit values when they all fit: the kernel then READS 4 B per row
-        bpt = 12 if narrow else B_PROBE_DENSE
+        # ALGORITHMIC bytes: 8 B key in + 8 B build index out per row. (When every key fits 32 bits the partitioned stream carries
+        # them as 4-byte values and the kernel moves 12 B per row; the algorithmic figure does not shrink with that.)
+        bpt = B_PROBE_DENSE
         kname = ("probe_dense_seg_kernel<4,false,false>" if narrow else "probe_dense_seg_kernel<8,false,false>") if seg else "probe_dense_kernel<8,false,true,false>"
         table_b = table_alg
     elif radix:
@@ -376,7 +377,8 @@ def run_b200(args):
     achieved = bytes_per_launch / (probe_launch_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": kname,
                 "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s", "frac": achieved / hbm_gbs, "traffic": None,
-                "peak_source": peak_src, "bytes_per_tuple": bpt, "table_bytes_per_launch": table_b,
+                "peak_source": peak_src, "bytes_per_tuple": bpt, "stream_key_bytes": (4 if (dense and st.get("narrow_probe_launches", 0) == st["probe_launches"]) else 8),
+                "table_bytes_per_launch": table_b,
                 "tuples_per_launch": rows_per_launch, "ms_per_launch": probe_launch_ms}
     # DRAM bytes of that kernel per launch from the committed ncu --set full capture of THIS build (scripts/make_traffic_json.py);
     # only quoted when the capture is of the kernel that ran and of the same number of rows
