@@ -335,6 +335,7 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
     __shared__ uint32_t s_wsum[SC_THREADS / 32];
     __shared__ uint32_t s_total;
     __shared__ uint32_t s_drop;          // bit p: this tile's run of bin p did not fit its region (single-pass mode)
+    __shared__ uint32_t s_wtot[SC_THREADS / 32][12];   // packed DEST ranking: rows per (warp, bin), then the warp's base inside the bin
     __shared__ KeyT *s_dkeys[RP_MAX_DEST + 2];
     __shared__ uint32_t *s_drid[RP_MAX_DEST + 2];
 
@@ -378,6 +379,7 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
         }
     };
     bool wide_seen = false;
+    const bool pk_mode = DEST && P1 <= 10u && ITEMS <= 63;
     const bool narrow_out = DEST && KW == 8 && a.narrow_out != 0u;
     uint32_t n_bulk[2] = {0, 0};         // bulk copies issued so far per buffer (mbarrier phase parity)
     fetch(t0, 0);
@@ -393,6 +395,7 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
 
         // ---- rank: bin of every key, rank inside the bin from a shared-memory atomic
         uint32_t packed[ITEMS];
+        unsigned long long pcnt = 0;          // DEST mode, <= 10 bins: this thread's rows per bin so far, 6 bits each (a thread has 16 rows)
         const uint32_t vbase = tile * (uint32_t)SC_TILE;
 #pragma unroll
         for (int v = 0; v < NVEC; v++) {
@@ -415,7 +418,14 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
                     in = vrow >= mis && vrow < vend;
                     if (in && a.validity != nullptr && !bit_valid(a.validity, a.bit_offset + (int64_t)(vrow - mis))) bin = a.n_bins;
                 }
-                if (DEST) {
+                if (DEST && pk_mode) {
+                    // up to 10 bins (8 ranks + NULL + hot): no shared memory, no vote at all while ranking. Every thread counts its
+                    // own rows per bin in ONE 64-bit register (6-bit fields); the per-bin prefix over the threads follows below.
+                    const uint32_t sh = bin * 6u;
+                    const uint32_t rk = (uint32_t)(pcnt >> sh) & 63u;
+                    if (in) pcnt += 1ULL << sh;
+                    packed[v * PER_VEC + j] = in ? ((bin << 16) | rk) : 0xffffffffu;
+                } else if (DEST) {
                     // few bins (ranks + NULL + hot <= 18): a per-lane shared-memory atomic would serialise 32 lanes on a handful of
                     // addresses (2 GPUs: 16-way). The lanes of a bin are matched with 5 ballots and ONE lane adds their number.
                     const uint32_t mb = in ? bin : 31u;
@@ -436,7 +446,30 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
                 }
             }
         }
+        // packed mode: exclusive prefix of the per-thread counts inside the warp (12-bit fields: bins 0..4 in pre_lo, 5..9 in
+        // pre_hi), warp totals to shared memory, then one short pass turns them into per-warp bases and the tile's histogram
+        unsigned long long pre_lo = 0, pre_hi = 0;
+        if (DEST && pk_mode) {
+            for (uint32_t b = 0; b < P1; b++) {
+                const uint32_t c = (uint32_t)(pcnt >> (6u * b)) & 63u;
+                uint32_t incl = c;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+                if (lane == 31) s_wtot[warp][b] = incl;
+                const unsigned long long e = (unsigned long long)(incl - c);
+                if (b < 5u) pre_lo |= e << (12u * b); else pre_hi |= e << (12u * (b - 5u));
+            }
+        }
         __syncthreads();
+        if (DEST && pk_mode) {
+            if ((uint32_t)t < P1) {
+                uint32_t run = 0;
+#pragma unroll
+                for (int w = 0; w < SC_THREADS / 32; w++) { const uint32_t c = s_wtot[w][t]; s_wtot[w][t] = run; run += c; }
+                s_cnt[t] = run;
+            }
+            __syncthreads();
+        }
 
         // ---- exclusive scan of s_cnt[0..P1) -> s_off; advance the CTA's cursors; clear the counts for the next tile
         {
@@ -479,7 +512,12 @@ __global__ void __launch_bounds__(SC_THREADS, SC_CTAS) part_scatter_kernel(PartA
 #pragma unroll
         for (int q = 0; q < ITEMS; q++) {
             if (!inner && packed[q] == 0xffffffffu) continue;
-            const uint32_t bin = packed[q] >> 16, rank = packed[q] & 0xffffu;
+            const uint32_t bin = packed[q] >> 16;
+            uint32_t rank = packed[q] & 0xffffu;
+            if (DEST && pk_mode) {      // + the rows of this bin in the warps and in the lanes in front of this thread
+                const unsigned long long pw = bin < 5u ? pre_lo : pre_hi;
+                rank += s_wtot[warp][bin] + ((uint32_t)(pw >> (12u * (bin < 5u ? bin : bin - 5u))) & 4095u);
+            }
             const uint32_t src = ((uint32_t)(q / PER_VEC) * SC_THREADS + t) * PER_VEC + (q % PER_VEC);
             s_perm[s_off[bin] + rank] = (bin << 16) | src;
         }
