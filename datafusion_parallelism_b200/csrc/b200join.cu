@@ -176,6 +176,7 @@ struct b200j_handle {
     bool shuffle_armed = false;        // b200j_shuffle_count done, b200j_shuffle_scatter pending
     PartPlan shuffle_plan;
     int64_t shuffle_n = 0;
+    uint32_t *static_hist = nullptr;   // device address of g_static_hist ON THIS HANDLE'S DEVICE (b200j_shuffle_count_static)
     Counters *d_ctr = nullptr;
     Counters *h_ctr = nullptr;         // pinned mirror
 
@@ -1701,6 +1702,89 @@ namespace {
 #include "gather_host.inl"
 }  // namespace
 
+// ---- allocation-free destination count (b200j_shuffle_count_static; no counterpart in the reference) ------------------------
+// part_hist_kernel<KW, DEST> with its per-CTA histograms (the scratch h->rscratch.cta_hist of the allocating path) in a
+// file-scope device array instead. A CTA takes ST_TILES_PER_CTA scatter tiles (32768 rows) whatever the batch size, so the
+// array's ST_MAX_GRID columns bound the batch: B200J_STATIC_MAX_ROWS rows (+ one column for a batch that starts off a
+// 16-byte boundary). Layout as everywhere: [bin][grid], bins = n_dest ranks + the NULL-key bin.
+namespace {
+constexpr int ST_TILES_PER_CTA = 4;
+constexpr int ST_MAX_GRID = 4096;
+static_assert((int64_t)ST_MAX_GRID * ST_TILES_PER_CTA * SC_TILE == (int64_t)B200J_STATIC_MAX_ROWS, "the header states the array's capacity");
+static_assert(B200J_MAX_DEST <= RP_MAX_DEST, "bins of the static histogram");
+constexpr size_t ST_HIST_ENTRIES = (size_t)(B200J_MAX_DEST + 1) * (ST_MAX_GRID + 1);
+
+static __device__ __align__(256) uint32_t g_static_hist[ST_HIST_ENTRIES];       // 272 KiB on every device that loads the library
+
+// In host code `g_static_hist` is only the host-side stand-in of the symbol, not a device address: the address the kernels
+// get is looked up here, once per handle, with the handle's device current.
+uint32_t *static_hist_address() {
+    void *p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_static_hist);
+    if (e != cudaSuccess || p == nullptr) {
+        cudaGetLastError();
+        throw Fail{B200J_ERR_CUDA, std::string("cudaGetSymbolAddress(g_static_hist) failed: ") + cudaGetErrorString(e)};
+    }
+    return (uint32_t *)p;
+}
+
+// One CTA per bin: sum of the bin's row of per-CTA counts -> counts[bin] (the caller's device buffer).
+__global__ void __launch_bounds__(256) static_count_sum_kernel(const uint32_t *__restrict__ cta_hist, uint32_t grid, long long *__restrict__ counts) {
+    __shared__ unsigned long long s_w[8];
+    const uint32_t *rowp = cta_hist + (size_t)blockIdx.x * grid;
+    unsigned long long sum = 0;
+    for (uint32_t i = threadIdx.x; i < grid; i += 256) sum += rowp[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_down_sync(0xffffffffu, sum, o);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long tot = 0;
+        for (int w = 0; w < 8; w++) tot += s_w[w];
+        counts[blockIdx.x] = (long long)tot;
+    }
+}
+
+void do_shuffle_count_static(H *h, const void *keys, const uint8_t *validity, int64_t bit_offset, int64_t n_rows, int32_t n_dest, int64_t *counts) {
+    REQUIRE(h->cfg.n_keys == 1 && h->key_widths[0] != B200J_T_UTF8, B200J_ERR_UNSUPPORTED, "the exchange partitions one fixed-width key column");
+    REQUIRE(n_dest >= 1 && n_dest <= B200J_MAX_DEST, B200J_ERR_INVALID, "n_dest must be in 1..16");
+    REQUIRE(counts != nullptr, B200J_ERR_INVALID, "counts is NULL");
+    REQUIRE(n_rows >= 0, B200J_ERR_INVALID, "n_rows is negative");
+    REQUIRE(n_rows <= (int64_t)B200J_STATIC_MAX_ROWS, B200J_ERR_INVALID,
+            "n_rows exceeds B200J_STATIC_MAX_ROWS (134217728): the static scratch array has no room for more; split the batch and add the counts");
+    REQUIRE(n_rows == 0 || keys != nullptr, B200J_ERR_INVALID, "keys is NULL");
+    REQUIRE(h->hot_n == 0, B200J_ERR_STATE, "b200j_shuffle_count_static does not route hot keys: clear the hot set or use b200j_shuffle_count");
+    REQUIRE(h->static_hist != nullptr, B200J_ERR_STATE, "static scratch address missing");
+    const int kw = h->key_widths[0];
+    REQUIRE(((uintptr_t)keys % (uintptr_t)kw) == 0, B200J_ERR_INVALID, "keys must be aligned to the key width");
+    if (n_rows == 0) {
+        CU(cudaMemsetAsync(counts, 0, (size_t)(n_dest + 1) * 8, h->stream));
+        return;
+    }
+    PartArgs a{};
+    a.keys = keys;
+    a.validity = validity;
+    a.bit_offset = bit_offset;
+    a.n = (uint32_t)n_rows;
+    a.mis = (uint32_t)(((uintptr_t)keys & 15) / (uintptr_t)kw);
+    a.n_dest = n_dest;
+    a.n_bins = (uint32_t)n_dest;
+    a.hk = h->hk;
+    a.tiles_per_cta = ST_TILES_PER_CTA;
+    a.cta_hist = h->static_hist;
+    const int64_t n_tiles = (n_rows + a.mis + SC_TILE - 1) / SC_TILE;
+    const int grid = (int)((n_tiles + ST_TILES_PER_CTA - 1) / ST_TILES_PER_CTA);
+    REQUIRE(grid >= 1 && grid <= ST_MAX_GRID + 1, B200J_ERR_INVALID, "n_rows exceeds B200J_STATIC_MAX_ROWS");
+    const int P1 = n_dest + 1;
+    const size_t hist_smem = (size_t)P1 * 4;
+    if (kw == 8) part_hist_kernel<8, true><<<grid, RP_THREADS, hist_smem, h->stream>>>(a);
+    else part_hist_kernel<4, true><<<grid, RP_THREADS, hist_smem, h->stream>>>(a);
+    static_count_sum_kernel<<<P1, 256, 0, h->stream>>>(h->static_hist, (uint32_t)grid, (long long *)counts);
+    h->st.kernel_launches += 2;
+    CU(cudaGetLastError());
+}
+}  // namespace
+
 extern "C" {
 
 int32_t b200j_abi_version(void) { return B200J_ABI_VERSION; }
@@ -1803,6 +1887,7 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
         if (const char *e = getenv("B200J_CACHE_LIMIT_BYTES")) h->cache_limit = (size_t)std::max<long long>(0, atoll(e));
         if (const char *e = getenv("B200J_GUARD")) h->guard = atoi(e) != 0;
         set_kernel_attributes();       // per device: opt-in shared-memory sizes of the partition kernels
+        h->static_hist = static_hist_address();        // per device as well: cfg->device is current here
         if (cfg->stream) {
             h->stream = (cudaStream_t)cfg->stream;
         } else {
@@ -1987,6 +2072,11 @@ int32_t b200j_gather_staged(b200j_handle *h, int32_t partition, const b200j_resu
 }
 int32_t b200j_hash_keys(b200j_handle *h, const b200j_batch *batch, uint64_t *out) {
     return guarded(h, [&] { do_hash_keys(h, batch, out); });
+}
+
+int32_t b200j_shuffle_count_static(b200j_handle *h, const void *keys, const uint8_t *validity, int64_t bit_offset, int64_t n_rows,
+                                   int32_t n_dest, int64_t *counts) {
+    return guarded(h, [&] { do_shuffle_count_static(h, keys, validity, bit_offset, n_rows, n_dest, counts); });
 }
 
 int32_t b200j_shuffle_count(b200j_handle *h, const b200j_batch *batch, int32_t n_dest, int64_t *counts) {

@@ -106,6 +106,18 @@ def shuffle_count(join: HashJoin, keys, n_dest: int, hot: bool = False) -> np.nd
     return np.array(list(counts), dtype=np.int64)
 
 
+STATIC_MAX_ROWS = 1 << 27        # B200J_STATIC_MAX_ROWS
+
+
+def shuffle_count_static(join: HashJoin, keys_ptr: int, n_rows: int, n_dest: int, counts_ptr: int, validity_ptr: int = 0,
+                         bit_offset: int = 0) -> None:
+    """b200j_shuffle_count_static: the counts of shuffle_count, written to the caller's DEVICE buffer `counts_ptr`
+    ([n_dest + 1] int64) by work enqueued on the handle's stream. Allocates nothing (the kernel's scratch is a static device
+    array of the library); at most STATIC_MAX_ROWS rows per call; calls that overlap on the GPU race on that array."""
+    join._check(N.lib().b200j_shuffle_count_static(join._h, keys_ptr or None, validity_ptr or None, bit_offset, n_rows, n_dest,
+                                                   counts_ptr or None))
+
+
 def shuffle_scatter(join: HashJoin, n_dest: int, dest_keys: Sequence[int], dest_rowid: Sequence[int], dest_offset: Sequence[int],
                     rowid_base: int = 0):
     """b200j_shuffle_scatter: write every (key, row id) of the counted batch to its destination buffer."""

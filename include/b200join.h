@@ -321,6 +321,28 @@ int32_t b200j_ipc_open(b200j_handle *h, const uint8_t *handle, void **peer_ptr);
 int32_t b200j_ipc_close(b200j_handle *h, void *peer_ptr);
 int32_t b200j_ipc_free(b200j_handle *h, void *ptr);
 
+/* ---- allocation-free destination count -------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it). Same result as b200j_shuffle_count
+ * (rows of one 4/8-byte key column per destination rank, counts[n_dest] = NULL-key rows), but
+ *   - the call allocates NOTHING, on the device or through any allocating library routine: the per-CTA histograms the count
+ *     kernel needs live in a file-scope __device__ array of the library (272 KiB, held by every GPU that loads the library
+ *     until the process exits), whose device address is looked up once per handle in b200j_create;
+ *   - inputs and outputs are the CALLER's device buffers: `keys` (n_rows values of the handle's key width, aligned to that
+ *     width), `validity` (Arrow LSB bitmap with `bit_offset`, or NULL), `counts` (n_dest + 1 int64 values, DEVICE memory);
+ *   - the work is only ENQUEUED on the handle's stream (no synchronisation, no host copy): read `counts` after
+ *     b200j_synchronize or after a stream-ordered copy of your own;
+ *   - at most B200J_STATIC_MAX_ROWS rows per call: more fails with B200J_ERR_INVALID "n_rows exceeds
+ *     B200J_STATIC_MAX_ROWS" (split the batch and add the counts);
+ *   - a hot-key set (b200j_shuffle_set_hot) is not supported here: B200J_ERR_STATE while one is set; it does not arm
+ *     b200j_shuffle_scatter (that call still wants a b200j_shuffle_count).
+ * EVERY call on EVERY handle of a device shares the one array, and it keeps the last call's contents. Nothing in it has to
+ * start at zero (each call overwrites every entry it later reads), but two calls whose kernels overlap on the GPU -- two
+ * handles with different streams, or one stream forked by the caller -- race on it: keep such calls ordered. */
+#define B200J_STATIC_MAX_ROWS 134217728          /* 2^27 = 4096 CTAs x 32768 rows: what the static array has room for */
+int32_t b200j_shuffle_count_static(b200j_handle *h, const void *keys, const uint8_t *validity, int64_t bit_offset, int64_t n_rows,
+                                   int32_t n_dest, int64_t *counts /* device, [n_dest + 1] */);
+
 /* ---- hashing (a1) ---------------------------------------------------------------------------- */
 /* create_hashes over the key columns of `batch` with the handle's RandomState: one u64 per row into
  * `out` (same memory space as the batch). Bit-identical to oracle/join_oracle.c:orc_create_hashes. */
