@@ -119,6 +119,15 @@ SIGNATURES = {
     "b200j_gather_staged": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(Result), C.c_uint32, C.POINTER(Gathered)]),
     "b200j_hash_keys": (C.c_int32, [C.c_void_p, C.POINTER(Batch), C.c_void_p]),
     "b200j_shuffle_count": (C.c_int32, [C.c_void_p, C.POINTER(Batch), C.c_int32, C.POINTER(C.c_int64)]),
+    "b200j_resolve_origin": (C.c_int32, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_void_p),
+                                         C.POINTER(C.c_uint32), C.c_void_p, C.c_void_p]),
+    "b200j_gather_pieces": (C.c_int32, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                        C.c_int32, C.c_void_p, C.c_void_p]),
+    "b200j_gather_pieces_utf8_offsets": (C.c_int32, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p),
+                                                     C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]),
+    "b200j_gather_pieces_utf8_data": (C.c_int32, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p),
+                                                  C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p]),
+    "b200j_utf8_rows_equal": (C.c_int32, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200j_shuffle_count_static": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]),
     "b200j_shuffle_set_hot": (C.c_int32, [C.c_void_p, C.POINTER(C.c_uint64), C.c_int32]),
     "b200j_shuffle_scatter": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.c_uint32]),

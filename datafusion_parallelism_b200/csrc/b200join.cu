@@ -10,6 +10,7 @@
 #include "radix_block.cuh"
 #include "probe.cuh"
 #include "gather.cuh"
+#include "gather_remote.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -1700,6 +1701,7 @@ int32_t guarded(b200j_handle *h, F &&f) {
 namespace {
 #include "radix_host.inl"
 #include "gather_host.inl"
+#include "gather_remote_host.inl"
 }  // namespace
 
 // ---- allocation-free destination count (b200j_shuffle_count_static; no counterpart in the reference) ------------------------
@@ -2050,6 +2052,32 @@ int32_t b200j_result_release(b200j_handle *h, b200j_result *r) {
         r->n = 0;
     });
 }
+int32_t b200j_resolve_origin(b200j_handle *h, int64_t n, const void *idx, int32_t idx_width, int32_t n_pieces, const int64_t *piece_rows,
+                             const uint32_t *const *piece_rowid, const uint32_t *piece_rowid_base, uint32_t *out_piece, uint32_t *out_row) {
+    return guarded(h, [&] { do_resolve_origin(h, n, idx, idx_width, n_pieces, piece_rows, piece_rowid, piece_rowid_base, out_piece, out_row); });
+}
+
+int32_t b200j_gather_pieces(b200j_handle *h, int64_t n, const uint32_t *piece, const uint32_t *row, int32_t n_pieces, const void *const *col_values,
+                            const uint8_t *const *col_validity, int32_t width, void *out_values, uint32_t *out_validity) {
+    return guarded(h, [&] { do_gather_pieces(h, n, piece, row, n_pieces, col_values, col_validity, width, out_values, out_validity); });
+}
+
+int32_t b200j_gather_pieces_utf8_offsets(b200j_handle *h, int64_t n, const uint32_t *piece, const uint32_t *row, int32_t n_pieces,
+                                         const int32_t *const *col_offsets, const uint8_t *const *col_validity, int32_t *out_offsets,
+                                         uint32_t *out_validity, int64_t *total_bytes) {
+    return guarded(h, [&] { do_gather_pieces_utf8_offsets(h, n, piece, row, n_pieces, col_offsets, col_validity, out_offsets, out_validity, total_bytes); });
+}
+
+int32_t b200j_gather_pieces_utf8_data(b200j_handle *h, int64_t n, const uint32_t *piece, const uint32_t *row, int32_t n_pieces,
+                                      const int32_t *const *col_offsets, const uint8_t *const *col_data, const int32_t *out_offsets, uint8_t *out_data) {
+    return guarded(h, [&] { do_gather_pieces_utf8_data(h, n, piece, row, n_pieces, col_offsets, col_data, out_offsets, out_data); });
+}
+
+int32_t b200j_utf8_rows_equal(b200j_handle *h, int64_t n, const int32_t *off_a, const uint8_t *data_a, const uint32_t *valid_a, const int32_t *off_b,
+                              const uint8_t *data_b, const uint32_t *valid_b, uint8_t *out) {
+    return guarded(h, [&] { do_utf8_rows_equal(h, n, off_a, data_a, valid_a, off_b, data_b, valid_b, out); });
+}
+
 int32_t b200j_gather(b200j_handle *h, const b200j_result *pairs, const b200j_batch *probe_batch, uint32_t want, b200j_gathered *out) {
     return guarded(h, [&] { do_gather(h, pairs, probe_batch, want, out); });
 }

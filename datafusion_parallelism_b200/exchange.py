@@ -174,6 +174,7 @@ class DistributedJoin:
         self.group = group
         self.world, self.rank = dist.get_world_size(), dist.get_rank()
         self.mode, self.kw = mode, key_width
+        self.track_origin = join_kwargs.pop("track_origin", False)   # keep (source rank, row id) of every build row for build_rows()
         self.narrow_keys = join_kwargs.pop("narrow_keys", True)      # mode "pull": 8-byte probe keys cross NVLink as 32-bit values while they fit
         self.stream = stream if stream is not None else torch.cuda.current_stream()
         join_kwargs.setdefault("device", torch.cuda.current_device())     # one process per GPU: the handle lives on this rank's device
@@ -192,6 +193,9 @@ class DistributedJoin:
         self.hot_join: Optional[HashJoin] = None
         self.hot_build_keys = self.hot_owner = self.hot_bidx = None
         self.build_rows_local = 0
+        self.build_rows_sent = 0        # rows of this rank's build batches so far: the row-id base of the next batch
+        self.build_null_rid = []        # row ids of this rank's NULL-key build rows (never sent), per build batch
+        self.build_origin = []          # OriginPieces per build batch received (row-id copies: where every local build row came from)
         self._key_dtype = torch.int64 if key_width == 8 else torch.int32
 
     # ---- buffers ----------------------------------------------------------------------------------------------
@@ -421,6 +425,101 @@ class DistributedJoin:
         side.recv_keys_ptr = side.recv_rid_ptr = None
         return int(plan.recv_rows[me])
 
+    # ---- output rows across ranks (late materialisation; rows.py, csrc/gather_remote.cuh) ---------------------------------
+    def _origin_pieces(self, side: _Side, rowid_base: int = 0, copy: bool = False):
+        """OriginPieces of the batch `side` received last: per source rank (in the order the local indices count them) the row
+        count and where that piece's row ids are -- in the peers' send regions (mode "pull") or in my receive buffer.
+        copy=True keeps private copies of the row ids (the build side: its regions are overwritten by the next build batch)."""
+        from .rows import OriginPieces
+        torch = self.torch
+        o = OriginPieces()
+        plan, me = side.plan, self.rank
+        if self.mode == "pull":          # one piece per source rank, in the rotated order the partition pass pulls them
+            spans = [(int(s), int(m), int(p)) for s, (p, m) in zip(plan.src_order, side.rid_pieces)]
+        else:                            # one receive buffer, the sources' segments in plan.src_order
+            base = side.rid_pieces[0][0]
+            spans = [(int(s), int(plan.counts[s, me]), int(base) + int(plan.src_offset[k]) * 4) for k, s in enumerate(plan.src_order)]
+        for s, m, p in spans:
+            if copy and m:
+                t = torch.as_tensor(_RawCudaArray(p, m, "<i4"), device=torch.device("cuda", torch.cuda.current_device())).clone()
+                o.add(s, m, t.data_ptr(), 0, keep=t)
+            else:
+                o.add(s, m, p if m else 0, 0)
+        return o
+
+    def share_columns(self, columns: Sequence):
+        """Collective. Makes this rank's columns of one side readable by every rank: each pyarrow array (fixed width or Utf8,
+        NULLs allowed) or device tensor is copied into cudaIpc-shared device buffers and the handles are all-gathered.
+        Returns one rows.SharedColumn per column (per-rank pointers). Keep the result alive while rows are gathered from it;
+        release it with unshare_columns (collective)."""
+        from .rows import SharedColumn, arrow_to_device
+        from .join import T_UTF8
+        torch, dist = self.torch, self.dist
+        dev = torch.device("cuda", torch.cuda.current_device())
+        out = []
+        for col in columns:
+            if _is_torch_tensor(col):
+                d_ = {"type": col.element_size(), "values": col.contiguous().view(torch.uint8), "validity": None, "data": None}
+            else:
+                d_ = arrow_to_device(torch, col, dev)
+            bufs = {}
+            # every rank must open every buffer: a rank without NULLs still allocates a (full) bitmap so that the collective is uniform
+            n_rows = int(d_.get("n", 0)) if not _is_torch_tensor(col) else int(col.shape[0])
+            if d_["validity"] is None:
+                d_["validity"] = torch.full(((n_rows + 7) // 8 + 1,), 0xFF, dtype=torch.uint8, device=dev)
+            for name in ("values", "validity", "data"):
+                t = d_[name]
+                if t is None:
+                    continue
+                nbytes = int(t.numel() * t.element_size())
+                pb = _PeerBuffer(self.xjoin, dist, nbytes + 64)
+                if nbytes:
+                    torch.as_tensor(_RawCudaArray(pb.local, nbytes, "|u1"), device=dev).copy_(t.contiguous().view(torch.uint8).reshape(-1))
+                bufs[name] = pb
+            torch.cuda.synchronize()
+            dist.barrier(group=self.group)
+            out.append(SharedColumn(d_["type"], bufs["values"].ptrs, bufs["validity"].ptrs,
+                                    bufs["data"].ptrs if "data" in bufs else None, keep=bufs))
+        return out
+
+    def unshare_columns(self, shared: Sequence):
+        for c in shared:
+            for pb in (c.keep or {}).values():
+                pb.close(self.dist)
+            c.keep = None
+
+    def build_rows(self, idx, n: int, idx_width: int = 8):
+        """rows.RowGatherer over LOCAL build indices (a probe result's build_idx, the finaliser's): gather(shared column) reads
+        the values from the ranks that own the rows."""
+        from .rows import RowGatherer, OriginPieces
+        if not self.track_origin:
+            raise B200JoinError(-5, "DistributedJoin(track_origin=True) is needed to map build rows back to their sources")
+        o = OriginPieces()
+        for part in self.build_origin:
+            for k in range(len(part)):
+                o.add(part.src[k], part.rows[k], part.rid_ptr[k], part.rid_base[k])
+        return RowGatherer(self.join, self.torch, idx, n, idx_width, o)
+
+    def probe_rows(self, idx, n: int, side: Optional[_Side] = None):
+        """rows.RowGatherer over LOCAL probe indices of the batch `side` (default: the last one) received."""
+        from .rows import RowGatherer
+        side = side if side is not None else self.probe
+        return RowGatherer(self.join, self.torch, idx, n, 4, self._origin_pieces(side))
+
+    def null_build_rows(self):
+        """Row ids (int32 device tensor) of this rank's build rows whose key is NULL (never sent; needs track_origin): Left /
+        Full / LeftAnti joins emit them here, with a NULL probe side."""
+        torch = self.torch
+        if not self.build_null_rid:
+            return torch.empty(0, dtype=torch.int32, device=torch.device("cuda", torch.cuda.current_device()))
+        return torch.cat(self.build_null_rid)
+
+    def null_probe_rows(self, side: Optional[_Side] = None):
+        """Row ids (int32 device tensor) of this rank's probe rows whose key is NULL: they were never sent. Right / Full /
+        RightAnti joins emit them here, with a NULL build side."""
+        side = side if side is not None else self.probe
+        return side.null_rid
+
     def received(self, side: _Side, what: str = "keys"):
         """The rows this rank received for one side as ONE local tensor (copies: tests, verification, late materialisation)."""
         torch = self.torch
@@ -458,6 +557,9 @@ class DistributedJoin:
     def reset(self):
         self.join.reset()
         self.build_rows_local = 0
+        self.build_rows_sent = 0
+        self.build_origin = []
+        self.build_null_rid = []
         if self.hot_join is not None:
             self.hot_join.close()
         self.hot = None
@@ -468,8 +570,14 @@ class DistributedJoin:
     def build_push(self, partition: int, keys: Sequence):
         """Exchange this rank's build rows, then append what this rank received to its local build side."""
         k = keys[0]
-        n_recv = self._timed("build", lambda: self._exchange(self.build, k, rowid_base=0))
+        base = self.build_rows_sent                 # row ids count this rank's build rows over all its batches
+        n_recv = self._timed("build", lambda: self._exchange(self.build, k, rowid_base=base))
+        self.build_rows_sent += int(k.shape[0])
         self.build_rows_local += n_recv
+        if self.track_origin:
+            self.build_origin.append(self._origin_pieces(self.build, copy=True))
+            if self.build.null_rid is not None and int(self.build.null_rid.shape[0]):
+                self.build_null_rid.append(self.build.null_rid.clone())      # the region is overwritten by the next build batch
         for ptr, m in self.build.pieces:          # mode "pull": one piece per source rank, copied out of the peers' send regions
             if m:
                 self.join.build_push(partition, [_dev_column(ptr, m, self.kw, keep=(self.build.keys,))])
@@ -812,6 +920,82 @@ class DistributedJoin:
             self.hot_join.close()
         self.xjoin.close()
         self.join.close()
+
+
+def _is_torch_tensor(x) -> bool:
+    return type(x).__module__.startswith("torch") and hasattr(x, "data_ptr")
+
+
+class DistributedKeyJoin:
+    """Join keyed on SEVERAL columns and / or Utf8 columns over the ranks ("composite / Utf8 keys through the
+    exchange"). The exchange and the local joins work on the ROW HASH of the key columns (create_hashes, b200j_hash_keys:
+    what the reference's table is keyed on, src/shared/shared.rs:11-16) as an 8-byte key; what the local join finds are
+    CANDIDATE pairs (B200J_OUT_MATCHES_ONLY). Their key columns are then read from the ranks that own the rows and compared
+    (equal_rows_arr, datafusion_private.rs:40-80: rows.equal_key_rows), and the surviving pairs go through the join-type
+    algebra of b200j_apply_pairs -- the same round trip a JoinFilter takes. Rows with a NULL key travel like any other row
+    and lose their candidates in the check, so Right / Full joins emit them from the rank that received them.
+    Key columns are pyarrow arrays; results are LOCAL index pairs: materialise them with .dj.build_rows / .dj.probe_rows."""
+
+    def __init__(self, join_type="inner", key_types: Sequence[int] = (8,), **kwargs):
+        import torch
+        self.torch = torch
+        kwargs.setdefault("mode", "pull")
+        self.dj = DistributedJoin(join_type, key_width=8, track_origin=True, narrow_keys=False, **kwargs)
+        self.hasher = HashJoin("inner", key_widths=tuple(key_types), device=torch.cuda.current_device())
+        self._build_batches: List[list] = []
+        self.build_key_cols = None
+        self.probe_key_cols = None
+
+    def _hashes(self, key_arrays):
+        h = self.hasher.hash_keys(list(key_arrays)).view(np.int64)
+        return self.torch.from_numpy(h.copy()).to(self.torch.device("cuda", self.torch.cuda.current_device()))
+
+    def build_push(self, partition: int, key_arrays: Sequence):
+        self._build_batches.append(list(key_arrays))
+        self.dj.build_push(partition, [self._hashes(key_arrays)])
+
+    def build_finish(self, partition: int):
+        import pyarrow as pa
+        n_cols = len(self._build_batches[0])
+        cols = [pa.concat_arrays([b[c].combine_chunks() if isinstance(b[c], pa.ChunkedArray) else b[c] for b in self._build_batches])
+                for c in range(n_cols)]
+        self.build_key_cols = self.dj.share_columns(cols)
+        self.dj.build_finish(partition)
+
+    def probe_batch(self, partition: int, key_arrays: Sequence, want: int = OUT_PAIRS):
+        from .join import OUT_MATCHES_ONLY
+        from .rows import equal_key_rows
+        torch, dj = self.torch, self.dj
+        if self.probe_key_cols is not None:
+            dj.unshare_columns(self.probe_key_cols)
+        self.probe_key_cols = dj.share_columns(list(key_arrays))
+        cand = dj.probe_batch(partition, [self._hashes(key_arrays)], want=OUT_PAIRS | OUT_MATCHES_ONLY)
+        n_recv = int(dj.probe.plan.recv_rows[dj.rank])
+        dev = torch.device("cuda", torch.cuda.current_device())
+        if cand.n:
+            cb, cp = cand.device_arrays()
+            cb_t, cp_t = torch.as_tensor(cb, device=dev), torch.as_tensor(cp, device=dev)
+            keep = equal_key_rows(dj.join, torch, dj.build_rows(cb_t, cand.n, cand.build_idx_width), dj.probe_rows(cp_t, cand.n),
+                                  self.build_key_cols, self.probe_key_cols)
+            kb, kp = cb_t[keep].contiguous(), cp_t[keep].contiguous()
+        else:
+            kb = torch.empty(0, dtype=torch.int64, device=dev)
+            kp = torch.empty(0, dtype=torch.int32, device=dev)
+        torch.cuda.current_stream().synchronize()
+        res = dj.join.apply_pairs_device(partition, n_recv, kb.data_ptr(), kp.data_ptr(), int(kb.shape[0]), want=want)
+        cand.release()
+        res.exchange_plan = dj.probe.plan
+        return res
+
+    def probe_finish(self, partition: int, want: int = OUT_PAIRS):
+        return self.dj.probe_finish(partition, want=want)
+
+    def close(self):
+        for cols in (self.probe_key_cols, self.build_key_cols):
+            if cols is not None:
+                self.dj.unshare_columns(cols)
+        self.hasher.close()
+        self.dj.close()
 
 
 class HostPairs:

@@ -330,6 +330,15 @@ class HashJoin:
                                               want, C.byref(r)))
         return PairResult(self, r)
 
+    def apply_pairs_device(self, partition: int, n_probe_rows: int, build_idx_ptr: int, probe_idx_ptr: int, n_pairs: int,
+                           want: int = OUT_PAIRS) -> PairResult:
+        """b200j_apply_pairs on DEVICE arrays (u64 build indices, u32 probe indices) of caller-filtered candidate pairs."""
+        r = N.Result()
+        r.struct_size = C.sizeof(N.Result)
+        self._check(N.lib().b200j_apply_pairs(self._h, partition, n_probe_rows, MEM_DEVICE, n_pairs, build_idx_ptr or None,
+                                              probe_idx_ptr or None, want, C.byref(r)))
+        return PairResult(self, r)
+
     def probe_finish(self, partition: int, want: int = OUT_PAIRS | OUT_HOST) -> PairResult:
         r = N.Result()
         r.struct_size = C.sizeof(N.Result)

@@ -321,6 +321,38 @@ int32_t b200j_ipc_open(b200j_handle *h, const uint8_t *handle, void **peer_ptr);
 int32_t b200j_ipc_close(b200j_handle *h, void *peer_ptr);
 int32_t b200j_ipc_free(b200j_handle *h, void *ptr);
 
+/* ---- output rows across GPUs (a6 over the exchange; the reference is single-process) ---------------------------
+ * take_multiple_record_batch (src/shared/shared.rs:83-92) when the join's sides were handed over as PIECES -- one piece per source
+ * rank of the multi-GPU exchange: the local join's indices count the rows this rank RECEIVED (build rows in build_push order,
+ * probe rows in piece order), while the columns stayed on the rank that owns the row, mapped into this process with
+ * b200j_ipc_open (or plain device pointers when several "ranks" share a GPU). Late materialisation in two steps, every array in
+ * DEVICE memory, every call enqueued on the handle's stream:
+ *   b200j_resolve_origin   index -> (piece, row at the piece's source). idx: u32 / u64 indices (idx_width 4 / 8) into the
+ *                          concatenation of the pieces; a NULL index (all ones) or one past the pieces gives row 0xffffffff.
+ *                          piece_rowid[p]: the u32 row ids that travelled with piece p (b200j_shuffle_* wrote them; may be peer
+ *                          memory; NULL = the position inside the piece), piece_rowid_base[p] is added (NULL = zeros).
+ *   b200j_gather_pieces    one fixed-width column (1/2/4/8/16 bytes): out_values[i] = col_values[piece[i]][row[i]], validity
+ *                          word i/32 bit i%32 = row is not 0xffffffff and the source row is valid (col_validity[p]: LSB bitmap
+ *                          from the column's row 0, or NULL; the array itself may be NULL). out_validity may be NULL.
+ *   b200j_gather_pieces_utf8_offsets / _data   one Utf8 column (int32 Arrow offsets + bytes per source): the first call writes the
+ *                          n + 1 output offsets and the validity words and RETURNS the byte total (it synchronises the stream);
+ *                          the caller allocates that many bytes and the second call copies them.
+ *   b200j_utf8_rows_equal  out[i] = 1 when row i of two gathered Utf8 columns holds the same bytes and both are valid: the key
+ *                          check of a join keyed on row hashes (equal_rows_arr, src/shared/datafusion_private.rs:40-80).
+ * At most B200J_MAX_PIECES pieces per call. */
+#define B200J_MAX_PIECES 64
+int32_t b200j_resolve_origin(b200j_handle *h, int64_t n, const void *idx, int32_t idx_width, int32_t n_pieces, const int64_t *piece_rows,
+                             const uint32_t *const *piece_rowid, const uint32_t *piece_rowid_base, uint32_t *out_piece, uint32_t *out_row);
+int32_t b200j_gather_pieces(b200j_handle *h, int64_t n, const uint32_t *piece, const uint32_t *row, int32_t n_pieces, const void *const *col_values,
+                            const uint8_t *const *col_validity, int32_t width, void *out_values, uint32_t *out_validity);
+int32_t b200j_gather_pieces_utf8_offsets(b200j_handle *h, int64_t n, const uint32_t *piece, const uint32_t *row, int32_t n_pieces,
+                                         const int32_t *const *col_offsets, const uint8_t *const *col_validity, int32_t *out_offsets,
+                                         uint32_t *out_validity, int64_t *total_bytes);
+int32_t b200j_gather_pieces_utf8_data(b200j_handle *h, int64_t n, const uint32_t *piece, const uint32_t *row, int32_t n_pieces,
+                                      const int32_t *const *col_offsets, const uint8_t *const *col_data, const int32_t *out_offsets, uint8_t *out_data);
+int32_t b200j_utf8_rows_equal(b200j_handle *h, int64_t n, const int32_t *off_a, const uint8_t *data_a, const uint32_t *valid_a, const int32_t *off_b,
+                              const uint8_t *data_b, const uint32_t *valid_b, uint8_t *out);
+
 /* ---- allocation-free destination count -------------------------------------------------------
  * No counterpart in the reference: added for callers that cannot call cudaMalloc
  * (code under CUDA graph capture, tight serving loops, harnesses that forbid it). Same result as b200j_shuffle_count
