@@ -177,6 +177,7 @@ struct b200j_handle {
     bool shuffle_armed = false;        // b200j_shuffle_count done, b200j_shuffle_scatter pending
     PartPlan shuffle_plan;
     int64_t shuffle_n = 0;
+    bool key_via_probe = true;         // b200j_gather: the build key column of matched pairs is read from the probe key column (B200J_KEY_VIA_PROBE=0: off)
     uint32_t *static_hist = nullptr;   // device address of g_static_hist ON THIS HANDLE'S DEVICE (b200j_shuffle_count_static)
     Counters *d_ctr = nullptr;
     Counters *h_ctr = nullptr;         // pinned mirror
@@ -1876,6 +1877,7 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
             else
                 cudaGetLastError();
             if (const char *e = getenv("B200J_FUSED_CTAS")) h->fused_ctas_per_sm = std::max(1, atoi(e));
+            if (const char *e = getenv("B200J_KEY_VIA_PROBE")) h->key_via_probe = atoi(e) != 0;
             if (const char *e = getenv("B200J_NO_DENSE")) h->dense_ok = atoi(e) == 0;
             if (const char *e = getenv("B200J_DENSE_MISS_MAX")) h->dense_miss_max = (float)atof(e);
             if (const char *e = getenv("B200J_L1_TABLE_BYTES")) h->l1_table_bytes = (uint64_t)atoll(e);

@@ -140,6 +140,55 @@ __global__ void __launch_bounds__(256) gather_fixed_multi_kernel(GatherCols cols
     }
 }
 
+// The build KEY column of an equi-join's output rows, without touching the build store: a matched pair's build key IS its probe
+// key (bit for bit: the table compares key values), and the probe key column is read at probe_idx -- near-sequential for the
+// dense probe's output -- instead of a random read into the whole build store per row. A row whose probe index is NULL (the
+// finaliser's rows, should a caller pass them with a batch) still reads the build store. Same 128-rows-per-warp shape as above.
+template <typename T, typename IdxT>
+__global__ void __launch_bounds__(256) gather_key_via_probe_kernel(const IdxT *__restrict__ bidx, const uint32_t *__restrict__ pidx, int64_t n,
+                                                                   const T *__restrict__ build_key, const uint8_t *__restrict__ build_validity,
+                                                                   const T *__restrict__ probe_key, T *__restrict__ dst, uint32_t *__restrict__ dst_valid,
+                                                                   unsigned long long *null_count) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    uint32_t nulls = 0;
+    for (int64_t row0 = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (32 * GF_ITEMS); row0 < n; row0 += warps * (32 * GF_ITEMS)) {
+        T v[GF_ITEMS];
+        bool valid[GF_ITEMS];
+#pragma unroll
+        for (int q = 0; q < GF_ITEMS; q++) {
+            const int64_t i = row0 + q * 32 + lane;
+            v[q] = T{};
+            valid[q] = false;
+            if (i < n) {
+                const IdxT b = __ldcs(bidx + i);
+                const uint32_t p = __ldcs(pidx + i);
+                if (!idx_is_null(b)) {
+                    if (p != 0xffffffffu) {
+                        v[q] = probe_key[p];
+                        valid[q] = true;
+                    } else if (build_key != nullptr && bit_valid(build_validity, (int64_t)b)) {
+                        v[q] = build_key[b];
+                        valid[q] = true;
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < GF_ITEMS; q++) {
+            const int64_t i = row0 + q * 32 + lane;
+            if (i < n) {
+                dst[i] = v[q];
+                if (!valid[q]) nulls++;
+            }
+            const uint32_t word = __ballot_sync(0xffffffffu, valid[q]);
+            if (lane == 0 && row0 + q * 32 < n) dst_valid[(row0 + q * 32) >> 5] = word;
+        }
+    }
+    const unsigned long long z = warp_sum_u32(nulls);
+    if (lane == 0 && z) atomicAdd(null_count, z);
+}
+
 __device__ __forceinline__ int64_t utf8_off(const GatherSrc &s, int64_t j) {
     return s.offsets64 ? reinterpret_cast<const int64_t *>(s.offsets)[j] : (int64_t)reinterpret_cast<const int32_t *>(s.offsets)[j];
 }

@@ -101,7 +101,7 @@ struct SideCol {
     GatherSrc src;
 };
 template <typename IdxT>
-void gather_side(GatherCtx &g, int first_col, const std::vector<SideCol> &sc, const IdxT *idx) {
+void gather_side(GatherCtx &g, int first_col, const std::vector<SideCol> &sc, const IdxT *idx, const void *key_via_probe = nullptr) {
     H *h = g.h;
     const int64_t n = g.n;
     GatherCols batch{};
@@ -134,6 +134,21 @@ void gather_side(GatherCtx &g, int first_col, const std::vector<SideCol> &sc, co
         void *dst = gather_dev_alloc(g, (size_t)n * sc[k].type + 16);
         oc.values = dst;
         oc.values_bytes = n * sc[k].type;
+        if (k == 0 && key_via_probe != nullptr && n > 0) {
+            // the build side's single fixed-width key column: taken from the probe batch's key column (gather_key_via_probe_kernel)
+            const int grid = grid_for(h, (n + 127) / 128, 8, 8);
+            if (sc[k].type == 8)
+                gather_key_via_probe_kernel<unsigned long long, IdxT><<<grid, 256, 0, h->stream>>>(
+                    idx, g.pidx, n, (const unsigned long long *)sc[k].src.values, sc[k].src.validity, (const unsigned long long *)key_via_probe,
+                    (unsigned long long *)dst, dvalid, g.d_nulls + col);
+            else
+                gather_key_via_probe_kernel<uint32_t, IdxT><<<grid, 256, 0, h->stream>>>(
+                    idx, g.pidx, n, (const uint32_t *)sc[k].src.values, sc[k].src.validity, (const uint32_t *)key_via_probe, (uint32_t *)dst, dvalid,
+                    g.d_nulls + col);
+            h->st.kernel_launches++;
+            CU(cudaGetLastError());
+            continue;
+        }
         GatherCol &gc = batch.c[batch.n];
         gc.values = sc[k].src.values;
         gc.validity = sc[k].src.validity;
@@ -219,6 +234,19 @@ void do_gather_impl(H *h, const b200j_result *pairs, const b200j_batch *probe_ba
         g.d_nulls_scratch = g.d_nulls + n_cols + 1;
         PhaseTimer tm(h, &h->st.ms_gather);
         int col = 0;
+        // the probe side's column descriptors first: the build side's key column is taken from the probe key column when it can be
+        std::vector<SideCol> psc;
+        const bool have_probe = staged_probe != nullptr || (probe_batch && probe_batch->n_rows > 0);
+        if (want_probe) {
+            for (int i = 0; i < nk + npp && staged_probe == nullptr; i++) {
+                const int type = i < nk ? h->key_widths[i] : h->probe_payload_types[i - nk];
+                GatherSrc s{};
+                if (have_probe)
+                    s = gather_stage_column(g, i < nk ? probe_batch->keys[i] : probe_batch->payload[i - nk], type, probe_batch->n_rows, probe_batch->mem);
+                psc.push_back(SideCol{type, s});
+            }
+            if (staged_probe) psc = *staged_probe;
+        }
         if (want_build) {
             std::vector<SideCol> sc;
             for (int i = 0; i < nk + nbp; i++) {
@@ -231,22 +259,15 @@ void do_gather_impl(H *h, const b200j_result *pairs, const b200j_batch *probe_ba
                 if (h->n_build == 0) s.values = s.offsets = nullptr;
                 sc.push_back(SideCol{cs.type, s});
             }
-            if (bwidth == 4) gather_side<uint32_t>(g, col, sc, reinterpret_cast<const uint32_t *>(g.bidx));     // B200J_OUT_BUILD_U32 pairs
-            else gather_side<uint64_t>(g, col, sc, g.bidx);
+            // single fixed-width key, both sides in the output, a probe side to read from: build key := probe key of the pair
+            const void *via = (h->key_via_probe && want_probe && have_probe && nk == 1 && !h->composite && g.pidx != nullptr && g.bidx != nullptr &&
+                               (h->key_widths[0] == 4 || h->key_widths[0] == 8)) ? psc[0].src.values : nullptr;
+            if (bwidth == 4) gather_side<uint32_t>(g, col, sc, reinterpret_cast<const uint32_t *>(g.bidx), via);     // B200J_OUT_BUILD_U32 pairs
+            else gather_side<uint64_t>(g, col, sc, g.bidx, via);
             col += nk + nbp;
         }
         if (want_probe) {
-            std::vector<SideCol> sc;
-            const bool have_probe = staged_probe != nullptr || (probe_batch && probe_batch->n_rows > 0);
-            for (int i = 0; i < nk + npp && staged_probe == nullptr; i++) {
-                const int type = i < nk ? h->key_widths[i] : h->probe_payload_types[i - nk];
-                GatherSrc s{};
-                if (have_probe)
-                    s = gather_stage_column(g, i < nk ? probe_batch->keys[i] : probe_batch->payload[i - nk], type, probe_batch->n_rows, probe_batch->mem);
-                sc.push_back(SideCol{type, s});
-            }
-            if (staged_probe) sc = *staged_probe;
-            gather_side<uint32_t>(g, col, sc, have_probe ? g.pidx : nullptr);
+            gather_side<uint32_t>(g, col, psc, have_probe ? g.pidx : nullptr);
             col += nk + npp;
         }
         tm.stop();
