@@ -19,6 +19,7 @@
 #include <cstdlib>
 #include <ctime>
 #include <mutex>
+#include <set>
 #include <string>
 #include <vector>
 
@@ -86,6 +87,13 @@ struct ResultOwner {
     void *probe_idx = nullptr;
     int32_t mem = B200J_MEM_DEVICE;
     int32_t bwidth = 8;               // bytes per build index: 4 after B200J_OUT_BUILD_U32 narrowing
+    // The dense probe behind the radix layout leaves the pairs in the order of the block-partitioned probe stream. When the
+    // caller of probe_device asks for it (want_seg), the stream's segment table stays with the result so that b200j_gather can
+    // walk the build side partition by partition (gather_seg_multi_kernel). Device memory, whatever `mem` says.
+    bool want_seg = false;
+    void *seg = nullptr;              // [seg_blocks][seg_P + 2] segment starts, then [seg_blocks] block bases
+    uint32_t seg_blocks = 0, seg_P = 0;
+    int64_t seg_n = 0;                // rows the table describes (= the result's rows)
 };
 
 struct CachedBlock {
@@ -177,6 +185,8 @@ struct b200j_handle {
     bool shuffle_armed = false;        // b200j_shuffle_count done, b200j_shuffle_scatter pending
     PartPlan shuffle_plan;
     int64_t shuffle_n = 0;
+    bool gather_seg = true;            // b200j_gather: build columns of a dense radix result are gathered partition by partition (B200J_GATHER_SEG=0: off)
+    std::set<const void *> seg_owners;  // live results that carry a segment table (b200j_gather checks a caller's _owner against it)
     bool key_via_probe = true;         // b200j_gather: the build key column of matched pairs is read from the probe key column (B200J_KEY_VIA_PROBE=0: off)
     uint32_t *static_hist = nullptr;   // device address of g_static_hist ON THIS HANDLE'S DEVICE (b200j_shuffle_count_static)
     Counters *d_ctr = nullptr;
@@ -861,8 +871,17 @@ void fill_result(b200j_result *out, ResultOwner *ro, int64_t n, int mem) {
     if (out->struct_size >= offsetof(b200j_result, build_idx_width) + sizeof(int32_t)) out->build_idx_width = ro->bwidth;
 }
 
+void drop_seg(H *h, ResultOwner *ro) {
+    if (ro->seg) {
+        h->seg_owners.erase(ro);
+        big_free(h, ro->seg);
+        ro->seg = nullptr;
+    }
+}
+
 void release_owner(H *h, ResultOwner *ro) {
     if (!ro) return;
+    drop_seg(h, ro);
     if (ro->mem == B200J_MEM_DEVICE) {
         if (ro->build_idx) big_free(h, ro->build_idx);
         if (ro->probe_idx) big_free(h, ro->probe_idx);
@@ -1143,6 +1162,7 @@ void move_result_to_host(H *h, ResultOwner *ro, int64_t n) {
     ro->build_idx = hb;
     ro->probe_idx = hp;
     ro->mem = B200J_MEM_HOST;
+    drop_seg(h, ro);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1424,6 +1444,7 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
     const int kw = h->key_widths[0];
     const int64_t n = b->n_rows;
     ResultOwner *ro = new ResultOwner();
+    ro->want_seg = true;
     std::vector<void *> temps;
     try {
         int64_t total = 0, n_bnull = 0;
@@ -1878,6 +1899,7 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
                 cudaGetLastError();
             if (const char *e = getenv("B200J_FUSED_CTAS")) h->fused_ctas_per_sm = std::max(1, atoi(e));
             if (const char *e = getenv("B200J_KEY_VIA_PROBE")) h->key_via_probe = atoi(e) != 0;
+            if (const char *e = getenv("B200J_GATHER_SEG")) h->gather_seg = atoi(e) != 0;
             if (const char *e = getenv("B200J_NO_DENSE")) h->dense_ok = atoi(e) == 0;
             if (const char *e = getenv("B200J_DENSE_MISS_MAX")) h->dense_miss_max = (float)atof(e);
             if (const char *e = getenv("B200J_L1_TABLE_BYTES")) h->l1_table_bytes = (uint64_t)atoll(e);
@@ -1987,7 +2009,7 @@ int32_t b200j_reset_stats(b200j_handle *h) {
     h->st.ms_build_copy = h->st.ms_build_partition = h->st.ms_build_insert = 0;
     h->st.ms_probe_partition = h->st.ms_probe = h->st.ms_gather = 0;
     h->st.probe_launches = h->st.kernel_launches = h->st.probe_retries = 0;
-    h->st.dense_probe_launches = h->st.compact_launches = h->st.seg_probe_launches = h->st.narrow_probe_launches = 0;
+    h->st.dense_probe_launches = h->st.compact_launches = h->st.seg_probe_launches = h->st.narrow_probe_launches = h->st.gather_seg_launches = 0;
     h->st.ms_exchange_partition = 0;
     return B200J_OK;
 }

@@ -189,6 +189,203 @@ __global__ void __launch_bounds__(256) gather_key_via_probe_kernel(const IdxT *_
     if (lane == 0 && z) atomicAdd(null_count, z);
 }
 
+// Both KEY columns of an equi-join's output rows in ONE pass over the index pairs: the probe key column (probe_key[probe_idx])
+// and the build key column, which for a matched pair is the same value (see gather_key_via_probe_kernel). One read of the
+// pairs, one random read per row, two coalesced writes -- instead of two launches that each read the pairs and the probe key.
+template <typename T, typename IdxT>
+__global__ void __launch_bounds__(256) gather_keys_both_kernel(const IdxT *__restrict__ bidx, const uint32_t *__restrict__ pidx, int64_t n,
+                                                               const T *__restrict__ build_key, const uint8_t *__restrict__ build_validity,
+                                                               const T *__restrict__ probe_key, const uint8_t *__restrict__ probe_validity,
+                                                               int64_t probe_bit_offset, T *__restrict__ dst_b, uint32_t *__restrict__ dst_b_valid,
+                                                               T *__restrict__ dst_p, uint32_t *__restrict__ dst_p_valid,
+                                                               unsigned long long *null_b, unsigned long long *null_p) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    uint32_t nulls_b = 0, nulls_p = 0;
+    for (int64_t row0 = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (32 * GF_ITEMS); row0 < n; row0 += warps * (32 * GF_ITEMS)) {
+        T vb[GF_ITEMS], vp[GF_ITEMS];
+        bool okb[GF_ITEMS], okp[GF_ITEMS];
+#pragma unroll
+        for (int q = 0; q < GF_ITEMS; q++) {
+            const int64_t i = row0 + q * 32 + lane;
+            vb[q] = T{};
+            vp[q] = T{};
+            okb[q] = okp[q] = false;
+            if (i < n) {
+                const IdxT b = __ldcs(bidx + i);
+                const uint32_t p = __ldcs(pidx + i);
+                if (p != 0xffffffffu) {
+                    const T v = probe_key[p];
+                    if (bit_valid(probe_validity, probe_bit_offset + (int64_t)p)) { vp[q] = v; okp[q] = true; }
+                    if (!idx_is_null(b)) { vb[q] = v; okb[q] = true; }            // a matched pair: the keys are equal, so neither is NULL
+                } else if (!idx_is_null(b) && build_key != nullptr && bit_valid(build_validity, (int64_t)b)) {
+                    vb[q] = build_key[b];
+                    okb[q] = true;
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < GF_ITEMS; q++) {
+            const int64_t i = row0 + q * 32 + lane;
+            if (i < n) {
+                __stcs(dst_b + i, vb[q]);
+                __stcs(dst_p + i, vp[q]);
+                if (!okb[q]) nulls_b++;
+                if (!okp[q]) nulls_p++;
+            }
+            const uint32_t wb = __ballot_sync(0xffffffffu, okb[q]), wp = __ballot_sync(0xffffffffu, okp[q]);
+            if (lane == 0 && row0 + q * 32 < n) {
+                dst_b_valid[(row0 + q * 32) >> 5] = wb;
+                dst_p_valid[(row0 + q * 32) >> 5] = wp;
+            }
+        }
+    }
+    const unsigned long long zb = warp_sum_u32(nulls_b), zp = warp_sum_u32(nulls_p);
+    if (lane == 0 && zb) atomicAdd(null_b, zb);
+    if (lane == 0 && zp) atomicAdd(null_p, zp);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Build-side gather in PARTITION order (round 2). The dense probe behind the radix layout leaves its pairs in the order of
+// the block-partitioned probe stream (radix_block.cuh): block after block, and inside a block partition after partition.
+// Gathering the build columns in that order touches, per 32 K output rows, build rows of ALL partitions -- one random 32 B
+// DRAM sector per row and column (measured: 26 ms per 1 B rows for one int64 column, the DRAM's random-sector rate). Walked
+// the way the probe walks -- for p = 0 .. P: the segments (p, b) of all blocks -- the rows in flight reference the build rows
+// of ONE partition: 1/P of the column's sectors (25 MB at C2), fetched from DRAM once and then served by the L2 for the
+// ~10 output rows that share each of them. Reads of the index array and writes of the output stay coalesced (a segment is
+// a contiguous run of output rows). Validity words straddle segments that different warps write at different times, so the
+// bitmaps are pre-set to all-valid by the host and NULL rows clear their bits with atomicAnd (rare).
+// ---------------------------------------------------------------------------------------------------------------------
+struct GatherSegArgs {
+    const uint32_t *seg;          // [n_blocks][P + 2] segment starts inside each block (radix_block.cuh)
+    const uint32_t *block_base;   // [n_blocks] first output row of every block
+    uint32_t        n_blocks;
+    uint32_t        P;
+    uint32_t        n_units;      // n_blocks * (P + 1): the last "partition" holds the NULL-key rows
+    unsigned int   *next;         // claim counter, zero at launch
+};
+constexpr int GS_UNITS = 4;       // segments per warp claim
+
+// Reads of the build columns: no L1 allocation (a sector is never reused by the same SM soon enough) and an L2 evict-last
+// policy (the current partition's sectors are the only data with reuse; index and output streams are evict-first).
+__device__ __forceinline__ uint64_t l2_evict_last_policy() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+template <typename T>
+__device__ __forceinline__ T ld_gather_keep(const T *p, uint64_t) { return __ldcg(p); }
+template <>
+__device__ __forceinline__ unsigned long long ld_gather_keep<unsigned long long>(const unsigned long long *p, uint64_t pol) {
+    unsigned long long v;
+    asm volatile("ld.global.L1::no_allocate.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(pol));
+    return v;
+}
+template <>
+__device__ __forceinline__ uint32_t ld_gather_keep<uint32_t>(const uint32_t *p, uint64_t pol) {
+    uint32_t v;
+    asm volatile("ld.global.L1::no_allocate.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+    return v;
+}
+
+template <typename T>
+__device__ __forceinline__ void gather_seg_items(const GatherCol &gc, const int64_t (&j)[GF_ITEMS], const bool (&have)[GF_ITEMS],
+                                                 const bool (&inr)[GF_ITEMS], int64_t row0, int lane, uint32_t &nulls, uint64_t pol) {
+    T v[GF_ITEMS];
+    bool valid[GF_ITEMS];
+#pragma unroll
+    for (int q = 0; q < GF_ITEMS; q++) {
+        valid[q] = have[q] && gc.values != nullptr && bit_valid(gc.validity, gc.bit_offset + j[q]);
+        v[q] = T{};
+        if (valid[q]) v[q] = ld_gather_keep(reinterpret_cast<const T *>(gc.values) + j[q], pol);
+    }
+#pragma unroll
+    for (int q = 0; q < GF_ITEMS; q++) {
+        const int64_t r0 = row0 + q * 32;
+        if (inr[q]) {
+            __stcs(reinterpret_cast<T *>(gc.dst) + r0 + lane, v[q]);
+            if (!valid[q]) nulls++;
+        }
+        const uint32_t inv = __ballot_sync(0xffffffffu, inr[q] && !valid[q]);
+        if (inv != 0u && lane == 0) {
+            const uint32_t sh = (uint32_t)(r0 & 31);
+            const uint32_t lo = inv << sh;
+            if (lo) atomicAnd(gc.dst_valid + (r0 >> 5), ~lo);
+            if (sh) {
+                const uint32_t hi = inv >> (32u - sh);
+                if (hi) atomicAnd(gc.dst_valid + (r0 >> 5) + 1, ~hi);
+            }
+        }
+    }
+}
+
+template <typename IdxT>
+__global__ void __launch_bounds__(256) gather_seg_multi_kernel(GatherCols cols, const IdxT *__restrict__ idx, int64_t n, GatherSegArgs sg,
+                                                               unsigned long long *null_counts /* [cols.n] */) {
+    constexpr uint32_t FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const uint64_t pol = l2_evict_last_policy();
+    uint32_t nulls[GF_MAX_COLS];
+#pragma unroll
+    for (int c = 0; c < GF_MAX_COLS; c++) nulls[c] = 0;
+    // bits past the last row are zero in every bitmap this library hands out
+    if (blockIdx.x == 0 && (int)threadIdx.x < cols.n && (n & 31) != 0)
+        atomicAnd(cols.c[threadIdx.x].dst_valid + (n >> 5), (1u << (uint32_t)(n & 31)) - 1u);
+    const uint32_t n_claims = (sg.n_units + GS_UNITS - 1) / GS_UNITS;
+    uint32_t claim = 0;
+    if (lane == 0) claim = atomicAdd(sg.next, 1u);
+    for (;;) {
+        const uint32_t cur = __shfl_sync(FULL, claim, 0);
+        if (cur >= n_claims) break;
+        if (lane == 0) claim = atomicAdd(sg.next, 1u);
+        uint32_t my_start = 0, my_len = 0;
+        {
+            const uint32_t u = cur * GS_UNITS + (uint32_t)lane;
+            if (lane < GS_UNITS && u < sg.n_units) {
+                const uint32_t p = u / sg.n_blocks, b = u - p * sg.n_blocks;
+                const uint32_t e0 = __ldg(sg.seg + (size_t)b * (sg.P + 2) + p), e1 = __ldg(sg.seg + (size_t)b * (sg.P + 2) + p + 1);
+                my_start = __ldg(sg.block_base + b) + e0;
+                my_len = e1 - e0;
+            }
+        }
+#pragma unroll 1
+        for (int s = 0; s < GS_UNITS; s++) {
+            const uint32_t len = __shfl_sync(FULL, my_len, s);
+            if (len == 0) continue;
+            const int64_t start = (int64_t)__shfl_sync(FULL, my_start, s);
+            for (uint32_t i0 = 0; i0 < len; i0 += 32 * GF_ITEMS) {
+                int64_t j[GF_ITEMS];
+                bool have[GF_ITEMS], inr[GF_ITEMS];
+#pragma unroll
+                for (int q = 0; q < GF_ITEMS; q++) {
+                    inr[q] = i0 + q * 32 + lane < len;
+                    const IdxT x = inr[q] ? __ldcs(idx + start + i0 + q * 32 + lane) : (IdxT)~(IdxT)0;
+                    have[q] = !idx_is_null(x);
+                    j[q] = have[q] ? (int64_t)x : 0;
+                }
+#pragma unroll
+                for (int c = 0; c < GF_MAX_COLS; c++) {
+                    if (c >= cols.n) break;
+                    const GatherCol &gc = cols.c[c];
+                    switch (gc.width) {
+                        case 1: gather_seg_items<uint8_t>(gc, j, have, inr, start + i0, lane, nulls[c], pol); break;
+                        case 2: gather_seg_items<uint16_t>(gc, j, have, inr, start + i0, lane, nulls[c], pol); break;
+                        case 4: gather_seg_items<uint32_t>(gc, j, have, inr, start + i0, lane, nulls[c], pol); break;
+                        case 8: gather_seg_items<unsigned long long>(gc, j, have, inr, start + i0, lane, nulls[c], pol); break;
+                        default: gather_seg_items<ulonglong2>(gc, j, have, inr, start + i0, lane, nulls[c], pol); break;
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < GF_MAX_COLS; c++) {
+        if (c >= cols.n) break;
+        const unsigned long long z = warp_sum_u32(nulls[c]);
+        if (lane == 0 && z) atomicAdd(null_counts + c, z);
+    }
+}
+
 __device__ __forceinline__ int64_t utf8_off(const GatherSrc &s, int64_t j) {
     return s.offsets64 ? reinterpret_cast<const int64_t *>(s.offsets)[j] : (int64_t)reinterpret_cast<const int32_t *>(s.offsets)[j];
 }

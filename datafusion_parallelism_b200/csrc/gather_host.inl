@@ -94,14 +94,29 @@ void gather_one_column(GatherCtx &g, int col, int type, const GatherSrc &src, co
     }
 }
 
+// output buffers of one fixed-width column: values + validity words (a few spare words: the kernels write whole words)
+void gather_out_fixed(GatherCtx &g, int col, int type, void **dst, uint32_t **dvalid) {
+    b200j_out_column &oc = g.own->cols[col];
+    oc = b200j_out_column{};
+    const size_t vwords = (size_t)((g.n + 31) / 32 + 4);
+    *dvalid = (uint32_t *)gather_dev_alloc(g, vwords * 4);
+    oc.validity = (uint8_t *)*dvalid;
+    *dst = gather_dev_alloc(g, (size_t)g.n * type + 16);
+    oc.values = *dst;
+    oc.values_bytes = g.n * type;
+}
+
 // All columns of one side: the fixed-width ones go through gather_fixed_multi_kernel, up to GF_MAX_COLS per launch (the
 // index array is read once per launch, not once per column); Utf8 columns take the three-pass path above.
 struct SideCol {
     int type;
     GatherSrc src;
 };
+// skip_first: column first_col has been produced already (gather_keys_both_kernel). seg_ro: the pairs are a dense radix result
+// that still carries its segment table -- the fixed-width columns are then gathered partition by partition.
 template <typename IdxT>
-void gather_side(GatherCtx &g, int first_col, const std::vector<SideCol> &sc, const IdxT *idx, const void *key_via_probe = nullptr) {
+void gather_side(GatherCtx &g, int first_col, const std::vector<SideCol> &sc, const IdxT *idx, const void *key_via_probe = nullptr,
+                 bool skip_first = false, const ResultOwner *seg_ro = nullptr) {
     H *h = g.h;
     const int64_t n = g.n;
     GatherCols batch{};
@@ -110,17 +125,33 @@ void gather_side(GatherCtx &g, int first_col, const std::vector<SideCol> &sc, co
         if (batch.n == 0) return;
         if (n > 0) {
             // the kernel's null counters are indexed by position in the batch: count into a scratch row, add up afterwards
-            const int grid = grid_for(h, (n + 127) / 128, 8, 8);
-            gather_fixed_multi_kernel<IdxT><<<grid, 256, 0, h->stream>>>(batch, idx, n, g.d_nulls_scratch);
+            if (seg_ro != nullptr) {
+                GatherSegArgs sg{};
+                sg.seg = (const uint32_t *)seg_ro->seg;
+                sg.block_base = sg.seg + (size_t)seg_ro->seg_blocks * (seg_ro->seg_P + 2);
+                sg.n_blocks = seg_ro->seg_blocks;
+                sg.P = seg_ro->seg_P;
+                sg.n_units = seg_ro->seg_blocks * (seg_ro->seg_P + 1);
+                sg.next = (unsigned int *)(g.d_nulls_scratch + GF_MAX_COLS);
+                for (int k = 0; k < batch.n; k++)          // all-valid bitmaps: NULL rows clear their bits
+                    CU(cudaMemsetAsync(batch.c[k].dst_valid, 0xff, (size_t)((n + 31) / 32) * 4, h->stream));
+                const int64_t n_claims = ((int64_t)sg.n_units + GS_UNITS - 1) / GS_UNITS;
+                const int grid = grid_for(h, n_claims, 8, 8);
+                gather_seg_multi_kernel<IdxT><<<grid, 256, 0, h->stream>>>(batch, idx, n, sg, g.d_nulls_scratch);
+                h->st.gather_seg_launches++;
+            } else {
+                const int grid = grid_for(h, (n + 127) / 128, 8, 8);
+                gather_fixed_multi_kernel<IdxT><<<grid, 256, 0, h->stream>>>(batch, idx, n, g.d_nulls_scratch);
+            }
             h->st.kernel_launches++;
             CU(cudaGetLastError());
             for (int k = 0; k < batch.n; k++)
                 CU(cudaMemcpyAsync(g.d_nulls + batch_cols[k], g.d_nulls_scratch + k, 8, cudaMemcpyDeviceToDevice, h->stream));
-            CU(cudaMemsetAsync(g.d_nulls_scratch, 0, GF_MAX_COLS * 8, h->stream));
+            CU(cudaMemsetAsync(g.d_nulls_scratch, 0, (GF_MAX_COLS + 1) * 8, h->stream));
         }
         batch = GatherCols{};
     };
-    for (size_t k = 0; k < sc.size(); k++) {
+    for (size_t k = skip_first ? 1 : 0; k < sc.size(); k++) {
         const int col = first_col + (int)k;
         if (sc[k].type == B200J_T_UTF8) {
             gather_one_column<IdxT>(g, col, sc[k].type, sc[k].src, idx);
@@ -228,12 +259,13 @@ void do_gather_impl(H *h, const b200j_result *pairs, const b200j_batch *probe_ba
         g.bidx = (const uint64_t *)stage_idx(pairs->build_idx, (size_t)bwidth);
         g.pidx = (const uint32_t *)stage_idx(pairs->probe_idx, 4);
         void *dn = nullptr;
-        CU(big_alloc(h, &dn, (size_t)(n_cols + 1 + GF_MAX_COLS) * 8)); g.temps.push_back(dn);
-        CU(cudaMemsetAsync(dn, 0, (size_t)(n_cols + 1 + GF_MAX_COLS) * 8, h->stream));
+        CU(big_alloc(h, &dn, (size_t)(n_cols + 2 + GF_MAX_COLS) * 8)); g.temps.push_back(dn);      // + the segment gather's claim counter
+        CU(cudaMemsetAsync(dn, 0, (size_t)(n_cols + 2 + GF_MAX_COLS) * 8, h->stream));
         g.d_nulls = (unsigned long long *)dn;
         g.d_nulls_scratch = g.d_nulls + n_cols + 1;
         PhaseTimer tm(h, &h->st.ms_gather);
         int col = 0;
+        bool keys_done = false;
         // the probe side's column descriptors first: the build side's key column is taken from the probe key column when it can be
         std::vector<SideCol> psc;
         const bool have_probe = staged_probe != nullptr || (probe_batch && probe_batch->n_rows > 0);
@@ -262,12 +294,42 @@ void do_gather_impl(H *h, const b200j_result *pairs, const b200j_batch *probe_ba
             // single fixed-width key, both sides in the output, a probe side to read from: build key := probe key of the pair
             const void *via = (h->key_via_probe && want_probe && have_probe && nk == 1 && !h->composite && g.pidx != nullptr && g.bidx != nullptr &&
                                (h->key_widths[0] == 4 || h->key_widths[0] == 8)) ? psc[0].src.values : nullptr;
-            if (bwidth == 4) gather_side<uint32_t>(g, col, sc, reinterpret_cast<const uint32_t *>(g.bidx), via);     // B200J_OUT_BUILD_U32 pairs
-            else gather_side<uint64_t>(g, col, sc, g.bidx, via);
+            if (via != nullptr && n > 0) {
+                // ... and both key columns come out of ONE pass over the pairs (gather_keys_both_kernel)
+                const int kw = h->key_widths[0], pcol = nk + nbp;
+                void *dst_b = nullptr, *dst_p = nullptr;
+                uint32_t *val_b = nullptr, *val_p = nullptr;
+                gather_out_fixed(g, col, kw, &dst_b, &val_b);
+                gather_out_fixed(g, pcol, kw, &dst_p, &val_p);
+                const int grid = grid_for(h, (n + 127) / 128, 8, 8);
+                auto launch = [&](auto T_, auto I_) {
+                    using T = decltype(T_);
+                    using I = decltype(I_);
+                    gather_keys_both_kernel<T, I><<<grid, 256, 0, h->stream>>>(
+                        (const I *)g.bidx, g.pidx, n, (const T *)sc[0].src.values, sc[0].src.validity, (const T *)psc[0].src.values, psc[0].src.validity,
+                        psc[0].src.bit_offset, (T *)dst_b, val_b, (T *)dst_p, val_p, g.d_nulls + col, g.d_nulls + pcol);
+                };
+                if (kw == 8 && bwidth == 4) launch((unsigned long long)0, (uint32_t)0);
+                else if (kw == 8) launch((unsigned long long)0, (uint64_t)0);
+                else if (bwidth == 4) launch((uint32_t)0, (uint32_t)0);
+                else launch((uint32_t)0, (uint64_t)0);
+                h->st.kernel_launches++;
+                CU(cudaGetLastError());
+                keys_done = true;
+            }
+            // a dense radix result that still carries its segment table: build columns partition by partition
+            const ResultOwner *seg_ro = nullptr;
+            if (h->gather_seg && pairs->mem == B200J_MEM_DEVICE && pairs->_owner != nullptr && h->seg_owners.count(pairs->_owner) != 0) {
+                const ResultOwner *cand = (const ResultOwner *)pairs->_owner;
+                if (cand->seg != nullptr && cand->seg_n == n && cand->build_idx == (const void *)pairs->build_idx && cand->bwidth == bwidth && n > 0)
+                    seg_ro = cand;
+            }
+            if (bwidth == 4) gather_side<uint32_t>(g, col, sc, reinterpret_cast<const uint32_t *>(g.bidx), keys_done ? nullptr : via, keys_done, seg_ro);     // B200J_OUT_BUILD_U32 pairs
+            else gather_side<uint64_t>(g, col, sc, g.bidx, keys_done ? nullptr : via, keys_done, seg_ro);
             col += nk + nbp;
         }
         if (want_probe) {
-            gather_side<uint32_t>(g, col, psc, have_probe ? g.pidx : nullptr);
+            gather_side<uint32_t>(g, col, psc, have_probe ? g.pidx : nullptr, nullptr, keys_done);
             col += nk + npp;
         }
         tm.stop();

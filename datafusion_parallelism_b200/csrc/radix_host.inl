@@ -570,13 +570,24 @@ int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces,
         const int64_t misses = (int64_t)h->h_ctr->build_null_out;       // rows without a match, NULL-key rows included
         h->miss_frac = n > n_null ? (float)((double)(misses - n_null) / (double)(n - n_null)) : 0.f;
         big_free(h, tk); tk = nullptr;
-        big_free(h, seg); seg = nullptr;
         if (pl.mode == PM_OUTER || misses == 0) {
             *n_build_null = misses;
             ro->build_idx = ob;
             ro->probe_idx = tr;
+            if (ro->want_seg && h->gather_seg) {
+                // the result keeps the stream's order: its segment table goes with it (b200j_gather walks the build side by partition)
+                ro->seg = seg;
+                ro->seg_blocks = n_blocks;
+                ro->seg_P = P;
+                ro->seg_n = n;
+                h->seg_owners.insert(ro);
+            } else {
+                big_free(h, seg);
+            }
+            seg = nullptr;
             return n;
         }
+        big_free(h, seg); seg = nullptr;
         const int64_t keep = n - misses;
         CU(big_alloc(h, &ob2, (size_t)std::max<int64_t>(keep, 1) * 8));
         CU(big_alloc(h, &op2, (size_t)std::max<int64_t>(keep, 1) * 4));
@@ -637,6 +648,7 @@ void do_probe_pieces(H *h, int32_t partition, int32_t n_pieces, const void *cons
     }
     REQUIRE(n < 0xffff0000LL, B200J_ERR_UNSUPPORTED, "probe batch of more than 2^32 - 2^16 rows (probe indices are UInt32)");
     ResultOwner *ro = new ResultOwner();
+    ro->want_seg = true;
     void *cat = nullptr;
     try {
         int64_t total = 0, n_bnull = 0;

@@ -210,6 +210,7 @@ typedef struct {
     double   ms_exchange_partition;   /* b200j_shuffle_count + b200j_shuffle_scatter kernels             */
     int64_t  seg_probe_launches;      /* dense probe launches over the block-locally partitioned stream (probe_dense_seg_kernel) */
     int64_t  narrow_probe_launches;   /* ... of which the stream carried 8-byte keys as 32-bit values                    */
+    int64_t  gather_seg_launches;     /* b200j_gather launches that walked the build side partition by partition (gather_seg_multi_kernel) */
 } b200j_stats;
 
 /* ---- lifecycle ------------------------------------------------------------------------------- */

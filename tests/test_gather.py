@@ -91,3 +91,129 @@ def test_gather_device_probe_batch_and_wide_column():
     pos[bk] = np.arange(nb)
     assert np.array_equal(gbw, bw[pos[gpk]])
     assert sorted(gpk.tolist()) == sorted(pk[pk < nb].tolist())
+
+
+def _gather_columns(env, join_type, bk, bcols, btypes, pk_dev, pk_valid, ppay_dev, want_pairs, pieces=None):
+    """Build + probe + gather on a fresh handle created under `env`; returns (stats, [(values bytes, validity bits | None, null_count)])."""
+    import ctypes as C
+    import os
+    import datafusion_parallelism_b200 as d
+    from datafusion_parallelism_b200.join import column
+    saved = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        j = d.HashJoin(join_type, key_widths=(8,), build_payload_types=btypes, probe_payload_types=(8,), layout="radix", radix_bits=4)
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    with j:
+        j.build_push(0, [bk], bcols)
+        j.build_finish(0)
+        if pieces is None:
+            keys = [pk_dev] if pk_valid is None else [column(pk_dev, validity=pk_valid)]
+            res = j.probe_batch(0, keys, want=want_pairs)
+        else:
+            keys = [pk_dev]
+            res = j.probe_pieces(0, pieces, want=want_pairs)
+        g = j.gather(res, keys, [ppay_dev], want=d.OUT_HOST)
+        n, out = g.n_rows, []
+        widths = [8] + list(btypes) + [8, 8]
+        assert g.n_cols == len(widths)
+        for i, w in enumerate(widths):
+            c = g.column_buffers(i)
+            vals = np.frombuffer(C.string_at(c["values"], n * w), dtype=np.uint8).reshape(n, w).copy()
+            bits = None
+            if c["validity"]:
+                bits = np.unpackbits(np.frombuffer(C.string_at(c["validity"], ((n + 31) // 32) * 4), dtype=np.uint8), bitorder="little")
+                assert not bits[n:].any(), "bits past the last row must be zero"
+                bits = bits[:n].astype(bool)
+                vals[~bits] = 0
+            out.append((vals, bits, c["null_count"]))
+        st = j.stats()
+        g.release()
+        res.release()
+    return st, out
+
+
+@pytest.mark.parametrize("join_type,miss", [("inner", False), ("right", True), ("full", True)])
+@pytest.mark.parametrize("u32", [False, True])
+@pytest.mark.parametrize("shape", ["batch", "misaligned", "pieces"])
+def test_partition_order_gather_equals_plain_gather(join_type, miss, u32, shape):
+    """The build side of a dense radix result is gathered partition by partition (gather_seg_multi_kernel) and both key columns
+    come out of one pass (gather_keys_both_kernel): same columns, bit for bit, as the plain row-order kernels, and as numpy."""
+    import torch
+    import datafusion_parallelism_b200 as d
+    rng = np.random.default_rng(23)
+    nb, npr = 60_000, 150_003                                     # 5 blocks of 32768 rows, the last one ragged
+    bk = rng.permutation(nb).astype(np.int64) + 1
+    b64 = rng.integers(-2**62, 2**62, nb).astype(np.int64)
+    b64_mask = rng.random(nb) < 0.07
+    b32 = rng.integers(-2**31, 2**31 - 1, nb).astype(np.int32)
+    b16 = rng.integers(0, 2**62, (nb, 2)).astype(np.int64).view([("a", "<i8"), ("b", "<i8")]).reshape(nb)
+    b8 = rng.integers(0, 255, nb).astype(np.uint8)
+    b2 = rng.integers(0, 65535, nb).astype(np.uint16)
+    bcols = [pa.array(b64, mask=b64_mask), b32, b16, b8, b2]
+    btypes = (8, 4, 16, 1, 2)
+    pk = rng.integers(1, nb + (nb // 5 if miss else 1), npr).astype(np.int64)
+    ppay = rng.integers(0, 2**40, npr).astype(np.int64)
+    store = torch.empty(npr + 1, dtype=torch.int64, device="cuda")
+    pk_dev = store[1:] if shape == "misaligned" else store[:npr]     # 8 bytes off a 16-byte boundary
+    pk_dev.copy_(torch.from_numpy(pk))
+    ppay_dev = torch.from_numpy(ppay).cuda()
+    pk_valid = None
+    if miss and shape != "pieces":                                # NULL probe keys: the rows of the stream's last segment per block
+        vmask = rng.random(npr) < 0.05
+        pk_valid = torch.from_numpy(np.packbits(~vmask, bitorder="little")).cuda()
+    else:
+        vmask = np.zeros(npr, dtype=bool)
+    pieces = None
+    if shape == "pieces":
+        cut = 70_001
+        pieces = [(pk_dev[:cut].data_ptr(), cut), (pk_dev[cut:].data_ptr(), npr - cut)]
+    want = d.OUT_PAIRS | (d.OUT_BUILD_U32 if u32 else 0)
+    st_new, new = _gather_columns({}, join_type, bk, bcols, btypes, pk_dev, pk_valid, ppay_dev, want, pieces)
+    st_old, old = _gather_columns({"B200J_GATHER_SEG": "0", "B200J_KEY_VIA_PROBE": "0"}, join_type, bk, bcols, btypes, pk_dev, pk_valid,
+                                  ppay_dev, want, pieces)
+    assert st_new["gather_seg_launches"] >= 1 and st_new["seg_probe_launches"] >= 1, st_new
+    assert st_old["gather_seg_launches"] == 0, st_old
+    assert len(new) == len(old)
+    for c, ((v1, m1, z1), (v2, m2, z2)) in enumerate(zip(new, old)):
+        assert z1 == z2, (c, z1, z2)
+        assert (m1 is None) == (m2 is None), c
+
+    def sorted_rows(cols):
+        # the order of the rows inside a segment of the partitioned stream differs from run to run (shared-memory atomics rank
+        # them): whole rows -- every column's bytes and validity -- are compared as sorted multisets
+        n_ = cols[0][0].shape[0]
+        parts = []
+        for v, m, _ in cols:
+            parts.append(v)
+            parts.append((m if m is not None else np.ones(n_, dtype=bool)).astype(np.uint8).reshape(n_, 1))
+        mat = np.ascontiguousarray(np.concatenate(parts, axis=1))
+        return np.sort(mat.view([("r", np.void, mat.shape[1])]).reshape(n_), axis=0)
+
+    assert np.array_equal(sorted_rows(new), sorted_rows(old))
+    # ... and against numpy on the rows themselves
+    n = new[0][0].shape[0]
+    gpk = new[-2][0].view(np.int64).reshape(n)
+    gbk = new[0][0].view(np.int64).reshape(n)
+    hit = new[0][1] if new[0][1] is not None else np.ones(n, dtype=bool)
+    pos = np.zeros(nb + 1 + nb // 5 + 1, dtype=np.int64)
+    pos[bk] = np.arange(nb)
+    assert np.array_equal(gbk[hit], gpk[hit])
+    rows = pos[gpk[hit]]
+    assert np.array_equal(new[2][0].view(np.int32).reshape(n)[hit], b32[rows])
+    assert np.array_equal(new[3][0][hit], np.ascontiguousarray(b16).view(np.uint8).reshape(nb, 16)[rows])
+    assert np.array_equal(new[4][0].reshape(n)[hit], b8[rows])
+    assert np.array_equal(new[5][0].view(np.uint16).reshape(n)[hit], b2[rows])
+    v64 = new[1][0].view(np.int64).reshape(n)
+    m64 = new[1][1] if new[1][1] is not None else np.ones(n, dtype=bool)
+    assert np.array_equal(m64[hit], ~b64_mask[rows])
+    assert np.array_equal(v64[hit & m64], b64[rows][m64[hit]])
+    if join_type == "inner":
+        assert n == int(((pk <= nb) & ~vmask).sum())
+    elif join_type == "right":
+        assert n == npr
