@@ -509,37 +509,63 @@ def verify_distributed(args, d, torch, dist, dev, join, bk, pk, rank, world):
 
 
 def run_gather_phase(args, d, torch, dev, join, bk, bpay, pk, hbm_gbs):
-    import ctypes as C
+    """b200j_gather, device to device, of the whole C2 result: once on plain pairs and once on pairs probed with
+    B200J_OUT_GATHER_HINT (the probe leaves its partitioned keys and the slot of every pair with the result). Every output row is
+    checked. The hinted probe's own extra time and the one-off slot-ordered payload copy are reported next to the gather's."""
+    from datafusion_parallelism_b200.exchange import _RawCudaArray
     n_build, n_probe = args.build_rows, args.probe_rows
     m = min(n_probe, args.chunk_rows)
-    join.reset()
-    join.build_push(0, [bk], [bpay])
-    join.build_finish(0)
-    r = join.probe_batch(0, [pk[:m]], want=d.OUT_PAIRS)
-    times = []
-    ok = None
-    for rep in range(3):
-        st0 = join.stats()["ms_gather"]
-        g = join.gather(r, [pk[:m]], want=0)                     # device in, device out
-        times.append(join.stats()["ms_gather"] - st0)
-        if rep == 0:
-            cols = [g.column_buffers(i) for i in range(g.n_cols)]
-            S = min(g.n_rows, 1 << 26)
-            from datafusion_parallelism_b200.exchange import _RawCudaArray
-            gbk, gbp, gpk = (torch.as_tensor(_RawCudaArray(c["values"], S, "<i8"), device=dev) for c in cols[:3])
-            b_, p_ = r.device_arrays()
-            tb = torch.as_tensor(b_, device=dev)[:S]
-            tp = torch.as_tensor(p_, device=dev)[:S].long() & 0xFFFFFFFF
-            ok = bool(torch.equal(gbk, gpk)) and bool(torch.equal(gbp, tb)) and bool(torch.equal(gpk, pk[:m][tp])) and g.n_rows == r.n
-            del gbk, gbp, gpk, tb, tp
-        g.release()
-    n_out = r.n
-    r.release()
-    ms = min(times)
-    bytes_per_row = 12 + 3 * 8 + 3 * 8          # index pair read + three 8-byte columns read + written
-    return {"ms": ms, "ms_all": times, "rows": n_out, "columns": "build key i64 + build payload i64 (random reads at build_idx) + probe key i64 (at probe_idx)",
-            "bytes_per_row": bytes_per_row, "rows_per_s": n_out / (ms * 1e-3), "gather_roofline_frac": n_out * bytes_per_row / (ms * 1e-3) / 1e9 / hbm_gbs,
-            "verified": ok}
+    out = {}
+    for mode, want in (("plain", d.OUT_PAIRS), ("hinted", d.OUT_PAIRS | d.OUT_GATHER_HINT)):
+        join.reset()
+        join.build_push(0, [bk], [bpay])
+        join.build_finish(0)
+        probe_ms = []
+        for rep in range(2):                                    # the second probe is the warm one
+            s0 = join.stats()
+            r = join.probe_batch(0, [pk[:m]], want=want)
+            s1 = join.stats()
+            probe_ms.append(s1["ms_probe"] - s0["ms_probe"] + s1["ms_probe_partition"] - s0["ms_probe_partition"])
+            if rep == 0:
+                r.release()
+        times, ok = [], None
+        for rep in range(3):
+            st0 = join.stats()["ms_gather"]
+            g = join.gather(r, [pk[:m]], want=0)                     # device in, device out
+            times.append(join.stats()["ms_gather"] - st0)
+            if rep == 0:
+                cols = [g.column_buffers(i) for i in range(g.n_cols)]
+                b_, p_ = r.device_arrays()
+                ok = g.n_rows == r.n and all(c["null_count"] == 0 for c in cols[:3])
+                S = 1 << 27
+                for lo in range(0, g.n_rows, S):                    # every output row: keys equal, payload = the build row, probe key = the probe row's
+                    k = min(S, g.n_rows - lo)
+                    gbk, gbp, gpk = (torch.as_tensor(_RawCudaArray(c["values"] + lo * 8, k, "<i8"), device=dev) for c in cols[:3])
+                    tb = torch.as_tensor(b_, device=dev)[lo:lo + k]
+                    tp = torch.as_tensor(p_, device=dev)[lo:lo + k].long() & 0xFFFFFFFF
+                    ok = ok and bool(torch.equal(gbk, gpk)) and bool(torch.equal(gbp, tb)) and bool(torch.equal(gpk, pk[:m][tp]))
+                    del gbk, gbp, gpk, tb, tp
+            g.release()
+        st = join.stats()
+        n_out = r.n
+        r.release()
+        out[mode] = {"ms": min(times), "ms_all": times, "probe_phase_ms": probe_ms[-1], "verified": ok,
+                     "gather_hint_launches": st.get("gather_hint_launches", 0), "gather_seg_launches": st.get("gather_seg_launches", 0),
+                     "ms_slot_order_once_per_build": st.get("ms_slot_order", 0.0)}
+    hinted = bool(out["hinted"]["gather_hint_launches"])
+    ms = out["hinted"]["ms"] if hinted else out["plain"]["ms"]
+    # ALGORITHMIC bytes per output row. Plain pairs (SURVEY §8d: "per output row sum(column widths) read + write", plus the pair):
+    # 12 B index pair + three 8-byte values read + three written = 60 B. Hinted: what that path has to move -- the row's key in the
+    # partitioned stream (4 B while the keys fit 32 bits, as here), its slot (4 B), one 8-byte payload value, three values written
+    # = 40 B; the fraction on SURVEY's 60 B is given beside it and exceeds what the kernels really move.
+    frac = lambda b, t: n_out * b / (t * 1e-3) / 1e9 / hbm_gbs
+    bytes_per_row = 40 if hinted else 60
+    return {"ms": ms, "mode": "B200J_OUT_GATHER_HINT" if hinted else "plain pairs", "rows": n_out,
+            "columns": "build key i64 + build payload i64 (at build_idx) + probe key i64 (at probe_idx)",
+            "bytes_per_row": bytes_per_row, "rows_per_s": n_out / (ms * 1e-3), "gather_roofline_frac": frac(bytes_per_row, ms),
+            "frac_on_survey_60B": frac(60, ms), "plain_gather_roofline_frac": frac(60, out["plain"]["ms"]),
+            "hint_extra_probe_ms": out["hinted"]["probe_phase_ms"] - out["plain"]["probe_phase_ms"],
+            "plain": out["plain"], "hinted": out["hinted"], "verified": bool(out["plain"]["verified"] and out["hinted"]["verified"])}
 
 
 def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):

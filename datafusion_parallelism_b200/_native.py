@@ -85,7 +85,8 @@ class Stats(C.Structure):
                 ("ms_probe_partition", C.c_double), ("ms_probe", C.c_double), ("ms_gather", C.c_double),
                 ("probe_launches", C.c_int64), ("kernel_launches", C.c_int64), ("probe_retries", C.c_int64),
                 ("dense_probe_launches", C.c_int64), ("compact_launches", C.c_int64), ("ms_exchange_partition", C.c_double),
-                ("seg_probe_launches", C.c_int64), ("narrow_probe_launches", C.c_int64), ("gather_seg_launches", C.c_int64)]
+                ("seg_probe_launches", C.c_int64), ("narrow_probe_launches", C.c_int64), ("gather_seg_launches", C.c_int64),
+                ("gather_hint_launches", C.c_int64), ("ms_slot_order", C.c_double)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_ if not n.startswith("_") and n != "struct_size"}

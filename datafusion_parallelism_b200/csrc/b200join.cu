@@ -94,6 +94,12 @@ struct ResultOwner {
     void *seg = nullptr;              // [seg_blocks][seg_P + 2] segment starts, then [seg_blocks] block bases
     uint32_t seg_blocks = 0, seg_P = 0;
     int64_t seg_n = 0;                // rows the table describes (= the result's rows)
+    // B200J_OUT_GATHER_HINT (want_aux): what else the dense probe can leave behind for the gather
+    bool want_aux = false;
+    void *aux_keys = nullptr;         // the partitioned probe keys = the probe key of every result row, in result order (no NULL keys in the batch)
+    int32_t aux_kw = 0;               // ... 4 or 8 bytes each (4: zero-extended values of 8-byte keys)
+    void *aux_slot = nullptr;         // u32 per result row: index of the table slot the row matched (0xffffffff: none)
+    int64_t aux_misses = 0;           // result rows without a match (NULL build index)
 };
 
 struct CachedBlock {
@@ -185,6 +191,11 @@ struct b200j_handle {
     bool shuffle_armed = false;        // b200j_shuffle_count done, b200j_shuffle_scatter pending
     PartPlan shuffle_plan;
     int64_t shuffle_n = 0;
+    // slot-ordered copies of the fixed-width build payload columns (B200J_OUT_GATHER_HINT): value of the row held by table slot s at
+    // index s, [n_slots + 2] entries (the last two: the side bucket of key 0); built on the first hinted gather after a build
+    struct SlotCol { DevBuf values, validity; bool has_nulls = false; };
+    std::vector<SlotCol> slot_cols;
+    bool slot_cols_ready = false;
     bool gather_seg = true;            // b200j_gather: build columns of a dense radix result are gathered partition by partition (B200J_GATHER_SEG=0: off)
     std::set<const void *> seg_owners;  // live results that carry a segment table (b200j_gather checks a caller's _owner against it)
     bool key_via_probe = true;         // b200j_gather: the build key column of matched pairs is read from the probe key column (B200J_KEY_VIA_PROBE=0: off)
@@ -670,6 +681,7 @@ KeyCols build_key_cols(H *h) {
 }
 
 void run_build(H *h) {
+    h->slot_cols_ready = false;          // the slot-ordered payload copies belong to the previous table
     const int64_t n = h->n_build;
     const int kw = h->table_kw;
     const float lf = h->cfg.load_factor > 0.f ? std::min(h->cfg.load_factor, 0.9f) : 0.5f;
@@ -877,6 +889,9 @@ void drop_seg(H *h, ResultOwner *ro) {
         big_free(h, ro->seg);
         ro->seg = nullptr;
     }
+    if (ro->aux_keys) big_free(h, ro->aux_keys);
+    if (ro->aux_slot) big_free(h, ro->aux_slot);
+    ro->aux_keys = ro->aux_slot = nullptr;
 }
 
 void release_owner(H *h, ResultOwner *ro) {
@@ -1445,6 +1460,7 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
     const int64_t n = b->n_rows;
     ResultOwner *ro = new ResultOwner();
     ro->want_seg = true;
+    ro->want_aux = (want & B200J_OUT_GATHER_HINT) != 0 && !(want & B200J_OUT_HOST) && !count_only && h->gather_seg;
     std::vector<void *> temps;
     try {
         int64_t total = 0, n_bnull = 0;
@@ -1969,6 +1985,7 @@ int32_t b200j_destroy(b200j_handle *h) {
             for (auto &c : *v) { fr(c.values); fr(c.offsets); fr(c.validity); }
     radix_release(h);
     fr(h->slots); fr(h->zero_slot); fr(h->rowids); fr(h->bigruns); fr(h->hot_table); fr(h->visited); fr(h->parts);
+    for (auto &sc : h->slot_cols) { fr(sc.values); fr(sc.validity); }
     cudaStreamSynchronize(h->stream);
     for (auto &b : h->blocks) cudaFreeAsync(b.p, h->stream);
     h->blocks.clear();
@@ -2009,7 +2026,8 @@ int32_t b200j_reset_stats(b200j_handle *h) {
     h->st.ms_build_copy = h->st.ms_build_partition = h->st.ms_build_insert = 0;
     h->st.ms_probe_partition = h->st.ms_probe = h->st.ms_gather = 0;
     h->st.probe_launches = h->st.kernel_launches = h->st.probe_retries = 0;
-    h->st.dense_probe_launches = h->st.compact_launches = h->st.seg_probe_launches = h->st.narrow_probe_launches = h->st.gather_seg_launches = 0;
+    h->st.dense_probe_launches = h->st.compact_launches = h->st.seg_probe_launches = h->st.narrow_probe_launches = h->st.gather_seg_launches = h->st.gather_hint_launches = 0;
+    h->st.ms_slot_order = 0;
     h->st.ms_exchange_partition = 0;
     return B200J_OK;
 }
@@ -2032,6 +2050,7 @@ int32_t b200j_reset(b200j_handle *h) {
         }
         if (!getenv("B200J_NO_NARROW") || atoi(getenv("B200J_NO_NARROW")) == 0) h->narrow_ok = true;
         h->n_slots = 0;
+        h->slot_cols_ready = false;
     });
 }
 

@@ -386,6 +386,114 @@ __global__ void __launch_bounds__(256) gather_seg_multi_kernel(GatherCols cols, 
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// B200J_OUT_GATHER_HINT: what the dense probe left with the result makes both remaining random reads of the gather go away.
+//
+// (1) Key columns from the partitioned key stream. The stream the probe walked holds the probe key of every result row IN
+//     RESULT ORDER (the result arrays are indexed by stream position), so both key columns of the output are a sequential copy
+//     (a widening one when the stream carries 8-byte keys as 32-bit values). Only the build key's validity needs the pairs, and
+//     only when some rows have no match. The batch has no NULL keys (the host checks), so the probe key column has no nulls.
+// (2) Build payload from slot-ordered copies. slot_order_kernel lays every fixed-width payload column out by TABLE SLOT (entry s
+//     = the value of the build row that slot s holds); the probe wrote the slot of every pair next to the build index. A
+//     partition's slots are one contiguous range, so its part of a slot-ordered column is a dense array (15 MB per 8-byte
+//     column at C2) that stays in L2 while gather_seg_multi_kernel walks the partition's segments -- where the arrival-ordered
+//     build store spreads a partition's rows over 780 K different 128 B lines (100 MB of L2 lines for 6 MB of values).
+// ---------------------------------------------------------------------------------------------------------------------
+template <typename KT, typename T, typename IdxT>
+__global__ void __launch_bounds__(256) gather_keys_stream_kernel(const KT *__restrict__ stream, const IdxT *__restrict__ bidx /* null: every row matched */,
+                                                                 int64_t n, T *__restrict__ dst_b, uint32_t *__restrict__ dst_b_valid,
+                                                                 T *__restrict__ dst_p, unsigned long long *null_b) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    uint32_t nulls = 0;
+    for (int64_t row0 = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (32 * GF_ITEMS); row0 < n; row0 += warps * (32 * GF_ITEMS)) {
+        T v[GF_ITEMS];
+        bool ok[GF_ITEMS];
+#pragma unroll
+        for (int q = 0; q < GF_ITEMS; q++) {
+            const int64_t i = row0 + q * 32 + lane;
+            v[q] = T{};
+            ok[q] = false;
+            if (i < n) {
+                v[q] = (T)__ldcs(stream + i);
+                ok[q] = bidx == nullptr || !idx_is_null(__ldcs(bidx + i));
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < GF_ITEMS; q++) {
+            const int64_t i = row0 + q * 32 + lane;
+            if (i < n) {
+                __stcs(dst_p + i, v[q]);
+                __stcs(dst_b + i, ok[q] ? v[q] : T{});
+                if (!ok[q]) nulls++;
+            }
+            if (bidx != nullptr) {
+                const uint32_t w = __ballot_sync(0xffffffffu, ok[q]);
+                if (lane == 0 && row0 + q * 32 < n) dst_b_valid[(row0 + q * 32) >> 5] = w;
+            }
+        }
+    }
+    const unsigned long long z = warp_sum_u32(nulls);
+    if (lane == 0 && z) atomicAdd(null_b, z);
+}
+
+struct SlotOrderCol {
+    const void    *src;          // the build store's column (arrival order)
+    const uint8_t *src_valid;    // its validity bitmap or null
+    void          *dst;          // [n_slots + 2] slot-ordered copy
+    uint32_t      *dst_valid;    // its validity words, or null when the column has no nulls
+    int32_t        width;
+    int32_t        _pad;
+};
+struct SlotOrderCols {
+    SlotOrderCol c[GF_MAX_COLS];
+    int32_t      n;
+    int32_t      _pad;
+};
+template <typename T>
+__device__ __forceinline__ void slot_order_one(const SlotOrderCol &c, uint64_t s, bool occ, uint32_t row, bool in_range, int lane) {
+    bool valid = false;
+    if (in_range) {
+        T v{};
+        if (occ) {
+            valid = bit_valid(c.src_valid, (int64_t)row);
+            v = reinterpret_cast<const T *>(c.src)[row];
+        }
+        reinterpret_cast<T *>(c.dst)[s] = v;
+    }
+    if (c.dst_valid != nullptr) {
+        const uint32_t w = __ballot_sync(0xffffffffu, valid);
+        if (lane == 0 && in_range) c.dst_valid[s >> 5] = w;
+    }
+}
+// unique build keys only (every occupied slot has count 1 and `row` is the build row)
+__global__ void __launch_bounds__(256) slot_order_kernel(const Slot *__restrict__ slots, uint64_t n_slots, const Slot *__restrict__ zero_slot,
+                                                         SlotOrderCols cols) {
+    const int lane = threadIdx.x & 31;
+    const uint64_t total = n_slots + 2, total_round = (total + 31) & ~31ull;
+    for (uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; s < total_round; s += (uint64_t)gridDim.x * blockDim.x) {
+        const bool in_range = s < total;
+        bool occ = false;
+        uint32_t row = 0;
+        if (in_range) {
+            const Slot v = load_slot(s < n_slots ? slots + s : zero_slot + (s - n_slots));
+            occ = s < n_slots ? v.key != 0ULL : v.count != 0u;
+            row = v.row;
+        }
+#pragma unroll
+        for (int c = 0; c < GF_MAX_COLS; c++) {
+            if (c >= cols.n) break;
+            switch (cols.c[c].width) {
+                case 1: slot_order_one<uint8_t>(cols.c[c], s, occ, row, in_range, lane); break;
+                case 2: slot_order_one<uint16_t>(cols.c[c], s, occ, row, in_range, lane); break;
+                case 4: slot_order_one<uint32_t>(cols.c[c], s, occ, row, in_range, lane); break;
+                case 8: slot_order_one<unsigned long long>(cols.c[c], s, occ, row, in_range, lane); break;
+                default: slot_order_one<ulonglong2>(cols.c[c], s, occ, row, in_range, lane); break;
+            }
+        }
+    }
+}
+
 __device__ __forceinline__ int64_t utf8_off(const GatherSrc &s, int64_t j) {
     return s.offsets64 ? reinterpret_cast<const int64_t *>(s.offsets)[j] : (int64_t)reinterpret_cast<const int32_t *>(s.offsets)[j];
 }

@@ -112,6 +112,52 @@ struct SideCol {
     int type;
     GatherSrc src;
 };
+constexpr int SIDECOL_SKIP = -12345;
+
+// Slot-ordered copies of the fixed-width build payload columns (B200J_OUT_GATHER_HINT, see gather.cuh): built once per build.
+// Returns false when they cannot be had (duplicate build keys, slot indices beyond 32 bits, nothing to copy).
+bool ensure_slot_cols(H *h) {
+    const int nbp = h->cfg.n_build_payload;
+    if (h->slot_cols_ready) return true;
+    if (h->layout != B200J_LAYOUT_RADIX || h->st.duplicate_rows != 0 || h->n_build == 0 || h->n_slots + 2 >= 0xffffffffULL) return false;
+    bool any = false;
+    for (int i = 0; i < nbp; i++) any |= h->bpayload[i].type != B200J_T_UTF8;
+    if (!any) return false;
+    h->slot_cols.resize(nbp);
+    const uint64_t total = h->n_slots + 2;
+    for (int i = 0; i < nbp; i++) {                      // buffers first (kept across builds): the timer below covers the kernels only
+        const ColStore &cs = h->bpayload[i];
+        if (cs.type == B200J_T_UTF8) continue;
+        dev_alloc(h, h->slot_cols[i].values, (size_t)total * cs.type + 32);
+        if (cs.has_nulls) dev_alloc(h, h->slot_cols[i].validity, (size_t)((total + 31) / 32 + 1) * 4);
+    }
+    PhaseTimer tm(h, &h->st.ms_slot_order);
+    SlotOrderCols batch{};
+    auto flush = [&]() {
+        if (batch.n == 0) return;
+        slot_order_kernel<<<grid_for(h, (int64_t)total, 256, 16), 256, 0, h->stream>>>((const Slot *)h->slots.p, h->n_slots, (const Slot *)h->zero_slot.p, batch);
+        h->st.kernel_launches++;
+        CU(cudaGetLastError());
+        batch = SlotOrderCols{};
+    };
+    for (int i = 0; i < nbp; i++) {
+        const ColStore &cs = h->bpayload[i];
+        if (cs.type == B200J_T_UTF8) continue;
+        H::SlotCol &sc = h->slot_cols[i];
+        sc.has_nulls = cs.has_nulls;
+        SlotOrderCol &c = batch.c[batch.n++];
+        c.src = cs.values.p;
+        c.src_valid = cs.has_nulls ? (const uint8_t *)cs.validity.p : nullptr;
+        c.dst = sc.values.p;
+        c.dst_valid = cs.has_nulls ? (uint32_t *)sc.validity.p : nullptr;
+        c.width = cs.type;
+        if (batch.n == GF_MAX_COLS) flush();
+    }
+    flush();
+    tm.stop();
+    h->slot_cols_ready = true;
+    return true;
+}
 // skip_first: column first_col has been produced already (gather_keys_both_kernel). seg_ro: the pairs are a dense radix result
 // that still carries its segment table -- the fixed-width columns are then gathered partition by partition.
 template <typename IdxT>
@@ -153,6 +199,7 @@ void gather_side(GatherCtx &g, int first_col, const std::vector<SideCol> &sc, co
     };
     for (size_t k = skip_first ? 1 : 0; k < sc.size(); k++) {
         const int col = first_col + (int)k;
+        if (sc[k].type == SIDECOL_SKIP) continue;            // produced by another launch
         if (sc[k].type == B200J_T_UTF8) {
             gather_one_column<IdxT>(g, col, sc[k].type, sc[k].src, idx);
             continue;
@@ -263,6 +310,15 @@ void do_gather_impl(H *h, const b200j_result *pairs, const b200j_batch *probe_ba
         CU(cudaMemsetAsync(dn, 0, (size_t)(n_cols + 2 + GF_MAX_COLS) * 8, h->stream));
         g.d_nulls = (unsigned long long *)dn;
         g.d_nulls_scratch = g.d_nulls + n_cols + 1;
+        // a dense radix result that still carries its segment table: build columns partition by partition
+        const ResultOwner *seg_ro = nullptr;
+        if (want_build && h->gather_seg && pairs->mem == B200J_MEM_DEVICE && pairs->_owner != nullptr && h->seg_owners.count(pairs->_owner) != 0) {
+            const ResultOwner *cand = (const ResultOwner *)pairs->_owner;
+            if (cand->seg != nullptr && cand->seg_n == n && cand->build_idx == (const void *)pairs->build_idx && cand->bwidth == bwidth && n > 0)
+                seg_ro = cand;
+        }
+        // B200J_OUT_GATHER_HINT: the slot-ordered payload copies are made once per build, outside the gather's own timing (ms_slot_order)
+        const bool slot_ok = seg_ro != nullptr && seg_ro->aux_slot != nullptr && nbp > 0 && ensure_slot_cols(h);
         PhaseTimer tm(h, &h->st.ms_gather);
         int col = 0;
         bool keys_done = false;
@@ -294,7 +350,39 @@ void do_gather_impl(H *h, const b200j_result *pairs, const b200j_batch *probe_ba
             // single fixed-width key, both sides in the output, a probe side to read from: build key := probe key of the pair
             const void *via = (h->key_via_probe && want_probe && have_probe && nk == 1 && !h->composite && g.pidx != nullptr && g.bidx != nullptr &&
                                (h->key_widths[0] == 4 || h->key_widths[0] == 8)) ? psc[0].src.values : nullptr;
-            if (via != nullptr && n > 0) {
+            bool hinted = false;
+            if (via != nullptr && n > 0 && seg_ro != nullptr && seg_ro->aux_keys != nullptr &&
+                (seg_ro->aux_kw == h->key_widths[0] || (seg_ro->aux_kw == 4 && h->key_widths[0] == 8))) {
+                // B200J_OUT_GATHER_HINT: both key columns are a sequential copy of the partitioned key stream
+                const int kw = h->key_widths[0], pcol = nk + nbp;
+                void *dst_b = nullptr, *dst_p = nullptr;
+                uint32_t *val_b = nullptr, *val_p = nullptr;
+                gather_out_fixed(g, col, kw, &dst_b, &val_b);
+                gather_out_fixed(g, pcol, kw, &dst_p, &val_p);
+                const int grid = grid_for(h, (n + 127) / 128, 8, 8);
+                const void *nullsrc = seg_ro->aux_misses > 0 ? (const void *)g.bidx : nullptr;
+                auto launch = [&](auto K_, auto T_, auto I_) {
+                    using K = decltype(K_);
+                    using T = decltype(T_);
+                    using I = decltype(I_);
+                    gather_keys_stream_kernel<K, T, I><<<grid, 256, 0, h->stream>>>((const K *)seg_ro->aux_keys, (const I *)nullsrc, n, (T *)dst_b, val_b,
+                                                                                    (T *)dst_p, g.d_nulls + col);
+                };
+                if (kw == 8 && seg_ro->aux_kw == 4) {
+                    if (bwidth == 4) launch((uint32_t)0, (unsigned long long)0, (uint32_t)0);
+                    else launch((uint32_t)0, (unsigned long long)0, (uint64_t)0);
+                } else if (kw == 8) {
+                    if (bwidth == 4) launch((unsigned long long)0, (unsigned long long)0, (uint32_t)0);
+                    else launch((unsigned long long)0, (unsigned long long)0, (uint64_t)0);
+                } else {
+                    if (bwidth == 4) launch((uint32_t)0, (uint32_t)0, (uint32_t)0);
+                    else launch((uint32_t)0, (uint32_t)0, (uint64_t)0);
+                }
+                h->st.kernel_launches++;
+                CU(cudaGetLastError());
+                keys_done = true;
+                hinted = true;
+            } else if (via != nullptr && n > 0) {
                 // ... and both key columns come out of ONE pass over the pairs (gather_keys_both_kernel)
                 const int kw = h->key_widths[0], pcol = nk + nbp;
                 void *dst_b = nullptr, *dst_p = nullptr;
@@ -317,13 +405,21 @@ void do_gather_impl(H *h, const b200j_result *pairs, const b200j_batch *probe_ba
                 CU(cudaGetLastError());
                 keys_done = true;
             }
-            // a dense radix result that still carries its segment table: build columns partition by partition
-            const ResultOwner *seg_ro = nullptr;
-            if (h->gather_seg && pairs->mem == B200J_MEM_DEVICE && pairs->_owner != nullptr && h->seg_owners.count(pairs->_owner) != 0) {
-                const ResultOwner *cand = (const ResultOwner *)pairs->_owner;
-                if (cand->seg != nullptr && cand->seg_n == n && cand->build_idx == (const void *)pairs->build_idx && cand->bwidth == bwidth && n > 0)
-                    seg_ro = cand;
+            // B200J_OUT_GATHER_HINT: fixed-width payload columns from their slot-ordered copies, indexed by the slot of every pair
+            if (slot_ok) {
+                std::vector<SideCol> ssc(sc.size(), SideCol{SIDECOL_SKIP, GatherSrc{}});
+                for (int i = 0; i < nbp; i++) {
+                    if (h->bpayload[i].type == B200J_T_UTF8) continue;
+                    GatherSrc s{};
+                    s.values = h->slot_cols[i].values.p;
+                    s.validity = h->slot_cols[i].has_nulls ? (const uint8_t *)h->slot_cols[i].validity.p : nullptr;
+                    ssc[nk + i] = SideCol{h->bpayload[i].type, s};
+                    sc[nk + i].type = SIDECOL_SKIP;
+                }
+                gather_side<uint32_t>(g, col, ssc, (const uint32_t *)seg_ro->aux_slot, nullptr, false, seg_ro);
+                hinted = true;
             }
+            if (hinted) h->st.gather_hint_launches++;
             if (bwidth == 4) gather_side<uint32_t>(g, col, sc, reinterpret_cast<const uint32_t *>(g.bidx), keys_done ? nullptr : via, keys_done, seg_ro);     // B200J_OUT_BUILD_U32 pairs
             else gather_side<uint64_t>(g, col, sc, g.bidx, keys_done ? nullptr : via, keys_done, seg_ro);
             col += nk + nbp;

@@ -389,9 +389,9 @@ static_assert(PD_CHUNK % PD_WTILE == 0, "a warp's claim is a whole number of its
 #ifndef B200J_DRAIN_PAIR
 #define B200J_DRAIN_PAIR 1      // a drained lookup fetches two consecutive buckets per round (0: one)
 #endif
-template <bool MARK, bool RADIX, bool L1>
+template <bool MARK, bool RADIX, bool L1, bool SLOT = false>
 __device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long long *qkey, uint32_t *qidx, uint32_t first, uint32_t cnt,
-                                            int lane, uint32_t &misses) {
+                                            int lane, uint32_t &misses, uint32_t *out_slot = nullptr) {
     // entries [first, first + cnt) of the warp's queue, one per lane (cnt <= 32)
     const bool act = (uint32_t)lane < cnt;
     const uint64_t key = act ? qkey[first + lane] : 0ULL;
@@ -402,17 +402,18 @@ __device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long lo
         locate<RADIX>(a.tv, (uint32_t)(h >> 32), base, nb);
         uint32_t b = next_bucket(home_bucket(h, nb), nb);          // the home bucket was full without the key
         unsigned long long res = ~0ULL;
+        uint32_t slot = 0xffffffffu;                               // SLOT: index of the slot that holds the key
 #if B200J_DRAIN_PAIR
         for (;;) {
             const uint32_t b2 = next_bucket(b, nb);
             unsigned long long k0, v0, k1, v1, k2, v2, k3, v3;
             load_bucket(bucket_ptr(a.tv, base, b), k0, v0, k1, v1, L1);
             load_bucket(bucket_ptr(a.tv, base, b2), k2, v2, k3, v3, L1);
-            if (k0 == key) { res = (uint32_t)v0; break; }
-            if (k1 == key) { res = (uint32_t)v1; break; }
+            if (k0 == key) { res = (uint32_t)v0; slot = 2u * (base + b); break; }
+            if (k1 == key) { res = (uint32_t)v1; slot = 2u * (base + b) + 1u; break; }
             if (k1 == 0ULL) break;
-            if (k2 == key) { res = (uint32_t)v2; break; }
-            if (k3 == key) { res = (uint32_t)v3; break; }
+            if (k2 == key) { res = (uint32_t)v2; slot = 2u * (base + b2); break; }
+            if (k3 == key) { res = (uint32_t)v3; slot = 2u * (base + b2) + 1u; break; }
             if (k3 == 0ULL) break;
             b = next_bucket(b2, nb);
         }
@@ -420,13 +421,14 @@ __device__ __forceinline__ void dense_drain(const ProbeArgs &a, unsigned long lo
         for (;;) {
             unsigned long long k0, v0, k1, v1;
             load_bucket(bucket_ptr(a.tv, base, b), k0, v0, k1, v1, L1);
-            if (k0 == key) { res = (uint32_t)v0; break; }
-            if (k1 == key) { res = (uint32_t)v1; break; }
+            if (k0 == key) { res = (uint32_t)v0; slot = 2u * (base + b); break; }
+            if (k1 == key) { res = (uint32_t)v1; slot = 2u * (base + b) + 1u; break; }
             if (k1 == 0ULL) break;
             b = next_bucket(b, nb);
         }
 #endif
         a.out_build[oi] = res;
+        if (SLOT) out_slot[oi] = slot;
         if (res == ~0ULL) misses++;
         else if (MARK) mark_visited(a.visited, (uint32_t)res);
     }
@@ -617,10 +619,14 @@ struct SegArgs {
     const uint32_t *block_base;   // [n_blocks] first row of every block in the partitioned arrays
     uint32_t        n_blocks;
     uint32_t        n_units;      // n_blocks * P, or n_blocks * (P + 1) when the batch has NULL keys
+    uint32_t       *out_slot;     // SLOT: [n] index of the table slot every row matched (0xffffffff: no match) -- what b200j_gather reads
+                                  //       the slot-ordered build columns with (B200J_OUT_GATHER_HINT)
+    uint32_t        zero_slot_index;   // SLOT: index that stands for the side bucket of key value 0
 };
 
-template <int KW, bool MARK, bool L1>
+template <int KW, bool MARK, bool L1, bool SLOT = false>
 __global__ void __launch_bounds__(PD_THREADS, B200J_SEG_MIN_CTAS) probe_dense_seg_kernel(ProbeArgs a, SegArgs sg) {
+    static_assert(!(SLOT && B200J_SEG_FLAT), "the slot output is written by the segment-by-segment walk only");
     using KeyT = typename std::conditional<KW == 8, unsigned long long, uint32_t>::type;
     constexpr uint32_t FULL = 0xffffffffu;
     __shared__ PDShared sh;
@@ -749,7 +755,10 @@ __global__ void __launch_bounds__(PD_THREADS, B200J_SEG_MIN_CTAS) probe_dense_se
             const uint32_t start = __shfl_sync(FULL, my_start, s);
             const uint32_t base = __shfl_sync(FULL, my_base, s), nb = __shfl_sync(FULL, my_nb, s);
             if (nb == 0) {                                      // NULL-key rows
-                for (uint32_t i = lane; i < len; i += 32) __stcs(out + start + i, ~0ULL);
+                for (uint32_t i = lane; i < len; i += 32) {
+                    __stcs(out + start + i, ~0ULL);
+                    if (SLOT) __stcs(sg.out_slot + start + i, 0xffffffffu);
+                }
                 misses += (len + 31u - (uint32_t)lane) / 32u;
                 continue;
             }
@@ -762,10 +771,13 @@ __global__ void __launch_bounds__(PD_THREADS, B200J_SEG_MIN_CTAS) probe_dense_se
                     key[q] = inb[q] ? (uint64_t)__ldcs(keys + start + i0 + q * 32 + lane) : 0ULL;
                 }
                 unsigned long long k0[PD_ITEMS], v0[PD_ITEMS], k1[PD_ITEMS], v1[PD_ITEMS];
+                uint32_t sl[SLOT ? PD_ITEMS : 1];               // SLOT: index of the even slot of the bucket looked at
 #pragma unroll
                 for (int q = 0; q < PD_ITEMS; q++) {
                     const uint64_t h = hash_one(a.hk, key[q]);
-                    const Slot *p = key[q] ? bucket_ptr(a.tv, base, home_bucket(h, nb)) : a.tv.zero_slot;
+                    const uint32_t hb = home_bucket(h, nb);
+                    const Slot *p = key[q] ? bucket_ptr(a.tv, base, hb) : a.tv.zero_slot;
+                    if constexpr (SLOT) sl[q] = key[q] ? 2u * (base + hb) : sg.zero_slot_index;
                     load_bucket(p, k0[q], v0[q], k1[q], v1[q], L1);
                 }
                 bool pend[PD_ITEMS];
@@ -779,6 +791,7 @@ __global__ void __launch_bounds__(PD_THREADS, B200J_SEG_MIN_CTAS) probe_dense_se
                     n_pend += pend[q] ? 1u : 0u;
                     if (inb[q] && !pend[q]) {
                         __stcs(out + start + i0 + q * 32 + lane, hit ? (unsigned long long)(uint32_t)v : ~0ULL);
+                        if constexpr (SLOT) __stcs(sg.out_slot + start + i0 + q * 32 + lane, hit ? sl[q] + (hit0 ? 0u : 1u) : 0xffffffffu);
                         if (!hit) misses++;
                         else if (MARK) mark_visited(a.visited, (uint32_t)v);
                     }
@@ -799,7 +812,7 @@ __global__ void __launch_bounds__(PD_THREADS, B200J_SEG_MIN_CTAS) probe_dense_se
                     __syncwarp();
                     while (qn >= 32u) {
                         qn -= 32u;
-                        dense_drain<MARK, true, L1>(a, qkey, qidx, qn, 32u, lane, misses);
+                        dense_drain<MARK, true, L1, SLOT>(a, qkey, qidx, qn, 32u, lane, misses, sg.out_slot);
                         __syncwarp();
                     }
                 }
@@ -807,7 +820,7 @@ __global__ void __launch_bounds__(PD_THREADS, B200J_SEG_MIN_CTAS) probe_dense_se
         }
     }
 #endif
-    if (qn) dense_drain<MARK, true, L1>(a, qkey, qidx, 0u, qn, lane, misses);
+    if (qn) dense_drain<MARK, true, L1, SLOT>(a, qkey, qidx, 0u, qn, lane, misses, sg.out_slot);
     const unsigned long long z = warp_sum_u32(misses);
     if (lane == 0 && z) atomicAdd(&a.ctr->build_null_out, z);
 }

@@ -462,7 +462,9 @@ int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces,
         n += pieces[i].n;
     }
     REQUIRE(n < 0xffff0000LL, B200J_ERR_UNSUPPORTED, "probe batch of more than 2^32 - 2^16 rows (probe indices are UInt32)");
-    void *tk = nullptr, *tr = nullptr, *seg = nullptr, *ob = nullptr, *ob2 = nullptr, *op2 = nullptr;
+    void *tk = nullptr, *tr = nullptr, *seg = nullptr, *ob = nullptr, *ob2 = nullptr, *op2 = nullptr, *oslot = nullptr;
+    // B200J_OUT_GATHER_HINT: the probe also writes the table slot of every row (slot indices must fit 32 bits)
+    const bool want_slot = ro->want_aux && ro->want_seg && h->n_slots + 2 < 0xffffffffULL;
     Trace tr_;
     try {
         // 8-byte keys travel through the partitioned stream as 32-bit values while they fit (see part_block_kernel NARROW)
@@ -475,6 +477,7 @@ int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces,
         if (!tr) CU(big_alloc(h, &tr, (size_t)n * 4 + 16));
         if (!seg) CU(big_alloc(h, &seg, (size_t)n_blocks * (P + 3) * 4 + 16));       // [n_blocks][P + 2] segment bounds, then [n_blocks] block bases
         if (!ob) CU(big_alloc(h, &ob, (size_t)n * 8 + 16));
+        if (want_slot && !oslot) CU(big_alloc(h, &oslot, (size_t)n * 4 + 16));
         uint32_t *block_base = (uint32_t *)seg + (size_t)n_blocks * (P + 2);
         CU(cudaMemsetAsync(h->d_part_rows, 0, ((size_t)(1 << PB_MAX_BITS) + 2) * 8, h->stream));
         {
@@ -539,6 +542,8 @@ int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces,
         sg.block_base = block_base;
         sg.n_blocks = n_blocks;
         sg.n_units = n_blocks * (n_null > 0 ? P + 1 : P);
+        sg.out_slot = (uint32_t *)oslot;
+        sg.zero_slot_index = (uint32_t)h->n_slots;
         {
             PhaseTimer tm(h, &h->st.ms_probe);
             const int64_t n_claims = ((int64_t)sg.n_units + SEG_UNITS - 1) / SEG_UNITS;
@@ -546,7 +551,10 @@ int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces,
             auto launch = [&](auto KW, auto MARK) {
                 constexpr int kw_ = decltype(KW)::value;
                 constexpr bool mk_ = decltype(MARK)::value;
-                if (l1) probe_dense_seg_kernel<kw_, mk_, true><<<grid, PD_THREADS, 0, h->stream>>>(a, sg);
+                if (want_slot) {
+                    if (l1) probe_dense_seg_kernel<kw_, mk_, true, true><<<grid, PD_THREADS, 0, h->stream>>>(a, sg);
+                    else probe_dense_seg_kernel<kw_, mk_, false, true><<<grid, PD_THREADS, 0, h->stream>>>(a, sg);
+                } else if (l1) probe_dense_seg_kernel<kw_, mk_, true><<<grid, PD_THREADS, 0, h->stream>>>(a, sg);
                 else probe_dense_seg_kernel<kw_, mk_, false><<<grid, PD_THREADS, 0, h->stream>>>(a, sg);
             };
             if (skw == 8) {
@@ -569,7 +577,6 @@ int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces,
         tr_.mark("segment probe + counters");
         const int64_t misses = (int64_t)h->h_ctr->build_null_out;       // rows without a match, NULL-key rows included
         h->miss_frac = n > n_null ? (float)((double)(misses - n_null) / (double)(n - n_null)) : 0.f;
-        big_free(h, tk); tk = nullptr;
         if (pl.mode == PM_OUTER || misses == 0) {
             *n_build_null = misses;
             ro->build_idx = ob;
@@ -580,14 +587,27 @@ int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces,
                 ro->seg_blocks = n_blocks;
                 ro->seg_P = P;
                 ro->seg_n = n;
+                ro->aux_misses = misses;
                 h->seg_owners.insert(ro);
+                if (ro->want_aux) {
+                    // ... and with B200J_OUT_GATHER_HINT the partitioned keys (= the probe key of every result row; not when the
+                    // batch has NULL keys, whose rows carry no key) and the slot of every pair
+                    if (n_null == 0) { ro->aux_keys = tk; ro->aux_kw = skw; tk = nullptr; }
+                    ro->aux_slot = oslot;
+                    oslot = nullptr;
+                }
             } else {
                 big_free(h, seg);
             }
             seg = nullptr;
+            if (tk) big_free(h, tk);
+            if (oslot) big_free(h, oslot);
+            tk = oslot = nullptr;
             return n;
         }
+        big_free(h, tk); tk = nullptr;
         big_free(h, seg); seg = nullptr;
+        if (oslot) { big_free(h, oslot); oslot = nullptr; }
         const int64_t keep = n - misses;
         CU(big_alloc(h, &ob2, (size_t)std::max<int64_t>(keep, 1) * 8));
         CU(big_alloc(h, &op2, (size_t)std::max<int64_t>(keep, 1) * 4));
@@ -609,7 +629,7 @@ int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces,
         ro->probe_idx = op2;
         return keep;
     } catch (...) {
-        for (void *p : {tk, tr, seg, ob, ob2, op2})
+        for (void *p : {tk, tr, seg, ob, ob2, op2, oslot})
             if (p) big_free(h, p);
         throw;
     }
@@ -649,6 +669,7 @@ void do_probe_pieces(H *h, int32_t partition, int32_t n_pieces, const void *cons
     REQUIRE(n < 0xffff0000LL, B200J_ERR_UNSUPPORTED, "probe batch of more than 2^32 - 2^16 rows (probe indices are UInt32)");
     ResultOwner *ro = new ResultOwner();
     ro->want_seg = true;
+    ro->want_aux = (want & B200J_OUT_GATHER_HINT) != 0 && !(want & B200J_OUT_HOST) && !count_only && h->gather_seg;
     void *cat = nullptr;
     try {
         int64_t total = 0, n_bnull = 0;

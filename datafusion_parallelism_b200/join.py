@@ -15,7 +15,7 @@ from . import _native as N
 JOIN_TYPES = {"inner": 0, "left": 1, "right": 2, "full": 3, "left_semi": 4, "right_semi": 5, "left_anti": 6, "right_anti": 7}
 LAYOUTS = {"auto": 0, "direct": 1, "radix": 2}
 MEM_HOST, MEM_DEVICE = 0, 1
-OUT_PAIRS, OUT_HOST, OUT_MATCHES_ONLY, OUT_COUNT_ONLY, OUT_BUILD_U32 = 1, 2, 4, 8, 16
+OUT_PAIRS, OUT_HOST, OUT_MATCHES_ONLY, OUT_COUNT_ONLY, OUT_BUILD_U32, OUT_GATHER_HINT = 1, 2, 4, 8, 16, 32
 FLAG_TIMING = 1
 NULL_BUILD = np.uint64(0xFFFFFFFFFFFFFFFF)
 NULL_PROBE = np.uint32(0xFFFFFFFF)

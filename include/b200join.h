@@ -94,6 +94,13 @@ extern "C" {
                                         points at uint32_t values, NULL side = UINT32_MAX, build_idx_width = 4. A host result
                                         crosses PCIe with 8 instead of 12 bytes per pair; arrow's take accepts UInt32 indices */
 
+#define B200J_OUT_GATHER_HINT   32u  /* the device result will be handed to b200j_gather: the library may keep auxiliary device
+                                        arrays with it until b200j_result_release -- the partitioned probe keys (4 or 8 B per row)
+                                        and the table slot of every pair (4 B per row) -- and keeps slot-ordered copies of the
+                                        fixed-width build payload columns in the handle; the gather then reads neither the probe
+                                        key column nor the build store at random. Ignored with B200J_OUT_HOST / COUNT_ONLY and
+                                        wherever the dense radix probe does not apply; the pairs themselves are unchanged        */
+
 typedef struct b200j_handle b200j_handle;
 
 /* One Arrow array's buffers (Arrow columnar format: LSB-first validity bitmap, 32-bit Utf8 offsets). */
@@ -211,6 +218,8 @@ typedef struct {
     int64_t  seg_probe_launches;      /* dense probe launches over the block-locally partitioned stream (probe_dense_seg_kernel) */
     int64_t  narrow_probe_launches;   /* ... of which the stream carried 8-byte keys as 32-bit values                    */
     int64_t  gather_seg_launches;     /* b200j_gather launches that walked the build side partition by partition (gather_seg_multi_kernel) */
+    int64_t  gather_hint_launches;    /* ... and launches that used what B200J_OUT_GATHER_HINT kept (stream keys, slot-ordered payload)    */
+    double   ms_slot_order;           /* building the slot-ordered payload copies (once per build, on the first hinted gather)            */
 } b200j_stats;
 
 /* ---- lifecycle ------------------------------------------------------------------------------- */

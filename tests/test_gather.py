@@ -141,7 +141,8 @@ def _gather_columns(env, join_type, bk, bcols, btypes, pk_dev, pk_valid, ppay_de
 @pytest.mark.parametrize("join_type,miss", [("inner", False), ("right", True), ("full", True)])
 @pytest.mark.parametrize("u32", [False, True])
 @pytest.mark.parametrize("shape", ["batch", "misaligned", "pieces"])
-def test_partition_order_gather_equals_plain_gather(join_type, miss, u32, shape):
+@pytest.mark.parametrize("hint", [False, True])
+def test_partition_order_gather_equals_plain_gather(join_type, miss, u32, shape, hint):
     """The build side of a dense radix result is gathered partition by partition (gather_seg_multi_kernel) and both key columns
     come out of one pass (gather_keys_both_kernel): same columns, bit for bit, as the plain row-order kernels, and as numpy."""
     import torch
@@ -174,11 +175,14 @@ def test_partition_order_gather_equals_plain_gather(join_type, miss, u32, shape)
         cut = 70_001
         pieces = [(pk_dev[:cut].data_ptr(), cut), (pk_dev[cut:].data_ptr(), npr - cut)]
     want = d.OUT_PAIRS | (d.OUT_BUILD_U32 if u32 else 0)
-    st_new, new = _gather_columns({}, join_type, bk, bcols, btypes, pk_dev, pk_valid, ppay_dev, want, pieces)
+    # hint: B200J_OUT_GATHER_HINT -- key columns from the partitioned key stream (gather_keys_stream_kernel, batches without NULL
+    # keys), fixed-width payload from the slot-ordered copies (slot_order_kernel) at the slot the probe recorded for every pair
+    st_new, new = _gather_columns({}, join_type, bk, bcols, btypes, pk_dev, pk_valid, ppay_dev, want | (d.OUT_GATHER_HINT if hint else 0), pieces)
     st_old, old = _gather_columns({"B200J_GATHER_SEG": "0", "B200J_KEY_VIA_PROBE": "0"}, join_type, bk, bcols, btypes, pk_dev, pk_valid,
                                   ppay_dev, want, pieces)
     assert st_new["gather_seg_launches"] >= 1 and st_new["seg_probe_launches"] >= 1, st_new
-    assert st_old["gather_seg_launches"] == 0, st_old
+    assert st_new["gather_hint_launches"] == (1 if hint else 0), st_new
+    assert st_old["gather_seg_launches"] == 0 and st_old["gather_hint_launches"] == 0, st_old
     assert len(new) == len(old)
     for c, ((v1, m1, z1), (v2, m2, z2)) in enumerate(zip(new, old)):
         assert z1 == z2, (c, z1, z2)
