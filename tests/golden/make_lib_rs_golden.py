@@ -4,7 +4,9 @@ The reference is a Rust crate that cannot be built or imported in this container
 vectors are a HAND TRANSCRIPTION of the literal input tables and literal expected output batches of the
 reference's own end-to-end tests in /root/reference/src/lib.rs (the same expectations are asserted there
 for stock DataFusion HashJoinExec and for all ten ParallelHashJoin versions).  Each scenario cites the
-lines it was transcribed from.  Run:  python tests/golden/make_lib_rs_golden.py
+lines it was transcribed from, and tests/test_golden_extraction.py re-derives every input table, every
+expected batch and the SQL of every scenario mechanically from the reference source wherever that tree is
+present and compares them with this transcription.  Run:  python tests/golden/make_lib_rs_golden.py
 """
 import json
 import os
