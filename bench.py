@@ -367,7 +367,7 @@ def run_b200(args):
         # ALGORITHMIC bytes: 8 B key in + 8 B build index out per row. (When every key fits 32 bits the partitioned stream carries
         # them as 4-byte values and the kernel moves 12 B per row; the algorithmic figure does not shrink with that.)
         bpt = B_PROBE_DENSE
-        kname = ("probe_dense_seg_kernel<4,false,false>" if narrow else "probe_dense_seg_kernel<8,false,false>") if seg else "probe_dense_kernel<8,false,true,false>"
+        kname = ("probe_dense_seg_kernel<4,false,false,false>" if narrow else "probe_dense_seg_kernel<8,false,false,false>") if seg else "probe_dense_kernel<8,false,true,false>"
         table_b = table_alg
     elif radix:
         bpt, kname, table_b = B_PROBE_KERNEL_RADIX, "probe_fast_kernel<8,PM_PAIRS,false,true>", table_alg
