@@ -196,6 +196,8 @@ struct b200j_handle {
     struct SlotCol { DevBuf values, validity; bool has_nulls = false; };
     std::vector<SlotCol> slot_cols;
     bool slot_cols_ready = false;
+    bool auto_hint = true;             // a handle whose device results have been gathered once treats later device probes as hinted (B200J_AUTO_HINT=0: off)
+    bool gather_seen = false;
     bool gather_seg = true;            // b200j_gather: build columns of a dense radix result are gathered partition by partition (B200J_GATHER_SEG=0: off)
     std::set<const void *> seg_owners;  // live results that carry a segment table (b200j_gather checks a caller's _owner against it)
     bool key_via_probe = true;         // b200j_gather: the build key column of matched pairs is read from the probe key column (B200J_KEY_VIA_PROBE=0: off)
@@ -1460,7 +1462,7 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
     const int64_t n = b->n_rows;
     ResultOwner *ro = new ResultOwner();
     ro->want_seg = true;
-    ro->want_aux = (want & B200J_OUT_GATHER_HINT) != 0 && !(want & B200J_OUT_HOST) && !count_only && h->gather_seg;
+    ro->want_aux = ((want & B200J_OUT_GATHER_HINT) != 0 || (h->auto_hint && h->gather_seen)) && !(want & B200J_OUT_HOST) && !count_only && h->gather_seg;
     std::vector<void *> temps;
     try {
         int64_t total = 0, n_bnull = 0;
@@ -1916,6 +1918,7 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
             if (const char *e = getenv("B200J_FUSED_CTAS")) h->fused_ctas_per_sm = std::max(1, atoi(e));
             if (const char *e = getenv("B200J_KEY_VIA_PROBE")) h->key_via_probe = atoi(e) != 0;
             if (const char *e = getenv("B200J_GATHER_SEG")) h->gather_seg = atoi(e) != 0;
+            if (const char *e = getenv("B200J_AUTO_HINT")) h->auto_hint = atoi(e) != 0;
             if (const char *e = getenv("B200J_NO_DENSE")) h->dense_ok = atoi(e) == 0;
             if (const char *e = getenv("B200J_DENSE_MISS_MAX")) h->dense_miss_max = (float)atof(e);
             if (const char *e = getenv("B200J_L1_TABLE_BYTES")) h->l1_table_bytes = (uint64_t)atoll(e);

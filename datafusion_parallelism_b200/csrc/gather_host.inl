@@ -310,6 +310,7 @@ void do_gather_impl(H *h, const b200j_result *pairs, const b200j_batch *probe_ba
         CU(cudaMemsetAsync(dn, 0, (size_t)(n_cols + 2 + GF_MAX_COLS) * 8, h->stream));
         g.d_nulls = (unsigned long long *)dn;
         g.d_nulls_scratch = g.d_nulls + n_cols + 1;
+        if (pairs->mem == B200J_MEM_DEVICE && want_build && n > 0) h->gather_seen = true;     // later device probes of this handle keep what the gather wants
         // a dense radix result that still carries its segment table: build columns partition by partition
         const ResultOwner *seg_ro = nullptr;
         if (want_build && h->gather_seg && pairs->mem == B200J_MEM_DEVICE && pairs->_owner != nullptr && h->seg_owners.count(pairs->_owner) != 0) {

@@ -463,8 +463,11 @@ int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces,
     }
     REQUIRE(n < 0xffff0000LL, B200J_ERR_UNSUPPORTED, "probe batch of more than 2^32 - 2^16 rows (probe indices are UInt32)");
     void *tk = nullptr, *tr = nullptr, *seg = nullptr, *ob = nullptr, *ob2 = nullptr, *op2 = nullptr, *oslot = nullptr;
-    // B200J_OUT_GATHER_HINT: the probe also writes the table slot of every row (slot indices must fit 32 bits)
-    const bool want_slot = ro->want_aux && ro->want_seg && h->n_slots + 2 < 0xffffffffULL;
+    // B200J_OUT_GATHER_HINT: the probe also writes the table slot of every row (slot indices must fit 32 bits) -- when there is a
+    // fixed-width build payload column for the gather to read through it; a join without one keeps only the key stream
+    bool fixed_payload = false;
+    for (int i = 0; i < h->cfg.n_build_payload; i++) fixed_payload |= h->bpayload[i].type != B200J_T_UTF8;
+    const bool want_slot = ro->want_aux && ro->want_seg && fixed_payload && h->n_slots + 2 < 0xffffffffULL;
     Trace tr_;
     try {
         // 8-byte keys travel through the partitioned stream as 32-bit values while they fit (see part_block_kernel NARROW)
@@ -669,7 +672,7 @@ void do_probe_pieces(H *h, int32_t partition, int32_t n_pieces, const void *cons
     REQUIRE(n < 0xffff0000LL, B200J_ERR_UNSUPPORTED, "probe batch of more than 2^32 - 2^16 rows (probe indices are UInt32)");
     ResultOwner *ro = new ResultOwner();
     ro->want_seg = true;
-    ro->want_aux = (want & B200J_OUT_GATHER_HINT) != 0 && !(want & B200J_OUT_HOST) && !count_only && h->gather_seg;
+    ro->want_aux = ((want & B200J_OUT_GATHER_HINT) != 0 || (h->auto_hint && h->gather_seen)) && !(want & B200J_OUT_HOST) && !count_only && h->gather_seg;
     void *cat = nullptr;
     try {
         int64_t total = 0, n_bnull = 0;

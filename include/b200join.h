@@ -99,7 +99,9 @@ extern "C" {
                                         and the table slot of every pair (4 B per row) -- and keeps slot-ordered copies of the
                                         fixed-width build payload columns in the handle; the gather then reads neither the probe
                                         key column nor the build store at random. Ignored with B200J_OUT_HOST / COUNT_ONLY and
-                                        wherever the dense radix probe does not apply; the pairs themselves are unchanged        */
+                                        wherever the dense radix probe does not apply; the pairs themselves are unchanged.
+                                        A handle whose device pairs have been through b200j_gather once treats every later
+                                        device probe as if it carried this flag (environment B200J_AUTO_HINT=0 turns that off)   */
 
 typedef struct b200j_handle b200j_handle;
 

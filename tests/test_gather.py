@@ -221,3 +221,35 @@ def test_partition_order_gather_equals_plain_gather(join_type, miss, u32, shape,
         assert n == int(((pk <= nb) & ~vmask).sum())
     elif join_type == "right":
         assert n == npr
+
+
+def test_hinted_gather_of_a_join_without_payload():
+    """B200J_OUT_GATHER_HINT on a join that has only its key column: the result keeps the partitioned key stream (no slot array:
+    there is no payload to read through it) and both key columns of the output are copied from it."""
+    import ctypes as C
+    import torch
+    import datafusion_parallelism_b200 as d
+    rng = np.random.default_rng(5)
+    nb, npr = 40_000, 100_001
+    bk = rng.permutation(nb).astype(np.int64) * 3 + 1
+    pk = bk[rng.integers(0, nb, npr)]
+    pk_dev = torch.from_numpy(pk).cuda()
+    with d.HashJoin("inner", key_widths=(8,), layout="radix", radix_bits=3) as j:
+        j.build_push(0, [bk])
+        j.build_finish(0)
+        res = j.probe_batch(0, [pk_dev], want=d.OUT_PAIRS | d.OUT_GATHER_HINT)
+        b_, p_ = res.device_arrays()
+        pidx = torch.as_tensor(p_, device="cuda").cpu().numpy().astype(np.int64) & 0xFFFFFFFF
+        bidx = torch.as_tensor(b_, device="cuda").cpu().numpy().astype(np.int64)
+        g = j.gather(res, [pk_dev], want=d.OUT_HOST)
+        n = g.n_rows
+        cols = [g.column_buffers(i) for i in range(g.n_cols)]
+        gb = np.frombuffer(C.string_at(cols[0]["values"], n * 8), dtype=np.int64).copy()
+        gp = np.frombuffer(C.string_at(cols[1]["values"], n * 8), dtype=np.int64).copy()
+        st = j.stats()
+        g.release()
+        res.release()
+    assert n == npr and g.n_cols == 2
+    assert all(c["null_count"] == 0 and not c["validity"] for c in cols)
+    assert st["gather_hint_launches"] == 1 and st["seg_probe_launches"] == 1, st
+    assert np.array_equal(gp, pk[pidx]) and np.array_equal(gb, bk[bidx]) and np.array_equal(gb, gp)
