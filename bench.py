@@ -65,6 +65,7 @@ def parse_args():
     ap.add_argument("--no-verify", action="store_true")
     ap.add_argument("--overlap-build", type=int, default=0, help="N>1: 1 = exchange the probe side while the local table is built")
     ap.add_argument("--e2e-wide", action="store_true", help="e2e returns (u64, u32) pairs instead of B200J_OUT_BUILD_U32's (u32, u32)")
+    ap.add_argument("--e2e-pairs", action="store_true", help="e2e returns index pairs instead of the probe-ordered build-index array (B200J_OUT_PROBE_ORDER)")
     ap.add_argument("--no-gather", action="store_true")
     ap.add_argument("--host-chunk-rows", type=int, default=1 << 27, help="N>1 e2e: probe rows per pipelined host chunk (DistributedJoin.probe_host_chunks)")
     ap.add_argument("--exchange-chunk-rows", type=int, default=0, help="N>1: > 0 = probe rows per exchange / local-join pipeline stage (DistributedJoin.probe_chunks)")
@@ -568,6 +569,26 @@ def run_gather_phase(args, d, torch, dev, join, bk, bpay, pk, hbm_gbs):
             "plain": out["plain"], "hinted": out["hinted"], "verified": bool(out["plain"]["verified"] and out["hinted"]["verified"])}
 
 
+def verify_host_result(np, r, build_keys, probe_keys, probe_order, sample=1 << 22):
+    """Host-side check of one e2e result (N = 1): the row count, and key equality build_key[build_idx] == probe_key[probe_idx] on a
+    random sample of the rows (every row of the 1:1 workload has a match)."""
+    import ctypes as C
+    n = r.n
+    if n != probe_keys.shape[0] or r.n_build_null != 0:
+        return False
+    rng = np.random.default_rng(1)
+    idx = rng.integers(0, n, min(sample, n))
+    bt = C.c_uint32 if r.build_idx_width == 4 else C.c_uint64
+    b = np.ctypeslib.as_array(C.cast(r.build_ptr, C.POINTER(bt)), shape=(n,))
+    if probe_order:
+        if not r.probe_order or r.probe_ptr:
+            return False
+        p = idx
+    else:
+        p = np.ctypeslib.as_array(C.cast(r.probe_ptr, C.POINTER(C.c_uint32)), shape=(n,))[idx].astype(np.int64)
+    return bool(np.array_equal(build_keys[b[idx].astype(np.int64)], probe_keys[p]))
+
+
 def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
     """Same join through host buffers: pinned Arrow key buffers in, pinned index pairs out, every step."""
     import numpy as np
@@ -591,9 +612,17 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
     checksum = 0
 
     host_chunk = min(chunk, args.host_chunk_rows)
-    # (build_idx u32, probe_idx u32) pairs come back unless --e2e-wide: 8 instead of 12 bytes per pair over PCIe
+    # What comes back over PCIe (N = 1). Default: B200J_OUT_PROBE_ORDER | B200J_OUT_BUILD_U32 -- the build keys are unique, so the result
+    # is ONE u32 array in the order of the probe batch (build_idx[i] = the match of probe row i): 4 bytes per probe row.
+    # --e2e-pairs: (u32 build_idx, u32 probe_idx) pairs, 8 bytes per pair; --e2e-wide: (u64, u32) pairs, 12 bytes.
+    probe_order = world == 1 and not (args.e2e_wide or args.e2e_pairs)
     out_flags = 0 if (args.e2e_wide or world > 1) else d.OUT_BUILD_U32
-    pair_bytes = 12 if (args.e2e_wide or world > 1) else 8
+    if probe_order:
+        out_flags |= d.OUT_PROBE_ORDER
+    pair_bytes = 12 if (args.e2e_wide or world > 1) else (4 if probe_order else 8)
+    fmt = {12: "(u64 build_idx, u32 probe_idx) pairs", 8: "(u32 build_idx, u32 probe_idx) pairs [B200J_OUT_BUILD_U32]",
+           4: "u32 build_idx per probe row, in probe order [B200J_OUT_PROBE_ORDER | B200J_OUT_BUILD_U32]"}[pair_bytes]
+    check = {"ok": None}
 
     def step_host():
         if world > 1:
@@ -617,6 +646,8 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
         for lo in range(0, n_probe, chunk):
             r = join.probe_batch(0, [hp.array[lo:lo + chunk]], want=d.OUT_PAIRS | d.OUT_HOST | out_flags)
             tot += r.n
+            if check["ok"] is None and lo == 0:
+                check["ok"] = verify_host_result(np, r, hb.array, hp.array[lo:lo + chunk], probe_order)     # first warm-up step only: outside the timed region
             r.release()
         return tot
 
@@ -640,8 +671,8 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
     if hpay is not None:
         hpay.free()
     return {"value": (n_build + n_probe) * world / (dt / steps), "unit": UNIT, "h2d_bytes_per_step": 8 * (n_build + n_probe) + (8 * n_build if world == 1 else 0),
-            "d2h_bytes_per_step": pair_bytes * tot, "pair_format": "(u64 build_idx, u32 probe_idx)" if pair_bytes == 12 else "(u32 build_idx, u32 probe_idx) [B200J_OUT_BUILD_U32]", "steps": steps, "ms_per_step": dt / steps * 1e3, "ms_steps_rank0": ms_steps,
-            "api": ("HashJoin.build_push/probe_batch(host numpy over b200j_host_alloc pinned buffers, OUT_PAIRS|OUT_HOST" + ("|OUT_BUILD_U32" if pair_bytes == 8 else "") + ") -> b200j_* C ABI" if world == 1 else
+            "d2h_bytes_per_step": pair_bytes * tot, "pair_format": fmt, "verified": check["ok"], "steps": steps, "ms_per_step": dt / steps * 1e3, "ms_steps_rank0": ms_steps,
+            "api": ("HashJoin.build_push/probe_batch(host numpy over b200j_host_alloc pinned buffers, OUT_PAIRS|OUT_HOST" + ("|OUT_BUILD_U32" if pair_bytes <= 8 else "") + ("|OUT_PROBE_ORDER" if probe_order else "") + ") -> b200j_* C ABI" if world == 1 else
                     f"DistributedJoin.build_push_host/probe_host_chunks(pinned numpy in, pinned pairs out, {host_chunk}-row chunks) -> b200j_* C ABI")}
 
 

@@ -64,7 +64,7 @@ class Config(C.Structure):
 class Result(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("mem", C.c_int32), ("n", C.c_int64), ("build_idx", C.c_void_p),
                 ("probe_idx", C.c_void_p), ("n_build_null", C.c_int64), ("n_probe_null", C.c_int64), ("_owner", C.c_void_p),
-                ("build_idx_width", C.c_int32), ("_pad", C.c_int32)]
+                ("build_idx_width", C.c_int32), ("probe_order", C.c_int32)]
 
 
 class OutColumn(C.Structure):
@@ -86,7 +86,7 @@ class Stats(C.Structure):
                 ("probe_launches", C.c_int64), ("kernel_launches", C.c_int64), ("probe_retries", C.c_int64),
                 ("dense_probe_launches", C.c_int64), ("compact_launches", C.c_int64), ("ms_exchange_partition", C.c_double),
                 ("seg_probe_launches", C.c_int64), ("narrow_probe_launches", C.c_int64), ("gather_seg_launches", C.c_int64),
-                ("gather_hint_launches", C.c_int64), ("ms_slot_order", C.c_double)]
+                ("gather_hint_launches", C.c_int64), ("ms_slot_order", C.c_double), ("probe_order_results", C.c_int64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_ if not n.startswith("_") and n != "struct_size"}

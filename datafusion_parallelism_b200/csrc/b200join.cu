@@ -87,6 +87,7 @@ struct ResultOwner {
     void *probe_idx = nullptr;
     int32_t mem = B200J_MEM_DEVICE;
     int32_t bwidth = 8;               // bytes per build index: 4 after B200J_OUT_BUILD_U32 narrowing
+    bool probe_order = false;         // B200J_OUT_PROBE_ORDER honoured: build_idx[i] belongs to probe row i, probe_idx is null
     // The dense probe behind the radix layout leaves the pairs in the order of the block-partitioned probe stream. When the
     // caller of probe_device asks for it (want_seg), the stream's segment table stays with the result so that b200j_gather can
     // walk the build side partition by partition (gather_seg_multi_kernel). Device memory, whatever `mem` says.
@@ -883,6 +884,7 @@ void fill_result(b200j_result *out, ResultOwner *ro, int64_t n, int mem) {
     out->probe_idx = (uint32_t *)ro->probe_idx;
     out->_owner = ro;
     if (out->struct_size >= offsetof(b200j_result, build_idx_width) + sizeof(int32_t)) out->build_idx_width = ro->bwidth;
+    if (out->struct_size >= offsetof(b200j_result, probe_order) + sizeof(int32_t)) out->probe_order = ro->probe_order ? 1 : 0;
 }
 
 void drop_seg(H *h, ResultOwner *ro) {
@@ -1163,6 +1165,30 @@ void narrow_result(H *h, ResultOwner *ro, int64_t n) {
     ro->bwidth = 4;
 }
 
+// B200J_OUT_PROBE_ORDER: the device pairs of a PM_OUTER probe against unique build keys (exactly one pair per probe row, probe
+// indices = base .. base + n - 1 in some order) become one build-index array in probe order; the pair arrays are recycled.
+void to_probe_order(H *h, ResultOwner *ro, int64_t n, uint32_t base, bool u32) {
+    if (ro->mem != B200J_MEM_DEVICE) return;
+    const size_t bw = u32 ? 4 : 8;
+    void *out = nullptr;
+    CU(big_alloc(h, &out, (size_t)std::max<int64_t>(n, 1) * bw + 16));
+    if (n > 0) {
+        const int grid = grid_for(h, n, 256 * 4, 8);
+        if (u32) reorder_by_probe_kernel<uint32_t><<<grid, 256, 0, h->stream>>>((const uint64_t *)ro->build_idx, (const uint32_t *)ro->probe_idx, n, base, (uint32_t *)out);
+        else reorder_by_probe_kernel<unsigned long long><<<grid, 256, 0, h->stream>>>((const uint64_t *)ro->build_idx, (const uint32_t *)ro->probe_idx, n, base, (unsigned long long *)out);
+        h->st.kernel_launches++;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { big_free(h, out); CU(e); }
+    drop_seg(h, ro);                          // the result no longer follows the partitioned stream
+    if (ro->build_idx) big_free(h, ro->build_idx);      // stream-ordered: the kernel above has been enqueued before any reuse
+    if (ro->probe_idx) big_free(h, ro->probe_idx);
+    ro->build_idx = out;
+    ro->probe_idx = nullptr;
+    ro->bwidth = (int32_t)bw;
+    ro->probe_order = true;
+}
+
 void move_result_to_host(H *h, ResultOwner *ro, int64_t n) {
     void *hb = nullptr, *hp = nullptr;
     if (ro->build_idx) {
@@ -1230,7 +1256,7 @@ struct HostPipe {               // everything the pipelined probe must give back
 };
 
 int64_t probe_host_pipelined(H *h, const b200j_column &kc, int64_t n, const ProbePlan &pl, bool count_only, bool narrow, ResultOwner *ro,
-                             int64_t *n_build_null) {
+                             int64_t *n_build_null, bool probe_order = false) {
     const size_t bw = narrow ? 4 : 8;        // bytes per build index in the pinned result
     const int kw = h->table_kw;
     const int64_t chunk = host_chunk_rows();
@@ -1254,7 +1280,7 @@ int64_t probe_host_pipelined(H *h, const b200j_column &kc, int64_t n, const Prob
     if (!count_only && want_probe) {
         host_cap = std::max<int64_t>(estimate_out_cap(h, n, pl), 1);
         if (want_build) hp.hb = pinned_take(h, (size_t)host_cap * bw);
-        hp.hp = pinned_take(h, (size_t)host_cap * 4);
+        if (!probe_order) hp.hp = pinned_take(h, (size_t)host_cap * 4);      // probe order: one array, build_idx[i] of probe row i
     }
     auto issue_h2d = [&](int64_t k) {
         const int b = (int)(k & 1);
@@ -1288,6 +1314,16 @@ int64_t probe_host_pipelined(H *h, const b200j_column &kc, int64_t n, const Prob
             continue;
         }
         try {
+            if (probe_order) {
+                // the chunk's pairs -> its slice of the one probe-ordered array (row ids of the radix layouts already count from `lo`)
+                REQUIRE(cnt == m, B200J_ERR_CUDA, "probe order: the chunk did not yield one pair per probe row");
+                to_probe_order(h, &pd.ro, m, h->layout == B200J_LAYOUT_RADIX ? (uint32_t)lo : 0u, narrow);
+                CU(cudaEventCreateWithFlags(&pd.done, cudaEventDisableTiming));
+                CU(cudaEventRecord(pd.done, h->stream));
+                CU(cudaStreamWaitEvent(h->copy_out, pd.done, 0));
+                CU(cudaMemcpyAsync((char *)hp.hb + (size_t)lo * bw, pd.ro.build_idx, (size_t)m * bw, cudaMemcpyDeviceToHost, h->copy_out));
+                CU(cudaEventRecord(pd.done, h->copy_out));
+            } else {
             if (cnt > 0 && lo > 0 && h->layout != B200J_LAYOUT_RADIX) {
                 add_base_u32_kernel<<<grid_for(h, cnt, 256, 8), 256, 0, h->stream>>>((uint32_t *)pd.ro.probe_idx, cnt, (uint32_t)lo);
                 h->st.kernel_launches++;
@@ -1320,6 +1356,7 @@ int64_t probe_host_pipelined(H *h, const b200j_column &kc, int64_t n, const Prob
                 CU(cudaMemcpyAsync((char *)hp.hp + (size_t)total * 4, pd.ro.probe_idx, (size_t)cnt * 4, cudaMemcpyDeviceToHost, h->copy_out));
             }
             CU(cudaEventRecord(pd.done, h->copy_out));
+            }
         } catch (...) {
             if (pd.done) cudaEventDestroy(pd.done);
             if (pd.ro.build_idx) big_free(h, pd.ro.build_idx);
@@ -1338,6 +1375,7 @@ int64_t probe_host_pipelined(H *h, const b200j_column &kc, int64_t n, const Prob
         ro->probe_idx = hp.hp;
         ro->mem = B200J_MEM_HOST;
         ro->bwidth = (int32_t)bw;
+        ro->probe_order = probe_order;
         hp.hb = hp.hp = nullptr;
     }
     return total;
@@ -1456,13 +1494,20 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
         do_probe_composite(h, partition, b, want, out);
         return;
     }
-    const ProbePlan pl = plan_for(h->cfg.join_type, (want & B200J_OUT_MATCHES_ONLY) != 0);
+    ProbePlan pl = plan_for(h->cfg.join_type, (want & B200J_OUT_MATCHES_ONLY) != 0);
     const bool count_only = (want & B200J_OUT_COUNT_ONLY) != 0;
     const int kw = h->key_widths[0];
     const int64_t n = b->n_rows;
+    // B200J_OUT_PROBE_ORDER: unique build keys -> every probe row has at most one match; probed as an outer join (one pair per
+    // probe row, NULL build index where there is none) and handed back as one array in the order of the batch
+    const int jt_ = h->cfg.join_type;
+    const bool probe_order = (want & B200J_OUT_PROBE_ORDER) != 0 && !(want & (B200J_OUT_MATCHES_ONLY | B200J_OUT_COUNT_ONLY)) &&
+                             out->struct_size >= offsetof(b200j_result, probe_order) + sizeof(int32_t) && h->st.duplicate_rows == 0 &&
+                             kw != B200J_T_UTF8 && (jt_ == B200J_INNER || jt_ == B200J_LEFT || jt_ == B200J_RIGHT || jt_ == B200J_FULL);
+    if (probe_order) pl.mode = PM_OUTER;
     ResultOwner *ro = new ResultOwner();
-    ro->want_seg = true;
-    ro->want_aux = ((want & B200J_OUT_GATHER_HINT) != 0 || (h->auto_hint && h->gather_seen)) && !(want & B200J_OUT_HOST) && !count_only && h->gather_seg;
+    ro->want_seg = !probe_order;
+    ro->want_aux = ((want & B200J_OUT_GATHER_HINT) != 0 || (h->auto_hint && h->gather_seen)) && !(want & B200J_OUT_HOST) && !count_only && h->gather_seg && !probe_order;
     std::vector<void *> temps;
     try {
         int64_t total = 0, n_bnull = 0;
@@ -1470,7 +1515,7 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
             const b200j_column &kc = b->keys[0];
             total = probe_device(h, n ? kc.values : nullptr, n ? kc.validity : nullptr, n ? kc.bit_offset : 0, n, pl, count_only, ro, &n_bnull);
         } else if (((want & B200J_OUT_HOST) || count_only) && n > host_chunk_rows() + host_chunk_rows() / 2) {
-            total = probe_host_pipelined(h, b->keys[0], n, pl, count_only, (want & B200J_OUT_BUILD_U32) != 0, ro, &n_bnull);
+            total = probe_host_pipelined(h, b->keys[0], n, pl, count_only, (want & B200J_OUT_BUILD_U32) != 0, ro, &n_bnull, probe_order);
         } else {
             const b200j_column &kc = b->keys[0];
             void *dk = nullptr;
@@ -1486,10 +1531,16 @@ void do_probe_batch(H *h, int32_t partition, const b200j_batch *b, uint32_t want
             if (ro->probe_idx) big_free(h, ro->probe_idx);
             ro->build_idx = ro->probe_idx = nullptr;
         } else {
+            if (probe_order && ro->mem == B200J_MEM_DEVICE) {
+                REQUIRE(total == n, B200J_ERR_CUDA, "probe order: the batch did not yield one pair per probe row");
+                to_probe_order(h, ro, n, 0u, (want & B200J_OUT_BUILD_U32) != 0);
+                if (!(want & B200J_OUT_HOST)) CU(cudaStreamSynchronize(h->stream));
+            }
             if (want & B200J_OUT_BUILD_U32) narrow_result(h, ro, total);
             if ((want & B200J_OUT_HOST) && ro->mem != B200J_MEM_HOST) move_result_to_host(h, ro, total);
             else if (want & B200J_OUT_BUILD_U32) CU(cudaStreamSynchronize(h->stream));
         }
+        if (probe_order) h->st.probe_order_results++;
         free_temps(h, temps);
         fill_result(out, ro, total, ro->mem);
         out->n_build_null = n_bnull;
@@ -2029,7 +2080,7 @@ int32_t b200j_reset_stats(b200j_handle *h) {
     h->st.ms_build_copy = h->st.ms_build_partition = h->st.ms_build_insert = 0;
     h->st.ms_probe_partition = h->st.ms_probe = h->st.ms_gather = 0;
     h->st.probe_launches = h->st.kernel_launches = h->st.probe_retries = 0;
-    h->st.dense_probe_launches = h->st.compact_launches = h->st.seg_probe_launches = h->st.narrow_probe_launches = h->st.gather_seg_launches = h->st.gather_hint_launches = 0;
+    h->st.dense_probe_launches = h->st.compact_launches = h->st.seg_probe_launches = h->st.narrow_probe_launches = h->st.gather_seg_launches = h->st.gather_hint_launches = h->st.probe_order_results = 0;
     h->st.ms_slot_order = 0;
     h->st.ms_exchange_partition = 0;
     return B200J_OK;

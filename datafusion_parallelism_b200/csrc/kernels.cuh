@@ -1153,6 +1153,19 @@ __global__ void __launch_bounds__(256) narrow_u64_u32_kernel(const uint64_t *__r
     if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) out[n - 1] = (uint32_t)in[n - 1];
 }
 
+// B200J_OUT_PROBE_ORDER: pairs (one per probe row, unique build keys) -> ONE array in the order of the probe batch,
+// out[probe_idx - base] = build_idx. The pairs of the dense probes come in the order of the partitioned stream, i.e. the probe
+// indices of 32 K consecutive pairs stay inside one 32 K-row window of `out`: the scattered 4 / 8 B writes merge in L2.
+template <typename OutT>
+__global__ void __launch_bounds__(256) reorder_by_probe_kernel(const uint64_t *__restrict__ bidx, const uint32_t *__restrict__ pidx, int64_t n,
+                                                               uint32_t base, OutT *__restrict__ out) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const unsigned long long b = __ldcs(reinterpret_cast<const unsigned long long *>(bidx) + i);
+        const uint32_t p = __ldcs(pidx + i) - base;
+        if ((int64_t)p < n) out[p] = (OutT)b;               // ~0ULL narrows to the 32-bit NULL index
+    }
+}
+
 // 32-bit key pieces of the multi-GPU exchange -> 8-byte keys (the concatenating fall-back of b200j_probe_pieces)
 __global__ void __launch_bounds__(256) widen_u32_u64_kernel(const uint32_t *__restrict__ in, unsigned long long *__restrict__ out, int64_t n) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = (unsigned long long)in[i];

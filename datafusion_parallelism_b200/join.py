@@ -15,7 +15,7 @@ from . import _native as N
 JOIN_TYPES = {"inner": 0, "left": 1, "right": 2, "full": 3, "left_semi": 4, "right_semi": 5, "left_anti": 6, "right_anti": 7}
 LAYOUTS = {"auto": 0, "direct": 1, "radix": 2}
 MEM_HOST, MEM_DEVICE = 0, 1
-OUT_PAIRS, OUT_HOST, OUT_MATCHES_ONLY, OUT_COUNT_ONLY, OUT_BUILD_U32, OUT_GATHER_HINT = 1, 2, 4, 8, 16, 32
+OUT_PAIRS, OUT_HOST, OUT_MATCHES_ONLY, OUT_COUNT_ONLY, OUT_BUILD_U32, OUT_GATHER_HINT, OUT_PROBE_ORDER = 1, 2, 4, 8, 16, 32, 64
 FLAG_TIMING = 1
 NULL_BUILD = np.uint64(0xFFFFFFFFFFFFFFFF)
 NULL_PROBE = np.uint32(0xFFFFFFFF)
@@ -125,6 +125,7 @@ class PairResult:
         self.n_build_null = int(res.n_build_null)
         self.n_probe_null = int(res.n_probe_null)
         self.build_idx_width = int(res.build_idx_width) or 8
+        self.probe_order = bool(res.probe_order)      # B200J_OUT_PROBE_ORDER honoured: build_idx[i] belongs to probe row i, no probe_idx array
 
     @property
     def build_ptr(self) -> int:
@@ -149,6 +150,8 @@ class PairResult:
             b = np.ctypeslib.as_array(C.cast(self._res.build_idx, C.POINTER(C.c_uint64)), shape=(n,)).copy()
         if n and self._res.probe_idx:
             p = np.ctypeslib.as_array(C.cast(self._res.probe_idx, C.POINTER(C.c_uint32)), shape=(n,)).copy()
+        elif self.probe_order:
+            p = np.arange(n, dtype=np.uint32)          # probe-order result: row i of the batch
         return b, p
 
     def device_arrays(self):

@@ -103,6 +103,15 @@ extern "C" {
                                         A handle whose device pairs have been through b200j_gather once treats every later
                                         device probe as if it carried this flag (environment B200J_AUTO_HINT=0 turns that off)   */
 
+#define B200J_OUT_PROBE_ORDER   64u  /* unique build keys (every probe row has at most one match -- a foreign-key join): the result is
+                                        ONE array in the order of the probe batch, build_idx[i] = the build row probe row i matches
+                                        or the NULL build index, and no probe_idx array (result.probe_order = 1, probe_idx = NULL,
+                                        n = the batch's rows; Inner / Left callers drop the NULL rows, the probe columns need no
+                                        take at all). 4 bytes per probe row back over PCIe with B200J_OUT_BUILD_U32 instead of 8.
+                                        Honoured for Inner / Left / Right / Full joins on a single fixed-width key without
+                                        B200J_OUT_MATCHES_ONLY / COUNT_ONLY when the build side has no duplicate keys; otherwise
+                                        the call returns ordinary pairs (probe_order = 0)                                       */
+
 typedef struct b200j_handle b200j_handle;
 
 /* One Arrow array's buffers (Arrow columnar format: LSB-first validity bitmap, 32-bit Utf8 offsets). */
@@ -167,7 +176,8 @@ typedef struct {
     int64_t   n_probe_null;
     void     *_owner;                 /* private                                                      */
     int32_t   build_idx_width;        /* 8 (uint64_t, the default) or 4 (B200J_OUT_BUILD_U32)          */
-    int32_t   _pad;
+    int32_t   probe_order;            /* 1: B200J_OUT_PROBE_ORDER was honoured -- probe_idx is NULL, n = the batch's rows and
+                                         build_idx[i] is the match of probe row i (or the NULL build index)   */
 } b200j_result;
 
 /* Gathered output column (Arrow layout), produced by b200j_gather. */
@@ -222,6 +232,7 @@ typedef struct {
     int64_t  gather_seg_launches;     /* b200j_gather launches that walked the build side partition by partition (gather_seg_multi_kernel) */
     int64_t  gather_hint_launches;    /* ... and launches that used what B200J_OUT_GATHER_HINT kept (stream keys, slot-ordered payload)    */
     double   ms_slot_order;           /* building the slot-ordered payload copies (once per build, on the first hinted gather)            */
+    int64_t  probe_order_results;     /* probe calls answered in probe order (B200J_OUT_PROBE_ORDER)                                      */
 } b200j_stats;
 
 /* ---- lifecycle ------------------------------------------------------------------------------- */
