@@ -288,6 +288,10 @@ void do_gather_impl(H *h, const b200j_result *pairs, const b200j_batch *probe_ba
         REQUIRE(probe_batch->n_payload == npp, B200J_ERR_INVALID, "gather needs every configured probe payload column");
     }
     const int64_t n = pairs->n;
+    const bool pairs_probe_order = pairs->struct_size >= offsetof(b200j_result, probe_order) + sizeof(int32_t) && pairs->probe_order != 0;
+    REQUIRE(!pairs_probe_order || (probe_batch == nullptr && staged_probe == nullptr), B200J_ERR_INVALID,
+            "gather of a probe-order result: the probe batch's own columns are the output's probe columns (row i belongs to build_idx[i]); "
+            "pass probe_batch = NULL to gather the build side");
     GatheredOwner *own = new GatheredOwner();
     GatherCtx g{h, n, nullptr, nullptr, {}, own, nullptr, nullptr};
     try {

@@ -282,7 +282,9 @@ int32_t b200j_probe_finish(b200j_handle *h, int32_t partition, uint32_t want, b2
 int32_t b200j_result_release(b200j_handle *h, b200j_result *r);
 
 /* Output gather (a6): build columns at build_idx, then probe columns of `probe_batch` at probe_idx.
- * probe_batch may be NULL for the finaliser (probe columns all NULL). */
+ * probe_batch may be NULL for the finaliser (probe columns all NULL). A B200J_OUT_PROBE_ORDER result is gathered with
+ * probe_batch = NULL: its build columns come out in the order of the probe batch, whose own columns are the output's
+ * probe columns as they are. */
 int32_t b200j_gather(b200j_handle *h, const b200j_result *pairs, const b200j_batch *probe_batch, uint32_t want,
                      b200j_gathered *out);
 int32_t b200j_gathered_release(b200j_handle *h, b200j_gathered *g);

@@ -106,3 +106,32 @@ def test_probe_order_is_declined_for_duplicate_build_keys_and_semi_joins():
         _, p = res.numpy()
         res.release()
     assert np.array_equal(np.sort(p), np.flatnonzero(pk < 5_000).astype(np.uint32))
+
+
+def test_gather_of_a_probe_order_result():
+    """b200j_gather takes a probe-order result with probe_batch = NULL: the build columns come out in the order of the probe
+    batch (NULL rows where a probe row has no match); handing it a probe batch is refused."""
+    import ctypes as C
+    import datafusion_parallelism_b200 as d
+    rng = np.random.default_rng(13)
+    nb, npr = 8_000, 30_000
+    bk = rng.permutation(nb).astype(np.int64)
+    bpay = (bk * 5 + 2).astype(np.int64)
+    pk = rng.integers(0, nb + 2_000, npr).astype(np.int64)
+    with d.HashJoin("right", key_widths=(8,), build_payload_types=(8,), layout="radix", radix_bits=3) as j:
+        j.build_push(0, [bk], [bpay])
+        j.build_finish(0)
+        res = j.probe_batch(0, [pk], want=d.OUT_PAIRS | d.OUT_PROBE_ORDER)          # device result
+        assert res.probe_order
+        with pytest.raises(d.B200JoinError):
+            j.gather(res, [pk])
+        g = j.gather(res, None, want=d.OUT_HOST)
+        n = g.n_rows
+        cols = [g.column_buffers(i) for i in range(2)]
+        key = np.frombuffer(C.string_at(cols[0]["values"], n * 8), dtype=np.int64)
+        pay = np.frombuffer(C.string_at(cols[1]["values"], n * 8), dtype=np.int64)
+        valid = np.unpackbits(np.frombuffer(C.string_at(cols[0]["validity"], (n + 31) // 32 * 4), dtype=np.uint8), bitorder="little")[:n].astype(bool)
+        g.release()
+        res.release()
+    assert n == npr and np.array_equal(valid, pk < nb)
+    assert np.array_equal(key[valid], pk[valid]) and np.array_equal(pay[valid], pk[valid] * 5 + 2)
