@@ -1,7 +1,7 @@
 #!/bin/bash
 # End-of-round validation on one B200 (run under gpurun): GPU suite, smoke, the contract bench line + reference arm,
 # ncu launch list and one ncu --set full capture of the library's kernels (summarised with scripts/ncu_summary.py).
-# usage: scripts/final_validation.sh <tag> [ncu-only]     -> gpurun_out/<tag>_*
+# usage: scripts/final_validation.sh <tag> [ncu-only | no-ncu-full]     -> gpurun_out/<tag>_*
 tag=${1:-final}
 mkdir -p gpurun_out
 if [ "$2" != "ncu-only" ]; then
@@ -14,10 +14,12 @@ python bench.py --impl reference > gpurun_out/${tag}_bench_reference_arm.json 2>
 fi
 ncu --metrics gpu__time_duration.sum --clock-control none -k 'regex:^(build_insert|csr_|gather_|part_|probe_|slot_order|compact_pairs|narrow_)' -c 200 --csv --log-file gpurun_out/${tag}_launches_bench_C2.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu --no-e2e --no-verify > gpurun_out/${tag}_ncu_launches.log 2>&1; echo "launch list rc $?"
+if [ "$2" != "no-ncu-full" ]; then
 # the .ncu-rep stays on the box (hundreds of MB with --import-source): only its per-kernel summary comes back
 timeout 900 ncu --set full --clock-control none --import-source on -k 'regex:^(build_insert|gather_|part_block|part_scatter|probe_|slot_order)' -c 70 -f -o /tmp/${tag}_full \
     python bench.py --steps 1 --warmup 1 --no-cpu --no-e2e --no-verify > gpurun_out/${tag}_ncu_full.log 2>&1; echo "full capture rc $?"
 python scripts/ncu_summary.py /tmp/${tag}_full.ncu-rep > gpurun_out/${tag}_ncu_full_bench_C2.txt 2>> gpurun_out/${tag}_ncu_full.log
+fi
 ls -la gpurun_out/${tag}_* | awk '{print $5, $9}'
 [ "$2" = "ncu-only" ] && exit 0
 python - <<PY
