@@ -197,6 +197,7 @@ struct b200j_handle {
     struct SlotCol { DevBuf values, validity; bool has_nulls = false; };
     std::vector<SlotCol> slot_cols;
     bool slot_cols_ready = false;
+    int64_t probed_since_build = 0;    // probe rows that went through the dense radix path since the table was built
     bool auto_hint = true;             // a handle whose device results have been gathered once treats later device probes as hinted (B200J_AUTO_HINT=0: off)
     bool gather_seen = false;
     bool gather_seg = true;            // b200j_gather: build columns of a dense radix result are gathered partition by partition (B200J_GATHER_SEG=0: off)
@@ -685,6 +686,7 @@ KeyCols build_key_cols(H *h) {
 
 void run_build(H *h) {
     h->slot_cols_ready = false;          // the slot-ordered payload copies belong to the previous table
+    h->probed_since_build = 0;
     const int64_t n = h->n_build;
     const int kw = h->table_kw;
     const float lf = h->cfg.load_factor > 0.f ? std::min(h->cfg.load_factor, 0.9f) : 0.5f;

@@ -467,7 +467,13 @@ int64_t probe_dense_blocked_pieces(H *h, const ProbePiece *pieces, int n_pieces,
     // fixed-width build payload column for the gather to read through it; a join without one keeps only the key stream
     bool fixed_payload = false;
     for (int i = 0; i < h->cfg.n_build_payload; i++) fixed_payload |= h->bpayload[i].type != B200J_T_UTF8;
-    const bool want_slot = ro->want_aux && ro->want_seg && fixed_payload && h->n_slots + 2 < 0xffffffffULL;
+    // ... and when the probe side is big enough to pay for the slot-ordered copies (a pass over the whole table, ~3 ms per 100 M
+    // build rows and column, against ~12 ms saved per 1 B gathered rows and column): at least two probe rows per build row so far
+    // ... and not when the last batch of an Inner / Left join had probe rows without a match: such a result is compacted and
+    // leaves the stream's order, so nothing of this could be used
+    const bool want_slot = ro->want_aux && ro->want_seg && fixed_payload && h->n_slots + 2 < 0xffffffffULL &&
+                           h->probed_since_build + n >= 2 * h->n_build && !(pl.mode == PM_PAIRS && h->miss_frac > 0.f);
+    h->probed_since_build += n;
     Trace tr_;
     try {
         // 8-byte keys travel through the partitioned stream as 32-bit values while they fit (see part_block_kernel NARROW)

@@ -96,9 +96,10 @@ extern "C" {
 
 #define B200J_OUT_GATHER_HINT   32u  /* the device result will be handed to b200j_gather: the library may keep auxiliary device
                                         arrays with it until b200j_result_release -- the partitioned probe keys (4 or 8 B per row)
-                                        and the table slot of every pair (4 B per row) -- and keeps slot-ordered copies of the
-                                        fixed-width build payload columns in the handle; the gather then reads neither the probe
-                                        key column nor the build store at random. Ignored with B200J_OUT_HOST / COUNT_ONLY and
+                                        and, once the handle has seen two probe rows per build row, the table slot of every pair
+                                        (4 B per row) -- and then keeps slot-ordered copies of the fixed-width build payload
+                                        columns in the handle; the gather then reads neither the probe key column nor the build
+                                        store at random. Ignored with B200J_OUT_HOST / COUNT_ONLY and
                                         wherever the dense radix probe does not apply; the pairs themselves are unchanged.
                                         A handle whose device pairs have been through b200j_gather once treats every later
                                         device probe as if it carried this flag (environment B200J_AUTO_HINT=0 turns that off)   */

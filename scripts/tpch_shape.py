@@ -23,6 +23,7 @@ ap.add_argument("--sf", type=float, default=100.0)
 ap.add_argument("--queries", default="q3,q5,q9")
 ap.add_argument("--verify", action="store_true")
 ap.add_argument("--chunk", type=int, default=1 << 28)
+ap.add_argument("--hint", action="store_true", help="probe with B200J_OUT_GATHER_HINT (measured neutral on these join trees: most joins are filtered, their results compacted)")
 a = ap.parse_args()
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(0)
@@ -92,7 +93,7 @@ def join(name, bkeys, bpay, pkeys, ppay):
         for lo in range(0, max(n_probe, 1), a.chunk):
             pk = [k[lo:lo + a.chunk] for k in pkeys]
             pp = [p[lo:lo + a.chunk] for p in ppay]
-            res = j.probe_batch(0, pk, want=d.OUT_PAIRS)
+            res = j.probe_batch(0, pk, want=d.OUT_PAIRS | (d.OUT_GATHER_HINT if a.hint else 0))
             gth = j.gather(res, pk, pp, want=0)                                      # device result
             n = gth.n_rows
             for c in range(n_cols):
@@ -103,7 +104,7 @@ def join(name, bkeys, bpay, pkeys, ppay):
         st = j.stats()
         outs = [torch.cat(p) for p in pieces]
     wall = (time.perf_counter() - t0) * 1e3
-    ms = {k: round(st[k], 3) for k in ("ms_build_copy", "ms_build_partition", "ms_build_insert", "ms_probe_partition", "ms_probe", "ms_gather")}
+    ms = {k: round(st[k], 3) for k in ("ms_build_copy", "ms_build_partition", "ms_build_insert", "ms_probe_partition", "ms_probe", "ms_gather", "ms_slot_order")}
     LOG.append({"join": name, "keys": nk, "build_rows": int(bkeys[0].numel()), "probe_rows": int(pkeys[0].numel()), "out_rows": int(outs[0].numel()),
                 "device_ms": round(sum(ms.values()), 3), "wall_ms": round(wall, 2), "layout": st["layout"], **ms})
     if a.verify:
