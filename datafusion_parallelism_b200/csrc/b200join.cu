@@ -198,6 +198,7 @@ struct b200j_handle {
     std::vector<SlotCol> slot_cols;
     bool slot_cols_ready = false;
     int64_t probed_since_build = 0;    // probe rows that went through the dense radix path since the table was built
+    int utf8_lanes = 0;                // lanes per row of the Utf8 gather copy (0 = from the average value length; B200J_UTF8_LANES)
     bool auto_hint = true;             // a handle whose device results have been gathered once treats later device probes as hinted (B200J_AUTO_HINT=0: off)
     bool gather_seen = false;
     bool gather_seg = true;            // b200j_gather: build columns of a dense radix result are gathered partition by partition (B200J_GATHER_SEG=0: off)
@@ -1972,6 +1973,7 @@ int32_t b200j_create(const b200j_config *cfg, b200j_handle **out) {
             if (const char *e = getenv("B200J_KEY_VIA_PROBE")) h->key_via_probe = atoi(e) != 0;
             if (const char *e = getenv("B200J_GATHER_SEG")) h->gather_seg = atoi(e) != 0;
             if (const char *e = getenv("B200J_AUTO_HINT")) h->auto_hint = atoi(e) != 0;
+            if (const char *e = getenv("B200J_UTF8_LANES")) h->utf8_lanes = atoi(e);
             if (const char *e = getenv("B200J_NO_DENSE")) h->dense_ok = atoi(e) == 0;
             if (const char *e = getenv("B200J_DENSE_MISS_MAX")) h->dense_miss_max = (float)atof(e);
             if (const char *e = getenv("B200J_L1_TABLE_BYTES")) h->l1_table_bytes = (uint64_t)atoll(e);

@@ -589,18 +589,21 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_apply_kernel(const int64_t 
     if (i0 <= n && n < i0 + SCAN_ITEMS) out32[n] = (int32_t)run;      // the thread whose range holds position n
 }
 
-// Utf8 pass 2: one warp per output row copies its bytes
-template <typename IdxT>
+// Utf8 pass 2: a group of LANES lanes per output row copies its bytes (LANES = 32: one warp per row). Short strings (names,
+// flags, dates: a dozen bytes) leave most of a warp idle when a whole warp takes one row, so the host picks the group size from
+// the average length of the gathered values: 4 lanes up to 6 bytes, 8 up to 16, 16 up to 48, a warp beyond. A group's loads and
+// stores are consecutive bytes of one row, i.e. one or two sectors per step either way.
+template <typename IdxT, int LANES>
 __global__ void __launch_bounds__(256) gather_utf8_copy_kernel(GatherSrc src, const IdxT *__restrict__ idx, int64_t n, const int64_t *__restrict__ start,
                                                                const int64_t *__restrict__ len, char *__restrict__ dst) {
-    const int lane = threadIdx.x & 31;
-    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += warps) {
+    const int sub = threadIdx.x & (LANES - 1);
+    const int64_t groups = ((int64_t)gridDim.x * blockDim.x) / LANES;
+    for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES; i < n; i += groups) {
         const int64_t l = len[i];
         if (l == 0) continue;
         const int64_t s = utf8_off(src, (int64_t)idx[i]), d = start[i];
         const char *sp = reinterpret_cast<const char *>(src.values) + s;
-        for (int64_t k = lane; k < l; k += 32) dst[d + k] = sp[k];
+        for (int64_t k = sub; k < l; k += LANES) dst[d + k] = sp[k];
     }
 }
 

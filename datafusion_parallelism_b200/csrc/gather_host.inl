@@ -88,7 +88,12 @@ void gather_one_column(GatherCtx &g, int col, int type, const GatherSrc &src, co
     oc.values = dst;
     oc.values_bytes = total;
     if (total > 0) {
-        gather_utf8_copy_kernel<IdxT><<<grid_for(h, n * 32, 256, 16), 256, 0, h->stream>>>(src, idx, n, start, len, dst);
+        double avg = (double)total / (double)n;                // bytes per gathered value (NULL rows count as 0)
+        if (h->utf8_lanes > 0) avg = h->utf8_lanes <= 4 ? 1.0 : h->utf8_lanes <= 8 ? 10.0 : h->utf8_lanes <= 16 ? 40.0 : 100.0;      // B200J_UTF8_LANES: tuning
+        if (avg <= 6.0) gather_utf8_copy_kernel<IdxT, 4><<<grid_for(h, n * 4, 256, 16), 256, 0, h->stream>>>(src, idx, n, start, len, dst);
+        else if (avg <= 16.0) gather_utf8_copy_kernel<IdxT, 8><<<grid_for(h, n * 8, 256, 16), 256, 0, h->stream>>>(src, idx, n, start, len, dst);
+        else if (avg <= 48.0) gather_utf8_copy_kernel<IdxT, 16><<<grid_for(h, n * 16, 256, 16), 256, 0, h->stream>>>(src, idx, n, start, len, dst);
+        else gather_utf8_copy_kernel<IdxT, 32><<<grid_for(h, n * 32, 256, 16), 256, 0, h->stream>>>(src, idx, n, start, len, dst);
         h->st.kernel_launches++;
         CU(cudaGetLastError());
     }
