@@ -435,7 +435,8 @@ def test_guarded_buffers_stay_intact(pkg, monkeypatch):
     every device block it allocates sits between two canaries that are verified when the block is freed; b200j_synchronize
     fails if any was overwritten. Run over every kernel family: block-local partition + segment probe (NULL keys, misaligned
     batches, 32-bit and 64-bit streams), two-pass partition + staged probe (duplicates), direct layout, composite and Utf8
-    keys, the gather, the pieces entry point, the pipelined host path, the single-pass exchange scatter."""
+    keys, the gather (plain, hinted: slot-ordered copies), probe-order results, the pieces entry point, the pipelined host path,
+    the single-pass exchange scatter."""
     import torch
     from datafusion_parallelism_b200.exchange import shuffle_local_scatter, shuffle_count, shuffle_scatter
     monkeypatch.setenv("B200J_GUARD", "1")
@@ -464,6 +465,17 @@ def test_guarded_buffers_stay_intact(pkg, monkeypatch):
                     g = j.gather(r, [dpk], want=0)
                     g.release()
                 r.release()
+                if jt != "left_anti":
+                    # the gather hint (key stream + slot array + slot-ordered payload copies) and the probe-order result, from
+                    # device and from pipelined host batches
+                    r = j.probe_batch(0, [dpk], want=pkg.OUT_PAIRS | pkg.OUT_GATHER_HINT)
+                    g = j.gather(r, [dpk], want=0)
+                    g.release()
+                    r.release()
+                    for keys, extra in (([dpk], 0), ([pa.array(pk, mask=~valid)], pkg.OUT_HOST)):
+                        r = j.probe_batch(0, keys, want=pkg.OUT_PAIRS | pkg.OUT_PROBE_ORDER | pkg.OUT_BUILD_U32 | extra)
+                        assert r.probe_order == (bk is uniq)
+                        r.release()
                 half = len(pk) // 2
                 r = j.probe_pieces(0, [(dpk[:half].data_ptr(), half), (dpk[half:].data_ptr(), len(pk) - half)], want=pkg.OUT_PAIRS)
                 r.release()
