@@ -141,6 +141,10 @@ int choose_radix_bits(H *h, int64_t n, float lf, int64_t budget) {
     const double target = std::max<double>(h->cfg.l2_budget_bytes > 0 ? (double)budget / 2.0 : (double)h->l2_bytes / 4.0, 1 << 20);
     int bits = 1;
     while (bits < RP_MAX_BITS && table_bytes / (double)(1 << bits) > target) bits++;
+    // the eighth bit is the expensive one: the block-local partition pass takes 7.2 instead of 5.4 ms per 1 B rows and its segments
+    // halve to 128 rows. Measured (profiles/r2_o_radix_bits_7_vs_8_crossover.txt): 134 M keys 12.9 (2^7) against 14.6 ms (2^8),
+    // 180 M keys 13.7 against 14.9, 250 M keys 15.5 against 15.6 -- 2^7 partitions stay until their tables pass half of the L2
+    if (bits == 8 && table_bytes / 128.0 <= 2.0 * target) bits = 7;
     return bits;
 }
 
