@@ -616,10 +616,10 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
     # is ONE u32 array in the order of the probe batch (build_idx[i] = the match of probe row i): 4 bytes per probe row.
     # --e2e-pairs: (u32 build_idx, u32 probe_idx) pairs, 8 bytes per pair; --e2e-wide: (u64, u32) pairs, 12 bytes.
     probe_order = world == 1 and not (args.e2e_wide or args.e2e_pairs)
-    out_flags = 0 if (args.e2e_wide or world > 1) else d.OUT_BUILD_U32
+    out_flags = 0 if args.e2e_wide else d.OUT_BUILD_U32
     if probe_order:
         out_flags |= d.OUT_PROBE_ORDER
-    pair_bytes = 12 if (args.e2e_wide or world > 1) else (4 if probe_order else 8)
+    pair_bytes = 12 if args.e2e_wide else (4 if probe_order else 8)
     fmt = {12: "(u64 build_idx, u32 probe_idx) pairs", 8: "(u32 build_idx, u32 probe_idx) pairs [B200J_OUT_BUILD_U32]",
            4: "u32 build_idx per probe row, in probe order [B200J_OUT_PROBE_ORDER | B200J_OUT_BUILD_U32]"}[pair_bytes]
     check = {"ok": None}
@@ -638,7 +638,7 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
             # N > 1: DistributedJoin's host-batch calls; H2D of chunk k+1 and D2H of chunk k-1's pairs overlap chunk k's exchange + join
             join.build_push_host(0, hb.array)
             join.build_finish(0)
-            for r in join.probe_host_chunks(0, hp.array, chunk_rows=host_chunk, want=d.OUT_PAIRS):
+            for r in join.probe_host_chunks(0, hp.array, chunk_rows=host_chunk, want=d.OUT_PAIRS | out_flags):
                 tot += r.n
             return tot
         join.build_push(0, [hb.array], [hpay.array])
@@ -673,7 +673,7 @@ def run_e2e(args, d, torch, dist, dev, rank, world, bk, pk, join, barrier):
     return {"value": (n_build + n_probe) * world / (dt / steps), "unit": UNIT, "h2d_bytes_per_step": 8 * (n_build + n_probe) + (8 * n_build if world == 1 else 0),
             "d2h_bytes_per_step": pair_bytes * tot, "pair_format": fmt, "verified": check["ok"], "steps": steps, "ms_per_step": dt / steps * 1e3, "ms_steps_rank0": ms_steps,
             "api": ("HashJoin.build_push/probe_batch(host numpy over b200j_host_alloc pinned buffers, OUT_PAIRS|OUT_HOST" + ("|OUT_BUILD_U32" if pair_bytes <= 8 else "") + ("|OUT_PROBE_ORDER" if probe_order else "") + ") -> b200j_* C ABI" if world == 1 else
-                    f"DistributedJoin.build_push_host/probe_host_chunks(pinned numpy in, pinned pairs out, {host_chunk}-row chunks) -> b200j_* C ABI")}
+                    f"DistributedJoin.build_push_host/probe_host_chunks(pinned numpy in, pinned pairs out" + ("" if pair_bytes == 12 else ", OUT_BUILD_U32") + f", {host_chunk}-row chunks) -> b200j_* C ABI")}
 
 
 def main():

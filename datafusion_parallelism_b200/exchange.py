@@ -811,7 +811,10 @@ class DistributedJoin:
         def finish(item):
             res, ev, off = item
             ev.synchronize()
-            res.host_build_idx = hs["out_b"][off:off + res.n].numpy().view(np.uint64)
+            if res.build_idx_width == 4:                 # B200J_OUT_BUILD_U32: 4-byte local build indices (8 instead of 12 bytes per pair over PCIe)
+                res.host_build_idx = hs["out_b"].view(torch.int32)[off:off + res.n].numpy().view(np.uint32)
+            else:
+                res.host_build_idx = hs["out_b"][off:off + res.n].numpy().view(np.uint64)
             res.host_probe_idx = hs["out_p"][off:off + res.n].numpy().view(np.uint32)
             res.release()
             return res
@@ -838,7 +841,10 @@ class DistributedJoin:
                 s_out.wait_event(done)
                 if res.n:
                     b_, p_ = res.device_arrays()
-                    hs["out_b"][off:off + res.n].copy_(torch.as_tensor(b_, device="cuda").view(torch.int64), non_blocking=True)
+                    if res.build_idx_width == 4:
+                        hs["out_b"].view(torch.int32)[off:off + res.n].copy_(torch.as_tensor(b_, device="cuda").view(torch.int32), non_blocking=True)
+                    else:
+                        hs["out_b"][off:off + res.n].copy_(torch.as_tensor(b_, device="cuda").view(torch.int64), non_blocking=True)
                     hs["out_p"][off:off + res.n].copy_(torch.as_tensor(p_, device="cuda").view(torch.int32), non_blocking=True)
                 ev_out.record(s_out)
             if pending is not None:

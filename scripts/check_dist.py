@@ -3,6 +3,7 @@ keys (checked on the rank that produced it, against the rows it received), and t
 1:1 workload's probe row count.  torchrun --nproc-per-node N scripts/check_dist.py [--mode p2p|nccl]"""
 import argparse, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
 import torch
 import torch.distributed as dist
 import datafusion_parallelism_b200 as d
@@ -93,20 +94,22 @@ with torch.cuda.stream(stream):
     j.build_push_host(0, hbk.numpy())
     j.build_finish(0)
     bkeys_h = torch.as_tensor(_RawCudaArray(j.build.recv_keys_ptr, j.build_rows_local, "<i8"), device=dev).cpu().numpy()
-    tot = 0
-    for r in j.probe_host_chunks(0, hpk.numpy(), chunk_rows=a.chunk, want=d.OUT_PAIRS):
-        side = r.side
-        n_recv = int(side.plan.recv_rows[rank])
-        pkeys_h = torch.as_tensor(_RawCudaArray(side.recv_keys_ptr, n_recv, "<i8"), device=dev).cpu().numpy()
-        assert r.n == n_recv == r.host_build_idx.shape[0] == r.host_probe_idx.shape[0]
-        assert (bkeys_h[r.host_build_idx.astype("int64")] == pkeys_h[r.host_probe_idx.astype("int64")]).all(), "host pair joins different keys"
-        src_rank, src_row = j.origin_probe(r.host_probe_idx[:1000], side=side)
-        for sr in range(world):                      # a pair's origin row on THIS rank really holds that key
-            if sr == rank:
-                m = src_rank == sr
-                rows = r.chunk_lo + src_row[m].astype("int64")
-                assert (hpk.numpy()[rows] == pkeys_h[r.host_probe_idx[:1000].astype("int64")][m]).all(), "origin_probe points at the wrong row"
-        tot += r.n
+    for want_h in (d.OUT_PAIRS, d.OUT_PAIRS | d.OUT_BUILD_U32):          # (u64, u32) pairs, then 4-byte build indices
+        tot = 0
+        for r in j.probe_host_chunks(0, hpk.numpy(), chunk_rows=a.chunk, want=want_h):
+            assert r.host_build_idx.dtype == (np.uint32 if want_h & d.OUT_BUILD_U32 else np.uint64)
+            side = r.side
+            n_recv = int(side.plan.recv_rows[rank])
+            pkeys_h = torch.as_tensor(_RawCudaArray(side.recv_keys_ptr, n_recv, "<i8"), device=dev).cpu().numpy()
+            assert r.n == n_recv == r.host_build_idx.shape[0] == r.host_probe_idx.shape[0]
+            assert (bkeys_h[r.host_build_idx.astype("int64")] == pkeys_h[r.host_probe_idx.astype("int64")]).all(), "host pair joins different keys"
+            src_rank, src_row = j.origin_probe(r.host_probe_idx[:1000], side=side)
+            for sr in range(world):                      # a pair's origin row on THIS rank really holds that key
+                if sr == rank:
+                    m = src_rank == sr
+                    rows = r.chunk_lo + src_row[m].astype("int64")
+                    assert (hpk.numpy()[rows] == pkeys_h[r.host_probe_idx[:1000].astype("int64")][m]).all(), "origin_probe points at the wrong row"
+            tot += r.n
 t = torch.tensor([tot], device=dev, dtype=torch.int64)
 dist.all_reduce(t)
 assert int(t.item()) == a.probe * world, (int(t.item()), a.probe * world)
