@@ -63,6 +63,26 @@ def test_struct_sizes_match_c_layout(native):
     assert sizes == [C.sizeof(m) for m in mirrors]
 
 
+def test_field_offsets_and_flag_values_match_the_header(native):
+    """offsetof of every field of the result and stats structs (the two that grew this round) equals the ctypes mirror's, and the
+    `want` flags of the Python veneer are the header's values."""
+    import datafusion_parallelism_b200.join as J
+    fields = {"b200j_result": [n for n, _ in native.Result._fields_], "b200j_stats": [n for n, _ in native.Stats._fields_]}
+    flags = ["PAIRS", "HOST", "MATCHES_ONLY", "COUNT_ONLY", "BUILD_U32", "GATHER_HINT", "PROBE_ORDER"]
+    body = "".join(f'printf("%zu ", offsetof({st}, {f}));' for st, fs in fields.items() for f in fs)
+    body += "".join(f'printf("%u ", (unsigned)B200J_OUT_{f});' for f in flags)
+    prog = '#include "b200join.h"\n#include <stdio.h>\n#include <stddef.h>\nint main(void){' + body + 'return 0;}'
+    d = os.path.join(ROOT, "oracle", "_build")
+    os.makedirs(d, exist_ok=True)
+    src, exe = os.path.join(d, "offsets.c"), os.path.join(d, "offsets")
+    open(src, "w").write(prog)
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), "-o", exe, src], check=True)
+    got = [int(x) for x in subprocess.run([exe], capture_output=True, text=True, check=True).stdout.split()]
+    want = [getattr(m, f).offset for m, st in ((native.Result, "b200j_result"), (native.Stats, "b200j_stats")) for f in fields[st]]
+    want += [getattr(J, "OUT_" + f) for f in flags]
+    assert got == want
+
+
 def test_product_never_touches_the_oracle():
     """oracle/ is test infrastructure: nothing under the package may import, link or open it."""
     bad = []
