@@ -135,3 +135,25 @@ def test_gather_of_a_probe_order_result():
         res.release()
     assert n == npr and np.array_equal(valid, pk < nb)
     assert np.array_equal(key[valid], pk[valid]) and np.array_equal(pay[valid], pk[valid] * 5 + 2)
+
+
+@pytest.mark.parametrize("mem", ["host", "device"])
+def test_probe_order_of_an_empty_and_a_one_row_batch(mem):
+    import torch
+    import datafusion_parallelism_b200 as d
+    bk = np.arange(1, 1001, dtype=np.int64)
+    with d.HashJoin("inner", key_widths=(8,)) as j:
+        j.build_push(0, [bk])
+        j.build_finish(0)
+        for pk in (np.zeros(0, dtype=np.int64), np.array([7], dtype=np.int64), np.array([5000], dtype=np.int64)):
+            keys = [torch.from_numpy(pk).cuda()] if mem == "device" else [pk]
+            res = j.probe_batch(0, keys, want=d.OUT_PAIRS | d.OUT_PROBE_ORDER | (0 if mem == "device" else d.OUT_HOST))
+            assert res.probe_order and res.n == len(pk) and res.probe_ptr == 0
+            if mem == "host" and len(pk):
+                b, p = res.numpy()
+                assert (int(b[0]) == 6) if pk[0] == 7 else (b[0] == NULL64)
+            elif len(pk):
+                b_, _ = res.device_arrays()
+                got = int(torch.as_tensor(b_, device="cuda").cpu().numpy()[0])
+                assert got == (6 if pk[0] == 7 else -1)
+            res.release()
