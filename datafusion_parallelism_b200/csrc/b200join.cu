@@ -754,6 +754,7 @@ void run_build(H *h) {
         if (n > 0 && direct_slots < 0xffffffffULL) {
             CU(big_alloc(h, &slot_of, (size_t)n * 4 + 16));
             a.slot_of = (uint32_t *)slot_of;
+            a.dup_bit = direct_slots < 0x7fffffffULL ? 1u : 0u;
         }
         if (n > 0) {
             const int grid = grid_for(h, n, TILE_ROWS, 8);

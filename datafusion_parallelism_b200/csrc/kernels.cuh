@@ -370,7 +370,11 @@ struct BuildArgs {
     HashKeys        hk;
     Counters       *ctr;
     uint32_t       *slot_of;      // [n] slot index every row went to (0xffffffff = the zero-key side slot), for csr_fill; may be null
+    uint32_t        dup_bit;      // 1: slot indices fit 31 bits and the insert sets bit 31 of slot_of[] for the rows that found their key already
+                                  //    present -- the only rows csr_fill has to place (it then skips the others without looking at their slot)
+    uint32_t        _pad2;
 };
+constexpr uint32_t SLOT_OF_DUP = 0x80000000u;
 
 // 128-bit compare-and-swap of a whole slot: {0, 0} -> {key, row | count 1}. One atomic claims the slot, stores the row id
 // and sets the count; returns the key word found (0 = claimed). The insert kernel is bound by L2 sector operations (ncu: 11
@@ -476,6 +480,7 @@ __global__ void __launch_bounds__(TILE_THREADS) build_insert_kernel(BuildArgs a)
             } else {
                 dups++;
                 if (pos == 1) multi++;
+                if (a.dup_bit && a.slot_of && key[q]) a.slot_of[row[q]] = (uint32_t)(s - a.tv.slots) | SLOT_OF_DUP;
             }
         }
     }
@@ -649,7 +654,11 @@ __global__ void __launch_bounds__(TILE_THREADS) csr_fill_kernel(BuildArgs a) {
             const uint32_t r = a.rowid ? __ldcs(a.rowid + row[q]) : (uint32_t)row[q];
             Slot *s;
             if (a.slot_of) {                                                 // the insert pass remembered where the row went
-                const uint32_t si = __ldcs(a.slot_of + row[q]);
+                uint32_t si = __ldcs(a.slot_of + row[q]);
+                if (a.dup_bit && si != 0xffffffffu) {
+                    if (!(si & SLOT_OF_DUP)) continue;                       // the row claimed its slot itself: placed by csr_scan if the slot became a run
+                    si &= ~SLOT_OF_DUP;
+                }
                 s = si == 0xffffffffu ? a.tv.zero_slot : a.tv.slots + si;
             } else {
                 uint32_t dummy = 0;

@@ -220,6 +220,7 @@ void radix_build(H *h, const void *keys, const uint8_t *validity, int kw, int64_
             CU(big_alloc(h, &so, (size_t)n_valid * 4 + 16));
             temps.push_back(so);
             a.slot_of = (uint32_t *)so;
+            a.dup_bit = (!fused && total < 0x7fffffffULL) ? 1u : 0u;      // build_insert_kernel marks the rows csr_fill has to place
         }
         if (fused) {
             FusedBuildArgs f{};
